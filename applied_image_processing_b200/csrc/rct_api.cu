@@ -1,0 +1,765 @@
+// rct_api.cu -- C ABI (include/rct.h) over the kernels in rct_kernels.cuh.
+// Build: nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad=false
+//        -Xcompiler -fPIC -shared   (see csrc/Makefile, __graft_entry__.build()).
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+
+#include "../../include/rct.h"
+#include "rct_kernels.cuh"
+
+using namespace rct;
+
+namespace {
+
+thread_local std::string t_err;
+thread_local long long t_launches = 0;
+
+int fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    t_err = buf;
+    return code;
+}
+
+#define CK(call)                                                                                       \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess)                                                                         \
+            return fail(RCT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
+                        __LINE__);                                                                     \
+    } while (0)
+
+#define LAUNCH(kernel, grid, block, stream, ...)                                     \
+    do {                                                                             \
+        kernel<<<grid, block, 0, stream>>>(__VA_ARGS__);                             \
+        ++t_launches;                                                                \
+        cudaError_t e_ = cudaGetLastError();                                         \
+        if (e_ != cudaSuccess)                                                       \
+            return fail(RCT_ERR_CUDA, "launch %s failed: %s", #kernel, cudaGetErrorString(e_)); \
+    } while (0)
+
+// ---- matrices / tables ---------------------------------------------------------------------
+std::mutex g_mu;
+double g_mat[36] = {
+    // RGB_TO_LMS (LST:12-14)
+    0x1.863f141205bc0p-2, 0x1.2816f0068db8cp-1, 0x1.495182a9930bep-5, 0x1.92d77318fc505p-3, 0x1.72e48e8a71de7p-1,
+    0x1.404ea4a8c154dp-4, 0x1.8adab9f559b3dp-6, 0x1.07c84b5dcc63fp-3, 0x1.b05532617c1bep-1,
+    // LMS_TO_LAB (LST:15-17)
+    0x1.279a74590331dp-1, 0x1.279a74590331dp-1, 0x1.279a74590331dp-1, 0x1.a20bd700c2c3fp-2, 0x1.a20bd700c2c3fp-2,
+    -0x1.a20bd700c2c3fp-1, 0x1.6a09e667f3bccp-1, -0x1.6a09e667f3bccp-1, 0x0.0p+0,
+    // LAB_TO_LMS = inv(LMS_TO_LAB) (LST:18), as numpy 2.3.5 / OpenBLAS 0.3.30 computes it
+    0x1.279a74590331cp-1, 0x1.a20bd700c2c3dp-2, 0x1.6a09e667f3bcdp-1, 0x1.279a74590331cp-1, 0x1.a20bd700c2c3dp-2,
+    -0x1.6a09e667f3bcdp-1, 0x1.279a74590331ap-1, -0x1.a20bd700c2c3dp-1, 0x1.06f92bd2a7fb7p-53,
+    // LMS_TO_RGB = inv(RGB_TO_LMS) (LST:19)
+    0x1.1dfeafe21594bp+2, -0x1.cb59bb64ad92ap+1, 0x1.e9e644ae9f486p-4, -0x1.383f59520175cp+0, 0x1.31090654d17b8p+1,
+    -0x1.4d11041a8966dp-3, 0x1.df4d2b5faca4cp-5, -0x1.0b582575423a0p-2, 0x1.34a6855f0509ap+0};
+unsigned g_mat_version = 1;
+unsigned g_dev_version[64] = {0};
+int g_sm_count[64] = {0};
+
+int ensure_device(int *dev_out)
+{
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev_out) *dev_out = dev;
+    if (dev < 0 || dev >= 64) return fail(RCT_ERR_ARG, "device index %d out of range", dev);
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (g_dev_version[dev] == g_mat_version) return RCT_OK;
+    MathTabs *h = new (std::nothrow) MathTabs;
+    if (!h) return fail(RCT_ERR_NOMEM, "out of host memory");
+    memcpy(h->log_inv, RCT_LOG_INV, sizeof h->log_inv);
+    memcpy(h->log_t10, RCT_LOG_T10, sizeof h->log_t10);
+    memcpy(h->exp2_t, RCT_EXP2_T, sizeof h->exp2_t);
+    for (int k = 0; k < 256; ++k) h->unit[k] = (double)((float)k / 255.0f);  // LST:71 float32 divide
+    cudaError_t e1 = cudaMemcpyToSymbol(g_tabs, h, sizeof(MathTabs));
+    delete h;
+    if (e1 != cudaSuccess) return fail(RCT_ERR_CUDA, "table upload failed: %s", cudaGetErrorString(e1));
+    CK(cudaMemcpyToSymbol(c_mat, g_mat, sizeof g_mat));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, dev));
+    g_sm_count[dev] = prop.multiProcessorCount;
+    g_dev_version[dev] = g_mat_version;
+    return RCT_OK;
+}
+
+inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
+
+struct Layout {
+    size_t cap, fine_cap, n_partials;
+    size_t off_ctrl, off_jobs, off_status, off_xtab, off_ytab;
+    size_t off_hist, hist_stride_u32, off_lut, lut_stride_u32;
+    size_t off_region, region_bytes;  // [slots][2] blocks of per-region arrays
+    size_t r_col, r_cnt, r_keyA, r_fb, r_slot, r_keyB, r_payB, r_cumB, r_fine, r_part;
+    size_t off_dbg_m, off_dbg_j, dbg_stride;
+    size_t total;
+};
+
+Layout make_layout(int H, int W, int slots, unsigned flags)
+{
+    Layout L{};
+    size_t npix = (size_t)H * (size_t)W;
+    L.cap = npix < (size_t)kCube ? npix : (size_t)kCube;
+    L.fine_cap = 2 * L.cap + kCoarse;
+    L.n_partials = (L.fine_cap + 1 + kScanChunk - 1) / kScanChunk + 1;
+    size_t o = 0;
+    L.off_ctrl = o; o = align_up(o + sizeof(FrameCtrl) * slots);
+    L.off_jobs = o; o = align_up(o + sizeof(Job) * 2 * slots);
+    L.off_status = o; o = align_up(o + sizeof(int) * slots);
+    L.off_xtab = o; o = align_up(o + sizeof(int) * (size_t)W);
+    L.off_ytab = o; o = align_up(o + sizeof(int) * (size_t)H);
+    L.hist_stride_u32 = 2 * (size_t)kCube;
+    L.off_hist = o; o = align_up(o + 4 * L.hist_stride_u32 * slots);
+    L.lut_stride_u32 = kCube;
+    L.off_lut = o; o = align_up(o + 4 * L.lut_stride_u32 * slots);
+    size_t r = 0;
+    L.r_col = r; r = align_up(r + 4 * L.cap);
+    L.r_cnt = r; r = align_up(r + 4 * L.cap);
+    L.r_keyA = r; r = align_up(r + 8 * L.cap);
+    L.r_fb = r; r = align_up(r + 4 * L.cap);
+    L.r_slot = r; r = align_up(r + 4 * L.cap);
+    L.r_keyB = r; r = align_up(r + 8 * L.cap);
+    L.r_payB = r; r = align_up(r + 4 * L.cap);
+    L.r_cumB = r; r = align_up(r + 4 * L.cap);
+    L.r_fine = r; r = align_up(r + 4 * (L.fine_cap + 1));
+    L.r_part = r; r = align_up(r + 4 * L.n_partials);
+    L.region_bytes = r;
+    L.off_region = o; o += L.region_bytes * 2 * slots;
+    L.dbg_stride = L.cap;
+    if (flags & RCT_FLAG_DEBUG) {
+        L.off_dbg_m = o; o = align_up(o + 8 * L.cap * slots);
+        L.off_dbg_j = o; o = align_up(o + 8 * L.cap * slots);
+    }
+    L.total = o;
+    return L;
+}
+
+}  // namespace
+
+struct rct_plan {
+    int device, H, W, sh, sw, slots;
+    unsigned flags;
+    bool resample, owns_ws;
+    uint8_t *ws;
+    Layout L;
+    FrameCtrl *ctrl;
+    Job *jobs;
+    int *status_slots;
+    int *xtab, *ytab;
+    unsigned *hist, *lut;
+    double *dbg_m;
+    long long *dbg_j;
+    int sm;
+    int aggregate;
+    // lazily allocated helpers
+    int *status_frames;
+    int status_frames_cap;
+    uint8_t *stage;  // device staging of the host entry point
+    size_t stage_bytes;
+    cudaStream_t own_stream;
+};
+
+extern "C" {
+
+int rct_version(void) { return 100; }
+const char *rct_last_error(void) { return t_err.c_str(); }
+long long rct_launch_count(int reset)
+{
+    long long v = t_launches;
+    if (reset) t_launches = 0;
+    return v;
+}
+
+int rct_set_matrices(const double *m36)
+{
+    if (!m36) return fail(RCT_ERR_ARG, "null matrices");
+    std::lock_guard<std::mutex> lk(g_mu);
+    memcpy(g_mat, m36, sizeof g_mat);
+    ++g_mat_version;
+    return RCT_OK;
+}
+int rct_get_matrices(double *m36)
+{
+    if (!m36) return fail(RCT_ERR_ARG, "null matrices");
+    std::lock_guard<std::mutex> lk(g_mu);
+    memcpy(m36, g_mat, sizeof g_mat);
+    return RCT_OK;
+}
+
+int rct_resample_table(int in_size, int out_size, int32_t *tab)
+{
+    if (in_size <= 0 || out_size <= 0 || !tab) return fail(RCT_ERR_ARG, "bad resample sizes");
+    // Pillow's nearest filter: accumulated double source coordinate
+    double scale = (double)in_size / (double)out_size;
+    double pos = 0.5 * scale;
+    for (int i = 0; i < out_size; ++i, pos += scale) {
+        int src = (int)pos;
+        tab[i] = src < in_size ? src : in_size - 1;
+    }
+    return RCT_OK;
+}
+
+size_t rct_plan_workspace_bytes(int H, int W, int slots, unsigned flags)
+{
+    if (H <= 0 || W <= 0 || slots <= 0) return 0;
+    return make_layout(H, W, slots, flags).total;
+}
+
+int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigned flags, void *workspace,
+                    size_t workspace_bytes, rct_plan **out)
+{
+    if (!out) return fail(RCT_ERR_ARG, "null plan pointer");
+    *out = nullptr;
+    if (H <= 0 || W <= 0 || sh <= 0 || sw <= 0 || slots <= 0 || slots > 4096)
+        return fail(RCT_ERR_ARG, "bad geometry H=%d W=%d sh=%d sw=%d slots=%d", H, W, sh, sw, slots);
+    if ((size_t)H * (size_t)W >= ((size_t)1 << 32)) return fail(RCT_ERR_ARG, "image too large (>= 2^32 pixels)");
+    CK(cudaSetDevice(device));
+    int rc = ensure_device(nullptr);
+    if (rc) return rc;
+    rct_plan *p = new (std::nothrow) rct_plan();
+    if (!p) return fail(RCT_ERR_NOMEM, "out of host memory");
+    p->device = device; p->H = H; p->W = W; p->sh = sh; p->sw = sw; p->slots = slots; p->flags = flags;
+    p->resample = (sh != H) || (sw != W);
+    p->L = make_layout(H, W, slots, flags);
+    p->sm = g_sm_count[device] > 0 ? g_sm_count[device] : 148;
+    p->aggregate = 0;
+    if (workspace) {
+        if (workspace_bytes < p->L.total) {
+            delete p;
+            return fail(RCT_ERR_ARG, "workspace too small: %zu < %zu", workspace_bytes, p->L.total);
+        }
+        if (((uintptr_t)workspace & 255) != 0) {
+            delete p;
+            return fail(RCT_ERR_ARG, "workspace must be 256-byte aligned");
+        }
+        p->ws = (uint8_t *)workspace;
+        p->owns_ws = false;
+    } else {
+        cudaError_t e = cudaMalloc((void **)&p->ws, p->L.total);
+        if (e != cudaSuccess) {
+            size_t need = p->L.total;
+            delete p;
+            return fail(RCT_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", need, cudaGetErrorString(e));
+        }
+        p->owns_ws = true;
+    }
+    const Layout &L = p->L;
+    p->ctrl = (FrameCtrl *)(p->ws + L.off_ctrl);
+    p->jobs = (Job *)(p->ws + L.off_jobs);
+    p->status_slots = (int *)(p->ws + L.off_status);
+    p->xtab = (int *)(p->ws + L.off_xtab);
+    p->ytab = (int *)(p->ws + L.off_ytab);
+    p->hist = (unsigned *)(p->ws + L.off_hist);
+    p->lut = (unsigned *)(p->ws + L.off_lut);
+    p->dbg_m = (flags & RCT_FLAG_DEBUG) ? (double *)(p->ws + L.off_dbg_m) : nullptr;
+    p->dbg_j = (flags & RCT_FLAG_DEBUG) ? (long long *)(p->ws + L.off_dbg_j) : nullptr;
+    // job descriptors
+    Job *hj = new (std::nothrow) Job[2 * slots];
+    int32_t *tab = new (std::nothrow) int32_t[(size_t)(W > H ? W : H)];
+    if (!hj || !tab) {
+        delete[] hj; delete[] tab;
+        rct_plan_destroy(p);
+        return fail(RCT_ERR_NOMEM, "out of host memory");
+    }
+    for (int s = 0; s < slots; ++s)
+        for (int r = 0; r < 2; ++r) {
+            uint8_t *b = p->ws + L.off_region + L.region_bytes * (size_t)(2 * s + r);
+            Job &j = hj[2 * s + r];
+            j.rc = &p->ctrl[s].r[r];
+            j.payA = (unsigned *)(b + L.r_col);
+            j.cntA = (unsigned *)(b + L.r_cnt);
+            j.keyA = (double *)(b + L.r_keyA);
+            j.fbA = (unsigned *)(b + L.r_fb);
+            j.slotA = (unsigned *)(b + L.r_slot);
+            j.keyB = (double *)(b + L.r_keyB);
+            j.payB = (unsigned *)(b + L.r_payB);
+            j.cumB = (unsigned *)(b + L.r_cumB);
+            j.fine = (unsigned *)(b + L.r_fine);
+            j.partials = (unsigned *)(b + L.r_part);
+            j.cap = (unsigned)L.cap;
+            j.pad_ = 0;
+        }
+    cudaError_t e = cudaMemcpy(p->jobs, hj, sizeof(Job) * 2 * slots, cudaMemcpyHostToDevice);
+    delete[] hj;
+    if (e == cudaSuccess && p->resample) {
+        rct_resample_table(sw, W, tab);
+        e = cudaMemcpy(p->xtab, tab, sizeof(int) * (size_t)W, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) {
+            rct_resample_table(sh, H, tab);
+            e = cudaMemcpy(p->ytab, tab, sizeof(int) * (size_t)H, cudaMemcpyHostToDevice);
+        }
+    }
+    delete[] tab;
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        rct_plan_destroy(p);
+        return fail(RCT_ERR_CUDA, "plan setup failed: %s", cudaGetErrorString(e));
+    }
+    *out = p;
+    return RCT_OK;
+}
+
+int rct_plan_destroy(rct_plan *p)
+{
+    if (!p) return RCT_OK;
+    cudaSetDevice(p->device);
+    if (p->own_stream) cudaStreamDestroy(p->own_stream);
+    if (p->owns_ws && p->ws) cudaFree(p->ws);
+    if (p->status_frames) cudaFree(p->status_frames);
+    if (p->stage) cudaFree(p->stage);
+    delete p;
+    return RCT_OK;
+}
+
+int rct_plan_set_option(rct_plan *p, int option, int value)
+{
+    if (!p) return fail(RCT_ERR_ARG, "null plan");
+    if (option == 0) p->aggregate = value;
+    else return fail(RCT_ERR_ARG, "unknown option %d", option);
+    return RCT_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+struct FrameSet {
+    const uint8_t *content, *sty, *mask;
+    uint8_t *out;
+    size_t cs, ss, ms, os;  // strides in bytes
+};
+
+PixArgs pix_args(rct_plan *p, const FrameSet &f, int mode, int label, size_t p_begin, size_t p_end, int *status_out)
+{
+    PixArgs a{};
+    a.content = f.content; a.sty = f.sty; a.mask = f.mask; a.out = f.out;
+    a.content_stride = f.cs; a.sty_stride = f.ss; a.mask_stride = f.ms; a.out_stride = f.os;
+    a.xtab = p->resample ? p->xtab : nullptr;
+    a.ytab = p->resample ? p->ytab : nullptr;
+    a.hist = p->hist; a.hist_stride = p->L.hist_stride_u32;
+    a.lut = p->lut; a.lut_stride = p->L.lut_stride_u32;
+    a.ctrl = p->ctrl; a.status_out = status_out;
+    a.W = p->W; a.sw = p->sw;
+    a.p_begin = p_begin; a.p_end = p_end;
+    a.mode = mode; a.label = label;
+    a.aggregate = p->aggregate;
+    return a;
+}
+
+unsigned pix_blocks(rct_plan *p, size_t npix, int nslots)
+{
+    size_t groups = (npix + 15) / 16;
+    size_t blocks = (groups + 255) / 256;
+    size_t maxb = (size_t)p->sm * 8;
+    if (nslots > 1) maxb = (maxb + nslots - 1) / nslots < (size_t)p->sm ? (size_t)p->sm : (maxb + nslots - 1) / nslots;
+    if (blocks > maxb) blocks = maxb;
+    return (unsigned)(blocks ? blocks : 1);
+}
+
+unsigned entry_blocks(rct_plan *p, int nslots)
+{
+    size_t blocks = (p->L.cap + 255) / 256;
+    size_t maxb = (size_t)p->sm * 4;
+    if (nslots > 1) maxb = maxb / nslots < 32 ? 32 : maxb / nslots;
+    if (blocks > maxb) blocks = maxb;
+    return (unsigned)(blocks ? blocks : 1);
+}
+
+int phase_hist(rct_plan *p, const FrameSet &f, int nslots, int mode, int label, size_t p_begin, size_t p_end,
+               cudaStream_t st)
+{
+    CK(cudaMemsetAsync(p->ctrl, 0, sizeof(FrameCtrl) * nslots, st));
+    CK(cudaMemsetAsync(p->hist, 0, 4 * p->L.hist_stride_u32 * nslots, st));
+    PixArgs a = pix_args(p, f, mode, label, p_begin, p_end, nullptr);
+    dim3 grid(pix_blocks(p, p_end - p_begin, nslots), nslots);
+    if (p->resample) LAUNCH(k_hist<true>, grid, 256, st, a);
+    else LAUNCH(k_hist<false>, grid, 256, st, a);
+    return RCT_OK;
+}
+
+int sort_jobs(const Job *jobs, int njobs, unsigned eblocks, size_t fine_cap, cudaStream_t st)
+{
+    unsigned sblocks_fine = (unsigned)((fine_cap + 1 + kScanChunk - 1) / kScanChunk);
+    LAUNCH(k_bucket_plan, dim3(1, njobs), 1024, st, jobs);
+    LAUNCH(k_zero_fine, dim3(eblocks, njobs), 256, st, jobs);
+    LAUNCH(k_bucket_count, dim3(eblocks, njobs), 256, st, jobs);
+    LAUNCH(k_scan_reduce<0>, dim3(sblocks_fine, njobs), 256, st, jobs);
+    LAUNCH(k_scan_partials<0>, dim3(1, njobs), 1024, st, jobs);
+    LAUNCH(k_scan_apply<0>, dim3(sblocks_fine, njobs), 256, st, jobs);
+    LAUNCH(k_scatter, dim3(eblocks, njobs), 256, st, jobs);
+    LAUNCH(k_bucket_sort, dim3(eblocks, njobs), 256, st, jobs);
+    LAUNCH(k_scan_reduce<1>, dim3(sblocks_fine, njobs), 256, st, jobs);
+    LAUNCH(k_scan_partials<1>, dim3(1, njobs), 1024, st, jobs);
+    LAUNCH(k_scan_apply<1>, dim3(sblocks_fine, njobs), 256, st, jobs);
+    return RCT_OK;
+}
+
+int phase_solve(rct_plan *p, int nslots, cudaStream_t st)
+{
+    unsigned eb = entry_blocks(p, nslots);
+    LAUNCH(k_compact, dim3(kCube / 1024, 2, nslots), 256, st, p->hist, p->L.hist_stride_u32, p->ctrl, p->jobs);
+    LAUNCH(k_lab_moments, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs);
+    LAUNCH(k_pca, dim3((nslots + 31) / 32), 32, st, p->ctrl, nslots);
+    LAUNCH(k_keys, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs);
+    int rc = sort_jobs(p->jobs, 2 * nslots, eb, p->L.fine_cap, st);
+    if (rc) return rc;
+    LAUNCH(k_match, dim3(eb * 2, nslots), 128, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32, p->dbg_m, p->dbg_j,
+           p->L.dbg_stride);
+    return RCT_OK;
+}
+
+int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label, size_t p_begin, size_t p_end,
+                int *status_out, cudaStream_t st)
+{
+    PixArgs a = pix_args(p, f, mode, label, p_begin, p_end, status_out);
+    dim3 grid(pix_blocks(p, p_end - p_begin, nslots), nslots);
+    if (p->resample) LAUNCH(k_apply<true>, grid, 256, st, a);
+    else LAUNCH(k_apply<false>, grid, 256, st, a);
+    return RCT_OK;
+}
+
+int check_mode(int mode, const void *mask)
+{
+    if (mode < 0 || mode > 2) return fail(RCT_ERR_ARG, "bad mode %d", mode);
+    if (mode != RCT_MODE_ALL && !mask) return fail(RCT_ERR_ARG, "mask required for mode %d", mode);
+    return RCT_OK;
+}
+
+int ensure_status_frames(rct_plan *p, int n)
+{
+    if (n <= p->status_frames_cap) return RCT_OK;
+    if (p->status_frames) CK(cudaFree(p->status_frames));
+    p->status_frames = nullptr;
+    p->status_frames_cap = 0;
+    int cap = n < 64 ? 64 : n;
+    CK(cudaMalloc((void **)&p->status_frames, sizeof(int) * (size_t)cap));
+    p->status_frames_cap = cap;
+    return RCT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rct_transfer_async(rct_plan *p, const uint8_t *content, size_t content_stride, const uint8_t *stylised,
+                       size_t stylised_stride, const uint8_t *mask, size_t mask_stride, uint8_t *out,
+                       size_t out_stride, int n_frames, int mode, int label, void *stream)
+{
+    if (!p || !content || !stylised || !out || n_frames <= 0) return fail(RCT_ERR_ARG, "null/invalid argument");
+    int rc = check_mode(mode, mask);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    rc = ensure_status_frames(p, n_frames);
+    if (rc) return rc;
+    const size_t npix = (size_t)p->H * (size_t)p->W;
+    for (int f0 = 0; f0 < n_frames; f0 += p->slots) {
+        int ns = n_frames - f0 < p->slots ? n_frames - f0 : p->slots;
+        FrameSet f{content + (size_t)f0 * content_stride, stylised + (size_t)f0 * stylised_stride,
+                   mask ? mask + (size_t)f0 * mask_stride : nullptr, out + (size_t)f0 * out_stride,
+                   content_stride, stylised_stride, mask_stride, out_stride};
+        if ((rc = phase_hist(p, f, ns, mode, label, 0, npix, st))) return rc;
+        if ((rc = phase_solve(p, ns, st))) return rc;
+        if ((rc = phase_apply(p, f, ns, mode, label, 0, npix, p->status_frames + f0, st))) return rc;
+    }
+    return RCT_OK;
+}
+
+int rct_plan_status(rct_plan *p, int *status_host, int n_frames, void *stream)
+{
+    if (!p || !status_host || n_frames <= 0 || n_frames > p->status_frames_cap)
+        return fail(RCT_ERR_ARG, "bad status request");
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(cudaMemcpyAsync(status_host, p->status_frames, sizeof(int) * (size_t)n_frames, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return RCT_OK;
+}
+
+int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *stylised_h, const uint8_t *mask_h,
+                      uint8_t *out_h, int n_frames, int mode, int label, int *status_host)
+{
+    if (!p || !content_h || !stylised_h || !out_h || n_frames <= 0) return fail(RCT_ERR_ARG, "null/invalid argument");
+    int rc = check_mode(mode, mask_h);
+    if (rc) return rc;
+    CK(cudaSetDevice(p->device));
+    const size_t npix = (size_t)p->H * (size_t)p->W, spix = (size_t)p->sh * (size_t)p->sw;
+    const size_t cb = align_up(npix * 3), sb = align_up(spix * 3), mb = align_up(npix);
+    const size_t per_slot = cb + sb + mb + cb;
+    const size_t need = per_slot * (size_t)p->slots;
+    if (p->stage_bytes < need) {
+        if (p->stage) CK(cudaFree(p->stage));
+        p->stage = nullptr;
+        p->stage_bytes = 0;
+        CK(cudaMalloc((void **)&p->stage, need));
+        p->stage_bytes = need;
+    }
+    rc = ensure_status_frames(p, n_frames);
+    if (rc) return rc;
+    cudaStream_t st = p->own_stream;
+    uint8_t *d_c = p->stage, *d_s = d_c + cb * p->slots, *d_m = d_s + sb * p->slots, *d_o = d_m + mb * p->slots;
+    for (int f0 = 0; f0 < n_frames; f0 += p->slots) {
+        int ns = n_frames - f0 < p->slots ? n_frames - f0 : p->slots;
+        // frames are contiguous on the host; device staging keeps aligned per-slot strides
+        CK(cudaMemcpy2DAsync(d_c, cb, content_h + (size_t)f0 * npix * 3, npix * 3, npix * 3, ns, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpy2DAsync(d_s, sb, stylised_h + (size_t)f0 * spix * 3, spix * 3, spix * 3, ns, cudaMemcpyHostToDevice, st));
+        if (mask_h) CK(cudaMemcpy2DAsync(d_m, mb, mask_h + (size_t)f0 * npix, npix, npix, ns, cudaMemcpyHostToDevice, st));
+        FrameSet f{d_c, d_s, mask_h ? d_m : nullptr, d_o, cb, sb, mb, cb};
+        if (mode == RCT_MODE_LABEL)  // untouched pixels keep the caller's values
+            CK(cudaMemcpy2DAsync(d_o, cb, out_h + (size_t)f0 * npix * 3, npix * 3, npix * 3, ns, cudaMemcpyHostToDevice, st));
+        if ((rc = phase_hist(p, f, ns, mode, label, 0, npix, st))) return rc;
+        if ((rc = phase_solve(p, ns, st))) return rc;
+        if ((rc = phase_apply(p, f, ns, mode, label, 0, npix, p->status_frames + f0, st))) return rc;
+        CK(cudaMemcpy2DAsync(out_h + (size_t)f0 * npix * 3, npix * 3, d_o, cb, npix * 3, ns, cudaMemcpyDeviceToHost, st));
+    }
+    int worst = 0;
+    int *tmp = status_host ? status_host : new (std::nothrow) int[n_frames];
+    if (!tmp) return fail(RCT_ERR_NOMEM, "out of host memory");
+    cudaError_t e = cudaMemcpyAsync(tmp, p->status_frames, sizeof(int) * (size_t)n_frames, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess)
+        for (int i = 0; i < n_frames; ++i)
+            if (tmp[i] > worst) worst = tmp[i];
+    if (!status_host) delete[] tmp;
+    if (e != cudaSuccess) return fail(RCT_ERR_CUDA, "host transfer failed: %s", cudaGetErrorString(e));
+    return worst;
+}
+
+// ---- row-sharded phases ---------------------------------------------------------------------
+int rct_shard_hist_async(rct_plan *p, const uint8_t *content, const uint8_t *stylised, const uint8_t *mask, int mode,
+                         int label, int row0, int rows, void *stream)
+{
+    if (!p || !content || !stylised || row0 < 0 || rows < 0 || row0 + rows > p->H)
+        return fail(RCT_ERR_ARG, "bad shard arguments");
+    int rc = check_mode(mode, mask);
+    if (rc) return rc;
+    FrameSet f{content, stylised, mask, nullptr, 0, 0, 0, 0};
+    return phase_hist(p, f, 1, mode, label, (size_t)row0 * p->W, (size_t)(row0 + rows) * p->W, (cudaStream_t)stream);
+}
+void *rct_plan_hist_ptr(rct_plan *p) { return p ? (void *)p->hist : nullptr; }
+size_t rct_plan_hist_bytes(rct_plan *p) { return p ? 4 * p->L.hist_stride_u32 : 0; }
+int rct_shard_solve_async(rct_plan *p, void *stream)
+{
+    if (!p) return fail(RCT_ERR_ARG, "null plan");
+    return phase_solve(p, 1, (cudaStream_t)stream);
+}
+int rct_shard_apply_async(rct_plan *p, const uint8_t *content, const uint8_t *stylised, const uint8_t *mask,
+                          uint8_t *out, int mode, int label, int row0, int rows, void *stream)
+{
+    if (!p || !content || !stylised || !out || row0 < 0 || rows < 0 || row0 + rows > p->H)
+        return fail(RCT_ERR_ARG, "bad shard arguments");
+    int rc = check_mode(mode, mask);
+    if (rc) return rc;
+    rc = ensure_status_frames(p, 1);
+    if (rc) return rc;
+    FrameSet f{content, stylised, mask, out, 0, 0, 0, 0};
+    return phase_apply(p, f, 1, mode, label, (size_t)row0 * p->W, (size_t)(row0 + rows) * p->W, p->status_frames,
+                       (cudaStream_t)stream);
+}
+
+// ---- stand-alone functions -----------------------------------------------------------------
+static unsigned flat_blocks(size_t n, int dev)
+{
+    size_t b = (n + 255) / 256, maxb = (size_t)(g_sm_count[dev] > 0 ? g_sm_count[dev] : 148) * 8;
+    if (b > maxb) b = maxb;
+    return (unsigned)(b ? b : 1);
+}
+
+int rct_rgb_to_lab(const uint8_t *rgb, double *lab, size_t n, void *stream)
+{
+    if (n == 0) return RCT_OK;
+    if (!rgb || !lab) return fail(RCT_ERR_ARG, "null pointer");
+    int dev, rc = ensure_device(&dev);
+    if (rc) return rc;
+    LAUNCH(k_rgb_to_lab, flat_blocks(n, dev), 256, (cudaStream_t)stream, rgb, lab, n);
+    return RCT_OK;
+}
+
+int rct_lab_to_rgb(const double *lab, uint8_t *rgb, double *rgb_float, size_t n, void *stream)
+{
+    if (n == 0) return RCT_OK;
+    if (!rgb || !lab) return fail(RCT_ERR_ARG, "null pointer");
+    int dev, rc = ensure_device(&dev);
+    if (rc) return rc;
+    LAUNCH(k_lab_to_rgb, flat_blocks(n, dev), 256, (cudaStream_t)stream, lab, rgb, rgb_float, n);
+    return RCT_OK;
+}
+
+size_t rct_pca_scratch_bytes(void) { return align_up(sizeof(RegionCtrl)) + 256; }
+
+int rct_apply_pca(const double *lab, size_t n, double *proj, double *mean3, double *comp3, void *scratch, void *stream)
+{
+    if (n == 0) return fail(RCT_ERR_ARG, "empty input");
+    if (!lab || !proj || !mean3 || !comp3 || !scratch) return fail(RCT_ERR_ARG, "null pointer");
+    int dev, rc = ensure_device(&dev);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    RegionCtrl *rcd = (RegionCtrl *)scratch;
+    int *bad = (int *)((uint8_t *)scratch + align_up(sizeof(RegionCtrl)));
+    CK(cudaMemsetAsync(scratch, 0, rct_pca_scratch_bytes(), st));
+    unsigned b = flat_blocks(n, dev);
+    if (b > 1024) b = 1024;
+    LAUNCH(k_pca_moments, b, 256, st, lab, n, rcd, bad);
+    LAUNCH(k_pca_solve, 1, 32, st, rcd, mean3, comp3);
+    LAUNCH(k_pca_project, flat_blocks(n, dev), 256, st, lab, n, rcd, proj);
+    return RCT_OK;
+}
+
+int rct_pca_inverse(const double *matched, size_t n, const double *mean3, const double *comp3, double *lab, void *stream)
+{
+    if (n == 0) return RCT_OK;
+    if (!matched || !mean3 || !comp3 || !lab) return fail(RCT_ERR_ARG, "null pointer");
+    int dev, rc = ensure_device(&dev);
+    if (rc) return rc;
+    LAUNCH(k_pca_inverse, flat_blocks(n, dev), 256, (cudaStream_t)stream, matched, n, mean3, comp3, lab);
+    return RCT_OK;
+}
+
+namespace {
+struct MatchLayout {
+    size_t off_rc[2], off_jobs, off_arr[2], a_fb, a_slot, a_keyB, a_payB, a_cumB, a_fine, a_part, arr_bytes[2], total;
+    size_t fine_cap[2];
+};
+MatchLayout match_layout(size_t nt, size_t ns)
+{
+    MatchLayout M{};
+    size_t o = 0;
+    for (int r = 0; r < 2; ++r) { M.off_rc[r] = o; o = align_up(o + sizeof(RegionCtrl)); }
+    M.off_jobs = o; o = align_up(o + 2 * sizeof(Job));
+    size_t n[2] = {nt, ns};
+    for (int r = 0; r < 2; ++r) {
+        size_t cap = n[r] ? n[r] : 1, fc = 2 * cap + kCoarse, np = (fc + 1 + kScanChunk - 1) / kScanChunk + 1;
+        M.fine_cap[r] = fc;
+        size_t a = 0;
+        a = align_up(a + 4 * cap);      // fb
+        a = align_up(a + 4 * cap);      // slot
+        a = align_up(a + 8 * cap);      // keyB
+        a = align_up(a + 4 * cap);      // payB
+        a = align_up(a + 4 * cap);      // cumB
+        a = align_up(a + 4 * (fc + 1)); // fine
+        a = align_up(a + 4 * np);       // partials
+        M.arr_bytes[r] = a;
+        M.off_arr[r] = o;
+        o += a;
+    }
+    M.total = o;
+    return M;
+}
+}  // namespace
+
+size_t rct_match_scratch_bytes(size_t nt, size_t ns) { return match_layout(nt, ns).total; }
+
+int rct_match_cdf(const double *target_proj, size_t nt, const double *source_proj, size_t ns, double *matched,
+                  int64_t *j_index, void *scratch, void *stream)
+{
+    if (nt == 0 || ns == 0) return fail(RCT_ERR_ARG, "empty input");
+    if (nt >= ((size_t)1 << 32) || ns >= ((size_t)1 << 32)) return fail(RCT_ERR_ARG, "input too long");
+    if (!target_proj || !source_proj || !matched || !scratch) return fail(RCT_ERR_ARG, "null pointer");
+    int dev, rc = ensure_device(&dev);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    MatchLayout M = match_layout(nt, ns);
+    uint8_t *ws = (uint8_t *)scratch;
+    Job hj[2];
+    const double *keys[2] = {target_proj, source_proj};
+    size_t n[2] = {nt, ns};
+    for (int r = 0; r < 2; ++r) {
+        size_t cap = n[r];
+        uint8_t *b = ws + M.off_arr[r];
+        size_t a = 0;
+        Job &j = hj[r];
+        j.rc = (RegionCtrl *)(ws + M.off_rc[r]);
+        j.keyA = keys[r]; j.payA = nullptr; j.cntA = nullptr;
+        j.fbA = (unsigned *)(b + a); a = align_up(a + 4 * cap);
+        j.slotA = (unsigned *)(b + a); a = align_up(a + 4 * cap);
+        j.keyB = (double *)(b + a); a = align_up(a + 8 * cap);
+        j.payB = (unsigned *)(b + a); a = align_up(a + 4 * cap);
+        j.cumB = (unsigned *)(b + a); a = align_up(a + 4 * cap);
+        j.fine = (unsigned *)(b + a); a = align_up(a + 4 * (M.fine_cap[r] + 1));
+        j.partials = (unsigned *)(b + a);
+        j.cap = (unsigned)cap; j.pad_ = 0;
+    }
+    CK(cudaMemsetAsync(ws, 0, M.off_jobs, st));
+    CK(cudaMemcpyAsync(ws + M.off_jobs, hj, sizeof hj, cudaMemcpyHostToDevice, st));
+    const Job *jobs = (const Job *)(ws + M.off_jobs);
+    size_t nmax = nt > ns ? nt : ns;
+    unsigned eb = flat_blocks(nmax, dev);
+    LAUNCH(k_key_range, flat_blocks(nt, dev), 256, st, target_proj, nt, hj[0].rc);
+    LAUNCH(k_key_range, flat_blocks(ns, dev), 256, st, source_proj, ns, hj[1].rc);
+    LAUNCH(k_key_range_finish, 1, 32, st, hj[0].rc, hj[1].rc, (unsigned long long)nt, (unsigned long long)ns);
+    LAUNCH(k_coarse_hist, dim3(eb, 2), 256, st, jobs);
+    size_t fc = M.fine_cap[0] > M.fine_cap[1] ? M.fine_cap[0] : M.fine_cap[1];
+    rc = sort_jobs(jobs, 2, eb, fc, st);
+    if (rc) return rc;
+    LAUNCH(k_match_generic, flat_blocks(nt, dev), 128, st, jobs, matched, (long long *)j_index);
+    return RCT_OK;
+}
+
+// ---- introspection -------------------------------------------------------------------------
+int rct_plan_info(rct_plan *p, int slot, rct_frame_info *info)
+{
+    if (!p || !info || slot < 0 || slot >= p->slots) return fail(RCT_ERR_ARG, "bad info request");
+    CK(cudaSetDevice(p->device));
+    CK(cudaDeviceSynchronize());
+    FrameCtrl *h = new (std::nothrow) FrameCtrl;
+    if (!h) return fail(RCT_ERR_NOMEM, "out of host memory");
+    cudaError_t e = cudaMemcpy(h, p->ctrl + slot, sizeof(FrameCtrl), cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) {
+        info->n_target = (int64_t)h->r[0].n_pix; info->n_source = (int64_t)h->r[1].n_pix;
+        info->d_target = h->r[0].d; info->d_source = h->r[1].d;
+        memcpy(info->t_mean, h->r[0].pca.mean, 24); memcpy(info->t_comp, h->r[0].pca.comp, 24);
+        memcpy(info->s_mean, h->r[1].pca.mean, 24); memcpy(info->s_comp, h->r[1].pca.comp, 24);
+        info->status = h->status;
+    }
+    delete h;
+    if (e != cudaSuccess) return fail(RCT_ERR_CUDA, "info copy failed: %s", cudaGetErrorString(e));
+    return RCT_OK;
+}
+
+int rct_plan_debug_hist(rct_plan *p, int slot, uint32_t *ht, uint32_t *hs)
+{
+    if (!p || slot < 0 || slot >= p->slots) return fail(RCT_ERR_ARG, "bad slot");
+    CK(cudaSetDevice(p->device));
+    CK(cudaDeviceSynchronize());
+    const unsigned *h = p->hist + (size_t)slot * p->L.hist_stride_u32;
+    if (ht) CK(cudaMemcpy(ht, h, 4 * (size_t)kCube, cudaMemcpyDeviceToHost));
+    if (hs) CK(cudaMemcpy(hs, h + kCube, 4 * (size_t)kCube, cudaMemcpyDeviceToHost));
+    return RCT_OK;
+}
+
+int rct_plan_debug_target(rct_plan *p, int slot, uint32_t *colour, double *key, int64_t *j, double *matched,
+                          uint32_t *cum)
+{
+    if (!p || slot < 0 || slot >= p->slots) return fail(RCT_ERR_ARG, "bad slot");
+    if (!(p->flags & RCT_FLAG_DEBUG)) return fail(RCT_ERR_ARG, "plan was not created with RCT_FLAG_DEBUG");
+    rct_frame_info info;
+    int rc = rct_plan_info(p, slot, &info);
+    if (rc) return rc;
+    size_t d = (size_t)info.d_target;
+    if (d == 0) return RCT_OK;
+    const Layout &L = p->L;
+    uint8_t *b = p->ws + L.off_region + L.region_bytes * (size_t)(2 * slot);
+    if (colour) CK(cudaMemcpy(colour, b + L.r_payB, 4 * d, cudaMemcpyDeviceToHost));
+    if (key) CK(cudaMemcpy(key, b + L.r_keyB, 8 * d, cudaMemcpyDeviceToHost));
+    if (cum) CK(cudaMemcpy(cum, b + L.r_cumB, 4 * d, cudaMemcpyDeviceToHost));
+    if (j) CK(cudaMemcpy(j, p->dbg_j + (size_t)slot * L.dbg_stride, 8 * d, cudaMemcpyDeviceToHost));
+    if (matched) CK(cudaMemcpy(matched, p->dbg_m + (size_t)slot * L.dbg_stride, 8 * d, cudaMemcpyDeviceToHost));
+    return RCT_OK;
+}
+
+int rct_plan_debug_lut(rct_plan *p, int slot, uint32_t *lut_host)
+{
+    if (!p || !lut_host || slot < 0 || slot >= p->slots) return fail(RCT_ERR_ARG, "bad slot");
+    CK(cudaSetDevice(p->device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(lut_host, p->lut + (size_t)slot * p->L.lut_stride_u32, 4 * (size_t)kCube, cudaMemcpyDeviceToHost));
+    return RCT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,1033 @@
+// rct_kernels.cuh -- sm_100a kernels of the regional colour-transfer path.
+//
+// Pipeline (one launch group = up to `slots` frames, blockIdx.z = slot, blockIdx.y = region
+// where a kernel works per region; region 0 = target/foreground, 1 = source/background):
+//
+//   k_hist          pixels -> two 2^24-bin colour-cube histograms        (a-1..a-3)
+//   k_compact       cube   -> list of distinct colours + counts
+//   k_lab_moments   list   -> exact integer moments, lab bounding box    (a-4, a-5)
+//   k_pca           moments-> mean_, components_[0], key range           (a-5)
+//   k_keys          list   -> float64 projection keys + coarse key histogram
+//   k_bucket_plan / k_zero_fine / k_bucket_count / scan / k_scatter / k_bucket_sort / scan
+//                   exact ascending sort of the distinct keys + cumulative pixel counts
+//   k_match         rank -> quantile lookup with np.interp semantics -> colour LUT (a-6, a-7)
+//   k_apply         pixels -> output through the LUT, fused with resample + combine (a-8, a-9)
+//
+// Everything after k_hist works per DISTINCT colour; the per-pixel passes (k_hist,
+// k_apply) are pure integer/byte streaming kernels.
+#pragma once
+#include "rct_math.cuh"
+
+namespace rct {
+
+constexpr int kCoarse = 4096;           // coarse key-histogram bins per region
+constexpr unsigned kCube = 1u << 24;    // colour-cube bins
+constexpr int kScanChunk = 4096;        // elements per scan block (256 threads x 16)
+
+struct RegionCtrl {
+    unsigned long long n_pix;           // region pixel count N (non-black pixels)
+    unsigned int d;                     // distinct colours
+    unsigned int n_fine;                // fine buckets in use
+    unsigned int n_fine_p1;             // n_fine + 1 (scan length)
+    unsigned int pad_;
+    long long limbs[9][3];              // exact moments: s1[0..2], s2[00,01,02,11,12,22]
+    unsigned long long lab_max[3];      // ord_enc(max lab_i)
+    unsigned long long lab_min[3];      // ~ord_enc(min lab_i)
+    Pca pca;
+    double klo, cscale;                 // coarse bin = floor((key-klo)*cscale)
+    unsigned int coarse[kCoarse];
+    unsigned int fine_base[kCoarse + 1];
+};
+
+struct FrameCtrl {
+    RegionCtrl r[2];
+    int status;
+    int pad_[3];
+};
+
+// One sort job = one region of one slot (or one array of the generic match_cdf call).
+struct Job {
+    RegionCtrl *rc;
+    const double *keyA;     // unsorted keys
+    const unsigned *payA;   // payload (colour index); NULL = identity
+    const unsigned *cntA;   // multiplicity; NULL = 1
+    unsigned *fbA, *slotA;  // per entry: fine bucket, slot within bucket
+    unsigned *fine;         // per fine bucket: count, then exclusive offset (n_fine+1)
+    unsigned *partials;     // scan scratch
+    double *keyB;           // sorted keys
+    unsigned *payB;         // sorted payload
+    unsigned *cumB;         // sorted counts, then inclusive cumulative counts
+    unsigned cap;
+    unsigned pad_;
+};
+
+// ------------------------------------------------------------------------------------------
+// streaming loads/stores of 16 RGB pixels (48 bytes) per thread
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 ldg_stream(const uint4 *p)
+{
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void stg_stream(uint4 *p, uint4 v)
+{
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+                 "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+
+__device__ __forceinline__ void load16_rgb(const uint8_t *base, size_t p0, int nvalid, bool vec, uint32_t c[16])
+{
+    if (vec && nvalid == 16) {
+        const uint4 *q = reinterpret_cast<const uint4 *>(base + 3 * p0);
+        uint4 a = ldg_stream(q), b = ldg_stream(q + 1), d = ldg_stream(q + 2);
+        uint32_t w[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, d.x, d.y, d.z, d.w};
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            c[4 * m + 0] = w[3 * m] & 0xffffffu;
+            c[4 * m + 1] = __funnelshift_r(w[3 * m], w[3 * m + 1], 24) & 0xffffffu;
+            c[4 * m + 2] = __funnelshift_r(w[3 * m + 1], w[3 * m + 2], 16) & 0xffffffu;
+            c[4 * m + 3] = w[3 * m + 2] >> 8;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            if (k < nvalid) {
+                const uint8_t *p = base + 3 * (p0 + k);
+                c[k] = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
+            } else {
+                c[k] = 0;
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ void store16_rgb(uint8_t *base, size_t p0, int nvalid, bool vec, const uint32_t c[16],
+                                            unsigned keep_mask /* bit k: write pixel k */)
+{
+    if (vec && nvalid == 16 && keep_mask == 0xffffu) {
+        uint32_t w[12];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            w[3 * m + 0] = c[4 * m] | (c[4 * m + 1] << 24);
+            w[3 * m + 1] = (c[4 * m + 1] >> 8) | (c[4 * m + 2] << 16);
+            w[3 * m + 2] = (c[4 * m + 2] >> 16) | (c[4 * m + 3] << 8);
+        }
+        uint4 *q = reinterpret_cast<uint4 *>(base + 3 * p0);
+        stg_stream(q, make_uint4(w[0], w[1], w[2], w[3]));
+        stg_stream(q + 1, make_uint4(w[4], w[5], w[6], w[7]));
+        stg_stream(q + 2, make_uint4(w[8], w[9], w[10], w[11]));
+    } else {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            if (k < nvalid && ((keep_mask >> k) & 1u)) {
+                uint8_t *p = base + 3 * (p0 + k);
+                p[0] = (uint8_t)c[k];
+                p[1] = (uint8_t)(c[k] >> 8);
+                p[2] = (uint8_t)(c[k] >> 16);
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ void load16_u8(const uint8_t *base, size_t p0, int nvalid, bool vec, uint32_t m[16])
+{
+    if (vec && nvalid == 16) {
+        uint4 a = ldg_stream(reinterpret_cast<const uint4 *>(base + p0));
+        uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int k = 0; k < 16; ++k) m[k] = (w[k >> 2] >> (8 * (k & 3))) & 255u;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) m[k] = (k < nvalid) ? base[p0 + k] : 0u;
+    }
+}
+
+// stylised pixels through the Pillow-NEAREST tables (a-1), never materialised
+__device__ __forceinline__ void gather16_rgb(const uint8_t *sty, const int *__restrict__ xtab,
+                                             const int *__restrict__ ytab, int W, int sw, size_t p0, int nvalid,
+                                             uint32_t c[16])
+{
+    int y = (int)(p0 / (size_t)W);
+    int x = (int)(p0 - (size_t)y * (size_t)W);
+    size_t rowoff = (size_t)__ldg(ytab + y) * (size_t)sw;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        if (k < nvalid) {
+            const uint8_t *p = sty + 3 * (rowoff + (size_t)__ldg(xtab + x));
+            c[k] = (uint32_t)__ldg(p) | ((uint32_t)__ldg(p + 1) << 8) | ((uint32_t)__ldg(p + 2) << 16);
+            if (++x == W) {
+                x = 0;
+                ++y;
+                if (k + 1 < nvalid) rowoff = (size_t)__ldg(ytab + y) * (size_t)sw;
+            }
+        } else {
+            c[k] = 0;
+        }
+    }
+}
+
+struct PixArgs {
+    const uint8_t *content, *sty, *mask;
+    uint8_t *out;
+    size_t content_stride, sty_stride, mask_stride, out_stride;  // bytes per frame
+    const int *xtab, *ytab;                                      // NULL when no resample
+    unsigned *hist;        // slot 0; slot s at + s*hist_stride (uint32 units): [2][2^24]
+    size_t hist_stride;
+    const unsigned *lut;   // slot 0; [2^24] per slot
+    size_t lut_stride;
+    FrameCtrl *ctrl;       // [slots]
+    int *status_out;       // [slots] or NULL
+    int W, sw;
+    size_t p_begin, p_end; // pixel range within a frame (row sharding)
+    int mode, label;
+    int aggregate;         // warp-aggregate equal colours before the atomic
+};
+
+__device__ __forceinline__ void region_flags(int mode, int label, uint32_t m, bool &in_t, bool &in_s)
+{
+    if (mode == 0) {
+        in_t = (m == 0);
+        in_s = !in_t;
+    } else if (mode == 1) {
+        in_t = in_s = (m == (uint32_t)label);
+    } else {
+        in_t = in_s = true;
+    }
+}
+
+__device__ __forceinline__ void hist_add(unsigned *hist, uint32_t col, bool valid, int aggregate)
+{
+    if (aggregate) {
+        unsigned lane = threadIdx.x & 31u;
+        uint32_t key = valid ? col : (0x80000000u | lane);
+        unsigned peers = __match_any_sync(0xffffffffu, key);
+        if (valid && (unsigned)(__ffs(peers) - 1) == lane) atomicAdd(hist + col, (unsigned)__popc(peers));
+    } else {
+        if (valid) atomicAdd(hist + col, 1u);
+    }
+}
+
+// k_hist: a-1 (resample), a-2 (mask algebra), a-3 (non-black selection) fused into one read
+// of the pixels; output = the two colour-cube histograms.
+template <bool RESAMPLE>
+__global__ void __launch_bounds__(256) k_hist(PixArgs a)
+{
+    const int slot = blockIdx.y;
+    const uint8_t *content = a.content + (size_t)slot * a.content_stride;
+    const uint8_t *sty = a.sty + (size_t)slot * a.sty_stride;
+    const uint8_t *mask = a.mask ? a.mask + (size_t)slot * a.mask_stride : nullptr;
+    unsigned *hist_t = a.hist + (size_t)slot * a.hist_stride;
+    unsigned *hist_s = hist_t + kCube;
+    const size_t npix = a.p_end - a.p_begin;
+    const size_t ngroups = (npix + 15) / 16;
+    const bool vec_c = (((uintptr_t)(content + 3 * a.p_begin)) & 15) == 0;
+    const bool vec_s = !RESAMPLE && (((uintptr_t)(sty + 3 * a.p_begin)) & 15) == 0;
+    const bool vec_m = mask && (((uintptr_t)(mask + a.p_begin)) & 15) == 0;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const unsigned lane = threadIdx.x & 31u;
+    // warp-uniform trip count (hist_add may use full-warp match)
+    for (size_t gbase = (size_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); gbase < ngroups; gbase += stride) {
+        size_t g = gbase + lane;
+        bool live = g < ngroups;
+        size_t p0 = a.p_begin + 16 * (live ? g : 0);
+        int nvalid = live ? (int)min((size_t)16, a.p_end - p0) : 0;
+        uint32_t c[16], s[16], m[16];
+        load16_rgb(content, p0, nvalid, vec_c, c);
+        if (RESAMPLE) gather16_rgb(sty, a.xtab, a.ytab, a.W, a.sw, p0, nvalid, s);
+        else load16_rgb(sty, p0, nvalid, vec_s, s);
+        if (mask) load16_u8(mask, p0, nvalid, vec_m, m);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            bool in_t, in_s;
+            region_flags(a.mode, a.label, mask ? m[k] : 0u, in_t, in_s);
+            bool ok = k < nvalid;
+            hist_add(hist_t, c[k], ok && in_t && c[k] != 0u, a.aggregate);
+            hist_add(hist_s, s[k], ok && in_s && s[k] != 0u, a.aggregate);
+        }
+    }
+}
+
+// k_apply: a-7..a-9 for pixels: target non-black -> LUT[colour]; target black -> black;
+// MASK mode non-target -> stylised pixel (background_np); LABEL mode non-target untouched.
+template <bool RESAMPLE>
+__global__ void __launch_bounds__(256) k_apply(PixArgs a)
+{
+    const int slot = blockIdx.y;
+    const uint8_t *content = a.content + (size_t)slot * a.content_stride;
+    const uint8_t *sty = a.sty + (size_t)slot * a.sty_stride;
+    const uint8_t *mask = a.mask ? a.mask + (size_t)slot * a.mask_stride : nullptr;
+    uint8_t *out = a.out + (size_t)slot * a.out_stride;
+    const unsigned *lut = a.lut + (size_t)slot * a.lut_stride;
+    const int status = a.ctrl[slot].status;
+    if (a.status_out && blockIdx.x == 0 && threadIdx.x == 0) a.status_out[slot] = status;
+    const size_t npix = a.p_end - a.p_begin;
+    const size_t ngroups = (npix + 15) / 16;
+    const bool vec_c = (((uintptr_t)(content + 3 * a.p_begin)) & 15) == 0;
+    const bool vec_s = !RESAMPLE && (((uintptr_t)(sty + 3 * a.p_begin)) & 15) == 0;
+    const bool vec_m = mask && (((uintptr_t)(mask + a.p_begin)) & 15) == 0;
+    const bool vec_o = (((uintptr_t)(out + 3 * a.p_begin)) & 15) == 0;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += stride) {
+        size_t p0 = a.p_begin + 16 * g;
+        int nvalid = (int)min((size_t)16, a.p_end - p0);
+        uint32_t c[16], s[16], m[16], o[16];
+        load16_rgb(content, p0, nvalid, vec_c, c);
+        if (mask) load16_u8(mask, p0, nvalid, vec_m, m);
+        if (a.mode == 0) {
+            if (RESAMPLE) gather16_rgb(sty, a.xtab, a.ytab, a.W, a.sw, p0, nvalid, s);
+            else load16_rgb(sty, p0, nvalid, vec_s, s);
+        }
+        unsigned keep = 0;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            bool in_t, in_s;
+            region_flags(a.mode, a.label, mask ? m[k] : 0u, in_t, in_s);
+            uint32_t v = 0;
+            if (in_t) {
+                keep |= 1u << k;
+                if (c[k] != 0u && k < nvalid) v = (status == 0) ? __ldg(lut + c[k]) : c[k];
+            } else if (a.mode == 0) {
+                keep |= 1u << k;
+                v = s[k];
+            }
+            o[k] = v;
+        }
+        store16_rgb(out, p0, nvalid, vec_o, o, keep);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// block-level helpers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned warp_excl_scan(unsigned v, unsigned &total)
+{
+    unsigned lane = threadIdx.x & 31u;
+    unsigned x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= (unsigned)o) x += y;
+    }
+    total = __shfl_sync(0xffffffffu, x, 31);
+    return x - v;
+}
+
+// exclusive scan of one value per thread across the block (blockDim.x <= 1024)
+__device__ __forceinline__ unsigned block_excl_scan(unsigned v, unsigned *s_warp /*[33]*/, unsigned &block_total)
+{
+    unsigned wtotal;
+    unsigned ex = warp_excl_scan(v, wtotal);
+    unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    unsigned nwarps = (blockDim.x + 31) >> 5;
+    __syncthreads();  // protect s_warp reuse
+    if (lane == 31) s_warp[warp] = wtotal;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned t = lane < nwarps ? s_warp[lane] : 0u, tt;
+        unsigned e = warp_excl_scan(t, tt);
+        if (lane < nwarps) s_warp[lane] = e;
+        if (lane == 0) s_warp[32] = tt;
+    }
+    __syncthreads();
+    block_total = s_warp[32];
+    return ex + s_warp[warp];
+}
+
+// k_compact: dense scan of the cube -> (colour, count) list per region; order irrelevant
+// (the moments are exact integers, the sort is by exact key).
+__global__ void __launch_bounds__(256) k_compact(unsigned *hist0, size_t hist_stride, FrameCtrl *ctrl,
+                                                 const Job *jobs)
+{
+    const int region = blockIdx.y, slot = blockIdx.z;
+    const unsigned *hist = hist0 + (size_t)slot * hist_stride + (size_t)region * kCube;
+    const Job &job = jobs[slot * 2 + region];
+    __shared__ unsigned s_warp[33];
+    __shared__ unsigned s_base;
+    unsigned bin0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
+    uint4 h = *reinterpret_cast<const uint4 *>(hist + bin0);
+    unsigned n = (h.x != 0) + (h.y != 0) + (h.z != 0) + (h.w != 0);
+    unsigned total;
+    unsigned off = block_excl_scan(n, s_warp, total);
+    if (total == 0) return;
+    if (threadIdx.x == 0) s_base = atomicAdd(&ctrl[slot].r[region].d, total);
+    __syncthreads();
+    unsigned pos = s_base + off;
+    unsigned *col = const_cast<unsigned *>(job.payA), *cnt = const_cast<unsigned *>(job.cntA);
+    unsigned hv[4] = {h.x, h.y, h.z, h.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (hv[k]) {
+            col[pos] = bin0 + k;
+            cnt[pos] = hv[k];
+            ++pos;
+        }
+}
+
+__device__ __forceinline__ long long warp_sum_ll(long long v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// k_lab_moments: a-4 + the reductions of a-5 over the distinct-colour list.
+__global__ void __launch_bounds__(256) k_lab_moments(FrameCtrl *ctrl, const Job *jobs)
+{
+    const int region = blockIdx.y, slot = blockIdx.z;
+    const Job &job = jobs[slot * 2 + region];
+    RegionCtrl *rc = &ctrl[slot].r[region];
+    const unsigned d = rc->d;
+    if ((size_t)blockIdx.x * blockDim.x >= d) return;
+    __shared__ MathTabs T;
+    __shared__ long long s_red[8][28];
+    __shared__ double s_mm[8][6];
+    stage_tabs(&T);
+    Moments m;
+    moments_zero(m);
+    double mx[3] = {-1e300, -1e300, -1e300}, mn[3] = {1e300, 1e300, 1e300};
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < d; e += (size_t)gridDim.x * blockDim.x) {
+        double lab[3];
+        rgb2lab(job.payA[e], &T, lab);
+        moments_add(m, lab, (long long)job.cntA[e]);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            mx[i] = fmax(mx[i], lab[i]);
+            mn[i] = fmin(mn[i], lab[i]);
+        }
+    }
+    long long v[28];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) split_limbs(m.s1[k], v + 3 * k);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) split_limbs(m.s2[k], v + 9 + 3 * k);
+    v[27] = m.n;
+    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+#pragma unroll
+    for (int k = 0; k < 28; ++k) {
+        long long s = warp_sum_ll(v[k]);
+        if (lane == 0) s_red[warp][k] = s;
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        double a = mx[i], b = mn[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a = fmax(a, __shfl_xor_sync(0xffffffffu, a, o));
+            b = fmin(b, __shfl_xor_sync(0xffffffffu, b, o));
+        }
+        if (lane == 0) {
+            s_mm[warp][i] = a;
+            s_mm[warp][3 + i] = b;
+        }
+    }
+    __syncthreads();
+    const unsigned nwarps = blockDim.x >> 5;
+    if (threadIdx.x < 9) {  // one moment each: sum limbs over warps, renormalise, publish
+        long long l[3] = {0, 0, 0};
+        for (unsigned w = 0; w < nwarps; ++w)
+            for (int j = 0; j < 3; ++j) l[j] += s_red[w][3 * threadIdx.x + j];
+        i128 tot = join_limbs(l);
+        split_limbs(tot, l);
+        for (int j = 0; j < 3; ++j)
+            atomicAdd(reinterpret_cast<unsigned long long *>(&rc->limbs[threadIdx.x][j]), (unsigned long long)l[j]);
+    } else if (threadIdx.x == 9) {
+        long long n = 0;
+        for (unsigned w = 0; w < nwarps; ++w) n += s_red[w][27];
+        atomicAdd(&rc->n_pix, (unsigned long long)n);
+    } else if (threadIdx.x >= 32 && threadIdx.x < 35) {
+        int i = threadIdx.x - 32;
+        double a = -1e300, b = 1e300;
+        for (unsigned w = 0; w < nwarps; ++w) {
+            a = fmax(a, s_mm[w][i]);
+            b = fmin(b, s_mm[w][3 + i]);
+        }
+        atomicMax(&rc->lab_max[i], ord_enc(a));
+        atomicMax(&rc->lab_min[i], ~ord_enc(b));
+    }
+}
+
+// k_pca: a-5 on the device (no host round trip): mean_, components_[0], sign rule, and the
+// key range used by the bucket sort.  One thread per slot.
+__global__ void k_pca(FrameCtrl *ctrl, int slots)
+{
+    int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= slots) return;
+    FrameCtrl *fc = &ctrl[slot];
+    for (int region = 0; region < 2; ++region) {
+        RegionCtrl *rc = &fc->r[region];
+        if (rc->n_pix == 0) continue;
+        i128 s1[3], s2[6];
+        for (int k = 0; k < 3; ++k) s1[k] = join_limbs(rc->limbs[k]);
+        for (int k = 0; k < 6; ++k) s2[k] = join_limbs(rc->limbs[3 + k]);
+        Pca p;
+        pca_from_moments((long long)rc->n_pix, s1, s2, &p);
+        rc->pca = p;
+        double lo = 0.0, hi = 0.0;
+        for (int i = 0; i < 3; ++i) {
+            double a = p.comp[i] * ord_dec(rc->lab_max[i]);
+            double b = p.comp[i] * ord_dec(~rc->lab_min[i]);
+            lo += fmin(a, b);
+            hi += fmax(a, b);
+        }
+        lo -= p.pm;
+        hi -= p.pm;
+        double span = hi - lo;
+        rc->klo = lo;
+        rc->cscale = (span > 0.0 && span < 1e300) ? (double)kCoarse / span : 0.0;
+    }
+    fc->status = (fc->r[0].n_pix == 0) ? 1 : (fc->r[1].n_pix == 0 ? 2 : 0);
+}
+
+__device__ __forceinline__ int coarse_bin(double key, double klo, double cscale, double &t)
+{
+    t = (key - klo) * cscale;
+    int cb = (int)floor(t);
+    if (!(t >= 0.0)) cb = 0;  // also catches NaN
+    if (cb > kCoarse - 1) cb = kCoarse - 1;
+    return cb;
+}
+
+// monotone non-decreasing map key -> fine bucket (coarse bins own consecutive fine ranges)
+__device__ __forceinline__ unsigned fine_bucket(double key, double klo, double cscale, const unsigned *fine_base)
+{
+    double t;
+    int cb = coarse_bin(key, klo, cscale, t);
+    unsigned base = fine_base[cb], nb = fine_base[cb + 1] - base;
+    double frac = t - (double)cb;
+    double f = frac * (double)nb;
+    unsigned sub = 0;
+    if (f > 0.0) sub = (f >= (double)nb) ? nb - 1 : (unsigned)f;
+    return base + sub;
+}
+
+// k_keys: projection key per distinct colour (C7) + privatised coarse histogram.
+__global__ void __launch_bounds__(256) k_keys(FrameCtrl *ctrl, const Job *jobs)
+{
+    const int region = blockIdx.y, slot = blockIdx.z;
+    const Job &job = jobs[slot * 2 + region];
+    RegionCtrl *rc = &ctrl[slot].r[region];
+    if (ctrl[slot].status != 0) return;
+    const unsigned d = rc->d;
+    if ((size_t)blockIdx.x * blockDim.x >= d) return;
+    __shared__ MathTabs T;
+    __shared__ unsigned s_hist[kCoarse];
+    for (int i = threadIdx.x; i < kCoarse; i += blockDim.x) s_hist[i] = 0;
+    stage_tabs(&T);
+    const double c0 = rc->pca.comp[0], c1 = rc->pca.comp[1], c2 = rc->pca.comp[2], pm = rc->pca.pm;
+    const double klo = rc->klo, cscale = rc->cscale;
+    double *keyA = const_cast<double *>(job.keyA);
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < d; e += (size_t)gridDim.x * blockDim.x) {
+        double lab[3], comp[3] = {c0, c1, c2};
+        rgb2lab(job.payA[e], &T, lab);
+        double key = project(lab, comp, pm);
+        keyA[e] = key;
+        double t;
+        atomicAdd(&s_hist[coarse_bin(key, klo, cscale, t)], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < kCoarse; i += blockDim.x) {
+        unsigned v = s_hist[i];
+        if (v) atomicAdd(&rc->coarse[i], v);
+    }
+}
+
+// coarse histogram of an arbitrary key array (generic match_cdf path)
+__global__ void __launch_bounds__(256) k_coarse_hist(const Job *jobs)
+{
+    const Job &job = jobs[blockIdx.y];
+    RegionCtrl *rc = job.rc;
+    const unsigned d = rc->d;
+    if ((size_t)blockIdx.x * blockDim.x >= d) return;
+    __shared__ unsigned s_hist[kCoarse];
+    for (int i = threadIdx.x; i < kCoarse; i += blockDim.x) s_hist[i] = 0;
+    __syncthreads();
+    const double klo = rc->klo, cscale = rc->cscale;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < d; e += (size_t)gridDim.x * blockDim.x) {
+        double t;
+        atomicAdd(&s_hist[coarse_bin(job.keyA[e], klo, cscale, t)], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < kCoarse; i += blockDim.x) {
+        unsigned v = s_hist[i];
+        if (v) atomicAdd(&rc->coarse[i], v);
+    }
+}
+
+// k_bucket_plan: histogram-equalising bucket layout: coarse bin with c keys gets max(1,2c)
+// consecutive fine buckets.  1024 threads, 4 coarse bins each.
+__global__ void __launch_bounds__(1024) k_bucket_plan(const Job *jobs)
+{
+    const Job &job = jobs[blockIdx.y];
+    RegionCtrl *rc = job.rc;
+    __shared__ unsigned s_warp[33];
+    unsigned nb[4], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        unsigned c = rc->coarse[threadIdx.x * 4 + k];
+        nb[k] = c ? 2u * c : 1u;
+        sum += nb[k];
+    }
+    unsigned total;
+    unsigned off = block_excl_scan(sum, s_warp, total);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        rc->fine_base[threadIdx.x * 4 + k] = off;
+        off += nb[k];
+    }
+    if (threadIdx.x == 1023) {
+        rc->fine_base[kCoarse] = total;
+        rc->n_fine = total;
+        rc->n_fine_p1 = total + 1;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_zero_fine(const Job *jobs)
+{
+    const Job &job = jobs[blockIdx.y];
+    const unsigned n = job.rc->n_fine_p1;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        job.fine[i] = 0;
+}
+
+__global__ void __launch_bounds__(256) k_bucket_count(const Job *jobs)
+{
+    const Job &job = jobs[blockIdx.y];
+    RegionCtrl *rc = job.rc;
+    const unsigned d = rc->d;
+    if (rc->n_fine == 0 || (size_t)blockIdx.x * blockDim.x >= d) return;
+    __shared__ unsigned s_base[kCoarse + 1];
+    for (int i = threadIdx.x; i <= kCoarse; i += blockDim.x) s_base[i] = rc->fine_base[i];
+    __syncthreads();
+    const double klo = rc->klo, cscale = rc->cscale;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < d; e += (size_t)gridDim.x * blockDim.x) {
+        unsigned fb = fine_bucket(job.keyA[e], klo, cscale, s_base);
+        job.fbA[e] = fb;
+        job.slotA[e] = atomicAdd(&job.fine[fb], 1u);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_scatter(const Job *jobs)
+{
+    const Job &job = jobs[blockIdx.y];
+    const unsigned d = job.rc->d;
+    if (job.rc->n_fine == 0) return;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < d; e += (size_t)gridDim.x * blockDim.x) {
+        unsigned pos = job.fine[job.fbA[e]] + job.slotA[e];
+        job.keyB[pos] = job.keyA[e];
+        job.payB[pos] = job.payA ? job.payA[e] : (unsigned)e;
+        job.cumB[pos] = job.cntA ? job.cntA[e] : 1u;
+    }
+}
+
+// k_bucket_sort: exact order inside each fine bucket (by key, then payload): one thread per
+// bucket, insertion sort in place.  Buckets hold ~0.5 keys on average.
+__global__ void __launch_bounds__(256) k_bucket_sort(const Job *jobs)
+{
+    const Job &job = jobs[blockIdx.y];
+    const unsigned nf = job.rc->n_fine;
+    for (size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x; b < nf; b += (size_t)gridDim.x * blockDim.x) {
+        unsigned lo = job.fine[b], hi = job.fine[b + 1];
+        for (unsigned i = lo + 1; i < hi; ++i) {
+            double k = job.keyB[i];
+            unsigned p = job.payB[i], c = job.cumB[i];
+            unsigned j = i;
+            while (j > lo) {
+                double kj = job.keyB[j - 1];
+                unsigned pj = job.payB[j - 1];
+                if (kj < k || (kj == k && pj < p)) break;
+                job.keyB[j] = kj;
+                job.payB[j] = pj;
+                job.cumB[j] = job.cumB[j - 1];
+                --j;
+            }
+            job.keyB[j] = k;
+            job.payB[j] = p;
+            job.cumB[j] = c;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// three-phase prefix sum over uint32, in place; WHICH selects the array of the job
+// (0: job.fine over n_fine_p1 elements, exclusive; 1: job.cumB over d elements, inclusive)
+// ------------------------------------------------------------------------------------------
+template <int WHICH>
+__device__ __forceinline__ void scan_target(const Job &job, unsigned *&data, unsigned &n)
+{
+    if (WHICH == 0) {
+        data = job.fine;
+        n = job.rc->n_fine ? job.rc->n_fine_p1 : 0;
+    } else {
+        data = job.cumB;
+        n = job.rc->n_fine ? job.rc->d : 0;
+    }
+}
+
+template <int WHICH>
+__global__ void __launch_bounds__(256) k_scan_reduce(const Job *jobs)
+{
+    const Job &job = jobs[blockIdx.y];
+    unsigned *data, n;
+    scan_target<WHICH>(job, data, n);
+    size_t base = (size_t)blockIdx.x * kScanChunk;
+    if (base >= n) return;
+    unsigned sum = 0;
+    for (int k = 0; k < 16; ++k) {
+        size_t i = base + k * 256 + threadIdx.x;
+        if (i < n) sum += data[i];
+    }
+    __shared__ unsigned s_w[8];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned t = 0;
+        for (int w = 0; w < 8; ++w) t += s_w[w];
+        job.partials[blockIdx.x] = t;
+    }
+}
+
+template <int WHICH>
+__global__ void __launch_bounds__(1024) k_scan_partials(const Job *jobs)
+{
+    const Job &job = jobs[blockIdx.y];
+    unsigned *data, n;
+    scan_target<WHICH>(job, data, n);
+    unsigned nblk = (unsigned)(((size_t)n + kScanChunk - 1) / kScanChunk);
+    __shared__ unsigned s_warp[33];
+    unsigned carry = 0;
+    for (unsigned base = 0; base < nblk; base += 1024) {
+        unsigned i = base + threadIdx.x;
+        unsigned v = i < nblk ? job.partials[i] : 0u;
+        unsigned total;
+        unsigned ex = block_excl_scan(v, s_warp, total);
+        if (i < nblk) job.partials[i] = carry + ex;
+        carry += total;
+    }
+}
+
+template <int WHICH>
+__global__ void __launch_bounds__(256) k_scan_apply(const Job *jobs)
+{
+    const Job &job = jobs[blockIdx.y];
+    unsigned *data, n;
+    scan_target<WHICH>(job, data, n);
+    size_t base = (size_t)blockIdx.x * kScanChunk;
+    if (base >= n) return;
+    __shared__ unsigned s_warp[33];
+    // thread t owns 16 consecutive elements
+    size_t i0 = base + (size_t)threadIdx.x * 16;
+    unsigned v[16], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        v[k] = (i0 + k < n) ? data[i0 + k] : 0u;
+        sum += v[k];
+    }
+    unsigned total;
+    unsigned off = block_excl_scan(sum, s_warp, total) + job.partials[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        unsigned incl = off + v[k];
+        if (i0 + k < n) data[i0 + k] = (WHICH == 0) ? off : incl;
+        off = incl;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// k_match: a-6 (match_cdf with np.linspace / np.interp semantics) + a-7 per distinct target
+// colour, in ascending key order.  Writes the colour -> output-RGB LUT.
+// ------------------------------------------------------------------------------------------
+struct Sorted {
+    const double *key;
+    const unsigned *cum;
+    unsigned d;
+    long long n;
+};
+
+// order statistic: q-th smallest (0-based) of the multiset
+__device__ __forceinline__ double os_lookup(const Sorted &v, long long q)
+{
+    unsigned lo = 0, hi = v.d - 1;  // smallest idx with cum[idx] > q
+    while (lo < hi) {
+        unsigned mid = (lo + hi) >> 1;
+        if ((long long)__ldg(v.cum + mid) > q) hi = mid; else lo = mid + 1;
+    }
+    return __ldg(v.key + lo);
+}
+
+// np.interp(x, np.linspace(0,1,v.n), sorted(v)) for 0 <= x <= 1
+__device__ double interp_lin_os(double x, const Sorted &v)
+{
+    const long long n = v.n;
+    if (n == 1) return os_lookup(v, 0);
+    long long m = (long long)(x * (double)(n - 1));
+    if (m < 0) m = 0;
+    if (m > n - 1) m = n - 1;
+    while (m + 1 <= n - 1 && lin(n, m + 1) <= x) ++m;
+    while (m > 0 && lin(n, m) > x) --m;
+    if (m >= n - 1) return os_lookup(v, n - 1);
+    double xm = lin(n, m);
+    double fm = os_lookup(v, m);
+    if (xm == x) return fm;
+    double fm1 = os_lookup(v, m + 1);
+    double slope = (fm1 - fm) / (lin(n, m + 1) - xm);
+    return slope * (x - xm) + fm;
+}
+
+struct MatchOut {
+    unsigned *lut;        // colour -> packed rgb (pipeline) or NULL
+    double *matched_pay;  // matched[payload] (generic match_cdf) or NULL
+    long long *j_pay;     // j[payload] or NULL
+    double *matchedB;     // debug, sorted order, or NULL
+    long long *jB;        // debug, sorted order, or NULL
+};
+
+__device__ __forceinline__ double match_one(const Sorted &t, const Sorted &s, unsigned i, long long &j_out)
+{
+    const double key = t.key[i];
+    unsigned i2 = i;
+    while (i2 + 1 < t.d && t.key[i2 + 1] == key) ++i2;  // ties share the upper rank
+    const long long r = (long long)t.cum[i2] - 1;
+    const long long T = t.n, S = s.n;
+    double m;
+    long long j;
+    if (T == S) {
+        j = r;
+        m = os_lookup(s, r);
+    } else if (T > S) {  // source stretched to T samples (LST:110-115)
+        j = r;
+        m = interp_lin_os(lin(T, r), s);
+    } else {  // target stretched to S samples (LST:116-121): t'[k] = interp(lin(S,k), lin(T,.), t)
+        if (T == 1) {
+            j = S - 1;
+        } else {
+            double xr = lin(T, r);
+            long long k = (long long)(xr * (double)(S - 1));
+            if (k < 0) k = 0;
+            if (k > S - 1) k = S - 1;
+            while (k + 1 <= S - 1 && interp_lin_os(lin(S, k + 1), t) <= key) ++k;
+            while (k > 0 && interp_lin_os(lin(S, k), t) > key) --k;
+            j = k;
+        }
+        if (j >= S - 1) {
+            m = os_lookup(s, S - 1);
+        } else {
+            double tj = interp_lin_os(lin(S, j), t);
+            double sj = os_lookup(s, j);
+            if (tj == key) {
+                m = sj;
+            } else {
+                double slope = (os_lookup(s, j + 1) - sj) / (interp_lin_os(lin(S, j + 1), t) - tj);
+                m = slope * (key - tj) + sj;
+            }
+        }
+    }
+    j_out = j;
+    return m;
+}
+
+// pipeline flavour: jobs[2*slot] = target, jobs[2*slot+1] = source
+__global__ void __launch_bounds__(128) k_match(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0, size_t lut_stride,
+                                               double *dbg_matched0, long long *dbg_j0, size_t dbg_stride)
+{
+    const int slot = blockIdx.y;
+    if (ctrl[slot].status != 0) return;
+    const Job &jt = jobs[2 * slot], &js = jobs[2 * slot + 1];
+    Sorted t{jt.keyB, jt.cumB, jt.rc->d, (long long)jt.rc->n_pix};
+    Sorted s{js.keyB, js.cumB, js.rc->d, (long long)js.rc->n_pix};
+    if ((size_t)blockIdx.x * blockDim.x >= t.d) return;
+    __shared__ MathTabs T;
+    stage_tabs(&T);
+    const Pca pca = jt.rc->pca;
+    unsigned *lut = lut0 + (size_t)slot * lut_stride;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < t.d; i += (size_t)gridDim.x * blockDim.x) {
+        long long j;
+        double m = match_one(t, s, (unsigned)i, j);
+        double lab[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) lab[c] = m * pca.comp[c] + pca.mean[c];  // inverse_transform
+        lut[jt.payB[i]] = lab2rgb(lab, &T, nullptr);
+        if (dbg_matched0) {
+            dbg_matched0[(size_t)slot * dbg_stride + i] = m;
+            dbg_j0[(size_t)slot * dbg_stride + i] = j;
+        }
+    }
+}
+
+// generic flavour (rct_match_cdf): jobs[0] = target, jobs[1] = source; payload = input index
+__global__ void __launch_bounds__(128) k_match_generic(const Job *jobs, double *matched, long long *jidx)
+{
+    const Job &jt = jobs[0], &js = jobs[1];
+    Sorted t{jt.keyB, jt.cumB, jt.rc->d, (long long)jt.rc->n_pix};
+    Sorted s{js.keyB, js.cumB, js.rc->d, (long long)js.rc->n_pix};
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < t.d; i += (size_t)gridDim.x * blockDim.x) {
+        long long j;
+        double m = match_one(t, s, (unsigned)i, j);
+        unsigned p = jt.payB[i];
+        matched[p] = m;
+        if (jidx) jidx[p] = j;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// the reference's stand-alone element-wise functions
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_rgb_to_lab(const uint8_t *rgb, double *lab, size_t n)
+{
+    __shared__ MathTabs T;
+    stage_tabs(&T);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const uint8_t *p = rgb + 3 * i;
+        uint32_t col = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
+        double v[3];
+        rgb2lab(col, &T, v);
+        lab[3 * i] = v[0];
+        lab[3 * i + 1] = v[1];
+        lab[3 * i + 2] = v[2];
+    }
+}
+
+__global__ void __launch_bounds__(256) k_lab_to_rgb(const double *lab, uint8_t *rgb, double *rgbf, size_t n)
+{
+    __shared__ MathTabs T;
+    stage_tabs(&T);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        double v[3] = {lab[3 * i], lab[3 * i + 1], lab[3 * i + 2]}, f[3];
+        uint32_t c = lab2rgb(v, &T, f);
+        rgb[3 * i] = (uint8_t)c;
+        rgb[3 * i + 1] = (uint8_t)(c >> 8);
+        rgb[3 * i + 2] = (uint8_t)(c >> 16);
+        if (rgbf) {
+            rgbf[3 * i] = f[0];
+            rgbf[3 * i + 1] = f[1];
+            rgbf[3 * i + 2] = f[2];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_pca_inverse(const double *matched, size_t n, const double *mean3,
+                                                     const double *comp3, double *lab)
+{
+    const double m0 = mean3[0], m1 = mean3[1], m2 = mean3[2], c0 = comp3[0], c1 = comp3[1], c2 = comp3[2];
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        double m = matched[i];
+        lab[3 * i] = m * c0 + m0;
+        lab[3 * i + 1] = m * c1 + m1;
+        lab[3 * i + 2] = m * c2 + m2;
+    }
+}
+
+// apply_pca on arbitrary float64 [n,3] data: moments pass ...
+__global__ void __launch_bounds__(256) k_pca_moments(const double *lab, size_t n, RegionCtrl *rc, int *bad)
+{
+    __shared__ long long s_red[8][28];
+    Moments m;
+    moments_zero(m);
+    bool oob = false;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+        double v[3] = {lab[3 * e], lab[3 * e + 1], lab[3 * e + 2]};
+        if (!(fabs(v[0]) < 64.0 && fabs(v[1]) < 64.0 && fabs(v[2]) < 64.0)) {
+            oob = true;
+            continue;
+        }
+        moments_add(m, v, 1);
+    }
+    if (oob) *bad = 1;
+    long long v[28];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) split_limbs(m.s1[k], v + 3 * k);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) split_limbs(m.s2[k], v + 9 + 3 * k);
+    v[27] = m.n;
+    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+#pragma unroll
+    for (int k = 0; k < 28; ++k) {
+        long long s = warp_sum_ll(v[k]);
+        if (lane == 0) s_red[warp][k] = s;
+    }
+    __syncthreads();
+    const unsigned nwarps = blockDim.x >> 5;
+    if (threadIdx.x < 9) {
+        long long l[3] = {0, 0, 0};
+        for (unsigned w = 0; w < nwarps; ++w)
+            for (int j = 0; j < 3; ++j) l[j] += s_red[w][3 * threadIdx.x + j];
+        i128 tot = join_limbs(l);
+        split_limbs(tot, l);
+        for (int j = 0; j < 3; ++j)
+            atomicAdd(reinterpret_cast<unsigned long long *>(&rc->limbs[threadIdx.x][j]), (unsigned long long)l[j]);
+    } else if (threadIdx.x == 9) {
+        long long nn = 0;
+        for (unsigned w = 0; w < nwarps; ++w) nn += s_red[w][27];
+        atomicAdd(&rc->n_pix, (unsigned long long)nn);
+    }
+}
+
+// ... eigen-solve ...
+__global__ void k_pca_solve(RegionCtrl *rc, double *mean3, double *comp3)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0 || rc->n_pix == 0) return;
+    i128 s1[3], s2[6];
+    for (int k = 0; k < 3; ++k) s1[k] = join_limbs(rc->limbs[k]);
+    for (int k = 0; k < 6; ++k) s2[k] = join_limbs(rc->limbs[3 + k]);
+    Pca p;
+    pca_from_moments((long long)rc->n_pix, s1, s2, &p);
+    rc->pca = p;
+    for (int i = 0; i < 3; ++i) {
+        mean3[i] = p.mean[i];
+        comp3[i] = p.comp[i];
+    }
+}
+
+// ... and projection (transform): X @ components_.T - mean_ @ components_.T
+__global__ void __launch_bounds__(256) k_pca_project(const double *lab, size_t n, const RegionCtrl *rc, double *proj)
+{
+    const double comp[3] = {rc->pca.comp[0], rc->pca.comp[1], rc->pca.comp[2]};
+    const double pm = rc->pca.pm;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+        double v[3] = {lab[3 * e], lab[3 * e + 1], lab[3 * e + 2]};
+        proj[e] = project(v, comp, pm);
+    }
+}
+
+// min/max of a key array -> klo / cscale of a job (generic match_cdf path)
+__global__ void __launch_bounds__(256) k_key_range(const double *key, size_t n, RegionCtrl *rc)
+{
+    double a = -1e308, b = 1e308;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+        double k = key[e];
+        a = fmax(a, k);
+        b = fmin(b, k);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a = fmax(a, __shfl_xor_sync(0xffffffffu, a, o));
+        b = fmin(b, __shfl_xor_sync(0xffffffffu, b, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMax(&rc->lab_max[0], ord_enc(a));
+        atomicMax(&rc->lab_min[0], ~ord_enc(b));
+    }
+}
+
+__global__ void k_key_range_finish(RegionCtrl *rc0, RegionCtrl *rc1, unsigned long long n0, unsigned long long n1)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    RegionCtrl *rcs[2] = {rc0, rc1};
+    unsigned long long ns[2] = {n0, n1};
+    for (int r = 0; r < 2; ++r) {
+        RegionCtrl *rc = rcs[r];
+        rc->n_pix = ns[r];
+        rc->d = (unsigned)ns[r];
+        double hi = ord_dec(rc->lab_max[0]), lo = ord_dec(~rc->lab_min[0]);
+        double span = hi - lo;
+        rc->klo = lo;
+        rc->cscale = (span > 0.0 && span < 1e300) ? (double)kCoarse / span : 0.0;
+    }
+}
+
+}  // namespace rct

@@ -1,0 +1,391 @@
+"""Drop-in for the hot path of the reference ``Style_3DGS/localized_style_transfer.py`` (LST).
+
+Same function names, positional order, defaults, return types and warning/empty-region
+behaviour as LST:11-168 and the tail LST:222-238, but every function runs hand-written
+sm_100a CUDA kernels through the C ABI in ``include/rct.h`` (``librct.so``).  numpy arrays
+in -> numpy arrays out (the reference's convention); CUDA ``torch`` tensors in -> CUDA
+tensors out, no host round trip.  There is no CPU fallback.
+
+PyTorch is used only for device memory, streams and (in :mod:`.sharded`) torch.distributed.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+
+import numpy as np
+import torch
+
+from . import _cabi
+from ._cabi import MODE_ALL, MODE_LABEL, MODE_MASK, check
+
+# ---- a-0: matrices for Reinhard's transform, computed exactly as LST:12-19 ------------------
+RGB_TO_LMS = np.array(
+    [[0.3811, 0.5783, 0.0402], [0.1967, 0.7244, 0.0782], [0.0241, 0.1288, 0.8444]]
+)
+LMS_TO_LAB = np.array(
+    [[1 / np.sqrt(3), 0, 0], [0, 1 / np.sqrt(6), 0], [0, 0, 1 / np.sqrt(2)]]
+) @ np.array([[1, 1, 1], [1, 1, -2], [1, -1, 0]])
+LAB_TO_LMS = np.linalg.inv(LMS_TO_LAB)
+LMS_TO_RGB = np.linalg.inv(RGB_TO_LMS)
+
+_matrices_installed = False
+_plan_lock = threading.Lock()
+_plans: dict = {}
+
+
+def _install_matrices():
+    global _matrices_installed
+    if not _matrices_installed:
+        m = np.ascontiguousarray(
+            np.stack([RGB_TO_LMS, LMS_TO_LAB, LAB_TO_LMS, LMS_TO_RGB]).astype(np.float64)
+        )
+        check(_cabi.lib().rct_set_matrices(m.ctypes.data_as(C.c_void_p)))
+        _matrices_installed = True
+
+
+def _require_cuda() -> torch.device:
+    if not torch.cuda.is_available():
+        raise RuntimeError(
+            "applied_image_processing_b200 needs a CUDA device (B200, sm_100a); "
+            "there is no CPU fallback for the colour-transfer path"
+        )
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _is_tensor(x) -> bool:
+    return isinstance(x, torch.Tensor)
+
+
+class Plan:
+    """A ``rct_plan`` plus the torch-owned workspace it lives in."""
+
+    def __init__(self, device: torch.device, H, W, sh, sw, slots=1, flags=0):
+        _install_matrices()
+        L = _cabi.lib()
+        self.device, self.H, self.W, self.sh, self.sw, self.slots, self.flags = device, H, W, sh, sw, slots, flags
+        nbytes = L.rct_plan_workspace_bytes(H, W, slots, flags)
+        if nbytes == 0:
+            raise ValueError("bad plan geometry")
+        with torch.cuda.device(device):
+            self.workspace = torch.empty(nbytes, dtype=torch.uint8, device=device)
+            handle = C.c_void_p()
+            check(L.rct_plan_create(device.index, H, W, sh, sw, slots, flags, self.workspace.data_ptr(),
+                                    nbytes, C.byref(handle)))
+        self.handle = handle
+        self.lock = threading.Lock()
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                _cabi.lib().rct_plan_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+    def set_option(self, option: int, value: int):
+        check(_cabi.lib().rct_plan_set_option(self.handle, option, value))
+
+    # -- introspection (parity tests) -------------------------------------------------------
+    def info(self, slot=0) -> dict:
+        fi = _cabi.FrameInfo()
+        check(_cabi.lib().rct_plan_info(self.handle, slot, C.byref(fi)))
+        return dict(
+            n_target=fi.n_target, n_source=fi.n_source, d_target=fi.d_target, d_source=fi.d_source,
+            t_mean=np.array(fi.t_mean), t_comp=np.array(fi.t_comp), s_mean=np.array(fi.s_mean),
+            s_comp=np.array(fi.s_comp), status=fi.status,
+        )
+
+    def debug_hist(self, slot=0):
+        ht = np.empty(1 << 24, np.uint32)
+        hs = np.empty(1 << 24, np.uint32)
+        check(_cabi.lib().rct_plan_debug_hist(self.handle, slot, ht.ctypes.data, hs.ctypes.data))
+        return ht, hs
+
+    def debug_target(self, slot=0) -> dict:
+        d = self.info(slot)["d_target"]
+        out = dict(colour=np.empty(d, np.uint32), key=np.empty(d, np.float64), j=np.empty(d, np.int64),
+                   matched=np.empty(d, np.float64), cum=np.empty(d, np.uint32))
+        check(_cabi.lib().rct_plan_debug_target(self.handle, slot, out["colour"].ctypes.data,
+                                                out["key"].ctypes.data, out["j"].ctypes.data,
+                                                out["matched"].ctypes.data, out["cum"].ctypes.data))
+        return out
+
+    def debug_lut(self, slot=0):
+        lut = np.empty(1 << 24, np.uint32)
+        check(_cabi.lib().rct_plan_debug_lut(self.handle, slot, lut.ctypes.data))
+        return lut
+
+
+def get_plan(device, H, W, sh, sw, slots=1, flags=0) -> Plan:
+    """Per-(device, geometry) plan cache (workspace cache behind a mutex)."""
+    key = (device.index, H, W, sh, sw, slots, flags)
+    with _plan_lock:
+        p = _plans.get(key)
+        if p is None:
+            p = Plan(device, H, W, sh, sw, slots, flags)
+            _plans[key] = p
+        return p
+
+
+def clear_plans():
+    with _plan_lock:
+        _plans.clear()
+
+
+def _warn(status: int):
+    # the reference prints, never raises (LST:141-147)
+    if status == _cabi.RCT_EMPTY_TARGET:
+        print("Warning: No foreground pixels found.")
+    elif status == _cabi.RCT_EMPTY_SOURCE:
+        print("Warning: No background pixels found for color transfer.")
+
+
+def _np_u8(a, name):
+    a = np.asarray(a)
+    if a.dtype != np.uint8:
+        raise TypeError(f"{name} must be uint8, got {a.dtype}")
+    return np.ascontiguousarray(a)
+
+
+def _transfer(content, stylised, mask, mode, label=0, out=None, slots=None, quiet=False):
+    """Shared driver: one image [H,W,3] or a batch [N,H,W,3]; numpy or CUDA tensors."""
+    L = _cabi.lib()
+    if _is_tensor(content):
+        dev = content.device
+        if dev.type != "cuda":
+            raise RuntimeError("tensor inputs must live on a CUDA device (no CPU fallback)")
+        for t in (content, stylised) + ((mask,) if mask is not None else ()):
+            if t.dtype != torch.uint8 or not t.is_contiguous() or t.device != dev:
+                raise TypeError("inputs must be contiguous uint8 tensors on one device")
+        batched = content.dim() == 4
+        n = content.shape[0] if batched else 1
+        H, W = content.shape[-3], content.shape[-2]
+        sty_b = stylised.dim() == 4
+        sh, sw = stylised.shape[-3], stylised.shape[-2]
+        mask_b = mask is not None and mask.dim() == 3
+        plan = get_plan(dev, H, W, sh, sw, slots or min(n, 8))
+        if out is None:
+            out = torch.empty_like(content) if mode != MODE_LABEL else content.clone()
+        with torch.cuda.device(dev), plan.lock:
+            check(L.rct_transfer_async(
+                plan.handle, content.data_ptr(), H * W * 3, stylised.data_ptr(), sh * sw * 3 if sty_b else 0,
+                mask.data_ptr() if mask is not None else None, H * W if mask_b else 0, out.data_ptr(),
+                H * W * 3, n, mode, label, _stream_ptr()))
+        return out
+    # numpy: the reference's own calling convention
+    dev = _require_cuda()
+    content = _np_u8(content, "content")
+    stylised = _np_u8(stylised, "stylised")
+    mask = _np_u8(mask, "mask") if mask is not None else None
+    batched = content.ndim == 4
+    n = content.shape[0] if batched else 1
+    H, W = content.shape[-3], content.shape[-2]
+    sh, sw = stylised.shape[-3], stylised.shape[-2]
+    if batched and stylised.ndim != 4:
+        stylised = np.ascontiguousarray(np.broadcast_to(stylised, (n,) + stylised.shape))
+    if batched and mask is not None and mask.ndim != 3:
+        mask = np.ascontiguousarray(np.broadcast_to(mask, (n,) + mask.shape))
+    plan = get_plan(dev, H, W, sh, sw, slots or min(n, 8))
+    if out is None:
+        out = np.empty_like(content) if mode != MODE_LABEL else content.copy()
+    status = np.zeros(n, np.int32)
+    with torch.cuda.device(dev), plan.lock:
+        check(L.rct_transfer_host(plan.handle, content.ctypes.data, stylised.ctypes.data,
+                                  mask.ctypes.data if mask is not None else None, out.ctypes.data, n, mode,
+                                  label, status.ctypes.data))
+    if not quiet:
+        for s in status:
+            _warn(int(s))
+    return out
+
+
+# ---- the reference's functions, same names and signatures ------------------------------------
+def rgb_to_lab_pixels(pixels_uint8):
+    """LST:67-77.  Nx3 uint8 RGB -> Nx3 float64 Reinhard lab."""
+    L = _cabi.lib()
+    _install_matrices()
+    if _is_tensor(pixels_uint8):
+        px = pixels_uint8.contiguous()
+        lab = torch.empty(px.shape, dtype=torch.float64, device=px.device)
+        with torch.cuda.device(px.device):
+            check(L.rct_rgb_to_lab(px.data_ptr(), lab.data_ptr(), px.numel() // 3, _stream_ptr()))
+        return lab
+    dev = _require_cuda()
+    px = torch.from_numpy(_np_u8(pixels_uint8, "pixels")).to(dev)
+    return rgb_to_lab_pixels(px).cpu().numpy()
+
+
+def lab_to_rgb_pixels(lab_pixels, return_float=False):
+    """LST:80-89.  Nx3 float64 lab -> Nx3 uint8 RGB (clip, *255, truncate)."""
+    L = _cabi.lib()
+    _install_matrices()
+    if _is_tensor(lab_pixels):
+        lab = lab_pixels.to(torch.float64).contiguous()
+        rgb = torch.empty(lab.shape, dtype=torch.uint8, device=lab.device)
+        rgbf = torch.empty(lab.shape, dtype=torch.float64, device=lab.device) if return_float else None
+        with torch.cuda.device(lab.device):
+            check(L.rct_lab_to_rgb(lab.data_ptr(), rgb.data_ptr(), rgbf.data_ptr() if return_float else None,
+                                   lab.numel() // 3, _stream_ptr()))
+        return (rgb, rgbf) if return_float else rgb
+    dev = _require_cuda()
+    lab = torch.from_numpy(np.ascontiguousarray(lab_pixels, np.float64)).to(dev)
+    r = lab_to_rgb_pixels(lab, return_float)
+    return (r[0].cpu().numpy(), r[1].cpu().numpy()) if return_float else r.cpu().numpy()
+
+
+def rgb_to_lab_image(image_uint8):
+    """LST:22-40.  [H,W,3] uint8 -> [H,W,3] float64 lab."""
+    shape = tuple(image_uint8.shape)
+    return rgb_to_lab_pixels(image_uint8.reshape(-1, 3)).reshape(shape)
+
+
+def lab_to_rgb_image(lab):
+    """LST:43-61.  [H,W,3] lab -> [H,W,3] uint8."""
+    shape = tuple(lab.shape)
+    return lab_to_rgb_pixels(lab.reshape(-1, 3)).reshape(shape)
+
+
+class RegionPCA:
+    """What the hot path uses of sklearn's fitted ``PCA(n_components=1)`` (LST:92-96, 161)."""
+
+    n_components = 1
+
+    def __init__(self, mean, comp):
+        self._mean, self._comp = mean, comp  # device float64 [3]
+
+    @property
+    def mean_(self):
+        return self._mean.cpu().numpy()
+
+    @property
+    def components_(self):
+        return self._comp.cpu().numpy().reshape(1, 3)
+
+    def inverse_transform(self, X):
+        """sklearn _base.py:205: X @ components_ + mean_."""
+        L = _cabi.lib()
+        as_np = not _is_tensor(X)
+        m = (torch.from_numpy(np.ascontiguousarray(X, np.float64)).to(self._mean.device) if as_np
+             else X.to(torch.float64)).contiguous().reshape(-1)
+        lab = torch.empty((m.numel(), 3), dtype=torch.float64, device=m.device)
+        with torch.cuda.device(m.device):
+            check(L.rct_pca_inverse(m.data_ptr(), m.numel(), self._mean.data_ptr(), self._comp.data_ptr(),
+                                    lab.data_ptr(), _stream_ptr()))
+        return lab.cpu().numpy() if as_np else lab
+
+
+def apply_pca(lab_data):
+    """LST:92-96: ``PCA(n_components=1).fit_transform`` -> (projection [N,1], pca)."""
+    L = _cabi.lib()
+    _install_matrices()
+    as_np = not _is_tensor(lab_data)
+    dev = _require_cuda() if as_np else lab_data.device
+    lab = (torch.from_numpy(np.ascontiguousarray(lab_data, np.float64)).to(dev) if as_np
+           else lab_data.to(torch.float64)).contiguous()
+    n = lab.shape[0]
+    proj = torch.empty((n, 1), dtype=torch.float64, device=dev)
+    mean = torch.empty(3, dtype=torch.float64, device=dev)
+    comp = torch.empty(3, dtype=torch.float64, device=dev)
+    scratch = torch.empty(L.rct_pca_scratch_bytes(), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(L.rct_apply_pca(lab.data_ptr(), n, proj.data_ptr(), mean.data_ptr(), comp.data_ptr(),
+                              scratch.data_ptr(), _stream_ptr()))
+    pca = RegionPCA(mean, comp)
+    return (proj.cpu().numpy() if as_np else proj), pca
+
+
+def match_cdf(target_proj, source_proj, return_index=False):
+    """LST:99-125: exact sort-based CDF matching along one dimension -> [N,1]."""
+    L = _cabi.lib()
+    as_np = not _is_tensor(target_proj)
+    dev = _require_cuda() if as_np else target_proj.device
+    t = (torch.from_numpy(np.ascontiguousarray(target_proj, np.float64)).to(dev) if as_np
+         else target_proj.to(torch.float64)).contiguous().reshape(-1)
+    s = (torch.from_numpy(np.ascontiguousarray(source_proj, np.float64)).to(dev) if not _is_tensor(source_proj)
+         else source_proj.to(torch.float64)).contiguous().reshape(-1)
+    matched = torch.empty(t.numel(), dtype=torch.float64, device=dev)
+    jidx = torch.empty(t.numel(), dtype=torch.int64, device=dev) if return_index else None
+    scratch = torch.empty(L.rct_match_scratch_bytes(t.numel(), s.numel()), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(L.rct_match_cdf(t.data_ptr(), t.numel(), s.data_ptr(), s.numel(), matched.data_ptr(),
+                              jidx.data_ptr() if return_index else None, scratch.data_ptr(), _stream_ptr()))
+        if as_np:
+            torch.cuda.current_stream().synchronize()
+    matched = matched.reshape(-1, 1)
+    if as_np:
+        matched = matched.cpu().numpy()
+        if return_index:
+            jidx = jidx.cpu().numpy()
+    return (matched, jidx) if return_index else matched
+
+
+def color_transfer_foreground(foreground_img, background_img):
+    """LST:128-168.  Recolour the non-black pixels of ``foreground_img`` so that their
+    principal-axis distribution matches the non-black pixels of ``background_img``."""
+    return _transfer(foreground_img, background_img, None, MODE_ALL)
+
+
+def regional_color_transfer(content, stylized, background_mask, slots=None):
+    """The tail of ``run_localized_style_transfer`` (LST:222-238) in one fused call:
+    NEAREST-resize ``stylized`` to the mask size if needed, mask algebra, colour transfer of
+    the foreground, final combination.  Accepts one image or a batch (leading dim)."""
+    return _transfer(content, stylized, background_mask, MODE_MASK, slots=slots)
+
+
+def regional_color_transfer_labels(content, stylized, labels, n_labels, slots=None):
+    """BASELINE.json config 5 (no counterpart in the reference): for every label l the content
+    pixels with that label are matched to the stylised pixels with that label."""
+    out = None
+    for lab in range(n_labels):
+        out = _transfer(content, stylized, labels, MODE_LABEL, label=lab, out=out, slots=slots, quiet=True)
+    return out
+
+
+def extract_foreground_deeplab(content_img, threshold=0.5):
+    """LST:171-188 -- out of scope: the north-star path starts after
+    the segmentation mask exists; DeepLabV3 stays stock torchvision."""
+    raise NotImplementedError(
+        "DeepLabV3 mask extraction is outside the accelerated path; pass background_mask= to "
+        "run_localized_style_transfer (weights are not available offline)"
+    )
+
+
+def run_localized_style_transfer(
+    content_img_path,
+    style_img_path,
+    output_path="../output",
+    file_name="test",
+    use_depth=False,
+    depth_offset=0.5,
+    depth_prominence=20,
+    *,
+    background_mask=None,
+    stylized_image=None,
+):
+    """LST:191-245 with the two out-of-scope producers injected: ``background_mask`` (uint8
+    [1,H,W] or [H,W], what extract_foreground_deeplab returns) and ``stylized_image`` (path or
+    uint8 array, what adain_inference writes).  The in-scope tail (LST:218-243) is unchanged:
+    resize -> masks -> colour transfer -> combine -> save JPEG; returns the saved path."""
+    from PIL import Image
+
+    content_np = np.array(Image.open(content_img_path).convert("RGB"))
+    if background_mask is None:
+        background_mask = extract_foreground_deeplab(content_np)
+    if stylized_image is None:
+        raise NotImplementedError("AdaIN inference is outside the accelerated path; pass stylized_image=")
+    background_mask = np.asarray(background_mask, np.uint8)
+    if background_mask.ndim == 3:
+        background_mask = background_mask[0]
+    if isinstance(stylized_image, str):
+        stylized_np = np.array(Image.open(stylized_image).convert("RGB"))
+    else:
+        stylized_np = np.asarray(stylized_image, np.uint8)
+    combined_image = regional_color_transfer(content_np, stylized_np, background_mask)
+    save_path = f"{output_path}/localized_style_transfer_result.jpg"
+    Image.fromarray(combined_image.astype(np.uint8)).save(save_path)
+    return save_path

@@ -1,0 +1,165 @@
+/*
+ * rct.h -- C ABI of librct.so: B200-native regional colour transfer.
+ *
+ * Drop-in boundary for the hot path of the reference
+ *   Style_3DGS/localized_style_transfer.py  (abbrev. LST), lines 11-168 and 222-238.
+ * Every entry point names the reference interface it replaces.  Signatures carry plain
+ * pointers and sizes only (no torch / numpy types).  Unless a name ends in `_host`, data
+ * pointers are DEVICE pointers and the call is asynchronous on `stream` (a cudaStream_t
+ * passed as void*; NULL = the legacy default stream).  No entry point synchronises the
+ * device except where stated.  There is no CPU fallback: without a CUDA device every
+ * compute entry point returns RCT_ERR_CUDA.
+ *
+ * Image layout: uint8, HWC, C-contiguous (what np.array(PIL.Image) yields, LST:200-201);
+ * batches are NHWC with explicit frame strides in bytes.
+ *
+ * Return convention: 0 = ok, 1 = empty target region ("Warning: No
+ * foreground pixels found", LST:141-143), 2 = empty source region (LST:145-147), <0 = error
+ * (rct_last_error() gives the text).  On 1/2 the output is what the reference returns in
+ * that case (the unmodified foreground composited with the background).
+ */
+#ifndef RCT_H_
+#define RCT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RCT_OK 0
+#define RCT_EMPTY_TARGET 1
+#define RCT_EMPTY_SOURCE 2
+#define RCT_ERR_CUDA (-1)
+#define RCT_ERR_ARG (-2)
+#define RCT_ERR_NOMEM (-3)
+
+/* Region selection modes of the fused pipeline.
+ * MASK : `mask` is the reference's background_mask (LST:218), values {0,1}.  Target =
+ *        content pixels with mask==0, source = stylised pixels with mask!=0; the output is
+ *        LST:238's combined_image.
+ * LABEL: `mask` is a label map; target = content, source = stylised, both restricted to
+ *        mask==label; only those output pixels are written (one pass per label; the 8-label
+ *        configuration of BASELINE.json, which has no counterpart in the reference).
+ * ALL  : color_transfer_foreground(content, stylised) itself (LST:128-168); `mask` ignored. */
+#define RCT_MODE_MASK 0
+#define RCT_MODE_LABEL 1
+#define RCT_MODE_ALL 2
+
+#define RCT_FLAG_DEBUG 1u /* keep per-colour rank / matched-value tables for rct_plan_debug_* */
+
+typedef struct rct_plan rct_plan; /* opaque; one per (device, geometry); not thread-safe */
+
+int rct_version(void);
+const char *rct_last_error(void); /* thread-local text of the last error on this thread */
+
+/* a-0: the four Reinhard matrices RGB_TO_LMS, LMS_TO_LAB, LAB_TO_LMS, LMS_TO_RGB (LST:12-19),
+ * 4 x 9 doubles, row-major.  The host computes them with numpy exactly as LST:12-19 does
+ * (the inverses carry LAPACK round-off) and installs them here; defaults are the values of
+ * numpy 2.3.5 / OpenBLAS 0.3.30.  Takes effect for plans created afterwards. */
+int rct_set_matrices(const double *m36);
+int rct_get_matrices(double *m36);
+
+/* a-1: Pillow Image.resize(..., Image.NEAREST) source-index table (LST:223-230): host
+ * function, writes out_size int32 indices (accumulated-double recurrence). */
+int rct_resample_table(int in_size, int out_size, int32_t *tab_host);
+
+/* ---- plans ----------------------------------------------------------------------------
+ * A plan fixes the geometry: content/mask/output are H x W, the stylised image is sh x sw
+ * (resampled to H x W on the fly with the a-1 tables when different, never materialised),
+ * and `slots` frames are processed per launch group.  `workspace` is device memory of at
+ * least rct_plan_workspace_bytes() bytes owned by the caller (e.g. a torch tensor), or
+ * NULL to let the library cudaMalloc it.  Creation synchronises the device once. */
+size_t rct_plan_workspace_bytes(int H, int W, int slots, unsigned flags);
+int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigned flags,
+                    void *workspace, size_t workspace_bytes, rct_plan **plan);
+int rct_plan_destroy(rct_plan *plan);
+/* tuning knobs; RCT_OPT_AGGREGATE (0/1): warp-aggregate equal colours before the histogram
+ * atomic (pays off on flat / low-colour images, costs a MATCH per pixel otherwise) */
+#define RCT_OPT_AGGREGATE 0
+int rct_plan_set_option(rct_plan *plan, int option, int value);
+
+/* ---- the fused pipeline: LST:222-238 + color_transfer_foreground (LST:128-168) ----------
+ * n_frames frames (any number; processed `slots` at a time), frame f at base + f*stride.
+ * stride 0 for `stylised`/`mask` broadcasts one image to all frames.  `mask` may be NULL in
+ * RCT_MODE_ALL.  Per-frame status codes are left in plan memory; rct_plan_status() fetches
+ * them (synchronises `stream`). */
+int rct_transfer_async(rct_plan *plan, const uint8_t *content, size_t content_stride,
+                       const uint8_t *stylised, size_t stylised_stride, const uint8_t *mask,
+                       size_t mask_stride, uint8_t *out, size_t out_stride, int n_frames,
+                       int mode, int label, void *stream);
+int rct_plan_status(rct_plan *plan, int *status_host, int n_frames, void *stream);
+
+/* Same through HOST buffers (the reference's calling convention: numpy arrays in, numpy
+ * array out).  Copies in, runs, copies out, synchronises; pinned host memory makes the
+ * copies true DMA.  Returns the worst per-frame status. */
+int rct_transfer_host(rct_plan *plan, const uint8_t *content_h, const uint8_t *stylised_h,
+                      const uint8_t *mask_h, uint8_t *out_h, int n_frames, int mode, int label,
+                      int *status_host /* [n_frames] or NULL */);
+
+/* ---- row-sharded single image: the pipeline in three phases ---------------
+ * Each rank owns rows [row0, row0+rows) of the H x W image described by the plan (slot 0).
+ * 1. rct_shard_hist_async   : zero the colour-cube histograms and count the local rows;
+ * 2. all-reduce (sum, uint32) the buffer rct_plan_hist_ptr()/rct_plan_hist_bytes() over the
+ *    ranks -- done by the caller (NCCL through torch.distributed);
+ * 3. rct_shard_solve_async  : statistics, PCA, exact CDF matching -> colour LUT (redundant,
+ *    identical on every rank);
+ * 4. rct_shard_apply_async  : write the local rows of the output.
+ * Pointers are to the FULL images (row offsets are applied inside). */
+int rct_shard_hist_async(rct_plan *plan, const uint8_t *content, const uint8_t *stylised,
+                         const uint8_t *mask, int mode, int label, int row0, int rows,
+                         void *stream);
+void *rct_plan_hist_ptr(rct_plan *plan);
+size_t rct_plan_hist_bytes(rct_plan *plan);
+int rct_shard_solve_async(rct_plan *plan, void *stream);
+int rct_shard_apply_async(rct_plan *plan, const uint8_t *content, const uint8_t *stylised,
+                          const uint8_t *mask, uint8_t *out, int mode, int label, int row0,
+                          int rows, void *stream);
+
+/* ---- the reference's individual functions ------------------------------------------------ */
+/* rgb_to_lab_pixels / rgb_to_lab_image (LST:67-77, 22-40): uint8 [n,3] -> float64 [n,3] */
+int rct_rgb_to_lab(const uint8_t *rgb, double *lab, size_t n, void *stream);
+/* lab_to_rgb_pixels / lab_to_rgb_image (LST:80-89, 43-61): float64 [n,3] -> uint8 [n,3];
+ * rgb_float (optional, may be NULL) receives the clipped [0,1] doubles before quantisation */
+int rct_lab_to_rgb(const double *lab, uint8_t *rgb, double *rgb_float, size_t n, void *stream);
+/* apply_pca (LST:92-96 -> sklearn PCA(1).fit_transform, covariance_eigh): float64 [n,3] ->
+ * projection [n], mean_[3], components_[3] (device pointers).  |lab| must be < 64.
+ * scratch: device memory of rct_pca_scratch_bytes() bytes. */
+size_t rct_pca_scratch_bytes(void);
+int rct_apply_pca(const double *lab, size_t n, double *proj, double *mean3, double *comp3,
+                  void *scratch, void *stream);
+/* pca.inverse_transform (LST:161; sklearn _base.py:205): matched [n] -> lab [n,3] */
+int rct_pca_inverse(const double *matched, size_t n, const double *mean3, const double *comp3,
+                    double *lab, void *stream);
+/* match_cdf (LST:99-125): exact sort-based quantile mapping of target_proj [nt] onto
+ * source_proj [ns]; matched [nt].  j_index (optional) receives the index np.interp resolves
+ * each query to (int64).  scratch: rct_match_scratch_bytes(nt, ns) bytes of device memory. */
+size_t rct_match_scratch_bytes(size_t nt, size_t ns);
+int rct_match_cdf(const double *target_proj, size_t nt, const double *source_proj, size_t ns,
+                  double *matched, int64_t *j_index, void *scratch, void *stream);
+
+/* ---- introspection for parity tests (RCT_FLAG_DEBUG plans; all synchronise) -------------- */
+typedef struct {
+    int64_t n_target, n_source;     /* region pixel counts (non-black, LST:134-138) */
+    int64_t d_target, d_source;     /* distinct colours per region */
+    double t_mean[3], t_comp[3];    /* fg_pca.mean_ / components_[0] */
+    double s_mean[3], s_comp[3];    /* bg_pca.* */
+    int status;
+} rct_frame_info;
+int rct_plan_info(rct_plan *plan, int slot, rct_frame_info *info_host);
+/* colour-cube histograms: 2 x 2^24 uint32 (target, source), index r | g<<8 | b<<16 */
+int rct_plan_debug_hist(rct_plan *plan, int slot, uint32_t *hist_t_host, uint32_t *hist_s_host);
+/* per target colour, in ascending key order: colour index, projection key, CDF index j
+ * (what np.interp resolved to), matched value, cumulative pixel count.  Arrays of d_target. */
+int rct_plan_debug_target(rct_plan *plan, int slot, uint32_t *colour, double *key, int64_t *j,
+                          double *matched, uint32_t *cum);
+int rct_plan_debug_lut(rct_plan *plan, int slot, uint32_t *lut_host /* 2^24 */);
+
+/* number of kernels launched by this library on this thread since the last reset */
+long long rct_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RCT_H_ */
