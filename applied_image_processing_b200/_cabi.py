@@ -13,6 +13,7 @@ RCT_OK, RCT_EMPTY_TARGET, RCT_EMPTY_SOURCE = 0, 1, 2
 MODE_MASK, MODE_LABEL, MODE_ALL = 0, 1, 2
 FLAG_DEBUG = 1
 OPT_AGGREGATE = 0
+OPT_TIMING = 1
 
 _lib = None
 _lock = threading.Lock()
@@ -41,6 +42,7 @@ SIGNATURES = {
     "rct_plan_create": (_i, [_i, _i, _i, _i, _i, _i, _u, _vp, _sz, C.POINTER(_vp)]),
     "rct_plan_destroy": (_i, [_vp]),
     "rct_plan_set_option": (_i, [_vp, _i, _i]),
+    "rct_plan_timing": (_i, [_vp, _vp, _vp, _i]),
     "rct_transfer_async": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _sz, _vp, _sz, _i, _i, _i, _vp]),
     "rct_plan_status": (_i, [_vp, _vp, _i, _vp]),
     "rct_transfer_host": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),

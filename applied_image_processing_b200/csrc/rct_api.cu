@@ -7,6 +7,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "../../include/rct.h"
 #include "rct_kernels.cuh"
@@ -164,6 +165,11 @@ struct rct_plan {
     uint8_t *stage;  // device staging of the host entry point
     size_t stage_bytes;
     cudaStream_t own_stream;
+    // RCT_OPT_TIMING: five events per launch group (memset | k_hist | solve | k_apply)
+    int timing;
+    std::vector<cudaEvent_t> ev_busy, ev_free;
+    double phase_ms[4];
+    long long phase_groups;
 };
 
 extern "C" {
@@ -312,6 +318,8 @@ int rct_plan_destroy(rct_plan *p)
     if (!p) return RCT_OK;
     cudaSetDevice(p->device);
     if (p->own_stream) cudaStreamDestroy(p->own_stream);
+    for (cudaEvent_t e : p->ev_busy) cudaEventDestroy(e);
+    for (cudaEvent_t e : p->ev_free) cudaEventDestroy(e);
     if (p->owns_ws && p->ws) cudaFree(p->ws);
     if (p->status_frames) cudaFree(p->status_frames);
     if (p->stage) cudaFree(p->stage);
@@ -322,7 +330,8 @@ int rct_plan_destroy(rct_plan *p)
 int rct_plan_set_option(rct_plan *p, int option, int value)
 {
     if (!p) return fail(RCT_ERR_ARG, "null plan");
-    if (option == 0) p->aggregate = value;
+    if (option == RCT_OPT_AGGREGATE) p->aggregate = value;
+    else if (option == RCT_OPT_TIMING) p->timing = value;
     else return fail(RCT_ERR_ARG, "unknown option %d", option);
     return RCT_OK;
 }
@@ -373,16 +382,34 @@ unsigned entry_blocks(rct_plan *p, int nslots)
     return (unsigned)(blocks ? blocks : 1);
 }
 
+int mark(rct_plan *p, cudaStream_t st)
+{
+    if (!p->timing) return RCT_OK;
+    cudaEvent_t e;
+    if (!p->ev_free.empty()) {
+        e = p->ev_free.back();
+        p->ev_free.pop_back();
+    } else {
+        CK(cudaEventCreate(&e));
+    }
+    p->ev_busy.push_back(e);
+    CK(cudaEventRecord(e, st));
+    return RCT_OK;
+}
+
 int phase_hist(rct_plan *p, const FrameSet &f, int nslots, int mode, int label, size_t p_begin, size_t p_end,
                cudaStream_t st)
 {
+    int rc;
+    if ((rc = mark(p, st))) return rc;
     CK(cudaMemsetAsync(p->ctrl, 0, sizeof(FrameCtrl) * nslots, st));
     CK(cudaMemsetAsync(p->hist, 0, 4 * p->L.hist_stride_u32 * nslots, st));
+    if ((rc = mark(p, st))) return rc;
     PixArgs a = pix_args(p, f, mode, label, p_begin, p_end, nullptr);
     dim3 grid(pix_blocks(p, p_end - p_begin, nslots), nslots);
     if (p->resample) LAUNCH(k_hist<true>, grid, 256, st, a);
     else LAUNCH(k_hist<false>, grid, 256, st, a);
-    return RCT_OK;
+    return mark(p, st);
 }
 
 int sort_jobs(const Job *jobs, int njobs, unsigned eblocks, size_t fine_cap, cudaStream_t st)
@@ -413,7 +440,7 @@ int phase_solve(rct_plan *p, int nslots, cudaStream_t st)
     if (rc) return rc;
     LAUNCH(k_match, dim3(eb * 2, nslots), 128, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32, p->dbg_m, p->dbg_j,
            p->L.dbg_stride);
-    return RCT_OK;
+    return mark(p, st);
 }
 
 int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label, size_t p_begin, size_t p_end,
@@ -423,7 +450,7 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
     dim3 grid(pix_blocks(p, p_end - p_begin, nslots), nslots);
     if (p->resample) LAUNCH(k_apply<true>, grid, 256, st, a);
     else LAUNCH(k_apply<false>, grid, 256, st, a);
-    return RCT_OK;
+    return mark(p, st);
 }
 
 int check_mode(int mode, const void *mask)
@@ -698,6 +725,32 @@ int rct_match_cdf(const double *target_proj, size_t nt, const double *source_pro
     rc = sort_jobs(jobs, 2, eb, fc, st);
     if (rc) return rc;
     LAUNCH(k_match_generic, flat_blocks(nt, dev), 128, st, jobs, matched, (long long *)j_index);
+    return RCT_OK;
+}
+
+// ---- phase timing (RCT_OPT_TIMING) -------------------------------------------------------------
+int rct_plan_timing(rct_plan *p, double *ms4, long long *groups, int reset)
+{
+    if (!p) return fail(RCT_ERR_ARG, "null plan");
+    CK(cudaSetDevice(p->device));
+    if (p->ev_busy.size() % 5 != 0) return fail(RCT_ERR_ARG, "timing events out of step (mixed entry points?)");
+    for (size_t g = 0; g + 5 <= p->ev_busy.size(); g += 5) {
+        CK(cudaEventSynchronize(p->ev_busy[g + 4]));
+        for (int k = 0; k < 4; ++k) {
+            float ms = 0.f;
+            CK(cudaEventElapsedTime(&ms, p->ev_busy[g + k], p->ev_busy[g + k + 1]));
+            p->phase_ms[k] += (double)ms;
+        }
+        ++p->phase_groups;
+    }
+    for (cudaEvent_t e : p->ev_busy) p->ev_free.push_back(e);
+    p->ev_busy.clear();
+    if (ms4) memcpy(ms4, p->phase_ms, sizeof p->phase_ms);
+    if (groups) *groups = p->phase_groups;
+    if (reset) {
+        memset(p->phase_ms, 0, sizeof p->phase_ms);
+        p->phase_groups = 0;
+    }
     return RCT_OK;
 }
 

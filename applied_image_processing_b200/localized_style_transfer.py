@@ -90,6 +90,14 @@ class Plan:
     def set_option(self, option: int, value: int):
         check(_cabi.lib().rct_plan_set_option(self.handle, option, value))
 
+    def timing(self, reset=True):
+        """Per-phase device time (ms) accumulated since the last reset, measured with CUDA events
+        on the launching stream (needs ``set_option(OPT_TIMING, 1)``)."""
+        ms = (C.c_double * 4)()
+        groups = C.c_longlong(0)
+        check(_cabi.lib().rct_plan_timing(self.handle, ms, C.byref(groups), int(reset)))
+        return dict(memset_ms=ms[0], hist_ms=ms[1], solve_ms=ms[2], apply_ms=ms[3], groups=groups.value)
+
     # -- introspection (parity tests) -------------------------------------------------------
     def info(self, slot=0) -> dict:
         fi = _cabi.FrameInfo()
@@ -330,11 +338,11 @@ def color_transfer_foreground(foreground_img, background_img):
     return _transfer(foreground_img, background_img, None, MODE_ALL)
 
 
-def regional_color_transfer(content, stylized, background_mask, slots=None):
+def regional_color_transfer(content, stylized, background_mask, slots=None, out=None):
     """The tail of ``run_localized_style_transfer`` (LST:222-238) in one fused call:
     NEAREST-resize ``stylized`` to the mask size if needed, mask algebra, colour transfer of
     the foreground, final combination.  Accepts one image or a batch (leading dim)."""
-    return _transfer(content, stylized, background_mask, MODE_MASK, slots=slots)
+    return _transfer(content, stylized, background_mask, MODE_MASK, slots=slots, out=out)
 
 
 def regional_color_transfer_labels(content, stylized, labels, n_labels, slots=None):

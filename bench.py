@@ -1,0 +1,336 @@
+#!/usr/bin/env python3
+"""bench.py -- megapixels/s of the regional colour transfer (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one pass of the hot path (LST:222-238 + color_transfer_foreground, LST:128-168)
+over a batch of `--frames` distinct synthetic 3840x2160 content/stylised pairs with binary
+fg/bg masks (BASELINE.json configs[1]); the batch is larger than L2, so no flush is needed
+between steps.  N>1: every rank processes its own batch (frames are independent units, no
+data-path collective) -> weak scaling; `value` = all ranks' pixels / max-over-ranks time.
+
+Printed keys (one JSON line, rank 0): see the task contract; `roofline` describes the
+dominant per-pixel kernel, `cpu_baseline` the C port of the reference (oracle/) timed on this
+box's host cores on a bounded sample, `e2e` the same metric through the public numpy API
+(pinned host buffers in, host buffer out, copies inside the timed region).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "megapixels/sec region colour transfer"
+UNIT = "MP/s"
+H4K, W4K = 2160, 3840
+ALG_BYTES_PER_PIXEL = {"hist": 7.0, "apply": 10.0, "pipeline": 10.0}  # SURVEY.md 8(d), DESIGN.md
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--frames", type=int, default=8, help="4K pairs per step and per rank")
+    ap.add_argument("--kind", default="U", choices=["U", "N"], help="synthetic image family (SURVEY 8d)")
+    ap.add_argument("--height", type=int, default=H4K)
+    ap.add_argument("--width", type=int, default=W4K)
+    ap.add_argument("--cpu-frames", type=int, default=0, help="frames in the CPU sample (0 = auto)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"{a.width}x{a.height} synthetic content/stylised pair, binary fg/bg ellipse mask (40% fg), "
+            f"image family {a.kind} (BASELINE.json configs[1]); {a.frames} distinct pairs per step per GPU")
+
+
+def make_frames(a, n, seed0):
+    from tests.synth import ellipse_mask, synth_image
+
+    cs = np.empty((n, a.height, a.width, 3), np.uint8)
+    ss = np.empty((n, a.height, a.width, 3), np.uint8)
+    ms = np.empty((n, a.height, a.width), np.uint8)
+    for i in range(n):
+        cs[i] = synth_image(a.height, a.width, seed0 + 2 * i, a.kind)
+        ss[i] = synth_image(a.height, a.width, seed0 + 2 * i + 1, a.kind)
+        ms[i] = ellipse_mask(a.height, a.width, 0.4, seed0 + i)
+    return cs, ss, ms
+
+
+# ---- CPU leg: the C port of the reference (oracle/), all host threads ------------------------------
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_pass(frames, threads):
+    """Run every frame through the oracle, `threads` at a time (ctypes releases the GIL)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from oracle import oracle as orc
+
+    orc.lib()
+    cs, ss, ms = frames
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        list(ex.map(lambda i: orc.transfer(cs[i], ss[i], ms[i])[1], range(cs.shape[0])))
+    return time.perf_counter() - t0
+
+
+def cpu_sample_size(a):
+    # ~6.7 s per 4K frame per core: one frame per thread, at most 8 threads' worth of memory
+    threads = max(1, min(host_threads(), 8))
+    n = a.cpu_frames or threads
+    return n, min(threads, n)
+
+
+def run_reference_arm(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # rank 0 alone runs the CPU arm
+    n, threads = cpu_sample_size(a)
+    frames = make_frames(a, n, 1000)
+    for _ in range(a.warmup):
+        cpu_pass(frames, threads)
+    times = [cpu_pass(frames, threads) for _ in range(a.steps)]
+    mp = n * a.height * a.width / 1e6
+    t = sum(times) / len(times)
+    val = mp / t
+    sample = f"{n} frame(s) of the workload per step, {threads} thread(s), one frame per thread"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(a), "cpu_sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---- clocks during the timed region -----------------------------------------------------------------
+class ClockSampler:
+    REASONS = {
+        0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+        0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+        0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting",
+    }
+
+    def __init__(self, device_index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            import torch
+
+            pynvml.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.nv = pynvml
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if r & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def start(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._loop, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join()
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ---- GPU arm ------------------------------------------------------------------------------------------
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def run_gpu_arm(a):
+    import torch
+    import torch.distributed as dist
+
+    import applied_image_processing_b200 as aip
+    from applied_image_processing_b200 import _cabi
+    from applied_image_processing_b200 import localized_style_transfer as lst
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the colour-transfer path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = _cabi.lib()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    n, H, W = a.frames, a.height, a.width
+    cs, ss, ms = make_frames(a, n, 1000 + 100 * rank)
+    # pinned host copies (e2e leg) and device-resident copies (value leg)
+    hc, hs, hm = (torch.from_numpy(x).pin_memory() for x in (cs, ss, ms))
+    ho = torch.empty_like(hc).pin_memory()
+    dc, ds, dm = hc.to(dev), hs.to(dev), hm.to(dev)
+    do = torch.empty_like(dc)
+    plan = lst.get_plan(dev, H, W, H, W, slots=n)
+    st = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        _cabi.check(L.rct_transfer_async(plan.handle, dc.data_ptr(), H * W * 3, ds.data_ptr(), H * W * 3,
+                                         dm.data_ptr(), H * W, do.data_ptr(), H * W * 3, n, _cabi.MODE_MASK, 0, st))
+
+    for _ in range(max(a.warmup, 3)):
+        step()
+    barrier()
+    plan.set_option(_cabi.OPT_TIMING, 1)
+    plan.timing(reset=True)
+    sampler = ClockSampler(local)
+    L.rct_launch_count(1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.start()
+    e0.record()
+    for _ in range(a.steps):
+        step()
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    launches = int(L.rct_launch_count(0))
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    phases = plan.timing(reset=True)
+    plan.set_option(_cabi.OPT_TIMING, 0)
+    status = np.zeros(n, np.int32)
+    _cabi.check(L.rct_plan_status(plan.handle, status.ctypes.data, n, st))
+    assert not status.any(), f"unexpected empty-region status {status}"
+    mp_step = world * n * H * W / 1e6
+    ms_step = ms_total / a.steps
+    value = mp_step / (ms_step * 1e-3)
+
+    # ---- roofline of the dominant per-pixel kernel (events on the launching stream) -------------------
+    peak, peak_src = peaks()
+    groups = max(1, phases["groups"])
+    kern = {}
+    for name, key in (("k_hist", "hist"), ("k_apply", "apply")):
+        ms_launch = phases[key + "_ms"] / groups
+        gb = ALG_BYTES_PER_PIXEL[key] * n * H * W / 1e9
+        kern[name] = {"ms_per_launch": ms_launch, "alg_bytes_per_pixel": ALG_BYTES_PER_PIXEL[key],
+                      "achieved_GBps": gb / (ms_launch * 1e-3) if ms_launch > 0 else None}
+    dom = max(kern, key=lambda k: kern[k]["ms_per_launch"])
+    phase_share = {k: phases[k + "_ms"] / groups / ms_step for k in ("memset", "hist", "solve", "apply")}
+    roofline = {
+        "bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_GBps"], "peak": peak, "unit": "GB/s",
+        "frac": kern[dom]["achieved_GBps"] / peak, "traffic": None, "peak_source": peak_src,
+        "kernels": kern, "phase_share_of_step": phase_share,
+        "pipeline_achieved_GBps_per_gpu": ALG_BYTES_PER_PIXEL["pipeline"] * n * H * W / 1e9 / (ms_step * 1e-3),
+    }
+    roofline["pipeline_frac"] = roofline["pipeline_achieved_GBps_per_gpu"] / peak
+
+    # ---- e2e: the public numpy API, pinned host buffers, copies inside the timed region ----------------
+    e2e = None
+    if not a.no_e2e:
+        hcn, hsn, hmn, hon = hc.numpy(), hs.numpy(), hm.numpy(), ho.numpy()
+        for _ in range(2):
+            aip.regional_color_transfer(hcn, hsn, hmn, out=hon)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(a.steps):
+            aip.regional_color_transfer(hcn, hsn, hmn, out=hon)
+        torch.cuda.synchronize()
+        t_e2e = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        e2e = {"value": mp_step * a.steps / t_e2e, "unit": UNIT,
+               "h2d_bytes_per_step": int(hc.numel() + hs.numel() + hm.numel()),
+               "d2h_bytes_per_step": int(ho.numel()), "ms_per_step": 1e3 * t_e2e / a.steps}
+        assert np.array_equal(hon, do.cpu().numpy()), "host path and device path disagree"
+
+    # ---- CPU baseline: C port of the reference on this box's host cores (rank 0, N=1 only) ------------
+    cpu = None
+    if world == 1 and not a.no_cpu:
+        nc, threads = cpu_sample_size(a)
+        t = cpu_pass((cs[:nc], ss[:nc], ms[:nc]), threads)
+        cpu = {"value": nc * H * W / 1e6 / t, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": f"{nc} frame(s) of the step's batch, {threads} thread(s), one pass ({t:.1f} s)"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a), "frames_per_step_per_gpu": n,
+                       "l2": f"inputs larger than L2: {(dc.numel() + ds.numel() + dm.numel()) / 1e6:.0f} MB read per step",
+                       "parallelism": f"frames sharded over {world} GPU(s), no collective"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference_arm(a)
+    else:
+        run_gpu_arm(a)
+
+
+if __name__ == "__main__":
+    main()

@@ -78,7 +78,14 @@ int rct_plan_destroy(rct_plan *plan);
 /* tuning knobs; RCT_OPT_AGGREGATE (0/1): warp-aggregate equal colours before the histogram
  * atomic (pays off on flat / low-colour images, costs a MATCH per pixel otherwise) */
 #define RCT_OPT_AGGREGATE 0
+/* RCT_OPT_TIMING (0/1): bracket the phases of every launch group of rct_transfer_async /
+ * rct_transfer_host with CUDA events on the launching stream; read with rct_plan_timing() */
+#define RCT_OPT_TIMING 1
 int rct_plan_set_option(rct_plan *plan, int option, int value);
+/* accumulated device time per phase since the last reset, in ms: [0] workspace memsets,
+ * [1] k_hist (pixels -> colour histograms), [2] solve (compact .. match -> LUT), [3] k_apply
+ * (pixels -> output); *groups = launch groups accumulated.  Synchronises the recorded events. */
+int rct_plan_timing(rct_plan *plan, double *ms4, long long *groups, int reset);
 
 /* ---- the fused pipeline: LST:222-238 + color_transfer_foreground (LST:128-168) ----------
  * n_frames frames (any number; processed `slots` at a time), frame f at base + f*stride.

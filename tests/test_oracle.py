@@ -1,0 +1,133 @@
+"""Pin the C oracle (oracle/rct_oracle.c) against the reference: the committed golden outputs
+of the reference's own functions (always) and the live, unmodified reference module (in the
+build container, where /root/reference exists).  CPU only."""
+import numpy as np
+import pytest
+
+from oracle import oracle as orc
+from oracle import ref_shim
+from tests import golden_io, synth
+
+# tolerances of BASELINE.json's north_star: integers bit-exact, float RGB <= 1e-4, <= 1 LSB
+TOL_RGBF = 1e-4
+TOL_PCA = 1e-9
+TOL_LAB = 1e-9
+
+
+@pytest.mark.parametrize("name", golden_io.PIPELINE_NAMES)
+def test_pipeline_vs_golden(name):
+    c, s, mask, g = golden_io.load_pipeline(name)
+    out, st, d = orc.transfer(c, s, mask, debug=True)
+    assert st == 0
+    assert d["n_t"] == int(g["n_fg"]) and d["n_s"] == int(g["n_bg"])
+    diff = np.abs(out.astype(np.int16) - g["combined"].astype(np.int16))
+    assert diff.max() <= 1, f"{name}: max uint8 diff {diff.max()}"
+    assert int((diff > 0).sum()) == 0, f"{name}: {(diff > 0).sum()} bytes differ from the reference"
+    np.testing.assert_allclose(d["t_mean"], g["fg_mean"], atol=TOL_PCA, rtol=0)
+    np.testing.assert_allclose(d["s_mean"], g["bg_mean"], atol=TOL_PCA, rtol=0)
+    np.testing.assert_allclose(d["t_comp"], g["fg_comp"], atol=TOL_PCA, rtol=0)
+    np.testing.assert_allclose(d["s_comp"], g["bg_comp"], atol=TOL_PCA, rtol=0)
+    px = g["sample_pixel"]
+    np.testing.assert_allclose(d["key"].ravel()[px], g["sample_proj"], atol=TOL_LAB, rtol=0)
+    np.testing.assert_allclose(d["matched"].ravel()[px], g["sample_matched"], atol=1e-9, rtol=0)
+    np.testing.assert_allclose(d["rgbf"].reshape(-1, 3)[px], g["sample_rgbf"], atol=TOL_RGBF, rtol=0)
+
+
+def test_resample_tables_vs_pillow_golden():
+    tabs = golden_io.load("resample")
+    for key, want in tabs.items():
+        i, o = (int(v) for v in key.split("_"))
+        got = orc.resample_table(i, o)
+        assert np.array_equal(got, want), f"NEAREST table {i}->{o} differs from Pillow"
+
+
+def test_functions_vs_golden():
+    g = golden_io.load("functions")
+    lab = orc.rgb_to_lab_pixels(g["px"])
+    np.testing.assert_allclose(lab, g["lab"], atol=TOL_LAB, rtol=0)
+    # exact black hits the 1e-6 clamp: l = -18/sqrt(3), alpha = beta = 0
+    np.testing.assert_allclose(lab[0], [-18 / np.sqrt(3), 0, 0], atol=1e-12)
+    back, rgbf = orc.lab_to_rgb_pixels(g["lab"], want_float=True)
+    assert np.abs(back.astype(int) - g["back"].astype(int)).max() <= 1
+    back2 = orc.lab_to_rgb_pixels(g["lab2"])
+    d2 = np.abs(back2.astype(int) - g["back2"].astype(int))
+    assert d2.max() <= 1 and (d2 > 0).mean() < 1e-3
+    proj, mean, comp = orc.apply_pca(g["lab"])
+    np.testing.assert_allclose(mean, g["pca_mean"], atol=TOL_PCA, rtol=0)
+    np.testing.assert_allclose(comp, g["pca_comp"], atol=TOL_PCA, rtol=0)
+    np.testing.assert_allclose(proj, g["proj"], atol=TOL_LAB, rtol=0)
+
+
+@pytest.mark.parametrize("tag", ["eq", "tgt_longer", "src_longer", "one_src", "one_tgt"])
+def test_match_cdf_vs_golden_bit_exact(tag):
+    """match_cdf is compare/sort/lerp only: np.sort, np.linspace and np.interp are restated
+    operation for operation, so the oracle must equal numpy BIT FOR BIT."""
+    g = golden_io.load("functions")
+    m = orc.match_cdf(g[f"cdf_{tag}_t"], g[f"cdf_{tag}_s"])
+    assert np.array_equal(m, g[f"cdf_{tag}_m"]), np.abs(m - g[f"cdf_{tag}_m"]).max()
+
+
+def test_empty_regions_follow_reference_convention():
+    c = synth.synth_image(32, 48, 0, "U")
+    s = synth.synth_image(32, 48, 1, "U")
+    all_bg = np.ones((32, 48), np.uint8)
+    out, st, _ = orc.transfer(c, s, all_bg)
+    assert st == 1 and np.array_equal(out, s)  # no foreground: combined == stylised
+    all_fg = np.zeros((32, 48), np.uint8)
+    out, st, _ = orc.transfer(c, s, all_fg)
+    assert st == 2 and np.array_equal(out, c)  # no background: foreground returned unmodified
+
+
+needs_ref = pytest.mark.skipif(not ref_shim.available(), reason="reference tree not present on this machine")
+
+
+@needs_ref
+@pytest.mark.parametrize("H,W,sh,sw,ck,sk,mk", [
+    (120, 200, 120, 200, "U", "U", "ellipse"),
+    (243, 364, 256, 384, "N", "N", "bernoulli"),
+    (200, 120, 77, 50, "N", "U", "ellipse"),
+])
+def test_pipeline_vs_live_reference(H, W, sh, sw, ck, sk, mk):
+    c = synth.synth_image(H, W, 40, ck)
+    s = synth.synth_image(sh, sw, 41, sk)
+    mask = synth.ellipse_mask(H, W, 0.35, 9) if mk == "ellipse" else synth.bernoulli_mask(H, W, 0.5, 9)
+    ref = ref_shim.ref_pipeline(c, s, mask)
+    out, st, _ = orc.transfer(c, s, mask)
+    assert st == 0
+    diff = np.abs(out.astype(np.int16) - ref.astype(np.int16))
+    assert diff.max() <= 1 and int((diff > 0).sum()) == 0
+
+
+@needs_ref
+def test_rank_indices_vs_live_reference():
+    """Level-2 vs level-1 rank mismatch count: the index np.interp resolves every
+    foreground pixel to, recomputed with numpy on the REFERENCE's own projections."""
+    lst = ref_shim.load_reference()
+    c = synth.synth_image(150, 220, 50, "U")
+    s = synth.synth_image(150, 220, 51, "N")
+    mask = synth.ellipse_mask(150, 220, 0.5, 3)
+    _, st, d = orc.transfer(c, s, mask, debug=True)
+    assert st == 0
+    fg = c * (1 - mask)[..., None]
+    bg = s * mask[..., None]
+    fsel, bsel = fg.sum(-1) > 0, bg.sum(-1) > 0
+    fp, _ = lst.apply_pca(lst.rgb_to_lab_pixels(fg[fsel]))
+    t_sorted = np.sort(fp, axis=0).ravel()
+    assert fsel.sum() > bsel.sum() or True
+    if fsel.sum() >= bsel.sum():  # queries are knots: j = upper rank - 1
+        j_ref = np.searchsorted(t_sorted, fp.ravel(), side="right") - 1
+        mism = int((d["j"][fsel] != j_ref).sum())
+        assert mism == 0, f"{mism} rank mismatches between oracle and reference"
+
+
+@needs_ref
+def test_reference_edge_cases():
+    lst = ref_shim.load_reference()
+    c = synth.synth_image(24, 24, 1, "U")
+    blk = np.zeros_like(c)
+    assert np.array_equal(lst.color_transfer_foreground(blk, c), blk)
+    out, st, _ = orc.transfer(blk, c, None, mode=orc.MODE_ALL)
+    assert st == 1 and np.array_equal(out, blk)
+    assert np.array_equal(lst.color_transfer_foreground(c, blk), c)
+    out, st, _ = orc.transfer(c, blk, None, mode=orc.MODE_ALL)
+    assert st == 2 and np.array_equal(out, c)
