@@ -266,3 +266,50 @@ def test_4k_properties():
     _, _, d = orc.transfer(c[::8, ::8].copy(), s[::8, ::8].copy(), mask[::8, ::8].copy())
     assert np.abs(info["t_mean"] - d["t_mean"]).max() < 0.02
     assert abs(abs(np.dot(info["t_comp"], d["t_comp"])) - 1) < 1e-3
+
+
+# ---- the row-sharded driver (sharded.py) with two ranks on one GPU ---------------------------------
+def _shard_worker(rank, world, port, H, W, sh, sw, q):
+    import os
+
+    import torch.distributed as dist
+
+    from applied_image_processing_b200 import sharded
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(0)
+    dist.init_process_group("gloo", rank=rank, world_size=world)  # NCCL refuses two ranks on one GPU
+    try:
+        c, s = synth.synth_image(H, W, 90, "U"), synth.synth_image(sh, sw, 91, "N")
+        mask = synth.ellipse_mask(H, W, 0.45, 2)
+        out, (r0, n) = sharded.regional_color_transfer_sharded(c, s, mask)
+        q.put((rank, r0, n, out))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_driver_two_ranks_one_gpu():
+    import socket
+
+    import torch.multiprocessing as mp
+
+    H, W, sh, sw, world = 151, 203, 120, 170, 2
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_shard_worker, args=(r, world, port, H, W, sh, sw, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=240) for _ in range(world)]
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    c, s = synth.synth_image(H, W, 90, "U"), synth.synth_image(sh, sw, 91, "N")
+    ref, st, _ = orc.transfer(c, s, synth.ellipse_mask(H, W, 0.45, 2))
+    assert st == 0
+    full = np.zeros_like(ref)
+    for rank, r0, n, out in got:
+        full[r0:r0 + n] = out
+    assert np.array_equal(full, ref)
