@@ -14,6 +14,7 @@ MODE_MASK, MODE_LABEL, MODE_ALL = 0, 1, 2
 FLAG_DEBUG = 1
 OPT_AGGREGATE = 0
 OPT_TIMING = 1
+OPT_PART_CAP = 2
 
 _lib = None
 _lock = threading.Lock()

@@ -94,22 +94,31 @@ int ensure_device(int *dev_out)
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
 struct Layout {
-    size_t cap, fine_cap, n_partials;
+    size_t cap, maxparts;
     size_t off_ctrl, off_jobs, off_status, off_xtab, off_ytab;
     size_t off_hist, hist_stride_u32, off_lut, lut_stride_u32;
     size_t off_region, region_bytes;  // [slots][2] blocks of per-region arrays
-    size_t r_col, r_cnt, r_keyA, r_fb, r_slot, r_keyB, r_payB, r_cumB, r_fine, r_part;
+    size_t r_col, r_cnt, r_keyA, r_keyP, r_auxP, r_pof, r_pstart, r_ppix;
+    size_t off_zero, zero_bytes, z_fcnt, z_pfill;  // [slots][2] blocks zeroed before every sort
     size_t off_dbg_m, off_dbg_j, dbg_stride;
     size_t total;
 };
+
+// per-job sort arrays that must start at zero (fine counts, part fill counters)
+void zero_zone(size_t maxparts, size_t &z_fcnt, size_t &z_pfill, size_t &bytes)
+{
+    size_t z = 0;
+    z_fcnt = z; z = align_up(z + 4 * (size_t)(kFineMax + 1));
+    z_pfill = z; z = align_up(z + 4 * maxparts * (size_t)kFillStride);
+    bytes = z;
+}
 
 Layout make_layout(int H, int W, int slots, unsigned flags)
 {
     Layout L{};
     size_t npix = (size_t)H * (size_t)W;
     L.cap = npix < (size_t)kCube ? npix : (size_t)kCube;
-    L.fine_cap = 2 * L.cap + kCoarse;
-    L.n_partials = (L.fine_cap + 1 + kScanChunk - 1) / kScanChunk + 1;
+    L.maxparts = L.cap / kPartT + 2;
     size_t o = 0;
     L.off_ctrl = o; o = align_up(o + sizeof(FrameCtrl) * slots);
     L.off_jobs = o; o = align_up(o + sizeof(Job) * 2 * slots);
@@ -124,15 +133,15 @@ Layout make_layout(int H, int W, int slots, unsigned flags)
     L.r_col = r; r = align_up(r + 4 * L.cap);
     L.r_cnt = r; r = align_up(r + 4 * L.cap);
     L.r_keyA = r; r = align_up(r + 8 * L.cap);
-    L.r_fb = r; r = align_up(r + 4 * L.cap);
-    L.r_slot = r; r = align_up(r + 4 * L.cap);
-    L.r_keyB = r; r = align_up(r + 8 * L.cap);
-    L.r_payB = r; r = align_up(r + 4 * L.cap);
-    L.r_cumB = r; r = align_up(r + 4 * L.cap);
-    L.r_fine = r; r = align_up(r + 4 * (L.fine_cap + 1));
-    L.r_part = r; r = align_up(r + 4 * L.n_partials);
+    L.r_keyP = r; r = align_up(r + 8 * L.cap);
+    L.r_auxP = r; r = align_up(r + 8 * L.cap);
+    L.r_pof = r; r = align_up(r + 2 * (size_t)kFineMax);
+    L.r_pstart = r; r = align_up(r + 4 * (L.maxparts + 1));
+    L.r_ppix = r; r = align_up(r + 4 * (L.maxparts + 1));
     L.region_bytes = r;
     L.off_region = o; o += L.region_bytes * 2 * slots;
+    zero_zone(L.maxparts, L.z_fcnt, L.z_pfill, L.zero_bytes);
+    L.off_zero = o; o += L.zero_bytes * 2 * slots;
     L.dbg_stride = L.cap;
     if (flags & RCT_FLAG_DEBUG) {
         L.off_dbg_m = o; o = align_up(o + 8 * L.cap * slots);
@@ -159,6 +168,7 @@ struct rct_plan {
     long long *dbg_j;
     int sm;
     int aggregate;
+    unsigned part_cap;  // entries a part may have for the shared-memory sort (RCT_OPT_PART_CAP)
     // lazily allocated helpers
     int *status_frames;
     int status_frames_cap;
@@ -236,6 +246,7 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     p->L = make_layout(H, W, slots, flags);
     p->sm = g_sm_count[device] > 0 ? g_sm_count[device] : 148;
     p->aggregate = 0;
+    p->part_cap = kPartCap;
     if (workspace) {
         if (workspace_bytes < p->L.total) {
             delete p;
@@ -277,20 +288,21 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     for (int s = 0; s < slots; ++s)
         for (int r = 0; r < 2; ++r) {
             uint8_t *b = p->ws + L.off_region + L.region_bytes * (size_t)(2 * s + r);
+            uint8_t *z = p->ws + L.off_zero + L.zero_bytes * (size_t)(2 * s + r);
             Job &j = hj[2 * s + r];
             j.rc = &p->ctrl[s].r[r];
             j.payA = (unsigned *)(b + L.r_col);
             j.cntA = (unsigned *)(b + L.r_cnt);
             j.keyA = (double *)(b + L.r_keyA);
-            j.fbA = (unsigned *)(b + L.r_fb);
-            j.slotA = (unsigned *)(b + L.r_slot);
-            j.keyB = (double *)(b + L.r_keyB);
-            j.payB = (unsigned *)(b + L.r_payB);
-            j.cumB = (unsigned *)(b + L.r_cumB);
-            j.fine = (unsigned *)(b + L.r_fine);
-            j.partials = (unsigned *)(b + L.r_part);
+            j.keyP = (double *)(b + L.r_keyP);
+            j.auxP = (unsigned long long *)(b + L.r_auxP);
+            j.pof = (unsigned short *)(b + L.r_pof);
+            j.pstart = (unsigned *)(b + L.r_pstart);
+            j.ppix = (unsigned *)(b + L.r_ppix);
+            j.fcnt = (unsigned *)(z + L.z_fcnt);
+            j.pfill = (unsigned *)(z + L.z_pfill);
             j.cap = (unsigned)L.cap;
-            j.pad_ = 0;
+            j.maxparts = (unsigned)L.maxparts;
         }
     cudaError_t e = cudaMemcpy(p->jobs, hj, sizeof(Job) * 2 * slots, cudaMemcpyHostToDevice);
     delete[] hj;
@@ -332,6 +344,7 @@ int rct_plan_set_option(rct_plan *p, int option, int value)
     if (!p) return fail(RCT_ERR_ARG, "null plan");
     if (option == RCT_OPT_AGGREGATE) p->aggregate = value;
     else if (option == RCT_OPT_TIMING) p->timing = value;
+    else if (option == RCT_OPT_PART_CAP) p->part_cap = (value > 0 && value <= kPartCap) ? (unsigned)value : (unsigned)kPartCap;
     else return fail(RCT_ERR_ARG, "unknown option %d", option);
     return RCT_OK;
 }
@@ -412,34 +425,53 @@ int phase_hist(rct_plan *p, const FrameSet &f, int nslots, int mode, int label, 
     return mark(p, st);
 }
 
-int sort_jobs(const Job *jobs, int njobs, unsigned eblocks, size_t fine_cap, cudaStream_t st)
+constexpr size_t kSmemFineHist = (size_t)(kFineMax + kCoarse + 1) * 4;
+constexpr size_t kSmemScatter = (size_t)(kCoarse + 1) * 4 + (size_t)kFineMax * 2;
+constexpr size_t kSmemPartSort = (size_t)kPartCap * 16 + (size_t)kPartCap * 8;
+
+int ensure_kernel_attrs()
 {
-    unsigned sblocks_fine = (unsigned)((fine_cap + 1 + kScanChunk - 1) / kScanChunk);
-    LAUNCH(k_bucket_plan, dim3(1, njobs), 1024, st, jobs);
-    LAUNCH(k_zero_fine, dim3(eblocks, njobs), 256, st, jobs);
-    LAUNCH(k_bucket_count, dim3(eblocks, njobs), 256, st, jobs);
-    LAUNCH(k_scan_reduce<0>, dim3(sblocks_fine, njobs), 256, st, jobs);
-    LAUNCH(k_scan_partials<0>, dim3(1, njobs), 1024, st, jobs);
-    LAUNCH(k_scan_apply<0>, dim3(sblocks_fine, njobs), 256, st, jobs);
-    LAUNCH(k_scatter, dim3(eblocks, njobs), 256, st, jobs);
-    LAUNCH(k_bucket_sort, dim3(eblocks, njobs), 256, st, jobs);
-    LAUNCH(k_scan_reduce<1>, dim3(sblocks_fine, njobs), 256, st, jobs);
-    LAUNCH(k_scan_partials<1>, dim3(1, njobs), 1024, st, jobs);
-    LAUNCH(k_scan_apply<1>, dim3(sblocks_fine, njobs), 256, st, jobs);
+    static thread_local int done_dev = -1;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (done_dev == dev) return RCT_OK;
+    CK(cudaFuncSetAttribute(k_fine_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemFineHist));
+    CK(cudaFuncSetAttribute(k_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemScatter));
+    CK(cudaFuncSetAttribute(k_part_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemPartSort));
+    done_dev = dev;
+    return RCT_OK;
+}
+
+// exact sort of njobs key lists (keys + coarse histograms ready; zero zones cleared)
+int sort_jobs(const Job *jobs, int njobs, unsigned eblocks, size_t cap, size_t maxparts, unsigned part_cap,
+              cudaStream_t st)
+{
+    int rc = ensure_kernel_attrs();
+    if (rc) return rc;
+    unsigned hblocks = (unsigned)((cap + kFineHistChunk - 1) / kFineHistChunk);
+    LAUNCH(k_plan_fine, dim3(1, njobs), 1024, st, jobs);
+    k_fine_hist<<<dim3(hblocks, njobs), 512, kSmemFineHist, st>>>(jobs);
+    k_plan_parts<<<dim3(1, njobs), 1024, 0, st>>>(jobs);
+    k_scatter<<<dim3(eblocks, njobs), 256, kSmemScatter, st>>>(jobs);
+    k_part_sort<<<dim3((unsigned)maxparts, njobs), kSortThreads, kSmemPartSort, st>>>(jobs, part_cap);
+    t_launches += 4;
+    CK(cudaGetLastError());
+    LAUNCH(k_part_scan, dim3(1, njobs), 1024, st, jobs);
     return RCT_OK;
 }
 
 int phase_solve(rct_plan *p, int nslots, cudaStream_t st)
 {
     unsigned eb = entry_blocks(p, nslots);
+    CK(cudaMemsetAsync(p->ws + p->L.off_zero, 0, p->L.zero_bytes * 2 * (size_t)nslots, st));
     LAUNCH(k_compact, dim3(kCube / 1024, 2, nslots), 256, st, p->hist, p->L.hist_stride_u32, p->ctrl, p->jobs);
     LAUNCH(k_lab_moments, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs);
     LAUNCH(k_pca, dim3((nslots + 31) / 32), 32, st, p->ctrl, nslots);
     LAUNCH(k_keys, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs);
-    int rc = sort_jobs(p->jobs, 2 * nslots, eb, p->L.fine_cap, st);
+    int rc = sort_jobs(p->jobs, 2 * nslots, eb, p->L.cap, p->L.maxparts, p->part_cap, st);
     if (rc) return rc;
-    LAUNCH(k_match, dim3(eb * 2, nslots), 128, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32, p->dbg_m, p->dbg_j,
-           p->L.dbg_stride);
+    LAUNCH(k_match, dim3((unsigned)p->L.maxparts, nslots), 256, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32,
+           p->dbg_m, p->dbg_j, p->L.dbg_stride);
     return mark(p, st);
 }
 
@@ -650,28 +682,28 @@ int rct_pca_inverse(const double *matched, size_t n, const double *mean3, const 
 
 namespace {
 struct MatchLayout {
-    size_t off_rc[2], off_jobs, off_arr[2], a_fb, a_slot, a_keyB, a_payB, a_cumB, a_fine, a_part, arr_bytes[2], total;
-    size_t fine_cap[2];
+    size_t off_rc[2], off_zero[2], zero_bytes[2], z_fcnt[2], z_pfill[2], off_jobs, off_arr[2], total;
+    size_t maxparts[2];
 };
 MatchLayout match_layout(size_t nt, size_t ns)
 {
     MatchLayout M{};
+    size_t n[2] = {nt ? nt : 1, ns ? ns : 1};
     size_t o = 0;
     for (int r = 0; r < 2; ++r) { M.off_rc[r] = o; o = align_up(o + sizeof(RegionCtrl)); }
+    for (int r = 0; r < 2; ++r) {  // everything up to off_jobs is zeroed per call
+        M.maxparts[r] = n[r] / kPartT + 2;
+        zero_zone(M.maxparts[r], M.z_fcnt[r], M.z_pfill[r], M.zero_bytes[r]);
+        M.off_zero[r] = o; o += M.zero_bytes[r];
+    }
     M.off_jobs = o; o = align_up(o + 2 * sizeof(Job));
-    size_t n[2] = {nt, ns};
     for (int r = 0; r < 2; ++r) {
-        size_t cap = n[r] ? n[r] : 1, fc = 2 * cap + kCoarse, np = (fc + 1 + kScanChunk - 1) / kScanChunk + 1;
-        M.fine_cap[r] = fc;
         size_t a = 0;
-        a = align_up(a + 4 * cap);      // fb
-        a = align_up(a + 4 * cap);      // slot
-        a = align_up(a + 8 * cap);      // keyB
-        a = align_up(a + 4 * cap);      // payB
-        a = align_up(a + 4 * cap);      // cumB
-        a = align_up(a + 4 * (fc + 1)); // fine
-        a = align_up(a + 4 * np);       // partials
-        M.arr_bytes[r] = a;
+        a = align_up(a + 8 * n[r]);                    // keyP
+        a = align_up(a + 8 * n[r]);                    // auxP
+        a = align_up(a + 2 * (size_t)kFineMax);        // pof
+        a = align_up(a + 4 * (M.maxparts[r] + 1));     // pstart
+        a = align_up(a + 4 * (M.maxparts[r] + 1));     // ppix
         M.off_arr[r] = o;
         o += a;
     }
@@ -686,7 +718,8 @@ int rct_match_cdf(const double *target_proj, size_t nt, const double *source_pro
                   int64_t *j_index, void *scratch, void *stream)
 {
     if (nt == 0 || ns == 0) return fail(RCT_ERR_ARG, "empty input");
-    if (nt >= ((size_t)1 << 32) || ns >= ((size_t)1 << 32)) return fail(RCT_ERR_ARG, "input too long");
+    // part ids are 16-bit: at most 65535 parts of >= kPartT entries
+    if (nt >= ((size_t)1 << 26) || ns >= ((size_t)1 << 26)) return fail(RCT_ERR_ARG, "input too long (>= 2^26)");
     if (!target_proj || !source_proj || !matched || !scratch) return fail(RCT_ERR_ARG, "null pointer");
     int dev, rc = ensure_device(&dev);
     if (rc) return rc;
@@ -697,20 +730,19 @@ int rct_match_cdf(const double *target_proj, size_t nt, const double *source_pro
     const double *keys[2] = {target_proj, source_proj};
     size_t n[2] = {nt, ns};
     for (int r = 0; r < 2; ++r) {
-        size_t cap = n[r];
         uint8_t *b = ws + M.off_arr[r];
         size_t a = 0;
         Job &j = hj[r];
         j.rc = (RegionCtrl *)(ws + M.off_rc[r]);
         j.keyA = keys[r]; j.payA = nullptr; j.cntA = nullptr;
-        j.fbA = (unsigned *)(b + a); a = align_up(a + 4 * cap);
-        j.slotA = (unsigned *)(b + a); a = align_up(a + 4 * cap);
-        j.keyB = (double *)(b + a); a = align_up(a + 8 * cap);
-        j.payB = (unsigned *)(b + a); a = align_up(a + 4 * cap);
-        j.cumB = (unsigned *)(b + a); a = align_up(a + 4 * cap);
-        j.fine = (unsigned *)(b + a); a = align_up(a + 4 * (M.fine_cap[r] + 1));
-        j.partials = (unsigned *)(b + a);
-        j.cap = (unsigned)cap; j.pad_ = 0;
+        j.keyP = (double *)(b + a); a = align_up(a + 8 * n[r]);
+        j.auxP = (unsigned long long *)(b + a); a = align_up(a + 8 * n[r]);
+        j.pof = (unsigned short *)(b + a); a = align_up(a + 2 * (size_t)kFineMax);
+        j.pstart = (unsigned *)(b + a); a = align_up(a + 4 * (M.maxparts[r] + 1));
+        j.ppix = (unsigned *)(b + a);
+        j.fcnt = (unsigned *)(ws + M.off_zero[r] + M.z_fcnt[r]);
+        j.pfill = (unsigned *)(ws + M.off_zero[r] + M.z_pfill[r]);
+        j.cap = (unsigned)n[r]; j.maxparts = (unsigned)M.maxparts[r];
     }
     CK(cudaMemsetAsync(ws, 0, M.off_jobs, st));
     CK(cudaMemcpyAsync(ws + M.off_jobs, hj, sizeof hj, cudaMemcpyHostToDevice, st));
@@ -721,10 +753,10 @@ int rct_match_cdf(const double *target_proj, size_t nt, const double *source_pro
     LAUNCH(k_key_range, flat_blocks(ns, dev), 256, st, source_proj, ns, hj[1].rc);
     LAUNCH(k_key_range_finish, 1, 32, st, hj[0].rc, hj[1].rc, (unsigned long long)nt, (unsigned long long)ns);
     LAUNCH(k_coarse_hist, dim3(eb, 2), 256, st, jobs);
-    size_t fc = M.fine_cap[0] > M.fine_cap[1] ? M.fine_cap[0] : M.fine_cap[1];
-    rc = sort_jobs(jobs, 2, eb, fc, st);
+    size_t mp = M.maxparts[0] > M.maxparts[1] ? M.maxparts[0] : M.maxparts[1];
+    rc = sort_jobs(jobs, 2, eb, nmax, mp, kPartCap, st);
     if (rc) return rc;
-    LAUNCH(k_match_generic, flat_blocks(nt, dev), 128, st, jobs, matched, (long long *)j_index);
+    LAUNCH(k_match_generic, (unsigned)M.maxparts[0], 256, st, jobs, matched, (long long *)j_index);
     return RCT_OK;
 }
 
@@ -795,12 +827,29 @@ int rct_plan_debug_target(rct_plan *p, int slot, uint32_t *colour, double *key, 
     int rc = rct_plan_info(p, slot, &info);
     if (rc) return rc;
     size_t d = (size_t)info.d_target;
-    if (d == 0) return RCT_OK;
+    if (d == 0 || info.status != 0) return RCT_OK;
     const Layout &L = p->L;
     uint8_t *b = p->ws + L.off_region + L.region_bytes * (size_t)(2 * slot);
-    if (colour) CK(cudaMemcpy(colour, b + L.r_payB, 4 * d, cudaMemcpyDeviceToHost));
-    if (key) CK(cudaMemcpy(key, b + L.r_keyB, 8 * d, cudaMemcpyDeviceToHost));
-    if (cum) CK(cudaMemcpy(cum, b + L.r_cumB, 4 * d, cudaMemcpyDeviceToHost));
+    if (key) CK(cudaMemcpy(key, b + L.r_keyP, 8 * d, cudaMemcpyDeviceToHost));
+    if (colour || cum) {
+        // sorted aux = payload | part-local cumulative count << 32; globalise with the part bases
+        std::vector<unsigned long long> aux(d);
+        std::vector<unsigned> pstart(L.maxparts + 1), pbase(L.maxparts + 1);
+        FrameCtrl *h = new (std::nothrow) FrameCtrl;
+        if (!h) return fail(RCT_ERR_NOMEM, "out of host memory");
+        cudaError_t e = cudaMemcpy(h, p->ctrl + slot, sizeof(FrameCtrl), cudaMemcpyDeviceToHost);
+        unsigned np = h->r[0].n_parts;
+        delete h;
+        if (e != cudaSuccess) return fail(RCT_ERR_CUDA, "debug copy failed: %s", cudaGetErrorString(e));
+        CK(cudaMemcpy(aux.data(), b + L.r_auxP, 8 * d, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(pstart.data(), b + L.r_pstart, 4 * (L.maxparts + 1), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(pbase.data(), b + L.r_ppix, 4 * (L.maxparts + 1), cudaMemcpyDeviceToHost));
+        for (unsigned q = 0; q < np; ++q)
+            for (unsigned i = pstart[q]; i < pstart[q + 1]; ++i) {
+                if (colour) colour[i] = (uint32_t)aux[i];
+                if (cum) cum[i] = pbase[q] + (uint32_t)(aux[i] >> 32);
+            }
+    }
     if (j) CK(cudaMemcpy(j, p->dbg_j + (size_t)slot * L.dbg_stride, 8 * d, cudaMemcpyDeviceToHost));
     if (matched) CK(cudaMemcpy(matched, p->dbg_m + (size_t)slot * L.dbg_stride, 8 * d, cudaMemcpyDeviceToHost));
     return RCT_OK;

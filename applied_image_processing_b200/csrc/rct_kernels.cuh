@@ -8,8 +8,9 @@
 //   k_lab_moments   list   -> exact integer moments, lab bounding box    (a-4, a-5)
 //   k_pca           moments-> mean_, components_[0], key range           (a-5)
 //   k_keys          list   -> float64 projection keys + coarse key histogram
-//   k_bucket_plan / k_zero_fine / k_bucket_count / scan / k_scatter / k_bucket_sort / scan
-//                   exact ascending sort of the distinct keys + cumulative pixel counts
+//   k_plan_fine / k_fine_hist / k_plan_parts / k_scatter / k_part_sort / k_part_scan   (rct_sort.cuh)
+//                   exact ascending sort of the distinct keys (two-level equalised partition
+//                   into shared-memory-sized parts) + cumulative pixel counts
 //   k_match         rank -> quantile lookup with np.interp semantics -> colour LUT (a-6, a-7)
 //   k_apply         pixels -> output through the LUT, fused with resample + combine (a-8, a-9)
 //
@@ -22,14 +23,18 @@ namespace rct {
 
 constexpr int kCoarse = 4096;           // coarse key-histogram bins per region
 constexpr unsigned kCube = 1u << 24;    // colour-cube bins
-constexpr int kScanChunk = 4096;        // elements per scan block (256 threads x 16)
+constexpr int kFineTarget = 16384;      // fine bins aimed at per sort job (equalised)
+constexpr int kFineMax = kFineTarget + kCoarse;  // upper bound on fine bins per job
+constexpr int kPartT = 2048;            // entries per part aimed at (part < kPartT + largest fine bin)
+constexpr int kPartCap = 4096;          // entries a part may have to be sorted in shared memory
+constexpr int kFillStride = 32;         // uint32 stride of the per-part fill counters (128 B apart)
 
 struct RegionCtrl {
     unsigned long long n_pix;           // region pixel count N (non-black pixels)
-    unsigned int d;                     // distinct colours
-    unsigned int n_fine;                // fine buckets in use
-    unsigned int n_fine_p1;             // n_fine + 1 (scan length)
-    unsigned int pad_;
+    unsigned int d;                     // distinct colours (sort entries)
+    unsigned int n_fine;                // fine bins in use
+    unsigned int n_parts;               // parts in use
+    unsigned int skip;                  // 1: the frame has an empty region, nothing to sort
     long long limbs[9][3];              // exact moments: s1[0..2], s2[00,01,02,11,12,22]
     unsigned long long lab_max[3];      // ord_enc(max lab_i)
     unsigned long long lab_min[3];      // ~ord_enc(min lab_i)
@@ -48,17 +53,17 @@ struct FrameCtrl {
 // One sort job = one region of one slot (or one array of the generic match_cdf call).
 struct Job {
     RegionCtrl *rc;
-    const double *keyA;     // unsorted keys
-    const unsigned *payA;   // payload (colour index); NULL = identity
-    const unsigned *cntA;   // multiplicity; NULL = 1
-    unsigned *fbA, *slotA;  // per entry: fine bucket, slot within bucket
-    unsigned *fine;         // per fine bucket: count, then exclusive offset (n_fine+1)
-    unsigned *partials;     // scan scratch
-    double *keyB;           // sorted keys
-    unsigned *payB;         // sorted payload
-    unsigned *cumB;         // sorted counts, then inclusive cumulative counts
-    unsigned cap;
-    unsigned pad_;
+    const double *keyA;          // unsorted keys
+    const unsigned *payA;        // payload (colour index); NULL = identity
+    const unsigned *cntA;        // multiplicity; NULL = 1
+    double *keyP;                // partitioned, then sorted keys
+    unsigned long long *auxP;    // lo: payload; hi: multiplicity, then part-local inclusive cumulative count
+    unsigned *fcnt;              // [kFineMax+1] fine-bin counts, then exclusive offsets (fcnt[n_fine] = d)
+    unsigned short *pof;         // [kFineMax] part of each fine bin
+    unsigned *pstart;            // [maxparts+1] first entry of each part
+    unsigned *ppix;              // [maxparts+1] pixels per part, then exclusive bases (ppix[n_parts] = N)
+    unsigned *pfill;             // [maxparts*kFillStride] scatter fill counters
+    unsigned cap, maxparts;
 };
 
 // ------------------------------------------------------------------------------------------
@@ -480,6 +485,7 @@ __global__ void k_pca(FrameCtrl *ctrl, int slots)
         rc->cscale = (span > 0.0 && span < 1e300) ? (double)kCoarse / span : 0.0;
     }
     fc->status = (fc->r[0].n_pix == 0) ? 1 : (fc->r[1].n_pix == 0 ? 2 : 0);
+    fc->r[0].skip = fc->r[1].skip = (fc->status != 0);
 }
 
 __device__ __forceinline__ int coarse_bin(double key, double klo, double cscale, double &t)
@@ -489,19 +495,6 @@ __device__ __forceinline__ int coarse_bin(double key, double klo, double cscale,
     if (!(t >= 0.0)) cb = 0;  // also catches NaN
     if (cb > kCoarse - 1) cb = kCoarse - 1;
     return cb;
-}
-
-// monotone non-decreasing map key -> fine bucket (coarse bins own consecutive fine ranges)
-__device__ __forceinline__ unsigned fine_bucket(double key, double klo, double cscale, const unsigned *fine_base)
-{
-    double t;
-    int cb = coarse_bin(key, klo, cscale, t);
-    unsigned base = fine_base[cb], nb = fine_base[cb + 1] - base;
-    double frac = t - (double)cb;
-    double f = frac * (double)nb;
-    unsigned sub = 0;
-    if (f > 0.0) sub = (f >= (double)nb) ? nb - 1 : (unsigned)f;
-    return base + sub;
 }
 
 // k_keys: projection key per distinct colour (C7) + privatised coarse histogram.
@@ -557,322 +550,7 @@ __global__ void __launch_bounds__(256) k_coarse_hist(const Job *jobs)
     }
 }
 
-// k_bucket_plan: histogram-equalising bucket layout: coarse bin with c keys gets max(1,2c)
-// consecutive fine buckets.  1024 threads, 4 coarse bins each.
-__global__ void __launch_bounds__(1024) k_bucket_plan(const Job *jobs)
-{
-    const Job &job = jobs[blockIdx.y];
-    RegionCtrl *rc = job.rc;
-    __shared__ unsigned s_warp[33];
-    unsigned nb[4], sum = 0;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        unsigned c = rc->coarse[threadIdx.x * 4 + k];
-        nb[k] = c ? 2u * c : 1u;
-        sum += nb[k];
-    }
-    unsigned total;
-    unsigned off = block_excl_scan(sum, s_warp, total);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        rc->fine_base[threadIdx.x * 4 + k] = off;
-        off += nb[k];
-    }
-    if (threadIdx.x == 1023) {
-        rc->fine_base[kCoarse] = total;
-        rc->n_fine = total;
-        rc->n_fine_p1 = total + 1;
-    }
-}
-
-__global__ void __launch_bounds__(256) k_zero_fine(const Job *jobs)
-{
-    const Job &job = jobs[blockIdx.y];
-    const unsigned n = job.rc->n_fine_p1;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-        job.fine[i] = 0;
-}
-
-__global__ void __launch_bounds__(256) k_bucket_count(const Job *jobs)
-{
-    const Job &job = jobs[blockIdx.y];
-    RegionCtrl *rc = job.rc;
-    const unsigned d = rc->d;
-    if (rc->n_fine == 0 || (size_t)blockIdx.x * blockDim.x >= d) return;
-    __shared__ unsigned s_base[kCoarse + 1];
-    for (int i = threadIdx.x; i <= kCoarse; i += blockDim.x) s_base[i] = rc->fine_base[i];
-    __syncthreads();
-    const double klo = rc->klo, cscale = rc->cscale;
-    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < d; e += (size_t)gridDim.x * blockDim.x) {
-        unsigned fb = fine_bucket(job.keyA[e], klo, cscale, s_base);
-        job.fbA[e] = fb;
-        job.slotA[e] = atomicAdd(&job.fine[fb], 1u);
-    }
-}
-
-__global__ void __launch_bounds__(256) k_scatter(const Job *jobs)
-{
-    const Job &job = jobs[blockIdx.y];
-    const unsigned d = job.rc->d;
-    if (job.rc->n_fine == 0) return;
-    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < d; e += (size_t)gridDim.x * blockDim.x) {
-        unsigned pos = job.fine[job.fbA[e]] + job.slotA[e];
-        job.keyB[pos] = job.keyA[e];
-        job.payB[pos] = job.payA ? job.payA[e] : (unsigned)e;
-        job.cumB[pos] = job.cntA ? job.cntA[e] : 1u;
-    }
-}
-
-// k_bucket_sort: exact order inside each fine bucket (by key, then payload): one thread per
-// bucket, insertion sort in place.  Buckets hold ~0.5 keys on average.
-__global__ void __launch_bounds__(256) k_bucket_sort(const Job *jobs)
-{
-    const Job &job = jobs[blockIdx.y];
-    const unsigned nf = job.rc->n_fine;
-    for (size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x; b < nf; b += (size_t)gridDim.x * blockDim.x) {
-        unsigned lo = job.fine[b], hi = job.fine[b + 1];
-        for (unsigned i = lo + 1; i < hi; ++i) {
-            double k = job.keyB[i];
-            unsigned p = job.payB[i], c = job.cumB[i];
-            unsigned j = i;
-            while (j > lo) {
-                double kj = job.keyB[j - 1];
-                unsigned pj = job.payB[j - 1];
-                if (kj < k || (kj == k && pj < p)) break;
-                job.keyB[j] = kj;
-                job.payB[j] = pj;
-                job.cumB[j] = job.cumB[j - 1];
-                --j;
-            }
-            job.keyB[j] = k;
-            job.payB[j] = p;
-            job.cumB[j] = c;
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------
-// three-phase prefix sum over uint32, in place; WHICH selects the array of the job
-// (0: job.fine over n_fine_p1 elements, exclusive; 1: job.cumB over d elements, inclusive)
-// ------------------------------------------------------------------------------------------
-template <int WHICH>
-__device__ __forceinline__ void scan_target(const Job &job, unsigned *&data, unsigned &n)
-{
-    if (WHICH == 0) {
-        data = job.fine;
-        n = job.rc->n_fine ? job.rc->n_fine_p1 : 0;
-    } else {
-        data = job.cumB;
-        n = job.rc->n_fine ? job.rc->d : 0;
-    }
-}
-
-template <int WHICH>
-__global__ void __launch_bounds__(256) k_scan_reduce(const Job *jobs)
-{
-    const Job &job = jobs[blockIdx.y];
-    unsigned *data, n;
-    scan_target<WHICH>(job, data, n);
-    size_t base = (size_t)blockIdx.x * kScanChunk;
-    if (base >= n) return;
-    unsigned sum = 0;
-    for (int k = 0; k < 16; ++k) {
-        size_t i = base + k * 256 + threadIdx.x;
-        if (i < n) sum += data[i];
-    }
-    __shared__ unsigned s_w[8];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = sum;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned t = 0;
-        for (int w = 0; w < 8; ++w) t += s_w[w];
-        job.partials[blockIdx.x] = t;
-    }
-}
-
-template <int WHICH>
-__global__ void __launch_bounds__(1024) k_scan_partials(const Job *jobs)
-{
-    const Job &job = jobs[blockIdx.y];
-    unsigned *data, n;
-    scan_target<WHICH>(job, data, n);
-    unsigned nblk = (unsigned)(((size_t)n + kScanChunk - 1) / kScanChunk);
-    __shared__ unsigned s_warp[33];
-    unsigned carry = 0;
-    for (unsigned base = 0; base < nblk; base += 1024) {
-        unsigned i = base + threadIdx.x;
-        unsigned v = i < nblk ? job.partials[i] : 0u;
-        unsigned total;
-        unsigned ex = block_excl_scan(v, s_warp, total);
-        if (i < nblk) job.partials[i] = carry + ex;
-        carry += total;
-    }
-}
-
-template <int WHICH>
-__global__ void __launch_bounds__(256) k_scan_apply(const Job *jobs)
-{
-    const Job &job = jobs[blockIdx.y];
-    unsigned *data, n;
-    scan_target<WHICH>(job, data, n);
-    size_t base = (size_t)blockIdx.x * kScanChunk;
-    if (base >= n) return;
-    __shared__ unsigned s_warp[33];
-    // thread t owns 16 consecutive elements
-    size_t i0 = base + (size_t)threadIdx.x * 16;
-    unsigned v[16], sum = 0;
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        v[k] = (i0 + k < n) ? data[i0 + k] : 0u;
-        sum += v[k];
-    }
-    unsigned total;
-    unsigned off = block_excl_scan(sum, s_warp, total) + job.partials[blockIdx.x];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        unsigned incl = off + v[k];
-        if (i0 + k < n) data[i0 + k] = (WHICH == 0) ? off : incl;
-        off = incl;
-    }
-}
-
-// ------------------------------------------------------------------------------------------
-// k_match: a-6 (match_cdf with np.linspace / np.interp semantics) + a-7 per distinct target
-// colour, in ascending key order.  Writes the colour -> output-RGB LUT.
-// ------------------------------------------------------------------------------------------
-struct Sorted {
-    const double *key;
-    const unsigned *cum;
-    unsigned d;
-    long long n;
-};
-
-// order statistic: q-th smallest (0-based) of the multiset
-__device__ __forceinline__ double os_lookup(const Sorted &v, long long q)
-{
-    unsigned lo = 0, hi = v.d - 1;  // smallest idx with cum[idx] > q
-    while (lo < hi) {
-        unsigned mid = (lo + hi) >> 1;
-        if ((long long)__ldg(v.cum + mid) > q) hi = mid; else lo = mid + 1;
-    }
-    return __ldg(v.key + lo);
-}
-
-// np.interp(x, np.linspace(0,1,v.n), sorted(v)) for 0 <= x <= 1
-__device__ double interp_lin_os(double x, const Sorted &v)
-{
-    const long long n = v.n;
-    if (n == 1) return os_lookup(v, 0);
-    long long m = (long long)(x * (double)(n - 1));
-    if (m < 0) m = 0;
-    if (m > n - 1) m = n - 1;
-    while (m + 1 <= n - 1 && lin(n, m + 1) <= x) ++m;
-    while (m > 0 && lin(n, m) > x) --m;
-    if (m >= n - 1) return os_lookup(v, n - 1);
-    double xm = lin(n, m);
-    double fm = os_lookup(v, m);
-    if (xm == x) return fm;
-    double fm1 = os_lookup(v, m + 1);
-    double slope = (fm1 - fm) / (lin(n, m + 1) - xm);
-    return slope * (x - xm) + fm;
-}
-
-struct MatchOut {
-    unsigned *lut;        // colour -> packed rgb (pipeline) or NULL
-    double *matched_pay;  // matched[payload] (generic match_cdf) or NULL
-    long long *j_pay;     // j[payload] or NULL
-    double *matchedB;     // debug, sorted order, or NULL
-    long long *jB;        // debug, sorted order, or NULL
-};
-
-__device__ __forceinline__ double match_one(const Sorted &t, const Sorted &s, unsigned i, long long &j_out)
-{
-    const double key = t.key[i];
-    unsigned i2 = i;
-    while (i2 + 1 < t.d && t.key[i2 + 1] == key) ++i2;  // ties share the upper rank
-    const long long r = (long long)t.cum[i2] - 1;
-    const long long T = t.n, S = s.n;
-    double m;
-    long long j;
-    if (T == S) {
-        j = r;
-        m = os_lookup(s, r);
-    } else if (T > S) {  // source stretched to T samples (LST:110-115)
-        j = r;
-        m = interp_lin_os(lin(T, r), s);
-    } else {  // target stretched to S samples (LST:116-121): t'[k] = interp(lin(S,k), lin(T,.), t)
-        if (T == 1) {
-            j = S - 1;
-        } else {
-            double xr = lin(T, r);
-            long long k = (long long)(xr * (double)(S - 1));
-            if (k < 0) k = 0;
-            if (k > S - 1) k = S - 1;
-            while (k + 1 <= S - 1 && interp_lin_os(lin(S, k + 1), t) <= key) ++k;
-            while (k > 0 && interp_lin_os(lin(S, k), t) > key) --k;
-            j = k;
-        }
-        if (j >= S - 1) {
-            m = os_lookup(s, S - 1);
-        } else {
-            double tj = interp_lin_os(lin(S, j), t);
-            double sj = os_lookup(s, j);
-            if (tj == key) {
-                m = sj;
-            } else {
-                double slope = (os_lookup(s, j + 1) - sj) / (interp_lin_os(lin(S, j + 1), t) - tj);
-                m = slope * (key - tj) + sj;
-            }
-        }
-    }
-    j_out = j;
-    return m;
-}
-
-// pipeline flavour: jobs[2*slot] = target, jobs[2*slot+1] = source
-__global__ void __launch_bounds__(128) k_match(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0, size_t lut_stride,
-                                               double *dbg_matched0, long long *dbg_j0, size_t dbg_stride)
-{
-    const int slot = blockIdx.y;
-    if (ctrl[slot].status != 0) return;
-    const Job &jt = jobs[2 * slot], &js = jobs[2 * slot + 1];
-    Sorted t{jt.keyB, jt.cumB, jt.rc->d, (long long)jt.rc->n_pix};
-    Sorted s{js.keyB, js.cumB, js.rc->d, (long long)js.rc->n_pix};
-    if ((size_t)blockIdx.x * blockDim.x >= t.d) return;
-    __shared__ MathTabs T;
-    stage_tabs(&T);
-    const Pca pca = jt.rc->pca;
-    unsigned *lut = lut0 + (size_t)slot * lut_stride;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < t.d; i += (size_t)gridDim.x * blockDim.x) {
-        long long j;
-        double m = match_one(t, s, (unsigned)i, j);
-        double lab[3];
-#pragma unroll
-        for (int c = 0; c < 3; ++c) lab[c] = m * pca.comp[c] + pca.mean[c];  // inverse_transform
-        lut[jt.payB[i]] = lab2rgb(lab, &T, nullptr);
-        if (dbg_matched0) {
-            dbg_matched0[(size_t)slot * dbg_stride + i] = m;
-            dbg_j0[(size_t)slot * dbg_stride + i] = j;
-        }
-    }
-}
-
-// generic flavour (rct_match_cdf): jobs[0] = target, jobs[1] = source; payload = input index
-__global__ void __launch_bounds__(128) k_match_generic(const Job *jobs, double *matched, long long *jidx)
-{
-    const Job &jt = jobs[0], &js = jobs[1];
-    Sorted t{jt.keyB, jt.cumB, jt.rc->d, (long long)jt.rc->n_pix};
-    Sorted s{js.keyB, js.cumB, js.rc->d, (long long)js.rc->n_pix};
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < t.d; i += (size_t)gridDim.x * blockDim.x) {
-        long long j;
-        double m = match_one(t, s, (unsigned)i, j);
-        unsigned p = jt.payB[i];
-        matched[p] = m;
-        if (jidx) jidx[p] = j;
-    }
-}
+#include "rct_sort.cuh"
 
 // ------------------------------------------------------------------------------------------
 // the reference's stand-alone element-wise functions

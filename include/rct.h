@@ -81,6 +81,9 @@ int rct_plan_destroy(rct_plan *plan);
 /* RCT_OPT_TIMING (0/1): bracket the phases of every launch group of rct_transfer_async /
  * rct_transfer_host with CUDA events on the launching stream; read with rct_plan_timing() */
 #define RCT_OPT_TIMING 1
+/* RCT_OPT_PART_CAP (1..4096): largest sort part handled in shared memory; lowering it forces the
+ * global-memory fallback of the exact sort (tests only) */
+#define RCT_OPT_PART_CAP 2
 int rct_plan_set_option(rct_plan *plan, int option, int value);
 /* accumulated device time per phase since the last reset, in ms: [0] workspace memsets,
  * [1] k_hist (pixels -> colour histograms), [2] solve (compact .. match -> LUT), [3] k_apply

@@ -313,3 +313,37 @@ def test_sharded_driver_two_ranks_one_gpu():
     for rank, r0, n, out in got:
         full[r0:r0 + n] = out
     assert np.array_equal(full, ref)
+
+
+# ---- exact sort: fallback paths ---------------------------------------------------------------------
+@pytest.mark.parametrize("cap", [1, 64, 700])
+def test_sort_global_fallback_is_exact(cap):
+    """Lower the shared-memory part capacity so that parts take the global-memory bitonic
+    fallback of the exact sort; results must not change."""
+    H, W = 180, 320
+    c, s = synth.synth_image(H, W, 40, "U"), synth.synth_image(H, W, 41, "N")
+    mask = synth.ellipse_mask(H, W, 0.55, 9)
+    plan = _debug_plan(H, W, H, W)
+    plan.set_option(_cabi.OPT_PART_CAP, cap)
+    out = _run_plan(plan, c, s, mask)
+    ref, st, d = orc.transfer(c, s, mask, debug=True)
+    assert st == 0 and np.array_equal(out, ref)
+    t = plan.debug_target()
+    assert np.all(np.diff(t["key"]) >= 0) and int(t["cum"][-1]) == d["n_t"]
+
+
+def test_match_cdf_degenerate_key_sets():
+    """All keys equal / two clusters / huge dynamic range: the equalised partition degenerates
+    (one fine bin holds everything) and the bitonic fallbacks take over."""
+    rng = np.random.default_rng(3)
+    cases = [
+        (np.full(9000, 0.25), rng.normal(0, 1, 5000)),
+        (rng.normal(0, 1, 7000), np.full(12000, -3.0)),
+        (np.concatenate([np.full(6000, 1.0), np.full(6000, 1.0 + 1e-12)]), rng.uniform(0, 1, 12000)),
+        (np.concatenate([rng.normal(0, 1e-9, 20000), [1e6, -1e6]]), rng.normal(0, 1, 30000)),
+        (rng.integers(0, 3, 50000).astype(np.float64), rng.integers(0, 5, 40000).astype(np.float64)),
+    ]
+    for t, s in cases:
+        m, j = aip.match_cdf(t, s, return_index=True)
+        om, oj = orc.match_cdf(t, s, want_index=True)
+        assert np.array_equal(j, oj) and np.array_equal(m, om)
