@@ -98,7 +98,7 @@ struct Layout {
     size_t off_ctrl, off_jobs, off_status, off_xtab, off_ytab;
     size_t off_hist, hist_stride_u32, off_lut, lut_stride_u32;
     size_t off_region, region_bytes;  // [slots][2] blocks of per-region arrays
-    size_t r_col, r_cnt, r_keyA, r_keyP, r_auxP, r_pof, r_pstart, r_ppix;
+    size_t r_col, r_cnt, r_keyA, r_recP, r_pof, r_pstart, r_ppix;
     size_t off_zero, zero_bytes, z_fcnt, z_pfill;  // [slots][2] blocks zeroed before every sort
     size_t off_dbg_m, off_dbg_j, dbg_stride;
     size_t total;
@@ -133,8 +133,7 @@ Layout make_layout(int H, int W, int slots, unsigned flags)
     L.r_col = r; r = align_up(r + 4 * L.cap);
     L.r_cnt = r; r = align_up(r + 4 * L.cap);
     L.r_keyA = r; r = align_up(r + 8 * L.cap);
-    L.r_keyP = r; r = align_up(r + 8 * L.cap);
-    L.r_auxP = r; r = align_up(r + 8 * L.cap);
+    L.r_recP = r; r = align_up(r + 16 * L.cap);
     L.r_pof = r; r = align_up(r + 2 * (size_t)kFineMax);
     L.r_pstart = r; r = align_up(r + 4 * (L.maxparts + 1));
     L.r_ppix = r; r = align_up(r + 4 * (L.maxparts + 1));
@@ -294,8 +293,7 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
             j.payA = (unsigned *)(b + L.r_col);
             j.cntA = (unsigned *)(b + L.r_cnt);
             j.keyA = (double *)(b + L.r_keyA);
-            j.keyP = (double *)(b + L.r_keyP);
-            j.auxP = (unsigned long long *)(b + L.r_auxP);
+            j.recP = (ulonglong2 *)(b + L.r_recP);
             j.pof = (unsigned short *)(b + L.r_pof);
             j.pstart = (unsigned *)(b + L.r_pstart);
             j.ppix = (unsigned *)(b + L.r_ppix);
@@ -427,7 +425,7 @@ int phase_hist(rct_plan *p, const FrameSet &f, int nslots, int mode, int label, 
 
 constexpr size_t kSmemFineHist = (size_t)(kFineMax + kCoarse + 1) * 4;
 constexpr size_t kSmemScatter = (size_t)(kCoarse + 1) * 4 + (size_t)kFineMax * 2;
-constexpr size_t kSmemPartSort = (size_t)kPartCap * 16 + (size_t)kPartCap * 8;
+constexpr size_t kSmemPartSort = (size_t)kPartCap * 16 + (size_t)kPartCap * 8;  // records + 2 counters each
 
 int ensure_kernel_attrs()
 {
@@ -699,8 +697,7 @@ MatchLayout match_layout(size_t nt, size_t ns)
     M.off_jobs = o; o = align_up(o + 2 * sizeof(Job));
     for (int r = 0; r < 2; ++r) {
         size_t a = 0;
-        a = align_up(a + 8 * n[r]);                    // keyP
-        a = align_up(a + 8 * n[r]);                    // auxP
+        a = align_up(a + 16 * n[r]);                   // recP
         a = align_up(a + 2 * (size_t)kFineMax);        // pof
         a = align_up(a + 4 * (M.maxparts[r] + 1));     // pstart
         a = align_up(a + 4 * (M.maxparts[r] + 1));     // ppix
@@ -735,8 +732,7 @@ int rct_match_cdf(const double *target_proj, size_t nt, const double *source_pro
         Job &j = hj[r];
         j.rc = (RegionCtrl *)(ws + M.off_rc[r]);
         j.keyA = keys[r]; j.payA = nullptr; j.cntA = nullptr;
-        j.keyP = (double *)(b + a); a = align_up(a + 8 * n[r]);
-        j.auxP = (unsigned long long *)(b + a); a = align_up(a + 8 * n[r]);
+        j.recP = (ulonglong2 *)(b + a); a = align_up(a + 16 * n[r]);
         j.pof = (unsigned short *)(b + a); a = align_up(a + 2 * (size_t)kFineMax);
         j.pstart = (unsigned *)(b + a); a = align_up(a + 4 * (M.maxparts[r] + 1));
         j.ppix = (unsigned *)(b + a);
@@ -830,10 +826,9 @@ int rct_plan_debug_target(rct_plan *p, int slot, uint32_t *colour, double *key, 
     if (d == 0 || info.status != 0) return RCT_OK;
     const Layout &L = p->L;
     uint8_t *b = p->ws + L.off_region + L.region_bytes * (size_t)(2 * slot);
-    if (key) CK(cudaMemcpy(key, b + L.r_keyP, 8 * d, cudaMemcpyDeviceToHost));
-    if (colour || cum) {
-        // sorted aux = payload | part-local cumulative count << 32; globalise with the part bases
-        std::vector<unsigned long long> aux(d);
+    {
+        // sorted records: key | payload | part-local cumulative count; globalise with the part bases
+        std::vector<ulonglong2> rec(d);
         std::vector<unsigned> pstart(L.maxparts + 1), pbase(L.maxparts + 1);
         FrameCtrl *h = new (std::nothrow) FrameCtrl;
         if (!h) return fail(RCT_ERR_NOMEM, "out of host memory");
@@ -841,13 +836,14 @@ int rct_plan_debug_target(rct_plan *p, int slot, uint32_t *colour, double *key, 
         unsigned np = h->r[0].n_parts;
         delete h;
         if (e != cudaSuccess) return fail(RCT_ERR_CUDA, "debug copy failed: %s", cudaGetErrorString(e));
-        CK(cudaMemcpy(aux.data(), b + L.r_auxP, 8 * d, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(rec.data(), b + L.r_recP, 16 * d, cudaMemcpyDeviceToHost));
         CK(cudaMemcpy(pstart.data(), b + L.r_pstart, 4 * (L.maxparts + 1), cudaMemcpyDeviceToHost));
         CK(cudaMemcpy(pbase.data(), b + L.r_ppix, 4 * (L.maxparts + 1), cudaMemcpyDeviceToHost));
         for (unsigned q = 0; q < np; ++q)
             for (unsigned i = pstart[q]; i < pstart[q + 1]; ++i) {
-                if (colour) colour[i] = (uint32_t)aux[i];
-                if (cum) cum[i] = pbase[q] + (uint32_t)(aux[i] >> 32);
+                if (key) memcpy(&key[i], &rec[i].x, 8);
+                if (colour) colour[i] = (uint32_t)rec[i].y;
+                if (cum) cum[i] = pbase[q] + (uint32_t)(rec[i].y >> 32);
             }
     }
     if (j) CK(cudaMemcpy(j, p->dbg_j + (size_t)slot * L.dbg_stride, 8 * d, cudaMemcpyDeviceToHost));

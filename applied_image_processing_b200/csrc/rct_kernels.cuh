@@ -56,8 +56,8 @@ struct Job {
     const double *keyA;          // unsorted keys
     const unsigned *payA;        // payload (colour index); NULL = identity
     const unsigned *cntA;        // multiplicity; NULL = 1
-    double *keyP;                // partitioned, then sorted keys
-    unsigned long long *auxP;    // lo: payload; hi: multiplicity, then part-local inclusive cumulative count
+    ulonglong2 *recP;            // partitioned, then sorted records: x = key bits, y = payload | count << 32
+                                 // (count becomes the part-local inclusive cumulative count)
     unsigned *fcnt;              // [kFineMax+1] fine-bin counts, then exclusive offsets (fcnt[n_fine] = d)
     unsigned short *pof;         // [kFineMax] part of each fine bin
     unsigned *pstart;            // [maxparts+1] first entry of each part
