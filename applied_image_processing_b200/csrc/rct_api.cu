@@ -424,8 +424,7 @@ int phase_hist(rct_plan *p, const FrameSet &f, int nslots, int mode, int label, 
 }
 
 constexpr size_t kSmemFineHist = (size_t)(kFineMax + kCoarse + 1) * 4;
-constexpr size_t kSmemScatter = (size_t)(kCoarse + 1) * 4 + (size_t)kFineMax * 2;
-constexpr size_t kSmemPartSort = (size_t)kPartCap * 16 + (size_t)kPartCap * 8;  // records + 2 counters each
+constexpr size_t kSmemPartSort = (size_t)kPartCap * 16 + ((size_t)kPartCap + kPartCap / 32 + 2) * 4;  // records + padded counters
 
 int ensure_kernel_attrs()
 {
@@ -434,7 +433,6 @@ int ensure_kernel_attrs()
     CK(cudaGetDevice(&dev));
     if (done_dev == dev) return RCT_OK;
     CK(cudaFuncSetAttribute(k_fine_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemFineHist));
-    CK(cudaFuncSetAttribute(k_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemScatter));
     CK(cudaFuncSetAttribute(k_part_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemPartSort));
     done_dev = dev;
     return RCT_OK;
@@ -450,7 +448,7 @@ int sort_jobs(const Job *jobs, int njobs, unsigned eblocks, size_t cap, size_t m
     LAUNCH(k_plan_fine, dim3(1, njobs), 1024, st, jobs);
     k_fine_hist<<<dim3(hblocks, njobs), 512, kSmemFineHist, st>>>(jobs);
     k_plan_parts<<<dim3(1, njobs), 1024, 0, st>>>(jobs);
-    k_scatter<<<dim3(eblocks, njobs), 256, kSmemScatter, st>>>(jobs);
+    k_scatter<<<dim3(eblocks, njobs), 256, 0, st>>>(jobs);
     k_part_sort<<<dim3((unsigned)maxparts, njobs), kSortThreads, kSmemPartSort, st>>>(jobs, part_cap);
     t_launches += 4;
     CK(cudaGetLastError());
@@ -468,7 +466,7 @@ int phase_solve(rct_plan *p, int nslots, cudaStream_t st)
     LAUNCH(k_keys, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs);
     int rc = sort_jobs(p->jobs, 2 * nslots, eb, p->L.cap, p->L.maxparts, p->part_cap, st);
     if (rc) return rc;
-    LAUNCH(k_match, dim3((unsigned)p->L.maxparts, nslots), 256, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32,
+    LAUNCH(k_match, dim3((unsigned)p->L.maxparts, nslots), kMatchThreads, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32,
            p->dbg_m, p->dbg_j, p->L.dbg_stride);
     return mark(p, st);
 }
@@ -752,7 +750,7 @@ int rct_match_cdf(const double *target_proj, size_t nt, const double *source_pro
     size_t mp = M.maxparts[0] > M.maxparts[1] ? M.maxparts[0] : M.maxparts[1];
     rc = sort_jobs(jobs, 2, eb, nmax, mp, kPartCap, st);
     if (rc) return rc;
-    LAUNCH(k_match_generic, (unsigned)M.maxparts[0], 256, st, jobs, matched, (long long *)j_index);
+    LAUNCH(k_match_generic, (unsigned)M.maxparts[0], kMatchThreads, st, jobs, matched, (long long *)j_index);
     return RCT_OK;
 }
 

@@ -36,8 +36,10 @@ struct RegionCtrl {
     unsigned int n_parts;               // parts in use
     unsigned int skip;                  // 1: the frame has an empty region, nothing to sort
     long long limbs[9][3];              // exact moments: s1[0..2], s2[00,01,02,11,12,22]
-    unsigned long long lab_max[3];      // ord_enc(max lab_i)
-    unsigned long long lab_min[3];      // ~ord_enc(min lab_i)
+    unsigned long long lab_max[3];      // [0]: ord_enc(max key) of the generic match_cdf path
+    unsigned long long lab_min[3];      // [0]: ~ord_enc(min key)
+    unsigned int cmax[3];               // per-channel maximum of the region's colours
+    unsigned int cmin_inv[3];           // 255 - per-channel minimum
     Pca pca;
     double klo, cscale;                 // coarse bin = floor((key-klo)*cscale)
     unsigned int coarse[kCoarse];
@@ -379,8 +381,11 @@ __device__ __forceinline__ long long warp_sum_ll(long long v)
     return v;
 }
 
-// k_lab_moments: a-4 + the reductions of a-5 over the distinct-colour list.
-__global__ void __launch_bounds__(256) k_lab_moments(FrameCtrl *ctrl, const Job *jobs)
+// k_lab_moments: a-4 + the reductions of a-5 over the distinct-colour list.  Multiplicities
+// below 128 (virtually all of them) take the 64-bit fast path of rct_math.cuh; the rest, and
+// the rare overflow-guard flushes, go through 48-bit limbs in shared memory.  The next
+// entry is loaded before the current one is evaluated (the loop is latency-bound otherwise).
+__global__ void __launch_bounds__(256, 2) k_lab_moments(FrameCtrl *ctrl, const Job *jobs)
 {
     const int region = blockIdx.y, slot = blockIdx.z;
     const Job &job = jobs[slot * 2 + region];
@@ -389,27 +394,74 @@ __global__ void __launch_bounds__(256) k_lab_moments(FrameCtrl *ctrl, const Job 
     if ((size_t)blockIdx.x * blockDim.x >= d) return;
     __shared__ MathTabs T;
     __shared__ long long s_red[8][28];
-    __shared__ double s_mm[8][6];
-    stage_tabs(&T);
-    Moments m;
-    moments_zero(m);
-    double mx[3] = {-1e300, -1e300, -1e300}, mn[3] = {1e300, 1e300, 1e300};
-    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < d; e += (size_t)gridDim.x * blockDim.x) {
-        double lab[3];
-        rgb2lab(job.payA[e], &T, lab);
-        moments_add(m, lab, (long long)job.cntA[e]);
+    __shared__ unsigned long long s_slow[9][3];
+    __shared__ unsigned s_box[8][2];
+    if (threadIdx.x < 27) s_slow[threadIdx.x / 3][threadIdx.x % 3] = 0ull;
+    stage_tabs(&T);  // ends with a barrier
+    MomentsFast f;
+    fast_zero(f);
+    long long npx = 0;
+    int terms = 0;
+    auto spill = [&](const i128 *s1, const i128 *s2) {  // exact add into the block's limbs
+        long long l[3];
 #pragma unroll
-        for (int i = 0; i < 3; ++i) {
-            mx[i] = fmax(mx[i], lab[i]);
-            mn[i] = fmin(mn[i], lab[i]);
+        for (int k = 0; k < 9; ++k) {
+            split_limbs(k < 3 ? s1[k] : s2[k - 3], l);
+#pragma unroll
+            for (int j = 0; j < 3; ++j) atomicAdd(&s_slow[k][j], (unsigned long long)l[j]);
         }
+    };
+    unsigned cmx = 0u, cmn = 0x00ffffffu;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned col = 0, cnt = 0;
+    if (e < d) {
+        col = job.payA[e];
+        cnt = job.cntA[e];
+    }
+    while (e < d) {
+        const size_t en = e + stride;
+        unsigned coln = 0, cntn = 0;
+        if (en < d) {
+            coln = job.payA[en];
+            cntn = job.cntA[en];
+        }
+        double lab[3];
+        rgb2lab(col, &T, lab);
+        long long q[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) q[i] = __double2ll_rn(lab[i] * 0x1p40);
+        cmx = __vmaxu4(cmx, col);
+        cmn = __vminu4(cmn, col);
+        npx += cnt;
+        if (cnt < 128u) {
+            fast_add(f, q, cnt);
+            if (++terms == kFastTerms) {
+                i128 s1[3], s2[6];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) s1[k] = fast_s1(f, k);
+#pragma unroll
+                for (int k = 0; k < 6; ++k) s2[k] = fast_s2(f, k);
+                spill(s1, s2);
+                fast_zero(f);
+                terms = 0;
+            }
+        } else {
+            Moments m;
+            moments_zero(m);
+            moments_add(m, lab, (long long)cnt);
+            spill(m.s1, m.s2);
+        }
+        col = coln;
+        cnt = cntn;
+        e = en;
     }
     long long v[28];
 #pragma unroll
-    for (int k = 0; k < 3; ++k) split_limbs(m.s1[k], v + 3 * k);
+    for (int k = 0; k < 3; ++k) split_limbs(fast_s1(f, k), v + 3 * k);
 #pragma unroll
-    for (int k = 0; k < 6; ++k) split_limbs(m.s2[k], v + 9 + 3 * k);
-    v[27] = m.n;
+    for (int k = 0; k < 6; ++k) split_limbs(fast_s2(f, k), v + 9 + 3 * k);
+    v[27] = npx;
     const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
 #pragma unroll
     for (int k = 0; k < 28; ++k) {
@@ -417,22 +469,19 @@ __global__ void __launch_bounds__(256) k_lab_moments(FrameCtrl *ctrl, const Job 
         if (lane == 0) s_red[warp][k] = s;
     }
 #pragma unroll
-    for (int i = 0; i < 3; ++i) {
-        double a = mx[i], b = mn[i];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            a = fmax(a, __shfl_xor_sync(0xffffffffu, a, o));
-            b = fmin(b, __shfl_xor_sync(0xffffffffu, b, o));
-        }
-        if (lane == 0) {
-            s_mm[warp][i] = a;
-            s_mm[warp][3 + i] = b;
-        }
+    for (int o = 16; o > 0; o >>= 1) {
+        cmx = __vmaxu4(cmx, __shfl_xor_sync(0xffffffffu, cmx, o));
+        cmn = __vminu4(cmn, __shfl_xor_sync(0xffffffffu, cmn, o));
+    }
+    if (lane == 0) {
+        s_box[warp][0] = cmx;
+        s_box[warp][1] = cmn;
     }
     __syncthreads();
     const unsigned nwarps = blockDim.x >> 5;
     if (threadIdx.x < 9) {  // one moment each: sum limbs over warps, renormalise, publish
-        long long l[3] = {0, 0, 0};
+        long long l[3];
+        for (int j = 0; j < 3; ++j) l[j] = (long long)s_slow[threadIdx.x][j];
         for (unsigned w = 0; w < nwarps; ++w)
             for (int j = 0; j < 3; ++j) l[j] += s_red[w][3 * threadIdx.x + j];
         i128 tot = join_limbs(l);
@@ -445,13 +494,13 @@ __global__ void __launch_bounds__(256) k_lab_moments(FrameCtrl *ctrl, const Job 
         atomicAdd(&rc->n_pix, (unsigned long long)n);
     } else if (threadIdx.x >= 32 && threadIdx.x < 35) {
         int i = threadIdx.x - 32;
-        double a = -1e300, b = 1e300;
+        unsigned a = 0u, b = 255u;
         for (unsigned w = 0; w < nwarps; ++w) {
-            a = fmax(a, s_mm[w][i]);
-            b = fmin(b, s_mm[w][3 + i]);
+            a = max(a, (s_box[w][0] >> (8 * i)) & 255u);
+            b = min(b, (s_box[w][1] >> (8 * i)) & 255u);
         }
-        atomicMax(&rc->lab_max[i], ord_enc(a));
-        atomicMax(&rc->lab_min[i], ~ord_enc(b));
+        atomicMax(&rc->cmax[i], a);
+        atomicMax(&rc->cmin_inv[i], 255u - b);
     }
 }
 
@@ -471,12 +520,30 @@ __global__ void k_pca(FrameCtrl *ctrl, int slots)
         Pca p;
         pca_from_moments((long long)rc->n_pix, s1, s2, &p);
         rc->pca = p;
-        double lo = 0.0, hi = 0.0;
+        // key range by interval arithmetic over the region's colour box: LMS is increasing in
+        // every channel (positive matrix), log10 is increasing, the two linear maps take the
+        // sign-wise extremes.  (A key a rounding error outside the range is clamped into the
+        // edge bins by coarse_bin, which keeps the bin map monotone.)
+        double ylo[3], yhi[3];
         for (int i = 0; i < 3; ++i) {
-            double a = p.comp[i] * ord_dec(rc->lab_max[i]);
-            double b = p.comp[i] * ord_dec(~rc->lab_min[i]);
-            lo += fmin(a, b);
-            hi += fmax(a, b);
+            double a = 0.0, b = 0.0;
+            for (int j = 0; j < 3; ++j) {
+                a += c_mat[3 * i + j] * g_tabs.unit[255u - rc->cmin_inv[j]];
+                b += c_mat[3 * i + j] * g_tabs.unit[rc->cmax[j]];
+            }
+            ylo[i] = clog10(a < 1e-6 ? 1e-6 : a, &g_tabs);
+            yhi[i] = clog10(b < 1e-6 ? 1e-6 : b, &g_tabs);
+        }
+        double lo = 0.0, hi = 0.0;
+        for (int k = 0; k < 3; ++k) {
+            double l0 = 0.0, l1 = 0.0;
+            for (int i = 0; i < 3; ++i) {
+                double m = c_mat[9 + 3 * k + i];
+                l0 += fmin(m * ylo[i], m * yhi[i]);
+                l1 += fmax(m * ylo[i], m * yhi[i]);
+            }
+            lo += fmin(p.comp[k] * l0, p.comp[k] * l1);
+            hi += fmax(p.comp[k] * l0, p.comp[k] * l1);
         }
         lo -= p.pm;
         hi -= p.pm;
@@ -513,13 +580,20 @@ __global__ void __launch_bounds__(256) k_keys(FrameCtrl *ctrl, const Job *jobs)
     const double c0 = rc->pca.comp[0], c1 = rc->pca.comp[1], c2 = rc->pca.comp[2], pm = rc->pca.pm;
     const double klo = rc->klo, cscale = rc->cscale;
     double *keyA = const_cast<double *>(job.keyA);
-    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < d; e += (size_t)gridDim.x * blockDim.x) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned col = e < d ? job.payA[e] : 0u;
+    while (e < d) {  // the next colour is in flight while this one is evaluated
+        const size_t en = e + stride;
+        const unsigned coln = en < d ? job.payA[en] : 0u;
         double lab[3], comp[3] = {c0, c1, c2};
-        rgb2lab(job.payA[e], &T, lab);
+        rgb2lab(col, &T, lab);
         double key = project(lab, comp, pm);
         keyA[e] = key;
         double t;
         atomicAdd(&s_hist[coarse_bin(key, klo, cscale, t)], 1u);
+        col = coln;
+        e = en;
     }
     __syncthreads();
     for (int i = threadIdx.x; i < kCoarse; i += blockDim.x) {

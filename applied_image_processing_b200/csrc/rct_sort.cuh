@@ -181,8 +181,8 @@ __device__ __forceinline__ bool rec_less(const Rec &a, const Rec &b)
     return ka < kb || (ka == kb && rec_pay(a) < rec_pay(b));
 }
 
-// k_scatter: dynamic shared memory = (kCoarse + 1) * 4 + kFineMax * 2 bytes.
-// Each thread moves kScatPer entries per trip so that the fill-counter atomics overlap.
+// k_scatter: entries -> their part.  The fine-bin tables are read through L1 (they are small
+// and hot); each thread moves kScatPer entries per trip so that the fill-counter atomics overlap.
 constexpr int kScatPer = 4;
 __global__ void __launch_bounds__(256) k_scatter(const Job *jobs)
 {
@@ -191,28 +191,25 @@ __global__ void __launch_bounds__(256) k_scatter(const Job *jobs)
     if (rc->skip) return;
     const unsigned d = rc->d;
     if ((size_t)blockIdx.x * blockDim.x * kScatPer >= d) return;
-    extern __shared__ unsigned s_dyn[];
-    unsigned *s_base = s_dyn;  // [kCoarse+1]
-    unsigned short *s_pof = reinterpret_cast<unsigned short *>(s_dyn + kCoarse + 1);
-    const unsigned nf = rc->n_fine;
-    for (unsigned i = threadIdx.x; i <= (unsigned)kCoarse; i += blockDim.x) s_base[i] = rc->fine_base[i];
-    for (unsigned i = threadIdx.x; i < nf; i += blockDim.x) s_pof[i] = job.pof[i];
-    __syncthreads();
+    const unsigned *fine_base = rc->fine_base;
+    const unsigned short *pof = job.pof;
     const double klo = rc->klo, cscale = rc->cscale;
     Rec *recP = job.recP;
     const size_t stride = (size_t)gridDim.x * blockDim.x * kScatPer;
     for (size_t e0 = (size_t)blockIdx.x * blockDim.x * kScatPer + threadIdx.x; e0 < d; e0 += stride) {
         double key[kScatPer];
-        unsigned p[kScatPer], pos[kScatPer];
+        unsigned p[kScatPer], pos[kScatPer], pay[kScatPer], cnt[kScatPer];
 #pragma unroll
         for (int k = 0; k < kScatPer; ++k) {
             size_t e = e0 + (size_t)k * blockDim.x;
             key[k] = e < d ? job.keyA[e] : 0.0;
+            pay[k] = (e < d && job.payA) ? job.payA[e] : (unsigned)e;
+            cnt[k] = (e < d && job.cntA) ? job.cntA[e] : 1u;
         }
 #pragma unroll
         for (int k = 0; k < kScatPer; ++k) {
             double ff;
-            p[k] = s_pof[fine_bin(key[k], klo, cscale, s_base, ff)];
+            p[k] = __ldg(pof + fine_bin(key[k], klo, cscale, fine_base, ff));
         }
 #pragma unroll
         for (int k = 0; k < kScatPer; ++k) {
@@ -222,11 +219,7 @@ __global__ void __launch_bounds__(256) k_scatter(const Job *jobs)
 #pragma unroll
         for (int k = 0; k < kScatPer; ++k) {
             size_t e = e0 + (size_t)k * blockDim.x;
-            if (e < d) {
-                unsigned pay = job.payA ? job.payA[e] : (unsigned)e;
-                unsigned cnt = job.cntA ? job.cntA[e] : 1u;
-                recP[__ldg(job.pstart + p[k]) + pos[k]] = make_rec(key[k], pay, cnt);
-            }
+            if (e < d) recP[__ldg(job.pstart + p[k]) + pos[k]] = make_rec(key[k], pay[k], cnt[k]);
         }
     }
 }
@@ -263,51 +256,40 @@ __device__ __forceinline__ unsigned warp_incl_scan(unsigned v)
     return v;
 }
 
-// In-place scan of s[0..n) in shared memory by the whole CTA (bank-conflict free: every
-// warp sweeps a contiguous segment 32 elements at a time).  INCLUSIVE selects the flavour;
-// GET reads element i, PUT stores the scanned value.  Returns the total.  Two barriers inside,
-// one after.
-template <bool INCLUSIVE, typename Get, typename Put>
-__device__ __forceinline__ unsigned cta_scan(unsigned n, unsigned *s_wtot /*[33]*/, Get get, Put put)
+// Shared-memory counters are stored padded (one spare word per 32) so that a thread sweeping
+// kSortItems consecutive counters never collides with its warp neighbours on a bank.
+__device__ __forceinline__ unsigned pad_idx(unsigned i) { return i + (i >> 5); }
+
+// In-place scan of the padded counters sc[0..n), n <= kSortItems * blockDim.x: thread t owns the
+// kSortItems consecutive counters starting at kSortItems*t.  Returns the total; ends with a barrier.
+constexpr int kSortThreads = 512;
+constexpr int kSortItems = kPartCap / kSortThreads;
+template <bool INCLUSIVE>
+__device__ __forceinline__ unsigned cta_scan_items(unsigned *sc, unsigned n, unsigned *s_warp /*[33]*/)
 {
-    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const unsigned seg = ((n + nwarps - 1) / nwarps + 31u) & ~31u;
-    const unsigned b0 = warp * seg, b1 = (b0 + seg < n) ? b0 + seg : n;
-    unsigned carry = 0;
-    for (unsigned base = b0; base < b1; base += 32) {
-        unsigned i = base + lane;
-        unsigned v = i < b1 ? get(i) : 0u;
-        unsigned inc = warp_incl_scan(v);
-        if (i < b1) put(i, carry + (INCLUSIVE ? inc : inc - v));
-        carry += __shfl_sync(0xffffffffu, inc, 31);
+    const unsigned i0 = threadIdx.x * kSortItems;
+    unsigned v[kSortItems], sum = 0;
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        v[k] = (i0 + k < n) ? sc[pad_idx(i0 + k)] : 0u;
+        sum += v[k];
     }
-    __syncthreads();  // also orders put() of phase 1 before the get() of phase 2
-    if (lane == 0) s_wtot[warp] = carry;
-    __syncthreads();
-    if (warp == 0) {
-        unsigned t = lane < nwarps ? s_wtot[lane] : 0u;
-        unsigned inc = warp_incl_scan(t);
-        if (lane < nwarps) s_wtot[lane] = inc - t;
-        if (lane == 31) s_wtot[32] = inc;
+    unsigned total;
+    unsigned off = block_excl_scan(sum, s_warp, total);
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        if (i0 + k < n) sc[pad_idx(i0 + k)] = INCLUSIVE ? off + v[k] : off;
+        off += v[k];
     }
-    __syncthreads();
-    const unsigned wbase = s_wtot[warp];
-    if (wbase)
-        for (unsigned base = b0; base < b1; base += 32) {
-            unsigned i = base + lane;
-            if (i < b1) put(i, get(i) + wbase);
-        }
-    const unsigned total = s_wtot[32];
     __syncthreads();
     return total;
 }
 
-// k_part_sort: dynamic shared memory = kPartCap*16 + 2*kPartCap*4 bytes.  512 threads, up to
-// kSortItems records per thread held in registers between the counting and the placing pass.
-// `cap` (<= kPartCap) can be lowered by the caller to exercise the fallback.
-constexpr int kSortThreads = 512;
-constexpr int kSortItems = kPartCap / kSortThreads;
-__global__ void __launch_bounds__(kSortThreads) k_part_sort(const Job *jobs, unsigned cap)
+// k_part_sort: dynamic shared memory = kSmemPartSort bytes.  512 threads, up to kSortItems
+// records per thread held in registers between the counting and the placing pass; one bucket
+// per record on average.  `cap` (<= kPartCap) can be lowered by the caller to exercise the
+// fallback.
+__global__ void __launch_bounds__(kSortThreads, 2) k_part_sort(const Job *jobs, unsigned cap)
 {
     const Job &job = jobs[blockIdx.y];
     RegionCtrl *rc = job.rc;
@@ -342,9 +324,8 @@ __global__ void __launch_bounds__(kSortThreads) k_part_sort(const Job *jobs, uns
 
     extern __shared__ unsigned s_dyn[];
     Rec *srec = reinterpret_cast<Rec *>(s_dyn);                    // [kPartCap]
-    unsigned *sc = reinterpret_cast<unsigned *>(srec + kPartCap);  // [2*kPartCap]
-    const unsigned nbk = 2 * n;
-    for (unsigned i = tid; i < nbk; i += kSortThreads) sc[i] = 0;
+    unsigned *sc = reinterpret_cast<unsigned *>(srec + kPartCap);  // [pad_idx(kPartCap) + 1]
+    for (unsigned i = tid; i <= pad_idx(n); i += kSortThreads) sc[i] = 0;
     if (tid == 0) s_flag = 0;
     const double klo = rc->klo, cscale = rc->cscale;
     const unsigned *fine_base = rc->fine_base;
@@ -363,48 +344,59 @@ __global__ void __launch_bounds__(kSortThreads) k_part_sort(const Job *jobs, uns
             double ff;
             unsigned fb = fine_bin(rec_key(r[k]), klo, cscale, fine_base, ff);
             unsigned o0 = __ldg(foff + fb), o1 = __ldg(foff + fb + 1);
-            double est = ((double)(o0 - start) + ff * (double)(o1 - o0)) * 2.0;  // estimated rank x 2
+            double est = (double)(o0 - start) + ff * (double)(o1 - o0);  // estimated rank in the part
             unsigned bb = (unsigned)est;
-            b[k] = bb < nbk ? bb : nbk - 1;
+            b[k] = bb < n ? bb : n - 1;
         }
     }
     __syncthreads();
     // pass 1: bucket sizes
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k)
-        if (tid + k * kSortThreads < n) atomicAdd(&sc[b[k]], 1u);
+        if (tid + k * kSortThreads < n) atomicAdd(&sc[pad_idx(b[k])], 1u);
     __syncthreads();
-    cta_scan<false>(nbk, s_warp, [&](unsigned i) { return sc[i]; }, [&](unsigned i, unsigned v) { sc[i] = v; });
+    cta_scan_items<false>(sc, n, s_warp);
     // pass 2: place (sc[b] becomes the end of bucket b)
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k)
-        if (tid + k * kSortThreads < n) srec[atomicAdd(&sc[b[k]], 1u)] = r[k];
+        if (tid + k * kSortThreads < n) srec[atomicAdd(&sc[pad_idx(b[k])], 1u)] = r[k];
     __syncthreads();
-    // exact order inside each bucket (buckets hold ~0.5 records on average)
-    for (unsigned bk = tid; bk < nbk; bk += kSortThreads) {
-        unsigned lo = bk ? sc[bk - 1] : 0u, hi = sc[bk];
-        if (hi - lo > 32u) {
-            s_flag = 1;  // clustered keys: leave it to the block-wide network below
-            continue;
-        }
-        for (unsigned i = lo + 1; i < hi; ++i) {
-            Rec x = srec[i];
-            unsigned j = i;
-            while (j > lo && rec_less(x, srec[j - 1])) {
-                srec[j] = srec[j - 1];
-                --j;
+    // exact order inside each bucket (one record per bucket on average): every record counts
+    // the members of its bucket that precede it -- no data movement, little divergence
+    unsigned fp[kSortItems];
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        fp[k] = 0;
+        if (tid + k * kSortThreads < n) {
+            unsigned lo = b[k] ? sc[pad_idx(b[k] - 1)] : 0u, hi = sc[pad_idx(b[k])];
+            if (hi - lo > 32u) {
+                s_flag = 1;  // clustered keys: leave it to the block-wide network below
+            } else {
+                unsigned rank = lo;
+                for (unsigned m = lo; m < hi; ++m) rank += rec_less(srec[m], r[k]) ? 1u : 0u;
+                fp[k] = rank;
             }
-            srec[j] = x;
         }
     }
     __syncthreads();
-    if (s_flag) block_bitonic(srec, n);  // ends with a barrier
-    // part-local inclusive cumulative counts
-    unsigned total = cta_scan<true>(
-        n, s_warp, [&](unsigned i) { return (unsigned)(srec[i].y >> 32); },
-        [&](unsigned i, unsigned v) { srec[i].y = (srec[i].y & 0xffffffffull) | ((unsigned long long)v << 32); });
+    if (s_flag) {
+        block_bitonic(srec, n);  // ends with a barrier
+    } else {
+#pragma unroll
+        for (int k = 0; k < kSortItems; ++k)
+            if (tid + k * kSortThreads < n) srec[fp[k]] = r[k];
+        __syncthreads();
+    }
+    // part-local inclusive cumulative counts (the counters are free again)
+    for (unsigned i = tid; i < n; i += kSortThreads) sc[pad_idx(i)] = rec_cnt(srec[i]);
+    __syncthreads();
+    unsigned total = cta_scan_items<true>(sc, n, s_warp);
     if (tid == 0) job.ppix[p] = total;
-    for (unsigned i = tid; i < n; i += kSortThreads) grec[i] = srec[i];
+    for (unsigned i = tid; i < n; i += kSortThreads) {
+        Rec x = srec[i];
+        x.y = (x.y & 0xffffffffull) | ((unsigned long long)sc[pad_idx(i)] << 32);
+        grec[i] = x;
+    }
 }
 
 // k_part_scan: exclusive scan of the part pixel totals (in place); ppix[n_parts] = N.
@@ -493,22 +485,33 @@ __device__ unsigned os_index(const Sorted &v, long long q, Hint &h)
     const unsigned b0 = __ldg(v.pbase + p);
     const unsigned ql = (unsigned)(q - (long long)b0);
     const unsigned ps = __ldg(v.pstart + p), pe = __ldg(v.pstart + p + 1);
+    // entries per rank inside this part (multiplicities are roughly even within a part)
+    const float scale = __fdividef((float)(pe - ps), (float)(__ldg(v.pbase + p + 1) - b0));
     unsigned idx;
     if (h.valid && h.p == p && h.i >= ps && h.i < pe) {
         idx = h.i;
-    } else {  // interpolate inside the part (multiplicities are roughly even within a part)
-        unsigned tot = __ldg(v.pbase + p + 1) - b0;
-        idx = ps + (unsigned)(((unsigned long long)ql * (pe - ps)) / tot);
+    } else {
+        idx = ps + (unsigned)((float)ql * scale);
         if (idx >= pe) idx = pe - 1;
     }
     h.p = p;
     h.valid = true;
 #pragma unroll 1
-    for (int s = 0; s < 8; ++s) {
-        if (cum_local(v, idx) <= ql) {
-            ++idx;  // stays < pe: ql < part total = cum_local(pe-1)
-        } else if (idx > ps && cum_local(v, idx - 1) > ql) {
-            --idx;
+    for (int s = 0; s < 8; ++s) {  // secant steps on the cumulative counts
+        const unsigned c = cum_local(v, idx);
+        if (c <= ql) {
+            unsigned step = (unsigned)((float)(ql + 1u - c) * scale);
+            idx += step ? step : 1u;
+            if (idx >= pe) idx = pe - 1;  // ql < part total = cum_local(pe-1)
+        } else if (idx > ps) {
+            const unsigned cp = cum_local(v, idx - 1);
+            if (cp <= ql) {
+                h.i = idx;
+                return idx;
+            }
+            unsigned step = (unsigned)((float)(cp - ql) * scale);
+            if (!step) step = 1u;
+            idx = (idx - ps > step) ? idx - step : ps;
         } else {
             h.i = idx;
             return idx;
@@ -525,6 +528,15 @@ __device__ unsigned os_index(const Sorted &v, long long q, Hint &h)
 
 __device__ __forceinline__ double os_value(const Sorted &v, long long q, Hint &h) { return key_at(v, os_index(v, q, h)); }
 
+// values at ranks q and q+1 with one search (q+1 < v.n)
+__device__ __forceinline__ void os_pair(const Sorted &v, long long q, Hint &h, double &v0, double &v1)
+{
+    unsigned idx = os_index(v, q, h);
+    v0 = key_at(v, idx);
+    long long g_end = (long long)__ldg(v.pbase + h.p) + (long long)cum_local(v, idx);  // first rank after idx
+    v1 = (q + 1 < g_end) ? v0 : key_at(v, idx + 1);
+}
+
 // np.interp(x, np.linspace(0,1,v.n), sorted(v)) for 0 <= x <= 1
 __device__ double interp_lin_os(double x, const Sorted &v, Hint &h)
 {
@@ -537,10 +549,44 @@ __device__ double interp_lin_os(double x, const Sorted &v, Hint &h)
     while (m > 0 && lin_of(v, m) > x) --m;
     if (m >= n - 1) return os_value(v, n - 1, h);
     double xm = lin_of(v, m);
-    double fm = os_value(v, m, h);
+    double fm, fm1;
+    os_pair(v, m, h, fm, fm1);
     if (xm == x) return fm;
-    double fm1 = os_value(v, m + 1, h);
     double slope = (fm1 - fm) / (lin_of(v, m + 1) - xm);
+    return slope * (x - xm) + fm;
+}
+
+// The neighbourhood of one target entry in rank space: ranks [g_lo, g_hi) hold `key`, rank g_hi
+// holds k_next, rank g_lo-1 holds k_prev.  The stretched-target evaluations of a-6 only ever
+// look at ranks next to the entry's own, so they resolve here without any search.
+struct TWin {
+    long long g_lo, g_hi;
+    double key, k_prev, k_next;
+};
+
+__device__ __forceinline__ double t_value(const Sorted &t, const TWin &w, long long m, Hint &ht)
+{
+    if (m >= w.g_lo && m < w.g_hi) return w.key;
+    if (m == w.g_hi) return w.k_next;
+    if (m == w.g_lo - 1) return w.k_prev;
+    return os_value(t, m, ht);
+}
+
+// t'[.] at x: np.interp(x, np.linspace(0,1,T), sorted target)
+__device__ double interp_target(double x, const Sorted &t, const TWin &w, Hint &ht)
+{
+    const long long n = t.n;
+    long long m = (long long)(x * (double)(n - 1));
+    if (m < 0) m = 0;
+    if (m > n - 1) m = n - 1;
+    while (m + 1 <= n - 1 && lin_of(t, m + 1) <= x) ++m;
+    while (m > 0 && lin_of(t, m) > x) --m;
+    if (m >= n - 1) return t_value(t, w, n - 1, ht);
+    double xm = lin_of(t, m);
+    double fm = t_value(t, w, m, ht);
+    if (xm == x) return fm;
+    double fm1 = t_value(t, w, m + 1, ht);
+    double slope = (fm1 - fm) / (lin_of(t, m + 1) - xm);
     return slope * (x - xm) + fm;
 }
 
@@ -549,10 +595,12 @@ __device__ double match_one(const Sorted &t, const Sorted &s, unsigned p, unsign
                             long long &j_out)
 {
     const double key = key_at(t, i);
-    const unsigned pe = __ldg(t.pstart + p + 1);
+    const unsigned ps = __ldg(t.pstart + p), pe = __ldg(t.pstart + p + 1);
     unsigned i2 = i;
     while (i2 + 1 < pe && key_at(t, i2 + 1) == key) ++i2;  // ties share the upper rank
-    const long long r = (long long)__ldg(t.pbase + p) + (long long)cum_local(t, i2) - 1;
+    const long long base = (long long)__ldg(t.pbase + p);
+    const long long g_hi = base + (long long)cum_local(t, i2);
+    const long long r = g_hi - 1;
     const long long T = t.n, S = s.n;
     double m;
     long long j;
@@ -563,23 +611,31 @@ __device__ double match_one(const Sorted &t, const Sorted &s, unsigned p, unsign
         j = r;
         m = interp_lin_os(lin_of(t, r), s, hs);
     } else {  // target stretched to S samples (LST:116-121): t'[k] = interp(lin(S,k), lin(T,.), t)
-        ht.p = p;
-        ht.i = i2;
-        ht.valid = true;
         // j = last k with t'[k] <= key; t'[j] and t'[j+1] are kept for the interpolation
         double tj = 0.0, tj1 = 0.0;
         bool have_j1 = false;
         if (T == 1) {
             j = S - 1;
         } else {
+            unsigned i1 = i;
+            while (i1 > ps && key_at(t, i1 - 1) == key) --i1;
+            TWin w;
+            w.key = key;
+            w.g_hi = g_hi;
+            w.g_lo = base + (i1 > ps ? (long long)cum_local(t, i1 - 1) : 0ll);
+            w.k_prev = i1 > 0 ? key_at(t, i1 - 1) : key;
+            w.k_next = i2 + 1 < t.d ? key_at(t, i2 + 1) : key;
+            ht.p = p;
+            ht.i = i2;
+            ht.valid = true;
             double xr = lin_of(t, r);
             long long k = (long long)(xr * (double)(S - 1));
             if (k < 0) k = 0;
             if (k > S - 1) k = S - 1;
-            double tk = interp_lin_os(lin_of(s, k), t, ht);
+            double tk = interp_target(lin_of(s, k), t, w, ht);
             if (tk <= key) {
                 while (k + 1 <= S - 1) {
-                    double tn = interp_lin_os(lin_of(s, k + 1), t, ht);
+                    double tn = interp_target(lin_of(s, k + 1), t, w, ht);
                     if (tn <= key) {
                         ++k;
                         tk = tn;
@@ -594,21 +650,22 @@ __device__ double match_one(const Sorted &t, const Sorted &s, unsigned p, unsign
                     tj1 = tk;
                     have_j1 = true;
                     --k;
-                    tk = interp_lin_os(lin_of(s, k), t, ht);
+                    tk = interp_target(lin_of(s, k), t, w, ht);
                 }
             }
             j = k;
             tj = tk;
+            if (j < S - 1 && tj != key && !have_j1) tj1 = interp_target(lin_of(s, j + 1), t, w, ht);
         }
         if (j >= S - 1) {
             m = os_value(s, S - 1, hs);
         } else {
-            double sj = os_value(s, j, hs);
+            double sj, sj1;
+            os_pair(s, j, hs, sj, sj1);
             if (tj == key) {
                 m = sj;
             } else {
-                if (!have_j1) tj1 = interp_lin_os(lin_of(s, j + 1), t, ht);
-                double slope = (os_value(s, j + 1, hs) - sj) / (tj1 - tj);
+                double slope = (sj1 - sj) / (tj1 - tj);
                 m = slope * (key - tj) + sj;
             }
         }
@@ -619,8 +676,10 @@ __device__ double match_one(const Sorted &t, const Sorted &s, unsigned p, unsign
 
 // pipeline flavour: jobs[2*slot] = target, jobs[2*slot+1] = source; one CTA per target part.
 // Writes the colour -> output-RGB LUT (a-7: inverse_transform, lab -> rgb, clip, truncate).
-__global__ void __launch_bounds__(256) k_match(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0, size_t lut_stride,
-                                               double *dbg_matched0, long long *dbg_j0, size_t dbg_stride)
+constexpr int kMatchThreads = 128;
+__global__ void __launch_bounds__(kMatchThreads) k_match(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0,
+                                                         size_t lut_stride, double *dbg_matched0, long long *dbg_j0,
+                                                         size_t dbg_stride)
 {
     const int slot = blockIdx.y;
     if (ctrl[slot].status != 0) return;
@@ -635,7 +694,11 @@ __global__ void __launch_bounds__(256) k_match(FrameCtrl *ctrl, const Job *jobs,
     const Pca pca = jt.rc->pca;
     unsigned *lut = lut0 + (size_t)slot * lut_stride;
     Hint ht{0, 0, false}, hs{0, 0, false};
-    for (unsigned i = ps + threadIdx.x; i < pe; i += blockDim.x) {
+    // every thread takes a contiguous run of entries: consecutive ranks -> the source position
+    // moves by a step or two per entry and the hinted search almost never has to search
+    const unsigned per = (pe - ps + kMatchThreads - 1) / kMatchThreads;
+    const unsigned i0 = ps + threadIdx.x * per, i1 = (i0 + per < pe) ? i0 + per : pe;
+    for (unsigned i = i0; i < i1; ++i) {
         long long j;
         double m = match_one(t, s, p, i, ht, hs, j);
         double lab[3];
@@ -650,7 +713,7 @@ __global__ void __launch_bounds__(256) k_match(FrameCtrl *ctrl, const Job *jobs,
 }
 
 // generic flavour (rct_match_cdf): jobs[0] = target, jobs[1] = source; payload = input index
-__global__ void __launch_bounds__(256) k_match_generic(const Job *jobs, double *matched, long long *jidx)
+__global__ void __launch_bounds__(kMatchThreads) k_match_generic(const Job *jobs, double *matched, long long *jidx)
 {
     const Job &jt = jobs[0], &js = jobs[1];
     const unsigned p = blockIdx.x;
@@ -658,7 +721,9 @@ __global__ void __launch_bounds__(256) k_match_generic(const Job *jobs, double *
     const Sorted t = sorted_of(jt), s = sorted_of(js);
     const unsigned ps = jt.pstart[p], pe = jt.pstart[p + 1];
     Hint ht{0, 0, false}, hs{0, 0, false};
-    for (unsigned i = ps + threadIdx.x; i < pe; i += blockDim.x) {
+    const unsigned per = (pe - ps + kMatchThreads - 1) / kMatchThreads;
+    const unsigned i0 = ps + threadIdx.x * per, i1 = (i0 + per < pe) ? i0 + per : pe;
+    for (unsigned i = i0; i < i1; ++i) {
         long long j;
         double m = match_one(t, s, p, i, ht, hs, j);
         unsigned pay = rec_pay(__ldg(t.rec + i));
