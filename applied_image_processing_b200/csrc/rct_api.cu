@@ -173,7 +173,9 @@ struct rct_plan {
     int status_frames_cap;
     uint8_t *stage;  // device staging of the host entry point
     size_t stage_bytes;
-    cudaStream_t own_stream;
+    cudaStream_t own_stream;            // compute stream of the host entry point
+    cudaStream_t h2d_stream, d2h_stream; // copy streams of the host entry point (overlap with compute)
+    cudaEvent_t ev_in[2], ev_comp[2], ev_out[2];
     // RCT_OPT_TIMING: five events per launch group (memset | k_hist | solve | k_apply)
     int timing;
     std::vector<cudaEvent_t> ev_busy, ev_free;
@@ -314,6 +316,13 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     }
     delete[] tab;
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->h2d_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->d2h_stream, cudaStreamNonBlocking);
+    for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+        e = cudaEventCreateWithFlags(&p->ev_in[b], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_comp[b], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_out[b], cudaEventDisableTiming);
+    }
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) {
         rct_plan_destroy(p);
@@ -328,6 +337,13 @@ int rct_plan_destroy(rct_plan *p)
     if (!p) return RCT_OK;
     cudaSetDevice(p->device);
     if (p->own_stream) cudaStreamDestroy(p->own_stream);
+    if (p->h2d_stream) cudaStreamDestroy(p->h2d_stream);
+    if (p->d2h_stream) cudaStreamDestroy(p->d2h_stream);
+    for (int b = 0; b < 2; ++b) {
+        if (p->ev_in[b]) cudaEventDestroy(p->ev_in[b]);
+        if (p->ev_comp[b]) cudaEventDestroy(p->ev_comp[b]);
+        if (p->ev_out[b]) cudaEventDestroy(p->ev_out[b]);
+    }
     for (cudaEvent_t e : p->ev_busy) cudaEventDestroy(e);
     for (cudaEvent_t e : p->ev_free) cudaEventDestroy(e);
     if (p->owns_ws && p->ws) cudaFree(p->ws);
@@ -546,8 +562,11 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
     CK(cudaSetDevice(p->device));
     const size_t npix = (size_t)p->H * (size_t)p->W, spix = (size_t)p->sh * (size_t)p->sw;
     const size_t cb = align_up(npix * 3), sb = align_up(spix * 3), mb = align_up(npix);
-    const size_t per_slot = cb + sb + mb + cb;
-    const size_t need = per_slot * (size_t)p->slots;
+    // Two staging sets: while group k computes, group k+1 is copied in and group k-1 is copied
+    // out (three streams, events between them).  Frames are contiguous on the host; device
+    // staging keeps aligned per-slot strides.
+    const size_t per_set = (cb + sb + mb + cb) * (size_t)p->slots;
+    const size_t need = 2 * per_set;
     if (p->stage_bytes < need) {
         if (p->stage) CK(cudaFree(p->stage));
         p->stage = nullptr;
@@ -557,22 +576,34 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
     }
     rc = ensure_status_frames(p, n_frames);
     if (rc) return rc;
-    cudaStream_t st = p->own_stream;
-    uint8_t *d_c = p->stage, *d_s = d_c + cb * p->slots, *d_m = d_s + sb * p->slots, *d_o = d_m + mb * p->slots;
-    for (int f0 = 0; f0 < n_frames; f0 += p->slots) {
+    cudaStream_t st = p->own_stream, sin = p->h2d_stream, sout = p->d2h_stream;
+    int k = 0;
+    for (int f0 = 0; f0 < n_frames; f0 += p->slots, ++k) {
+        const int b = k & 1;
         int ns = n_frames - f0 < p->slots ? n_frames - f0 : p->slots;
-        // frames are contiguous on the host; device staging keeps aligned per-slot strides
-        CK(cudaMemcpy2DAsync(d_c, cb, content_h + (size_t)f0 * npix * 3, npix * 3, npix * 3, ns, cudaMemcpyHostToDevice, st));
-        CK(cudaMemcpy2DAsync(d_s, sb, stylised_h + (size_t)f0 * spix * 3, spix * 3, spix * 3, ns, cudaMemcpyHostToDevice, st));
-        if (mask_h) CK(cudaMemcpy2DAsync(d_m, mb, mask_h + (size_t)f0 * npix, npix, npix, ns, cudaMemcpyHostToDevice, st));
-        FrameSet f{d_c, d_s, mask_h ? d_m : nullptr, d_o, cb, sb, mb, cb};
+        uint8_t *d_c = p->stage + per_set * b, *d_s = d_c + cb * p->slots, *d_m = d_s + sb * p->slots,
+                *d_o = d_m + mb * p->slots;
+        if (k >= 2) {  // set b was last used by group k-2
+            CK(cudaStreamWaitEvent(sin, p->ev_comp[b], 0));
+            CK(cudaStreamWaitEvent(sin, p->ev_out[b], 0));
+        }
+        CK(cudaMemcpy2DAsync(d_c, cb, content_h + (size_t)f0 * npix * 3, npix * 3, npix * 3, ns, cudaMemcpyHostToDevice, sin));
+        CK(cudaMemcpy2DAsync(d_s, sb, stylised_h + (size_t)f0 * spix * 3, spix * 3, spix * 3, ns, cudaMemcpyHostToDevice, sin));
+        if (mask_h) CK(cudaMemcpy2DAsync(d_m, mb, mask_h + (size_t)f0 * npix, npix, npix, ns, cudaMemcpyHostToDevice, sin));
         if (mode == RCT_MODE_LABEL)  // untouched pixels keep the caller's values
-            CK(cudaMemcpy2DAsync(d_o, cb, out_h + (size_t)f0 * npix * 3, npix * 3, npix * 3, ns, cudaMemcpyHostToDevice, st));
+            CK(cudaMemcpy2DAsync(d_o, cb, out_h + (size_t)f0 * npix * 3, npix * 3, npix * 3, ns, cudaMemcpyHostToDevice, sin));
+        CK(cudaEventRecord(p->ev_in[b], sin));
+        CK(cudaStreamWaitEvent(st, p->ev_in[b], 0));
+        FrameSet f{d_c, d_s, mask_h ? d_m : nullptr, d_o, cb, sb, mb, cb};
         if ((rc = phase_hist(p, f, ns, mode, label, 0, npix, st))) return rc;
         if ((rc = phase_solve(p, ns, st))) return rc;
         if ((rc = phase_apply(p, f, ns, mode, label, 0, npix, p->status_frames + f0, st))) return rc;
-        CK(cudaMemcpy2DAsync(out_h + (size_t)f0 * npix * 3, npix * 3, d_o, cb, npix * 3, ns, cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(p->ev_comp[b], st));
+        CK(cudaStreamWaitEvent(sout, p->ev_comp[b], 0));
+        CK(cudaMemcpy2DAsync(out_h + (size_t)f0 * npix * 3, npix * 3, d_o, cb, npix * 3, ns, cudaMemcpyDeviceToHost, sout));
+        CK(cudaEventRecord(p->ev_out[b], sout));
     }
+    CK(cudaStreamSynchronize(sout));
     int worst = 0;
     int *tmp = status_host ? status_host : new (std::nothrow) int[n_frames];
     if (!tmp) return fail(RCT_ERR_NOMEM, "out of host memory");

@@ -198,7 +198,9 @@ def _transfer(content, stylised, mask, mode, label=0, out=None, slots=None, quie
         stylised = np.ascontiguousarray(np.broadcast_to(stylised, (n,) + stylised.shape))
     if batched and mask is not None and mask.ndim != 3:
         mask = np.ascontiguousarray(np.broadcast_to(mask, (n,) + mask.shape))
-    plan = get_plan(dev, H, W, sh, sw, slots or min(n, 8))
+    # host path: groups of ~n/4 frames so that copy-in, compute and copy-out of successive
+    # groups overlap inside rct_transfer_host (two staging sets, three streams)
+    plan = get_plan(dev, H, W, sh, sw, slots or max(1, min(8, (n + 3) // 4)))
     if out is None:
         out = np.empty_like(content) if mode != MODE_LABEL else content.copy()
     status = np.zeros(n, np.int32)

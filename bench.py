@@ -42,19 +42,37 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--frames", type=int, default=8, help="4K pairs per step and per rank")
+    ap.add_argument("--workload", default="4k", choices=["4k", "1080p", "labels", "16k"],
+                    help="4k: BASELINE configs[1] (default, the quoted metric); 1080p: configs[2] frame batch; "
+                         "labels: configs[4] 8-label 1080p batch; 16k: configs[3] one image row-sharded over the ranks")
+    ap.add_argument("--frames", type=int, default=0, help="frames per step and per rank (0 = workload default)")
+    ap.add_argument("--slots", type=int, default=0, help="frames per launch group (0 = min(frames, 8))")
     ap.add_argument("--kind", default="U", choices=["U", "N"], help="synthetic image family (SURVEY 8d)")
-    ap.add_argument("--height", type=int, default=H4K)
-    ap.add_argument("--width", type=int, default=W4K)
+    ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--width", type=int, default=0)
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    dflt = {"4k": (H4K, W4K, 8), "1080p": (1080, 1920, 32), "labels": (1080, 1920, 16), "16k": (8640, 15360, 1)}[a.workload]
+    a.height = a.height or dflt[0]
+    a.width = a.width or dflt[1]
+    a.frames = a.frames or dflt[2]
+    a.slots = a.slots or min(a.frames, 8)
+    return a
 
 
 def workload_name(a):
+    if a.workload == "16k":
+        return (f"one {a.width}x{a.height} synthetic content/stylised pair, binary fg/bg ellipse mask (40% fg), image "
+                f"family {a.kind}, row-sharded over the ranks with an all-reduce of the colour histograms "
+                f"(BASELINE.json configs[3])")
+    if a.workload == "labels":
+        return (f"{a.width}x{a.height} synthetic frames with 8-label Voronoi masks, per-label exact transfer, image "
+                f"family {a.kind} (BASELINE.json configs[4], exact-rank mode); {a.frames} frames per step per GPU")
+    cfg = "configs[1]" if a.workload == "4k" else "configs[2]"
     return (f"{a.width}x{a.height} synthetic content/stylised pair, binary fg/bg ellipse mask (40% fg), "
-            f"image family {a.kind} (BASELINE.json configs[1]); {a.frames} distinct pairs per step per GPU")
+            f"image family {a.kind} (BASELINE.json {cfg}); {a.frames} distinct pairs per step per GPU")
 
 
 def make_frames(a, n, seed0):
@@ -66,7 +84,12 @@ def make_frames(a, n, seed0):
     for i in range(n):
         cs[i] = synth_image(a.height, a.width, seed0 + 2 * i, a.kind)
         ss[i] = synth_image(a.height, a.width, seed0 + 2 * i + 1, a.kind)
-        ms[i] = ellipse_mask(a.height, a.width, 0.4, seed0 + i)
+        if a.workload == "labels":
+            from tests.synth import voronoi_labels
+
+            ms[i] = voronoi_labels(a.height, a.width, 8, seed0 + i)
+        else:
+            ms[i] = ellipse_mask(a.height, a.width, 0.4, seed0 + i)
     return cs, ss, ms
 
 
@@ -78,7 +101,7 @@ def host_threads():
         return os.cpu_count() or 1
 
 
-def cpu_pass(frames, threads):
+def cpu_pass(frames, threads, labels=False):
     """Run every frame through the oracle, `threads` at a time (ctypes releases the GIL)."""
     from concurrent.futures import ThreadPoolExecutor
 
@@ -86,9 +109,18 @@ def cpu_pass(frames, threads):
 
     orc.lib()
     cs, ss, ms = frames
+
+    def one(i):
+        if labels:
+            out = cs[i].copy()
+            for lab in range(8):
+                orc.transfer(cs[i], ss[i], ms[i], mode=orc.MODE_LABEL, label=lab, out=out)
+            return 0
+        return orc.transfer(cs[i], ss[i], ms[i])[1]
+
     t0 = time.perf_counter()
     with ThreadPoolExecutor(max_workers=threads) as ex:
-        list(ex.map(lambda i: orc.transfer(cs[i], ss[i], ms[i])[1], range(cs.shape[0])))
+        list(ex.map(one, range(cs.shape[0])))
     return time.perf_counter() - t0
 
 
@@ -104,14 +136,20 @@ def run_reference_arm(a):
     if rank != 0:
         return  # rank 0 alone runs the CPU arm
     n, threads = cpu_sample_size(a)
+    full_h = a.height
+    if a.workload == "16k":  # one 16K image takes minutes on one core: time a 1/16 band of it per thread
+        a.height = a.height // 16
     frames = make_frames(a, n, 1000)
+    labels = a.workload == "labels"
     for _ in range(a.warmup):
-        cpu_pass(frames, threads)
-    times = [cpu_pass(frames, threads) for _ in range(a.steps)]
+        cpu_pass(frames, threads, labels)
+    times = [cpu_pass(frames, threads, labels) for _ in range(a.steps)]
     mp = n * a.height * a.width / 1e6
+    band_note = f" (each a {a.height}-row band of the {full_h}-row image)" if a.workload == "16k" else ""
+    a.height = full_h
     t = sum(times) / len(times)
     val = mp / t
-    sample = f"{n} frame(s) of the workload per step, {threads} thread(s), one frame per thread"
+    sample = f"{n} frame(s) of the workload per step{band_note}, {threads} thread(s), one frame per thread"
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak",
@@ -224,17 +262,27 @@ def run_gpu_arm(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    if a.workload == "16k":
+        return run_gpu_16k(a, torch, dist, world, rank, local, dev, barrier, max_over_ranks)
     n, H, W = a.frames, a.height, a.width
+    labels = a.workload == "labels"
     cs, ss, ms = make_frames(a, n, 1000 + 100 * rank)
     # pinned host copies (e2e leg) and device-resident copies (value leg)
     hc, hs, hm = (torch.from_numpy(x).pin_memory() for x in (cs, ss, ms))
     ho = torch.empty_like(hc).pin_memory()
     dc, ds, dm = hc.to(dev), hs.to(dev), hm.to(dev)
     do = torch.empty_like(dc)
-    plan = lst.get_plan(dev, H, W, H, W, slots=n)
+    plan = lst.get_plan(dev, H, W, H, W, slots=a.slots)
     st = torch.cuda.current_stream().cuda_stream
 
     def step():
+        if labels:  # configs[4]: every label is an independent exact transfer; untouched pixels keep the content
+            do.copy_(dc)
+            for lab in range(8):
+                _cabi.check(L.rct_transfer_async(plan.handle, dc.data_ptr(), H * W * 3, ds.data_ptr(), H * W * 3,
+                                                 dm.data_ptr(), H * W, do.data_ptr(), H * W * 3, n,
+                                                 _cabi.MODE_LABEL, lab, st))
+            return
         _cabi.check(L.rct_transfer_async(plan.handle, dc.data_ptr(), H * W * 3, ds.data_ptr(), H * W * 3,
                                          dm.data_ptr(), H * W, do.data_ptr(), H * W * 3, n, _cabi.MODE_MASK, 0, st))
 
@@ -270,11 +318,11 @@ def run_gpu_arm(a):
     kern = {}
     for name, key in (("k_hist", "hist"), ("k_apply", "apply")):
         ms_launch = phases[key + "_ms"] / groups
-        gb = ALG_BYTES_PER_PIXEL[key] * n * H * W / 1e9
+        gb = ALG_BYTES_PER_PIXEL[key] * min(a.slots, n) * H * W / 1e9
         kern[name] = {"ms_per_launch": ms_launch, "alg_bytes_per_pixel": ALG_BYTES_PER_PIXEL[key],
                       "achieved_GBps": gb / (ms_launch * 1e-3) if ms_launch > 0 else None}
     dom = max(kern, key=lambda k: kern[k]["ms_per_launch"])
-    phase_share = {k: phases[k + "_ms"] / groups / ms_step for k in ("memset", "hist", "solve", "apply")}
+    phase_share = {k: phases[k + "_ms"] / a.steps / ms_step for k in ("memset", "hist", "solve", "apply")}
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_GBps"], "peak": peak, "unit": "GB/s",
         "frac": kern[dom]["achieved_GBps"] / peak, "traffic": None, "peak_source": peak_src,
@@ -287,12 +335,19 @@ def run_gpu_arm(a):
     e2e = None
     if not a.no_e2e:
         hcn, hsn, hmn, hon = hc.numpy(), hs.numpy(), hm.numpy(), ho.numpy()
+
+        def api_call():
+            if labels:
+                hon[...] = aip.regional_color_transfer_labels(hcn, hsn, hmn, 8)
+            else:
+                aip.regional_color_transfer(hcn, hsn, hmn, out=hon)
+
         for _ in range(2):
-            aip.regional_color_transfer(hcn, hsn, hmn, out=hon)
+            api_call()
         barrier()
         t0 = time.perf_counter()
         for _ in range(a.steps):
-            aip.regional_color_transfer(hcn, hsn, hmn, out=hon)
+            api_call()
         torch.cuda.synchronize()
         t_e2e = max_over_ranks(time.perf_counter() - t0)
         barrier()
@@ -305,7 +360,9 @@ def run_gpu_arm(a):
     cpu = None
     if world == 1 and not a.no_cpu:
         nc, threads = cpu_sample_size(a)
-        t = cpu_pass((cs[:nc], ss[:nc], ms[:nc]), threads)
+        nc = min(nc, n)
+        threads = min(threads, nc)
+        t = cpu_pass((cs[:nc], ss[:nc], ms[:nc]), threads, labels)
         cpu = {"value": nc * H * W / 1e6 / t, "unit": UNIT, "cores": threads, "kind": "port",
                "sample": f"{nc} frame(s) of the step's batch, {threads} thread(s), one pass ({t:.1f} s)"}
 
@@ -314,9 +371,112 @@ def run_gpu_arm(a):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(a), "frames_per_step_per_gpu": n,
+            "config": {"workload": workload_name(a), "frames_per_step_per_gpu": n, "frames_per_launch_group": a.slots,
                        "l2": f"inputs larger than L2: {(dc.numel() + ds.numel() + dm.numel()) / 1e6:.0f} MB read per step",
                        "parallelism": f"frames sharded over {world} GPU(s), no collective"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_gpu_16k(a, torch, dist, world, rank, local, dev, barrier, max_over_ranks):
+    """BASELINE.json configs[3]: ONE image, rows sharded over the ranks; the only exchange is the
+    all-reduce (NCCL) of the two colour-cube histograms.  Strong scaling: total work is fixed."""
+    from applied_image_processing_b200 import _cabi, sharded
+    from tests.synth import ellipse_mask, synth_image
+
+    H, W = a.height, a.width
+    L = _cabi.lib()
+    c = synth_image(H, W, 2000, a.kind)
+    s = synth_image(H, W, 2001, a.kind)
+    m = ellipse_mask(H, W, 0.4, 2002)
+    tr = sharded.ShardedTransfer(H, W, H, W, dev)
+    r0, r1 = tr.row0, tr.row0 + tr.rows
+    hc, hs, hm = (torch.from_numpy(np.ascontiguousarray(x[r0:r1])).pin_memory() for x in (c, s, m))
+    del c, s, m
+    ho = torch.empty_like(hc).pin_memory()
+    dc, ds, dm = hc.to(dev), hs.to(dev), hm.to(dev)
+    do = torch.empty_like(dc)
+    for _ in range(max(a.warmup, 3)):
+        tr(dc, ds, dm, do)
+    barrier()
+    sampler = ClockSampler(local)
+    L.rct_launch_count(1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    acc = {"hist_ms": 0.0, "allreduce_ms": 0.0, "solve_ms": 0.0, "apply_ms": 0.0}
+    sampler.start()
+    e0.record()
+    for _ in range(a.steps):
+        tr(dc, ds, dm, do, timed=True)
+        for k, v in tr.phase_ms().items():  # syncs this step's last event: steps are serial anyway
+            acc[k] += v
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    launches = int(L.rct_launch_count(0))
+    ms_step = max_over_ranks(e0.elapsed_time(e1)) / a.steps
+    assert tr.status() == 0
+    mp_step = H * W / 1e6
+    value = mp_step / (ms_step * 1e-3)
+    phases = {k: max_over_ranks(v / a.steps) for k, v in acc.items()}
+    peak, peak_src = peaks()
+    npix_rank = (H + world - 1) // world * W
+    kern = {
+        "k_hist": {"ms_per_launch": phases["hist_ms"], "alg_bytes_per_pixel": 7.0,
+                   "achieved_GBps": 7.0 * npix_rank / 1e9 / (phases["hist_ms"] * 1e-3)},
+        "k_apply": {"ms_per_launch": phases["apply_ms"], "alg_bytes_per_pixel": 10.0,
+                    "achieved_GBps": 10.0 * npix_rank / 1e9 / (phases["apply_ms"] * 1e-3)},
+    }
+    dom = max(kern, key=lambda k: kern[k]["ms_per_launch"])
+    hist_bytes = int(L.rct_plan_hist_bytes(tr.plan.handle))
+    roofline = {
+        "bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_GBps"], "peak": peak, "unit": "GB/s",
+        "frac": kern[dom]["achieved_GBps"] / peak, "traffic": None, "peak_source": peak_src, "kernels": kern,
+        "phase_ms_max_over_ranks": phases, "allreduce_bytes": hist_bytes,
+        "allreduce_busbw_GBps": (2.0 * (world - 1) / world * hist_bytes / 1e9 / (phases["allreduce_ms"] * 1e-3)
+                                 if world > 1 and phases["allreduce_ms"] > 0 else None),
+        "pipeline_achieved_GBps_all_gpus": 10.0 * H * W / 1e9 / (ms_step * 1e-3),
+    }
+    e2e = None
+    if not a.no_e2e:
+        def api_call():
+            dc.copy_(hc, non_blocking=True)
+            ds.copy_(hs, non_blocking=True)
+            dm.copy_(hm, non_blocking=True)
+            tr(dc, ds, dm, do)
+            ho.copy_(do, non_blocking=True)
+            torch.cuda.synchronize()
+
+        api_call()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(a.steps):
+            api_call()
+        t_e2e = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        e2e = {"value": mp_step * a.steps / t_e2e, "unit": UNIT,
+               "h2d_bytes_per_step": int(hc.numel() + hs.numel() + hm.numel()) * world,
+               "d2h_bytes_per_step": int(ho.numel()) * world, "ms_per_step": 1e3 * t_e2e / a.steps}
+    cpu = None
+    if world == 1 and not a.no_cpu:
+        hb = H // 16
+        threads = max(1, min(host_threads(), 8))
+        cs = np.stack([hc.numpy()[i * hb:(i + 1) * hb] for i in range(threads)])
+        ss = np.stack([hs.numpy()[i * hb:(i + 1) * hb] for i in range(threads)])
+        ms_ = np.stack([hm.numpy()[i * hb:(i + 1) * hb] for i in range(threads)])
+        t = cpu_pass((cs, ss, ms_), threads)
+        cpu = {"value": threads * hb * W / 1e6 / t, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": f"{threads} bands of {hb} rows of the image, one per thread, one pass ({t:.1f} s)"}
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a), "rows_per_rank": tr.rows,
+                       "l2": f"inputs larger than L2: {(dc.numel() + ds.numel() + dm.numel()) / 1e6:.0f} MB read per rank per step",
+                       "parallelism": f"rows sharded over {world} GPU(s); one NCCL all-reduce of {hist_bytes >> 20} MiB per step"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
         }
         print(json.dumps(line), flush=True)
