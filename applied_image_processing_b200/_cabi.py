@@ -15,6 +15,8 @@ FLAG_DEBUG = 1
 OPT_AGGREGATE = 0
 OPT_TIMING = 1
 OPT_PART_CAP = 2
+OPT_FRONTEND = 3
+OPT_APPLY = 4
 
 _lib = None
 _lock = threading.Lock()

@@ -98,7 +98,8 @@ struct Layout {
     size_t off_ctrl, off_jobs, off_status, off_xtab, off_ytab;
     size_t off_hist, hist_stride_u32, off_lut, lut_stride_u32;
     size_t off_region, region_bytes;  // [slots][2] blocks of per-region arrays
-    size_t r_col, r_cnt, r_keyA, r_recP, r_pof, r_pstart, r_ppix;
+    size_t r_col, r_cnt, r_keyA, r_recP, r_pof, r_pstart, r_ppix, r_items;
+    size_t off_cmap, cmap_stride_u32;  // [slots] chunk maps of k_front_hist
     size_t off_zero, zero_bytes, z_fcnt, z_pfill;  // [slots][2] blocks zeroed before every sort
     size_t off_dbg_m, off_dbg_j, dbg_stride;
     size_t total;
@@ -137,8 +138,13 @@ Layout make_layout(int H, int W, int slots, unsigned flags)
     L.r_pof = r; r = align_up(r + 2 * (size_t)kFineMax);
     L.r_pstart = r; r = align_up(r + 4 * (L.maxparts + 1));
     L.r_ppix = r; r = align_up(r + 4 * (L.maxparts + 1));
+    // front-end items (4 B per region pixel) die before the sort records are born: share the memory
+    if (4 * npix <= 16 * L.cap) L.r_items = L.r_recP;
+    else { L.r_items = r; r = align_up(r + 4 * npix); }
     L.region_bytes = r;
     L.off_region = o; o += L.region_bytes * 2 * slots;
+    L.cmap_stride_u32 = 2 * (size_t)kNB + 2 * npix / kChunk + 2;
+    L.off_cmap = o; o = align_up(o + 4 * L.cmap_stride_u32 * slots);
     zero_zone(L.maxparts, L.z_fcnt, L.z_pfill, L.zero_bytes);
     L.off_zero = o; o += L.zero_bytes * 2 * slots;
     L.dbg_stride = L.cap;
@@ -167,6 +173,9 @@ struct rct_plan {
     long long *dbg_j;
     int sm;
     int aggregate;
+    int apply_tma;    // RCT_OPT_APPLY: 1 = bulk-async staged apply kernel where the geometry allows
+    int front;        // RCT_OPT_FRONTEND: 1 = colour-partitioned shared-memory histograms, 0 = colour cube
+    bool cube_dirty;  // the partition front end needs (and leaves) an all-zero colour cube
     unsigned part_cap;  // entries a part may have for the shared-memory sort (RCT_OPT_PART_CAP)
     // lazily allocated helpers
     int *status_frames;
@@ -247,6 +256,9 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     p->L = make_layout(H, W, slots, flags);
     p->sm = g_sm_count[device] > 0 ? g_sm_count[device] : 148;
     p->aggregate = 0;
+    p->front = 1;
+    p->apply_tma = 1;
+    p->cube_dirty = true;
     p->part_cap = kPartCap;
     if (workspace) {
         if (workspace_bytes < p->L.total) {
@@ -358,6 +370,8 @@ int rct_plan_set_option(rct_plan *p, int option, int value)
     if (!p) return fail(RCT_ERR_ARG, "null plan");
     if (option == RCT_OPT_AGGREGATE) p->aggregate = value;
     else if (option == RCT_OPT_TIMING) p->timing = value;
+    else if (option == RCT_OPT_FRONTEND) p->front = value ? 1 : 0;
+    else if (option == RCT_OPT_APPLY) p->apply_tma = value ? 1 : 0;
     else if (option == RCT_OPT_PART_CAP) p->part_cap = (value > 0 && value <= kPartCap) ? (unsigned)value : (unsigned)kPartCap;
     else return fail(RCT_ERR_ARG, "unknown option %d", option);
     return RCT_OK;
@@ -431,11 +445,74 @@ int phase_hist(rct_plan *p, const FrameSet &f, int nslots, int mode, int label, 
     if ((rc = mark(p, st))) return rc;
     CK(cudaMemsetAsync(p->ctrl, 0, sizeof(FrameCtrl) * nslots, st));
     CK(cudaMemsetAsync(p->hist, 0, 4 * p->L.hist_stride_u32 * nslots, st));
+    p->cube_dirty = true;
     if ((rc = mark(p, st))) return rc;
     PixArgs a = pix_args(p, f, mode, label, p_begin, p_end, nullptr);
     dim3 grid(pix_blocks(p, p_end - p_begin, nslots), nslots);
     if (p->resample) LAUNCH(k_hist<true>, grid, 256, st, a);
     else LAUNCH(k_hist<false>, grid, 256, st, a);
+    return mark(p, st);
+}
+
+FrontArgs front_args(rct_plan *p)
+{
+    FrontArgs f{};
+    const Layout &L = p->L;
+    f.items0 = (unsigned *)(p->ws + L.off_region + L.r_items);
+    f.items_stride = L.region_bytes / 4;
+    f.cmap0 = (unsigned *)(p->ws + L.off_cmap);
+    f.cmap_stride = L.cmap_stride_u32;
+    f.cmap_cap = (unsigned)L.cmap_stride_u32;
+    f.items_cap = (unsigned)((size_t)p->H * (size_t)p->W);
+    return f;
+}
+
+// colour-partitioned front end: pixels -> (colour, count) lists, no colour cube (rct_front.cuh)
+int phase_front(rct_plan *p, const FrameSet &f, int nslots, int mode, int label, size_t p_begin, size_t p_end,
+                cudaStream_t st)
+{
+    int rc;
+    if ((rc = mark(p, st))) return rc;
+    CK(cudaMemsetAsync(p->ctrl, 0, sizeof(FrameCtrl) * nslots, st));
+    if (p->cube_dirty) {  // split buckets merge through windows of the cube and leave it zero again
+        CK(cudaMemsetAsync(p->hist, 0, 4 * p->L.hist_stride_u32 * p->slots, st));
+        p->cube_dirty = false;
+    }
+    if ((rc = mark(p, st))) return rc;
+    static thread_local int attr_dev = -1;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (attr_dev != dev) {
+        CK(cudaFuncSetAttribute(k_front_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemFrontHist));
+        attr_dev = dev;
+    }
+    PixArgs a = pix_args(p, f, mode, label, p_begin, p_end, nullptr);
+    FrontArgs fa = front_args(p);
+    const size_t npix = p_end - p_begin;
+    dim3 gcount(pix_blocks(p, npix, nslots), nslots);
+    size_t ntiles = ((npix + 15) / 16 + kPartThreads - 1) / kPartThreads;
+    size_t maxb = ((size_t)p->sm * 4 + nslots - 1) / nslots;  // two waves of 2 CTAs per SM over all slots
+    if (ntiles < 1) ntiles = 1;
+    dim3 gpart((unsigned)(ntiles < maxb ? ntiles : maxb), nslots);
+    const bool two = mode != RCT_MODE_MASK;
+#define FRONT_DISPATCH(K, grid, threads, ...)                                      \
+    do {                                                                           \
+        if (p->resample) {                                                         \
+            if (two) LAUNCH((K<true, true>), grid, threads, st, __VA_ARGS__);      \
+            else LAUNCH((K<true, false>), grid, threads, st, __VA_ARGS__);         \
+        } else {                                                                   \
+            if (two) LAUNCH((K<false, true>), grid, threads, st, __VA_ARGS__);     \
+            else LAUNCH((K<false, false>), grid, threads, st, __VA_ARGS__);        \
+        }                                                                          \
+    } while (0)
+    FRONT_DISPATCH(k_front_count, gcount, 256, a);
+    LAUNCH(k_front_scan, dim3(nslots), kNB, st, p->ctrl, fa);
+    FRONT_DISPATCH(k_front_part, gpart, kPartThreads, a, fa);
+#undef FRONT_DISPATCH
+    k_front_hist<<<dim3((unsigned)p->L.cmap_stride_u32, nslots), kFrontHistThreads, kSmemFrontHist, st>>>(
+        p->ctrl, p->jobs, fa, p->hist, p->L.hist_stride_u32);
+    ++t_launches;
+    CK(cudaGetLastError());
     return mark(p, st);
 }
 
@@ -472,11 +549,12 @@ int sort_jobs(const Job *jobs, int njobs, unsigned eblocks, size_t cap, size_t m
     return RCT_OK;
 }
 
-int phase_solve(rct_plan *p, int nslots, cudaStream_t st)
+int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)
 {
     unsigned eb = entry_blocks(p, nslots);
     CK(cudaMemsetAsync(p->ws + p->L.off_zero, 0, p->L.zero_bytes * 2 * (size_t)nslots, st));
-    LAUNCH(k_compact, dim3(kCube / 1024, 2, nslots), 256, st, p->hist, p->L.hist_stride_u32, p->ctrl, p->jobs);
+    if (from_cube)
+        LAUNCH(k_compact, dim3(kCube / 1024, 2, nslots), 256, st, p->hist, p->L.hist_stride_u32, p->ctrl, p->jobs);
     LAUNCH(k_lab_moments, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs);
     LAUNCH(k_pca, dim3((nslots + 31) / 32), 32, st, p->ctrl, nslots);
     LAUNCH(k_keys, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs);
@@ -491,6 +569,33 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
                 int *status_out, cudaStream_t st)
 {
     PixArgs a = pix_args(p, f, mode, label, p_begin, p_end, status_out);
+    // bulk-async staged pipeline (rct_apply.cuh) when the geometry allows 16-byte bulk copies
+    uintptr_t al = (uintptr_t)f.content | (uintptr_t)f.sty | (uintptr_t)f.mask | (uintptr_t)f.out | (uintptr_t)p_begin;
+    if (nslots > 1) al |= f.cs | f.ss | f.ms | f.os;
+    const size_t npix16 = (p_end - p_begin) & ~(size_t)15;
+    if (p->apply_tma && mode == RCT_MODE_MASK && !p->resample && f.mask && (al & 15) == 0 && npix16 > 0) {
+        static thread_local int attr_dev = -1;
+        int dev = 0;
+        CK(cudaGetDevice(&dev));
+        if (attr_dev != dev) {
+            CK(cudaFuncSetAttribute(k_apply_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ApSmem)));
+            attr_dev = dev;
+        }
+        PixArgs b = a;
+        b.p_end = p_begin + npix16;
+        const size_t tiles = (npix16 + kApTile - 1) / kApTile, total = tiles * (size_t)nslots;
+        const size_t maxb = (size_t)p->sm * 2;
+        k_apply_tma<<<(unsigned)(total < maxb ? total : maxb), kApThreads, sizeof(ApSmem), st>>>(b, (unsigned)tiles,
+                                                                                                   (unsigned)nslots);
+        ++t_launches;
+        CK(cudaGetLastError());
+        if (npix16 < p_end - p_begin) {  // ragged tail of < 16 pixels per frame
+            PixArgs c = a;
+            c.p_begin = p_begin + npix16;
+            LAUNCH(k_apply<false>, dim3(1, nslots), 256, st, c);
+        }
+        return mark(p, st);
+    }
     dim3 grid(pix_blocks(p, p_end - p_begin, nslots), nslots);
     if (p->resample) LAUNCH(k_apply<true>, grid, 256, st, a);
     else LAUNCH(k_apply<false>, grid, 256, st, a);
@@ -536,8 +641,9 @@ int rct_transfer_async(rct_plan *p, const uint8_t *content, size_t content_strid
         FrameSet f{content + (size_t)f0 * content_stride, stylised + (size_t)f0 * stylised_stride,
                    mask ? mask + (size_t)f0 * mask_stride : nullptr, out + (size_t)f0 * out_stride,
                    content_stride, stylised_stride, mask_stride, out_stride};
-        if ((rc = phase_hist(p, f, ns, mode, label, 0, npix, st))) return rc;
-        if ((rc = phase_solve(p, ns, st))) return rc;
+        if ((rc = p->front ? phase_front(p, f, ns, mode, label, 0, npix, st)
+                           : phase_hist(p, f, ns, mode, label, 0, npix, st))) return rc;
+        if ((rc = phase_solve(p, ns, st, !p->front))) return rc;
         if ((rc = phase_apply(p, f, ns, mode, label, 0, npix, p->status_frames + f0, st))) return rc;
     }
     return RCT_OK;
@@ -595,8 +701,9 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
         CK(cudaEventRecord(p->ev_in[b], sin));
         CK(cudaStreamWaitEvent(st, p->ev_in[b], 0));
         FrameSet f{d_c, d_s, mask_h ? d_m : nullptr, d_o, cb, sb, mb, cb};
-        if ((rc = phase_hist(p, f, ns, mode, label, 0, npix, st))) return rc;
-        if ((rc = phase_solve(p, ns, st))) return rc;
+        if ((rc = p->front ? phase_front(p, f, ns, mode, label, 0, npix, st)
+                           : phase_hist(p, f, ns, mode, label, 0, npix, st))) return rc;
+        if ((rc = phase_solve(p, ns, st, !p->front))) return rc;
         if ((rc = phase_apply(p, f, ns, mode, label, 0, npix, p->status_frames + f0, st))) return rc;
         CK(cudaEventRecord(p->ev_comp[b], st));
         CK(cudaStreamWaitEvent(sout, p->ev_comp[b], 0));
@@ -633,7 +740,7 @@ size_t rct_plan_hist_bytes(rct_plan *p) { return p ? 4 * p->L.hist_stride_u32 : 
 int rct_shard_solve_async(rct_plan *p, void *stream)
 {
     if (!p) return fail(RCT_ERR_ARG, "null plan");
-    return phase_solve(p, 1, (cudaStream_t)stream);
+    return phase_solve(p, 1, (cudaStream_t)stream, true);
 }
 int rct_shard_apply_async(rct_plan *p, const uint8_t *content, const uint8_t *stylised, const uint8_t *mask,
                           uint8_t *out, int mode, int label, int row0, int rows, void *stream)
@@ -837,9 +944,15 @@ int rct_plan_debug_hist(rct_plan *p, int slot, uint32_t *ht, uint32_t *hs)
     if (!p || slot < 0 || slot >= p->slots) return fail(RCT_ERR_ARG, "bad slot");
     CK(cudaSetDevice(p->device));
     CK(cudaDeviceSynchronize());
-    const unsigned *h = p->hist + (size_t)slot * p->L.hist_stride_u32;
+    unsigned *h = p->hist + (size_t)slot * p->L.hist_stride_u32;
+    if (!p->cube_dirty) {  // partition front end: the cube is all zero; rebuild it from the colour lists
+        LAUNCH(k_list_to_cube, 1024, 256, 0, p->ctrl, p->jobs, slot, 0, h);
+        LAUNCH(k_list_to_cube, 1024, 256, 0, p->ctrl, p->jobs, slot, 1, h + kCube);
+        CK(cudaDeviceSynchronize());
+    }
     if (ht) CK(cudaMemcpy(ht, h, 4 * (size_t)kCube, cudaMemcpyDeviceToHost));
     if (hs) CK(cudaMemcpy(hs, h + kCube, 4 * (size_t)kCube, cudaMemcpyDeviceToHost));
+    if (!p->cube_dirty) CK(cudaMemset(h, 0, 4 * p->L.hist_stride_u32));
     return RCT_OK;
 }
 

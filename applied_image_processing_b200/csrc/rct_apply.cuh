@@ -1,0 +1,194 @@
+// rct_apply.cuh -- the fused apply pass (a-7..a-9) as a bulk-async (TMA 1-D) staged pipeline.
+// Included by rct_kernels.cuh inside namespace rct (needs PixArgs, FrameCtrl).
+//
+// k_apply (rct_kernels.cuh) keeps a thread's 112 input bytes in registers across two dependent
+// round trips (pixels, then LUT gathers) and is latency-bound at 1/3 occupancy.  Here one elected
+// thread streams content / stylised / mask tiles into a 3-stage shared-memory ring with
+// cp.async.bulk (completion on an mbarrier), all threads resolve their 16 pixels against the
+// colour LUT, and the output tile leaves through a 2-stage ring with cp.async.bulk stores:
+// loads of tiles i+1, i+2 and the store of tile i-1 are in flight while tile i is looked up.
+// Tiles are walked slot-major by the whole grid, so one frame's LUT is hot in L2 at a time.
+//
+// MASK mode, no resample, 16-byte aligned frames only (the reference's own geometry); anything
+// else -- and the last npix % 16 pixels -- goes through k_apply.
+#pragma once
+
+constexpr int kApThreads = 256;
+constexpr int kApTile = kApThreads * 16;  // pixels per tile
+constexpr int kApStages = 3;
+constexpr int kApOut = 2;
+
+struct ApSmem {
+    alignas(128) uint8_t c[kApStages][kApTile * 3];
+    alignas(128) uint8_t s[kApStages][kApTile * 3];
+    alignas(128) uint8_t m[kApStages][kApTile];
+    alignas(128) uint8_t o[kApOut][kApTile * 3];
+    alignas(8) unsigned long long full[kApStages];
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, unsigned bytes, unsigned long long *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void *dst_gmem, const void *src_smem, unsigned bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read()
+{
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait()
+{
+    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
+// 12 little-endian words = 16 RGB pixels <-> 16 packed colours r | g<<8 | b<<16
+__device__ __forceinline__ void unpack16(const uint32_t w[12], uint32_t c[16])
+{
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        c[4 * q + 0] = w[3 * q] & 0xffffffu;
+        c[4 * q + 1] = __funnelshift_r(w[3 * q], w[3 * q + 1], 24) & 0xffffffu;
+        c[4 * q + 2] = __funnelshift_r(w[3 * q + 1], w[3 * q + 2], 16) & 0xffffffu;
+        c[4 * q + 3] = w[3 * q + 2] >> 8;
+    }
+}
+__device__ __forceinline__ void pack16(const uint32_t c[16], uint32_t w[12])
+{
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        w[3 * q + 0] = c[4 * q] | (c[4 * q + 1] << 24);
+        w[3 * q + 1] = (c[4 * q + 1] >> 8) | (c[4 * q + 2] << 16);
+        w[3 * q + 2] = (c[4 * q + 2] >> 16) | (c[4 * q + 3] << 8);
+    }
+}
+
+// a.p_begin and (a.p_end - a.p_begin) are multiples of 16; all frame bases 16-byte aligned.
+__global__ void __launch_bounds__(kApThreads, 2) k_apply_tma(PixArgs a, unsigned tiles_per_frame, unsigned nslots)
+{
+    extern __shared__ __align__(128) uint8_t ap_smem_raw[];
+    ApSmem &S = *reinterpret_cast<ApSmem *>(ap_smem_raw);
+    const unsigned tid = threadIdx.x;
+    const unsigned total = tiles_per_frame * nslots;
+    if (a.status_out && blockIdx.x == 0)
+        for (unsigned q = tid; q < nslots; q += kApThreads) a.status_out[q] = a.ctrl[q].status;
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < kApStages; ++s) mbar_init(&S.full[s], 1u);
+        fence_mbar_init();
+        fence_proxy_async();
+    }
+    __syncthreads();
+    const unsigned G = gridDim.x;
+    const unsigned cnt = blockIdx.x < total ? (total - blockIdx.x + G - 1) / G : 0u;
+
+    auto tile_geom = [&](unsigned i, unsigned &slot, size_t &p0, unsigned &n) {
+        const unsigned T = blockIdx.x + i * G;
+        slot = T / tiles_per_frame;
+        const unsigned t = T - slot * tiles_per_frame;
+        p0 = a.p_begin + (size_t)t * kApTile;
+        const size_t left = a.p_end - p0;
+        n = left < (size_t)kApTile ? (unsigned)left : (unsigned)kApTile;
+    };
+    auto issue = [&](unsigned i) {
+        unsigned slot, n;
+        size_t p0;
+        tile_geom(i, slot, p0, n);
+        const unsigned st = i % kApStages;
+        mbar_expect_tx(&S.full[st], 7u * n);
+        bulk_g2s(S.c[st], a.content + (size_t)slot * a.content_stride + 3 * p0, 3u * n, &S.full[st]);
+        bulk_g2s(S.s[st], a.sty + (size_t)slot * a.sty_stride + 3 * p0, 3u * n, &S.full[st]);
+        bulk_g2s(S.m[st], a.mask + (size_t)slot * a.mask_stride + p0, n, &S.full[st]);
+    };
+
+    if (tid == 0) {
+        for (unsigned i = 0; i < (unsigned)(kApStages - 1) && i < cnt; ++i) issue(i);
+    }
+    for (unsigned i = 0; i < cnt; ++i) {
+        const unsigned st = i % kApStages, par = (i / kApStages) & 1u, ob = i % kApOut;
+        if (tid == 0) {
+            if (i + kApStages - 1 < cnt) issue(i + kApStages - 1);  // refills the stage consumed in iteration i-1
+            bulk_wait_read<kApOut - 1>();                           // the store that last used o[ob] has read it
+        }
+        unsigned slot, n;
+        size_t p0;
+        tile_geom(i, slot, p0, n);
+        mbar_wait(&S.full[st], par);
+        const bool active = tid * 16u < n;
+        uint32_t wc[12], ws[12], wm[4];
+        if (active) {
+            const uint4 *qc = reinterpret_cast<const uint4 *>(S.c[st] + 48u * tid);
+            const uint4 *qs = reinterpret_cast<const uint4 *>(S.s[st] + 48u * tid);
+            const uint4 x0 = qc[0], x1 = qc[1], x2 = qc[2], y0 = qs[0], y1 = qs[1], y2 = qs[2];
+            const uint4 z = *reinterpret_cast<const uint4 *>(S.m[st] + 16u * tid);
+            wc[0] = x0.x; wc[1] = x0.y; wc[2] = x0.z; wc[3] = x0.w; wc[4] = x1.x; wc[5] = x1.y; wc[6] = x1.z; wc[7] = x1.w;
+            wc[8] = x2.x; wc[9] = x2.y; wc[10] = x2.z; wc[11] = x2.w;
+            ws[0] = y0.x; ws[1] = y0.y; ws[2] = y0.z; ws[3] = y0.w; ws[4] = y1.x; ws[5] = y1.y; ws[6] = y1.z; ws[7] = y1.w;
+            ws[8] = y2.x; ws[9] = y2.y; ws[10] = y2.z; ws[11] = y2.w;
+            wm[0] = z.x; wm[1] = z.y; wm[2] = z.z; wm[3] = z.w;
+        }
+        __syncthreads();  // stage st is free for the producer; o[ob] is free for the writers
+        if (active) {
+            const unsigned *lut = a.lut + (size_t)slot * a.lut_stride;
+            const int status = a.ctrl[slot].status;
+            uint32_t c[16], s[16], o[16];
+            unpack16(wc, c);
+            unpack16(ws, s);
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const uint32_t mk = (wm[k >> 2] >> (8 * (k & 3))) & 255u;
+                uint32_t v;
+                if (mk == 0u) v = (c[k] != 0u && status == 0) ? __ldg(lut + c[k]) : c[k];  // c == 0 stays black
+                else v = s[k];
+                o[k] = v;
+            }
+            uint32_t wo[12];
+            pack16(o, wo);
+            uint4 *qo = reinterpret_cast<uint4 *>(S.o[ob] + 48u * tid);
+            qo[0] = make_uint4(wo[0], wo[1], wo[2], wo[3]);
+            qo[1] = make_uint4(wo[4], wo[5], wo[6], wo[7]);
+            qo[2] = make_uint4(wo[8], wo[9], wo[10], wo[11]);
+        }
+        fence_proxy_async();
+        __syncthreads();
+        if (tid == 0) {
+            bulk_s2g(a.out + (size_t)slot * a.out_stride + 3 * p0, S.o[ob], 3u * n);
+            bulk_commit();
+        }
+    }
+    if (tid == 0) bulk_wait<0>();
+}

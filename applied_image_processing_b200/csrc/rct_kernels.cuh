@@ -3,8 +3,10 @@
 // Pipeline (one launch group = up to `slots` frames, blockIdx.z = slot, blockIdx.y = region
 // where a kernel works per region; region 0 = target/foreground, 1 = source/background):
 //
-//   k_hist          pixels -> two 2^24-bin colour-cube histograms        (a-1..a-3)
-//   k_compact       cube   -> list of distinct colours + counts
+//   k_front_*       pixels -> list of distinct colours + counts per region (a-1..a-3), by colour
+//                   partition + shared-memory histograms (rct_front.cuh; the default front end)
+//   k_hist          pixels -> two 2^24-bin colour-cube histograms        (row-sharded path: the
+//   k_compact       cube   -> list of distinct colours + counts           cubes are what is all-reduced)
 //   k_lab_moments   list   -> exact integer moments, lab bounding box    (a-4, a-5)
 //   k_pca           moments-> mean_, components_[0], key range           (a-5)
 //   k_keys          list   -> float64 projection keys + coarse key histogram
@@ -46,10 +48,26 @@ struct RegionCtrl {
     unsigned int fine_base[kCoarse + 1];
 };
 
+// colour-partitioned front end (rct_front.cuh): bucket = colour >> kBucketShift
+constexpr int kBucketShift = 14;
+constexpr int kBucketBins = 1 << kBucketShift;  // colours per bucket = bins of the shared-memory histogram
+constexpr int kNB = 1024;                       // buckets per region
+constexpr unsigned kChunk = 65536;              // items one CTA of k_front_hist accumulates
+
+struct FrontCtrl {
+    unsigned bcnt[2 * kNB];      // items per (region, bucket)
+    unsigned bticket[2 * kNB];   // chunk CTAs done per split bucket
+    unsigned bstart[2][kNB + 1]; // exclusive offsets inside the region's item array
+    unsigned bcur[2 * kNB];      // write cursors of k_front_part
+    unsigned nchunks;            // CTAs of k_front_hist with work
+    unsigned pad_[3];
+};
+
 struct FrameCtrl {
     RegionCtrl r[2];
     int status;
     int pad_[3];
+    FrontCtrl front;
 };
 
 // One sort job = one region of one slot (or one array of the generic match_cdf call).
@@ -624,6 +642,8 @@ __global__ void __launch_bounds__(256) k_coarse_hist(const Job *jobs)
     }
 }
 
+#include "rct_front.cuh"
+#include "rct_apply.cuh"
 #include "rct_sort.cuh"
 
 // ------------------------------------------------------------------------------------------

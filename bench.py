@@ -53,6 +53,10 @@ def parse_args():
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--front", type=int, default=1, choices=[0, 1],
+                    help="1: colour-partition front end (default); 0: colour-cube histograms (A/B runs)")
+    ap.add_argument("--apply", type=int, default=1, choices=[0, 1],
+                    help="1: bulk-async staged apply kernel (default); 0: register-staged k_apply (A/B runs)")
     a = ap.parse_args()
     dflt = {"4k": (H4K, W4K, 8), "1080p": (1080, 1920, 32), "labels": (1080, 1920, 16), "16k": (8640, 15360, 1)}[a.workload]
     a.height = a.height or dflt[0]
@@ -273,6 +277,8 @@ def run_gpu_arm(a):
     dc, ds, dm = hc.to(dev), hs.to(dev), hm.to(dev)
     do = torch.empty_like(dc)
     plan = lst.get_plan(dev, H, W, H, W, slots=a.slots)
+    plan.set_option(_cabi.OPT_FRONTEND, a.front)
+    plan.set_option(_cabi.OPT_APPLY, a.apply)
     st = torch.cuda.current_stream().cuda_stream
 
     def step():
@@ -316,7 +322,9 @@ def run_gpu_arm(a):
     peak, peak_src = peaks()
     groups = max(1, phases["groups"])
     kern = {}
-    for name, key in (("k_hist", "hist"), ("k_apply", "apply")):
+    front_name = "k_front_count+scan+part+hist" if a.front else "k_hist"
+    apply_name = "k_apply_tma" if (a.apply and not labels) else "k_apply"
+    for name, key in ((front_name, "hist"), (apply_name, "apply")):
         ms_launch = phases[key + "_ms"] / groups
         gb = ALG_BYTES_PER_PIXEL[key] * min(a.slots, n) * H * W / 1e9
         kern[name] = {"ms_per_launch": ms_launch, "alg_bytes_per_pixel": ALG_BYTES_PER_PIXEL[key],

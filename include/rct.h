@@ -84,6 +84,13 @@ int rct_plan_destroy(rct_plan *plan);
 /* RCT_OPT_PART_CAP (1..4096): largest sort part handled in shared memory; lowering it forces the
  * global-memory fallback of the exact sort (tests only) */
 #define RCT_OPT_PART_CAP 2
+/* RCT_OPT_FRONTEND: how pixels become the per-region (colour, count) lists.  1 (default): colour
+ * partition + shared-memory histograms (streaming passes only); 0: the two 2^24-bin colour-cube
+ * histograms in device memory (what the row-sharded path all-reduces).  Same lists either way. */
+#define RCT_OPT_FRONTEND 3
+/* RCT_OPT_APPLY: 1 (default): the apply pass runs as a bulk-async (TMA 1-D) staged pipeline when
+ * the call is MASK mode, not resampled and 16-byte aligned; 0: always the register-staged kernel. */
+#define RCT_OPT_APPLY 4
 int rct_plan_set_option(rct_plan *plan, int option, int value);
 /* accumulated device time per phase since the last reset, in ms: [0] workspace memsets,
  * [1] k_hist (pixels -> colour histograms), [2] solve (compact .. match -> LUT), [3] k_apply

@@ -347,3 +347,90 @@ def test_match_cdf_degenerate_key_sets():
         m, j = aip.match_cdf(t, s, return_index=True)
         om, oj = orc.match_cdf(t, s, want_index=True)
         assert np.array_equal(j, oj) and np.array_equal(m, om)
+
+
+# ---- front ends (colour partition vs colour cube) and apply kernels (bulk-async vs register) ----------
+def _flat_pair(H, W):
+    """One colour per region on > 65536 pixels: every item lands in one bucket, which is split
+    over several CTAs that merge through the cube window (rct_front.cuh)."""
+    c = np.empty((H, W, 3), np.uint8)
+    c[...] = (200, 31, 7)
+    s = np.empty((H, W, 3), np.uint8)
+    s[...] = (9, 140, 77)
+    c[::7, ::5] = (200, 31, 8)     # a second colour in the same bucket
+    s[::3, ::11] = (250, 1, 1)     # and one in a different bucket
+    return c, s
+
+
+@pytest.mark.parametrize("case", ["U", "N", "flat", "resample", "ragged"])
+def test_front_ends_and_apply_kernels_agree(case):
+    if case == "flat":
+        H, W = 400, 512
+        c, s = _flat_pair(H, W)
+        sh, sw = H, W
+    elif case == "resample":
+        H, W, sh, sw = 300, 416, 211, 307
+        c, s = synth.synth_image(H, W, 11, "N"), synth.synth_image(sh, sw, 12, "U")
+    elif case == "ragged":
+        H, W, sh, sw = 251, 333, 251, 333  # npix % 16 != 0: bulk-async kernel + scalar tail
+        c, s = synth.synth_image(H, W, 13, "U"), synth.synth_image(sh, sw, 14, "N")
+    else:
+        H, W, sh, sw = 360, 640, 360, 640
+        c, s = synth.synth_image(H, W, 15, case), synth.synth_image(sh, sw, 16, case)
+    mask = synth.ellipse_mask(H, W, 0.4, 4)
+    ref, st, d = orc.transfer(c, s, mask, debug=True)
+    assert st == 0
+    for front in (1, 0):
+        for apply_tma in (1, 0):
+            plan = _debug_plan(H, W, sh, sw)
+            plan.set_option(_cabi.OPT_FRONTEND, front)
+            plan.set_option(_cabi.OPT_APPLY, apply_tma)
+            out = _run_plan(plan, c, s, mask)
+            out2 = _run_plan(plan, c, s, mask)  # second run: the cube windows were left zero
+            info = plan.info()
+            assert info["n_target"] == d["n_t"] and info["n_source"] == d["n_s"], (front, apply_tma)
+            ht, hs = plan.debug_hist()
+            assert np.array_equal(ht, d["hist_t"]) and np.array_equal(hs, d["hist_s"]), (front, apply_tma)
+            assert np.array_equal(out, ref), (front, apply_tma, int((out != ref).sum()))
+            assert np.array_equal(out2, ref), (front, apply_tma, "second run")
+
+
+def test_partition_front_end_all_and_label_modes():
+    """Two-pass item generation (a pixel feeds both regions) of the partition front end."""
+    H, W = 200, 304
+    c, s = synth.synth_image(H, W, 21, "N"), synth.synth_image(H, W, 22, "U")
+    labels = synth.voronoi_labels(H, W, 4, 6)
+    for mode, mask, label in ((_cabi.MODE_ALL, None, 0), (_cabi.MODE_LABEL, labels, 2)):
+        outs = []
+        for front in (1, 0):
+            plan = _debug_plan(H, W, H, W)
+            plan.set_option(_cabi.OPT_FRONTEND, front)
+            L = _cabi.lib()
+            dc, ds = torch.from_numpy(c).cuda(), torch.from_numpy(s).cuda()
+            dm = torch.from_numpy(mask).cuda() if mask is not None else None
+            out = dc.clone()
+            _cabi.check(L.rct_transfer_async(plan.handle, dc.data_ptr(), c.size, ds.data_ptr(), s.size,
+                                             dm.data_ptr() if dm is not None else None, H * W, out.data_ptr(), c.size,
+                                             1, mode, label, torch.cuda.current_stream().cuda_stream))
+            torch.cuda.synchronize()
+            outs.append((out.cpu().numpy(), plan.debug_hist()))
+        ref = c.copy()
+        if mode == _cabi.MODE_ALL:
+            ref, st, _ = orc.transfer(c, s, None, mode=orc.MODE_ALL)
+        else:
+            orc.transfer(c, s, labels, mode=orc.MODE_LABEL, label=label, out=ref)
+        for out, _ in outs:
+            assert np.array_equal(out, ref)
+        assert np.array_equal(outs[0][1][0], outs[1][1][0]) and np.array_equal(outs[0][1][1], outs[1][1][1])
+
+
+def test_batch_apply_kernels_agree_on_aligned_and_unaligned_strides():
+    for (H, W) in ((120, 160), (97, 131)):  # frame stride % 16 == 0 / != 0 (falls back per call)
+        n = 4
+        cs = np.stack([synth.synth_image(H, W, 300 + i, "U") for i in range(n)])
+        ss = np.stack([synth.synth_image(H, W, 400 + i, "N") for i in range(n)])
+        ms = np.stack([synth.ellipse_mask(H, W, 0.3 + 0.1 * i, i) for i in range(n)])
+        refs = np.stack([orc.transfer(cs[i], ss[i], ms[i])[0] for i in range(n)])
+        out = aip.regional_color_transfer(torch.from_numpy(cs).cuda(), torch.from_numpy(ss).cuda(),
+                                          torch.from_numpy(ms).cuda(), slots=3)
+        assert np.array_equal(out.cpu().numpy(), refs)
