@@ -17,6 +17,7 @@ OPT_TIMING = 1
 OPT_PART_CAP = 2
 OPT_FRONTEND = 3
 OPT_APPLY = 4
+OPT_MATCH = 5
 
 _lib = None
 _lock = threading.Lock()

@@ -174,6 +174,7 @@ struct rct_plan {
     int sm;
     int aggregate;
     int apply_tma;    // RCT_OPT_APPLY: 1 = bulk-async staged apply kernel where the geometry allows
+    int match_interleave;  // RCT_OPT_MATCH
     int front;        // RCT_OPT_FRONTEND: 1 = colour-partitioned shared-memory histograms, 0 = colour cube
     bool cube_dirty;  // the partition front end needs (and leaves) an all-zero colour cube
     unsigned part_cap;  // entries a part may have for the shared-memory sort (RCT_OPT_PART_CAP)
@@ -257,6 +258,7 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     p->sm = g_sm_count[device] > 0 ? g_sm_count[device] : 148;
     p->aggregate = 0;
     p->front = 1;
+    p->match_interleave = 1;
     p->apply_tma = 1;
     p->cube_dirty = true;
     p->part_cap = kPartCap;
@@ -371,7 +373,8 @@ int rct_plan_set_option(rct_plan *p, int option, int value)
     if (option == RCT_OPT_AGGREGATE) p->aggregate = value;
     else if (option == RCT_OPT_TIMING) p->timing = value;
     else if (option == RCT_OPT_FRONTEND) p->front = value ? 1 : 0;
-    else if (option == RCT_OPT_APPLY) p->apply_tma = value ? 1 : 0;
+    else if (option == RCT_OPT_MATCH) p->match_interleave = value ? 1 : 0;
+    else if (option == RCT_OPT_APPLY) p->apply_tma = (value >= 0 && value <= 4) ? value : 1;
     else if (option == RCT_OPT_PART_CAP) p->part_cap = (value > 0 && value <= kPartCap) ? (unsigned)value : (unsigned)kPartCap;
     else return fail(RCT_ERR_ARG, "unknown option %d", option);
     return RCT_OK;
@@ -561,7 +564,7 @@ int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)
     int rc = sort_jobs(p->jobs, 2 * nslots, eb, p->L.cap, p->L.maxparts, p->part_cap, st);
     if (rc) return rc;
     LAUNCH(k_match, dim3((unsigned)p->L.maxparts, nslots), kMatchThreads, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32,
-           p->dbg_m, p->dbg_j, p->L.dbg_stride);
+           p->dbg_m, p->dbg_j, p->L.dbg_stride, p->match_interleave);
     return mark(p, st);
 }
 
@@ -579,14 +582,34 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
         CK(cudaGetDevice(&dev));
         if (attr_dev != dev) {
             CK(cudaFuncSetAttribute(k_apply_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ApSmem)));
+            CK(cudaFuncSetAttribute((k_apply_warp<true, 8>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
+            CK(cudaFuncSetAttribute((k_apply_warp<false, 8>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
+            CK(cudaFuncSetAttribute((k_apply_warp<true, 16>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<16>)));
+            CK(cudaFuncSetAttribute((k_apply_warp<true, 16>), cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+            CK(cudaFuncSetAttribute(k_apply_tma, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             attr_dev = dev;
         }
         PixArgs b = a;
         b.p_end = p_begin + npix16;
-        const size_t tiles = (npix16 + kApTile - 1) / kApTile, total = tiles * (size_t)nslots;
-        const size_t maxb = (size_t)p->sm * 2;
-        k_apply_tma<<<(unsigned)(total < maxb ? total : maxb), kApThreads, sizeof(ApSmem), st>>>(b, (unsigned)tiles,
-                                                                                                   (unsigned)nslots);
+        if (p->apply_tma == 3) {  // CTA-wide ring (kept for A/B)
+            const size_t tiles = (npix16 + kApTile - 1) / kApTile, total = tiles * (size_t)nslots;
+            const size_t maxb = (size_t)p->sm * 2;
+            k_apply_tma<<<(unsigned)(total < maxb ? total : maxb), kApThreads, sizeof(ApSmem), st>>>(b, (unsigned)tiles,
+                                                                                                       (unsigned)nslots);
+        } else if (p->apply_tma == 4) {  // one pipeline per warp, 512-pixel tiles, bulk-async loads
+            const size_t tiles = (npix16 + AwCfg<16>::kTile - 1) / AwCfg<16>::kTile, total = tiles * (size_t)nslots;
+            const size_t need = (total + AwCfg<16>::kWarps - 1) / AwCfg<16>::kWarps, maxb = (size_t)p->sm * AwCfg<16>::kMinBlocks;
+            k_apply_warp<true, 16><<<(unsigned)(need < maxb ? need : maxb), AwCfg<16>::kThreads, sizeof(AwSmem<16>), st>>>(
+                b, (unsigned)tiles, (unsigned)nslots);
+        } else {  // one pipeline per warp, 256-pixel tiles: 1 = bulk-async (TMA 1-D) loads, 2 = cp.async (LDGSTS)
+            const size_t tiles = (npix16 + AwCfg<8>::kTile - 1) / AwCfg<8>::kTile, total = tiles * (size_t)nslots;
+            const size_t need = (total + AwCfg<8>::kWarps - 1) / AwCfg<8>::kWarps, maxb = (size_t)p->sm * AwCfg<8>::kMinBlocks;
+            const unsigned grid = (unsigned)(need < maxb ? need : maxb);
+            if (p->apply_tma == 2)
+                k_apply_warp<false, 8><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
+            else
+                k_apply_warp<true, 8><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
+        }
         ++t_launches;
         CK(cudaGetLastError());
         if (npix16 < p_end - p_begin) {  // ragged tail of < 16 pixels per frame

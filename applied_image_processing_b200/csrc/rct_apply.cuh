@@ -73,6 +73,14 @@ __device__ __forceinline__ void bulk_wait()
 {
     asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
+// LUT gather that does not allocate in L1: with ~200 KB of the SM carved out as shared memory
+// the L1 is a few dozen lines, and an allocating gather can only be in flight while it holds one
+__device__ __forceinline__ uint32_t ldg_gather(const unsigned *p)
+{
+    uint32_t v;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
@@ -95,6 +103,42 @@ __device__ __forceinline__ void pack16(const uint32_t c[16], uint32_t w[12])
         w[3 * q + 1] = (c[4 * q + 1] >> 8) | (c[4 * q + 2] << 16);
         w[3 * q + 2] = (c[4 * q + 2] >> 16) | (c[4 * q + 3] << 8);
     }
+}
+
+// 16 pixels (12 words each of content / stylised, 4 words of mask) -> 12 output words.
+// Target pixels (mask 0) take LUT[colour] (black stays black; a frame with an empty region keeps
+// its content), the others the stylised pixel.  The gathers go out in two batches of eight with
+// little else live: given too few registers the compiler recycles the address registers of
+// loads still in flight and the gathers serialise on their latency (measured: 21 us per tile).
+__device__ __forceinline__ void apply16(const uint32_t wc[12], const uint32_t ws[12], const uint32_t wm[4],
+                                        const unsigned *lut, int status, uint32_t wo[12])
+{
+    uint32_t c[16];
+    unpack16(wc, c);
+    unsigned tgt = 0, want = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const uint32_t mk = (wm[k >> 2] >> (8 * (k & 3))) & 255u;
+        if (mk == 0u) {
+            tgt |= 1u << k;
+            if (c[k] != 0u && status == 0) want |= 1u << k;
+        }
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        uint32_t t[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t[k] = __ldg(lut + (((want >> (8 * h + k)) & 1u) ? c[8 * h + k] : 0u));
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            if ((want >> (8 * h + k)) & 1u) c[8 * h + k] = t[k];
+    }
+    uint32_t s[16];
+    unpack16(ws, s);
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+        if (!((tgt >> k) & 1u)) c[k] = s[k];
+    pack16(c, wo);
 }
 
 // a.p_begin and (a.p_end - a.p_begin) are multiples of 16; all frame bases 16-byte aligned.
@@ -165,19 +209,8 @@ __global__ void __launch_bounds__(kApThreads, 2) k_apply_tma(PixArgs a, unsigned
         if (active) {
             const unsigned *lut = a.lut + (size_t)slot * a.lut_stride;
             const int status = a.ctrl[slot].status;
-            uint32_t c[16], s[16], o[16];
-            unpack16(wc, c);
-            unpack16(ws, s);
-#pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                const uint32_t mk = (wm[k >> 2] >> (8 * (k & 3))) & 255u;
-                uint32_t v;
-                if (mk == 0u) v = (c[k] != 0u && status == 0) ? __ldg(lut + c[k]) : c[k];  // c == 0 stays black
-                else v = s[k];
-                o[k] = v;
-            }
             uint32_t wo[12];
-            pack16(o, wo);
+            apply16(wc, ws, wm, lut, status, wo);
             uint4 *qo = reinterpret_cast<uint4 *>(S.o[ob] + 48u * tid);
             qo[0] = make_uint4(wo[0], wo[1], wo[2], wo[3]);
             qo[1] = make_uint4(wo[4], wo[5], wo[6], wo[7]);
@@ -191,4 +224,216 @@ __global__ void __launch_bounds__(kApThreads, 2) k_apply_tma(PixArgs a, unsigned
         }
     }
     if (tid == 0) bulk_wait<0>();
+}
+
+// ------------------------------------------------------------------------------------------
+// k_apply_warp: the same pass with one independent 2-stage pipeline PER WARP -- no CTA barrier
+// anywhere, so the warps of an SM drift apart and their phases (tile load in flight, LUT gathers,
+// output stores) overlap instead of marching in lock step.  A warp tile is 32 * PXL pixels
+// (PXL = 8: 1.75 KB of input, 16: 3.5 KB).  The prefetch depth is deliberately shallow: every byte
+// of streaming traffic queued in L2 / DRAM ahead of a LUT gather adds to the gather's latency, and
+// the gathers (not the streams) are what a tile waits for.
+//   BULK = true : lane 0 issues three cp.async.bulk copies per tile, completion on the warp's own
+//                 mbarrier (TMA 1-D);
+//   BULK = false: every lane issues 16-byte cp.async (LDGSTS) copies, cp.async.wait_group.
+// Output goes straight from registers to global memory (3 * PXL contiguous bytes per lane).
+// ------------------------------------------------------------------------------------------
+constexpr int kAwStages = 2;
+template <int PXL>
+struct AwCfg {
+    static constexpr int kWarps = PXL == 8 ? 8 : 7;
+    static constexpr int kThreads = kWarps * 32;
+    static constexpr int kTile = 32 * PXL;
+    static constexpr int kMinBlocks = PXL == 8 ? 4 : 3;
+};
+template <int PXL>
+struct AwWarpSmem {
+    alignas(128) uint8_t c[kAwStages][32 * PXL * 3];
+    alignas(128) uint8_t s[kAwStages][32 * PXL * 3];
+    alignas(128) uint8_t m[kAwStages][32 * PXL];
+};
+template <int PXL>
+struct AwSmem {
+    AwWarpSmem<PXL> w[AwCfg<PXL>::kWarps];
+    alignas(8) unsigned long long full[AwCfg<PXL>::kWarps][kAwStages];
+};
+
+__device__ __forceinline__ void cp_async16(void *dst_smem, const void *src_gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src_gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait()
+{
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// 8 pixels: 6 words each of content / stylised, 2 words of mask -> 6 output words
+__device__ __forceinline__ void apply8(const uint32_t wc[6], const uint32_t ws[6], const uint32_t wm[2],
+                                       const unsigned *lut, int status, uint32_t wo[6])
+{
+    uint32_t c[8], s[8];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        c[4 * q + 0] = wc[3 * q] & 0xffffffu;
+        c[4 * q + 1] = __funnelshift_r(wc[3 * q], wc[3 * q + 1], 24) & 0xffffffu;
+        c[4 * q + 2] = __funnelshift_r(wc[3 * q + 1], wc[3 * q + 2], 16) & 0xffffffu;
+        c[4 * q + 3] = wc[3 * q + 2] >> 8;
+    }
+    unsigned tgt = 0, want = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const uint32_t mk = (wm[k >> 2] >> (8 * (k & 3))) & 255u;
+        if (mk == 0u) {
+            tgt |= 1u << k;
+            if (c[k] != 0u && status == 0) want |= 1u << k;
+        }
+    }
+    uint32_t t[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t[k] = __ldg(lut + (((want >> k) & 1u) ? c[k] : 0u));
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        s[4 * q + 0] = ws[3 * q] & 0xffffffu;
+        s[4 * q + 1] = __funnelshift_r(ws[3 * q], ws[3 * q + 1], 24) & 0xffffffu;
+        s[4 * q + 2] = __funnelshift_r(ws[3 * q + 1], ws[3 * q + 2], 16) & 0xffffffu;
+        s[4 * q + 3] = ws[3 * q + 2] >> 8;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if ((want >> k) & 1u) c[k] = t[k];
+        if (!((tgt >> k) & 1u)) c[k] = s[k];
+    }
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        wo[3 * q + 0] = c[4 * q] | (c[4 * q + 1] << 24);
+        wo[3 * q + 1] = (c[4 * q + 1] >> 8) | (c[4 * q + 2] << 16);
+        wo[3 * q + 2] = (c[4 * q + 2] >> 16) | (c[4 * q + 3] << 8);
+    }
+}
+
+__device__ __forceinline__ void stg_stream8(void *p, uint32_t x, uint32_t y)
+{
+    asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(x), "r"(y) : "memory");
+}
+
+template <bool BULK, int PXL>
+__global__ void __launch_bounds__(AwCfg<PXL>::kThreads, AwCfg<PXL>::kMinBlocks)
+    k_apply_warp(PixArgs a, unsigned tiles_per_frame, unsigned nslots)
+{
+    constexpr int kWarps = AwCfg<PXL>::kWarps, kTile = AwCfg<PXL>::kTile;
+    extern __shared__ __align__(128) uint8_t aw_smem_raw[];
+    AwSmem<PXL> &S = *reinterpret_cast<AwSmem<PXL> *>(aw_smem_raw);
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    AwWarpSmem<PXL> &W = S.w[warp];
+    const unsigned total = tiles_per_frame * nslots;
+    if (a.status_out && blockIdx.x == 0)
+        for (unsigned q = threadIdx.x; q < nslots; q += AwCfg<PXL>::kThreads) a.status_out[q] = a.ctrl[q].status;
+    if (BULK) {
+        if (lane == 0) {
+#pragma unroll
+            for (int s = 0; s < kAwStages; ++s) mbar_init(&S.full[warp][s], 1u);
+            fence_mbar_init();
+            fence_proxy_async();
+        }
+        __syncwarp();
+    }
+    const unsigned GW = gridDim.x * kWarps, w0 = blockIdx.x * kWarps + warp;
+    const unsigned cnt = w0 < total ? (total - w0 + GW - 1) / GW : 0u;
+
+    auto tile_geom = [&](unsigned i, unsigned &slot, size_t &p0, unsigned &n) {
+        const unsigned T = w0 + i * GW;
+        slot = T / tiles_per_frame;
+        const unsigned t = T - slot * tiles_per_frame;
+        p0 = a.p_begin + (size_t)t * kTile;
+        const size_t left = a.p_end - p0;
+        n = left < (size_t)kTile ? (unsigned)left : (unsigned)kTile;
+    };
+    auto issue = [&](unsigned i) {
+        unsigned slot, n;
+        size_t p0;
+        tile_geom(i, slot, p0, n);
+        const unsigned st = i % kAwStages;
+        const uint8_t *gc = a.content + (size_t)slot * a.content_stride + 3 * p0;
+        const uint8_t *gs = a.sty + (size_t)slot * a.sty_stride + 3 * p0;
+        const uint8_t *gm = a.mask + (size_t)slot * a.mask_stride + p0;
+        if (BULK) {
+            if (lane == 0) {
+                mbar_expect_tx(&S.full[warp][st], 7u * n);
+                bulk_g2s(W.c[st], gc, 3u * n, &S.full[warp][st]);
+                bulk_g2s(W.s[st], gs, 3u * n, &S.full[warp][st]);
+                bulk_g2s(W.m[st], gm, n, &S.full[warp][st]);
+            }
+        } else {
+            const unsigned n3 = 3u * n / 16u, n1 = n / 16u;  // 16-byte chunks
+            for (unsigned q = lane; q < n3; q += 32u) {
+                cp_async16(W.c[st] + 16u * q, gc + 16u * q);
+                cp_async16(W.s[st] + 16u * q, gs + 16u * q);
+            }
+            if (lane < n1) cp_async16(W.m[st] + 16u * lane, gm + 16u * lane);
+        }
+    };
+
+    if (cnt > 0) issue(0);
+    if (!BULK) cp_async_commit();
+    for (unsigned i = 0; i < cnt; ++i) {
+        const unsigned st = i % kAwStages;
+        if (i + 1 < cnt) issue(i + 1);  // stage (i+1)%2 was released by the __syncwarp ending iteration i-1
+        if (BULK) {
+            mbar_wait(&S.full[warp][st], (i / kAwStages) & 1u);
+        } else {
+            cp_async_commit();  // possibly empty: keeps one group per iteration
+            cp_async_wait<1>();
+            __syncwarp();
+        }
+        unsigned slot, n;
+        size_t p0;
+        tile_geom(i, slot, p0, n);
+        const bool active = lane * (unsigned)PXL < n;
+        const unsigned *lut = a.lut + (size_t)slot * a.lut_stride;
+        const int status = a.ctrl[slot].status;
+        if (PXL == 16) {
+            uint32_t wc[12], ws[12], wm[4], wo[12];
+            if (active) {
+                const uint4 *qc = reinterpret_cast<const uint4 *>(W.c[st] + 48u * lane);
+                const uint4 *qs = reinterpret_cast<const uint4 *>(W.s[st] + 48u * lane);
+                const uint4 x0 = qc[0], x1 = qc[1], x2 = qc[2], y0 = qs[0], y1 = qs[1], y2 = qs[2];
+                const uint4 z = *reinterpret_cast<const uint4 *>(W.m[st] + 16u * lane);
+                wc[0] = x0.x; wc[1] = x0.y; wc[2] = x0.z; wc[3] = x0.w; wc[4] = x1.x; wc[5] = x1.y; wc[6] = x1.z;
+                wc[7] = x1.w; wc[8] = x2.x; wc[9] = x2.y; wc[10] = x2.z; wc[11] = x2.w;
+                ws[0] = y0.x; ws[1] = y0.y; ws[2] = y0.z; ws[3] = y0.w; ws[4] = y1.x; ws[5] = y1.y; ws[6] = y1.z;
+                ws[7] = y1.w; ws[8] = y2.x; ws[9] = y2.y; ws[10] = y2.z; ws[11] = y2.w;
+                wm[0] = z.x; wm[1] = z.y; wm[2] = z.z; wm[3] = z.w;
+            }
+            __syncwarp();  // the stage is read: the next iteration may refill it
+            if (active) {
+                apply16(wc, ws, wm, lut, status, wo);
+                uint4 *qo = reinterpret_cast<uint4 *>(a.out + (size_t)slot * a.out_stride + 3 * p0 + 48u * lane);
+                stg_stream(qo, make_uint4(wo[0], wo[1], wo[2], wo[3]));
+                stg_stream(qo + 1, make_uint4(wo[4], wo[5], wo[6], wo[7]));
+                stg_stream(qo + 2, make_uint4(wo[8], wo[9], wo[10], wo[11]));
+            }
+        } else {
+            uint32_t wc[6], ws[6], wm[2], wo[6];
+            if (active) {
+                const uint2 *qc = reinterpret_cast<const uint2 *>(W.c[st] + 24u * lane);
+                const uint2 *qs = reinterpret_cast<const uint2 *>(W.s[st] + 24u * lane);
+                const uint2 x0 = qc[0], x1 = qc[1], x2 = qc[2], y0 = qs[0], y1 = qs[1], y2 = qs[2];
+                const uint2 z = *reinterpret_cast<const uint2 *>(W.m[st] + 8u * lane);
+                wc[0] = x0.x; wc[1] = x0.y; wc[2] = x1.x; wc[3] = x1.y; wc[4] = x2.x; wc[5] = x2.y;
+                ws[0] = y0.x; ws[1] = y0.y; ws[2] = y1.x; ws[3] = y1.y; ws[4] = y2.x; ws[5] = y2.y;
+                wm[0] = z.x; wm[1] = z.y;
+            }
+            __syncwarp();
+            if (active) {
+                apply8(wc, ws, wm, lut, status, wo);
+                uint8_t *qo = a.out + (size_t)slot * a.out_stride + 3 * p0 + 24u * lane;
+                stg_stream8(qo, wo[0], wo[1]);
+                stg_stream8(qo + 8, wo[2], wo[3]);
+                stg_stream8(qo + 16, wo[4], wo[5]);
+            }
+        }
+    }
+    if (!BULK) cp_async_wait<0>();
 }

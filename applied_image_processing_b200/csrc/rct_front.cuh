@@ -198,8 +198,25 @@ __global__ void __launch_bounds__(kPartThreads, 2) k_front_part(PixArgs a, Front
             uint32_t it[16];
 #pragma unroll
             for (int k = 0; k < 16; ++k) it[k] = (TWO_PASS && pass) ? it1[k] : it0[k];
+            // rank of every item inside its (tile, bucket) run: the count atomic returns it (one
+            // shared-memory atomic per run of equal buckets), packed two 16-bit ranks per register
             const unsigned long long lens = item_runs(it);
-            count_runs(it, lens, s_cnt);
+            unsigned rk[8];
+            {
+                unsigned base = 0, off = 0;
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    if (run_leader(it, k)) {
+                        base = atomicAdd(&s_cnt[it[k] >> kBucketShift], run_len(lens, k));
+                        off = 0;
+                    } else {
+                        ++off;
+                    }
+                    const unsigned rank = (base + off) & 0xffffu;  // < tile size (8192)
+                    if (k & 1) rk[k >> 1] |= rank << 16;
+                    else rk[k >> 1] = rank;
+                }
+            }
             __syncthreads();
             // one reservation per bucket the tile touches
             for (int i = threadIdx.x; i < 2 * kNB; i += kPartThreads) {
@@ -207,17 +224,10 @@ __global__ void __launch_bounds__(kPartThreads, 2) k_front_part(PixArgs a, Front
                 if (n) s_base[i] = atomicAdd(&fc.bcur[i], n);
             }
             __syncthreads();
-            unsigned base = 0, off = 0;
 #pragma unroll
             for (int k = 0; k < 16; ++k) {
                 if (it[k] != kInvalidItem) {
-                    if (run_leader(it, k)) {
-                        base = atomicAdd(&s_base[it[k] >> kBucketShift], run_len(lens, k));
-                        off = 0;
-                    } else {
-                        ++off;
-                    }
-                    const unsigned pos = base + off;
+                    const unsigned pos = s_base[it[k] >> kBucketShift] + ((rk[k >> 1] >> (16 * (k & 1))) & 0xffffu);
                     unsigned *dst = (it[k] >> 24) ? items_s : items_t;
                     if (pos < f.items_cap) dst[pos] = it[k] & 0x00ffffffu;
                 }
@@ -246,11 +256,26 @@ __global__ void __launch_bounds__(kFrontHistThreads) k_front_hist(FrameCtrl *ctr
     __shared__ unsigned s_wbase[kFrontHistThreads / 32];
     __shared__ unsigned s_gbase, s_last;
     const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    for (unsigned i = tid; i < (unsigned)kBucketBins; i += kFrontHistThreads) s_hist[i] = 0;
+    uint4 *s_hist4 = reinterpret_cast<uint4 *>(s_hist);
+    for (unsigned i = tid; i < (unsigned)kBucketBins / 4; i += kFrontHistThreads) s_hist4[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
     const unsigned *items = f.items0 + (size_t)(2 * slot + r) * f.items_stride;
-    for (unsigned i = i0 + tid; i < i1; i += kFrontHistThreads)
-        atomicAdd(&s_hist[__ldcs(items + i) & (unsigned)(kBucketBins - 1)], 1u);
+    {
+        constexpr unsigned kMask = (unsigned)(kBucketBins - 1);
+        unsigned a0 = (i0 + 3u) & ~3u, a1 = i1 & ~3u;  // 16-byte aligned body [a0, a1)
+        if (a0 > i1) a0 = i1;
+        if (a1 < a0) a1 = a0;
+        if (i0 + tid < a0) atomicAdd(&s_hist[__ldcs(items + i0 + tid) & kMask], 1u);
+        if (a1 + tid < i1) atomicAdd(&s_hist[__ldcs(items + a1 + tid) & kMask], 1u);
+        const uint4 *items4 = reinterpret_cast<const uint4 *>(items);
+        for (unsigned q = a0 / 4 + tid; q < a1 / 4; q += kFrontHistThreads) {
+            const uint4 v = __ldcs(items4 + q);
+            atomicAdd(&s_hist[v.x & kMask], 1u);
+            atomicAdd(&s_hist[v.y & kMask], 1u);
+            atomicAdd(&s_hist[v.z & kMask], 1u);
+            atomicAdd(&s_hist[v.w & kMask], 1u);
+        }
+    }
     __syncthreads();
     if (nch > 1) {
         // merge through the bucket's window of the colour cube; the last CTA to arrive compacts

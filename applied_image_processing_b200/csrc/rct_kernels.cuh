@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(256) k_hist(PixArgs a)
 // k_apply: a-7..a-9 for pixels: target non-black -> LUT[colour]; target black -> black;
 // MASK mode non-target -> stylised pixel (background_np); LABEL mode non-target untouched.
 template <bool RESAMPLE>
-__global__ void __launch_bounds__(256) k_apply(PixArgs a)
+__global__ void __launch_bounds__(256, 3) k_apply(PixArgs a)
 {
     const int slot = blockIdx.y;
     const uint8_t *content = a.content + (size_t)slot * a.content_stride;
@@ -306,17 +306,26 @@ __global__ void __launch_bounds__(256) k_apply(PixArgs a)
             if (RESAMPLE) gather16_rgb(sty, a.xtab, a.ytab, a.W, a.sw, p0, nvalid, s);
             else load16_rgb(sty, p0, nvalid, vec_s, s);
         }
-        unsigned keep = 0;
+        // every lane gathers (entry 0 where no lookup is wanted) and selects afterwards: gathers
+        // inside divergent branches serialise on their latency (see rct_apply.cuh)
+        unsigned keep = 0, tgt = 0;
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
             bool in_t, in_s;
             region_flags(a.mode, a.label, mask ? m[k] : 0u, in_t, in_s);
+            if (in_t) tgt |= 1u << k;
+            if (in_t || a.mode == 0) keep |= 1u << k;
+        }
+        uint32_t t[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+            t[k] = __ldg(lut + ((((tgt >> k) & 1u) && status == 0 && k < nvalid) ? c[k] : 0u));
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
             uint32_t v = 0;
-            if (in_t) {
-                keep |= 1u << k;
-                if (c[k] != 0u && k < nvalid) v = (status == 0) ? __ldg(lut + c[k]) : c[k];
+            if ((tgt >> k) & 1u) {
+                if (c[k] != 0u && k < nvalid) v = (status == 0) ? t[k] : c[k];
             } else if (a.mode == 0) {
-                keep |= 1u << k;
                 v = s[k];
             }
             o[k] = v;

@@ -448,6 +448,7 @@ __device__ __forceinline__ double lin_of(const Sorted &v, long long k)
 struct Hint {
     unsigned p, i;
     bool valid;
+    bool fresh;  // ignore .i: start every search from the interpolated position (interleaved traversal)
 };
 
 __device__ __forceinline__ unsigned cum_local(const Sorted &v, unsigned i)
@@ -488,7 +489,7 @@ __device__ unsigned os_index(const Sorted &v, long long q, Hint &h)
     // entries per rank inside this part (multiplicities are roughly even within a part)
     const float scale = __fdividef((float)(pe - ps), (float)(__ldg(v.pbase + p + 1) - b0));
     unsigned idx;
-    if (h.valid && h.p == p && h.i >= ps && h.i < pe) {
+    if (!h.fresh && h.valid && h.p == p && h.i >= ps && h.i < pe) {
         idx = h.i;
     } else {
         idx = ps + (unsigned)((float)ql * scale);
@@ -679,7 +680,7 @@ __device__ double match_one(const Sorted &t, const Sorted &s, unsigned p, unsign
 constexpr int kMatchThreads = 128;
 __global__ void __launch_bounds__(kMatchThreads) k_match(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0,
                                                          size_t lut_stride, double *dbg_matched0, long long *dbg_j0,
-                                                         size_t dbg_stride)
+                                                         size_t dbg_stride, int interleave)
 {
     const int slot = blockIdx.y;
     if (ctrl[slot].status != 0) return;
@@ -693,12 +694,17 @@ __global__ void __launch_bounds__(kMatchThreads) k_match(FrameCtrl *ctrl, const 
     stage_tabs(&T);
     const Pca pca = jt.rc->pca;
     unsigned *lut = lut0 + (size_t)slot * lut_stride;
-    Hint ht{0, 0, false}, hs{0, 0, false};
-    // every thread takes a contiguous run of entries: consecutive ranks -> the source position
-    // moves by a step or two per entry and the hinted search almost never has to search
+    Hint ht{0, 0, false, false}, hs{0, 0, false, false};
+    // interleave: the CTA sweeps the part 128 consecutive entries at a time, so neighbouring lanes
+    // read neighbouring target and source records (coalesced, L1-resident) and every source
+    // search starts from the position interpolated inside the source part.  Otherwise every
+    // thread takes one contiguous run of entries and carries its search position along.
+    hs.fresh = interleave != 0;
     const unsigned per = (pe - ps + kMatchThreads - 1) / kMatchThreads;
-    const unsigned i0 = ps + threadIdx.x * per, i1 = (i0 + per < pe) ? i0 + per : pe;
-    for (unsigned i = i0; i < i1; ++i) {
+    const unsigned first = interleave ? ps + threadIdx.x : ps + threadIdx.x * per;
+    const unsigned step = interleave ? (unsigned)kMatchThreads : 1u;
+    const unsigned last = interleave ? pe : ((first + per < pe) ? first + per : pe);
+    for (unsigned i = first; i < last; i += step) {
         long long j;
         double m = match_one(t, s, p, i, ht, hs, j);
         double lab[3];
@@ -720,7 +726,7 @@ __global__ void __launch_bounds__(kMatchThreads) k_match_generic(const Job *jobs
     if (p >= jt.rc->n_parts) return;
     const Sorted t = sorted_of(jt), s = sorted_of(js);
     const unsigned ps = jt.pstart[p], pe = jt.pstart[p + 1];
-    Hint ht{0, 0, false}, hs{0, 0, false};
+    Hint ht{0, 0, false, false}, hs{0, 0, false, false};
     const unsigned per = (pe - ps + kMatchThreads - 1) / kMatchThreads;
     const unsigned i0 = ps + threadIdx.x * per, i1 = (i0 + per < pe) ? i0 + per : pe;
     for (unsigned i = i0; i < i1; ++i) {

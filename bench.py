@@ -55,8 +55,10 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--front", type=int, default=1, choices=[0, 1],
                     help="1: colour-partition front end (default); 0: colour-cube histograms (A/B runs)")
-    ap.add_argument("--apply", type=int, default=1, choices=[0, 1],
-                    help="1: bulk-async staged apply kernel (default); 0: register-staged k_apply (A/B runs)")
+    ap.add_argument("--match", type=int, default=1, choices=[0, 1], help="k_match traversal (RCT_OPT_MATCH), A/B runs")
+    ap.add_argument("--apply", type=int, default=1, choices=[0, 1, 2, 3, 4],
+                    help="apply kernel (RCT_OPT_APPLY): 1 per-warp bulk-async pipeline, 256-px tiles (default), 2 same with "
+                         "cp.async, 4 per-warp bulk-async 512-px tiles, 3 CTA-wide bulk-async ring, 0 register-staged k_apply")
     a = ap.parse_args()
     dflt = {"4k": (H4K, W4K, 8), "1080p": (1080, 1920, 32), "labels": (1080, 1920, 16), "16k": (8640, 15360, 1)}[a.workload]
     a.height = a.height or dflt[0]
@@ -279,6 +281,7 @@ def run_gpu_arm(a):
     plan = lst.get_plan(dev, H, W, H, W, slots=a.slots)
     plan.set_option(_cabi.OPT_FRONTEND, a.front)
     plan.set_option(_cabi.OPT_APPLY, a.apply)
+    plan.set_option(_cabi.OPT_MATCH, a.match)
     st = torch.cuda.current_stream().cuda_stream
 
     def step():
@@ -323,7 +326,7 @@ def run_gpu_arm(a):
     groups = max(1, phases["groups"])
     kern = {}
     front_name = "k_front_count+scan+part+hist" if a.front else "k_hist"
-    apply_name = "k_apply_tma" if (a.apply and not labels) else "k_apply"
+    apply_name = {0: "k_apply", 1: "k_apply_warp<bulk,8>", 2: "k_apply_warp<cp.async,8>", 3: "k_apply_tma", 4: "k_apply_warp<bulk,16>"}[0 if labels else a.apply]
     for name, key in ((front_name, "hist"), (apply_name, "apply")):
         ms_launch = phases[key + "_ms"] / groups
         gb = ALG_BYTES_PER_PIXEL[key] * min(a.slots, n) * H * W / 1e9

@@ -88,9 +88,15 @@ int rct_plan_destroy(rct_plan *plan);
  * partition + shared-memory histograms (streaming passes only); 0: the two 2^24-bin colour-cube
  * histograms in device memory (what the row-sharded path all-reduces).  Same lists either way. */
 #define RCT_OPT_FRONTEND 3
-/* RCT_OPT_APPLY: 1 (default): the apply pass runs as a bulk-async (TMA 1-D) staged pipeline when
- * the call is MASK mode, not resampled and 16-byte aligned; 0: always the register-staged kernel. */
+/* RCT_OPT_APPLY: the apply pass when the call is MASK mode, not resampled and 16-byte aligned.
+ * 1 (default): one bulk-async (TMA 1-D, cp.async.bulk + mbarrier) staged pipeline per warp;
+ * 2: the same pipeline fed by cp.async (LDGSTS); 3: one CTA-wide bulk-async ring; 0: always the
+ * register-staged kernel (which also serves every other geometry). */
 #define RCT_OPT_APPLY 4
+/* RCT_OPT_MATCH: traversal of a sorted target part by the CDF-match kernel.  1 (default): lanes
+ * interleaved (coalesced, every search starts from an interpolated position); 0: one contiguous
+ * run per thread with hinted searches.  Same results. */
+#define RCT_OPT_MATCH 5
 int rct_plan_set_option(rct_plan *plan, int option, int value);
 /* accumulated device time per phase since the last reset, in ms: [0] workspace memsets,
  * [1] k_hist (pixels -> colour histograms), [2] solve (compact .. match -> LUT), [3] k_apply

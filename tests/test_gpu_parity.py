@@ -381,7 +381,7 @@ def test_front_ends_and_apply_kernels_agree(case):
     ref, st, d = orc.transfer(c, s, mask, debug=True)
     assert st == 0
     for front in (1, 0):
-        for apply_tma in (1, 0):
+        for apply_tma in (1, 2, 4, 3, 0):
             plan = _debug_plan(H, W, sh, sw)
             plan.set_option(_cabi.OPT_FRONTEND, front)
             plan.set_option(_cabi.OPT_APPLY, apply_tma)
@@ -434,3 +434,31 @@ def test_batch_apply_kernels_agree_on_aligned_and_unaligned_strides():
         out = aip.regional_color_transfer(torch.from_numpy(cs).cuda(), torch.from_numpy(ss).cuda(),
                                           torch.from_numpy(ms).cuda(), slots=3)
         assert np.array_equal(out.cpu().numpy(), refs)
+
+
+@pytest.mark.parametrize("fg", [0.25, 0.5, 0.75])
+def test_match_traversals_agree(fg):
+    """RCT_OPT_MATCH: lane-interleaved vs one contiguous run per thread; target smaller / equal /
+    larger than the source (the three branches of match_cdf, LST:108-121)."""
+    H, W = 300, 400
+    c, s = synth.synth_image(H, W, 31, "U"), synth.synth_image(H, W, 32, "N")
+    mask = synth.ellipse_mask(H, W, fg, 8)
+    if fg == 0.5:  # force N_fg == N_bg exactly: equal counts of non-black pixels
+        mask = (np.arange(H * W).reshape(H, W) % 2).astype(np.uint8)
+        c, s = synth.synth_image(H, W, 31, "U", 0), synth.synth_image(H, W, 32, "N", 0)
+        c[c.sum(-1) == 0] = 1
+        s[s.sum(-1) == 0] = 1
+    ref, st, d = orc.transfer(c, s, mask, debug=True)
+    assert st == 0
+    colour = (c[..., 0].astype(np.uint32) | (c[..., 1].astype(np.uint32) << 8) | (c[..., 2].astype(np.uint32) << 16))
+    sel = d["j"] >= 0
+    for order in (1, 0):
+        plan = _debug_plan(H, W, H, W)
+        plan.set_option(_cabi.OPT_MATCH, order)
+        out = _run_plan(plan, c, s, mask)
+        assert np.array_equal(out, ref), (order, int((out != ref).sum()))
+        t = plan.debug_target()
+        o = np.argsort(t["colour"])
+        pos = o[np.searchsorted(t["colour"][o], colour[sel])]
+        assert np.array_equal(t["j"][pos], d["j"][sel]), order
+        assert np.array_equal(t["matched"][pos], d["matched"][sel]), order
