@@ -18,6 +18,7 @@ OPT_PART_CAP = 2
 OPT_FRONTEND = 3
 OPT_APPLY = 4
 OPT_MATCH = 5
+TK_COUNT = 19
 
 _lib = None
 _lock = threading.Lock()
@@ -47,6 +48,8 @@ SIGNATURES = {
     "rct_plan_destroy": (_i, [_vp]),
     "rct_plan_set_option": (_i, [_vp, _i, _i]),
     "rct_plan_timing": (_i, [_vp, _vp, _vp, _i]),
+    "rct_plan_kernel_timing": (_i, [_vp, _vp, _vp, _i]),
+    "rct_kernel_timing_name": (C.c_char_p, [_i]),
     "rct_transfer_async": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _sz, _vp, _sz, _i, _i, _i, _vp]),
     "rct_plan_status": (_i, [_vp, _vp, _i, _vp]),
     "rct_transfer_host": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),

@@ -191,6 +191,11 @@ struct rct_plan {
     std::vector<cudaEvent_t> ev_busy, ev_free;
     double phase_ms[4];
     long long phase_groups;
+    // RCT_OPT_TIMING == 2: one event after every kernel of rct_transfer_async (ktiming ids)
+    std::vector<cudaEvent_t> kev;
+    std::vector<int> kev_id;
+    double kernel_ms[RCT_TK_COUNT];
+    long long kernel_groups;
 };
 
 extern "C" {
@@ -360,6 +365,7 @@ int rct_plan_destroy(rct_plan *p)
     }
     for (cudaEvent_t e : p->ev_busy) cudaEventDestroy(e);
     for (cudaEvent_t e : p->ev_free) cudaEventDestroy(e);
+    for (cudaEvent_t e : p->kev) cudaEventDestroy(e);
     if (p->owns_ws && p->ws) cudaFree(p->ws);
     if (p->status_frames) cudaFree(p->status_frames);
     if (p->stage) cudaFree(p->stage);
@@ -374,7 +380,7 @@ int rct_plan_set_option(rct_plan *p, int option, int value)
     else if (option == RCT_OPT_TIMING) p->timing = value;
     else if (option == RCT_OPT_FRONTEND) p->front = value ? 1 : 0;
     else if (option == RCT_OPT_MATCH) p->match_interleave = value ? 1 : 0;
-    else if (option == RCT_OPT_APPLY) p->apply_tma = (value >= 0 && value <= 4) ? value : 1;
+    else if (option == RCT_OPT_APPLY) p->apply_tma = (value >= 0 && value <= 5) ? value : 1;
     else if (option == RCT_OPT_PART_CAP) p->part_cap = (value > 0 && value <= kPartCap) ? (unsigned)value : (unsigned)kPartCap;
     else return fail(RCT_ERR_ARG, "unknown option %d", option);
     return RCT_OK;
@@ -426,9 +432,31 @@ unsigned entry_blocks(rct_plan *p, int nslots)
     return (unsigned)(blocks ? blocks : 1);
 }
 
+// timing == 2: an event after each kernel; the interval since the previous event is that kernel's
+int kmark(rct_plan *p, cudaStream_t st, int id)
+{
+    if (!p || p->timing != 2) return RCT_OK;
+    cudaEvent_t e;
+    if (!p->ev_free.empty()) {
+        e = p->ev_free.back();
+        p->ev_free.pop_back();
+    } else {
+        CK(cudaEventCreate(&e));
+    }
+    p->kev.push_back(e);
+    p->kev_id.push_back(id);
+    CK(cudaEventRecord(e, st));
+    return RCT_OK;
+}
+#define KMARK(id)                               \
+    do {                                        \
+        int rc_ = kmark(p, st, id);             \
+        if (rc_) return rc_;                    \
+    } while (0)
+
 int mark(rct_plan *p, cudaStream_t st)
 {
-    if (!p->timing) return RCT_OK;
+    if (p->timing != 1) return RCT_OK;
     cudaEvent_t e;
     if (!p->ev_free.empty()) {
         e = p->ev_free.back();
@@ -447,13 +475,16 @@ int phase_hist(rct_plan *p, const FrameSet &f, int nslots, int mode, int label, 
     int rc;
     if ((rc = mark(p, st))) return rc;
     CK(cudaMemsetAsync(p->ctrl, 0, sizeof(FrameCtrl) * nslots, st));
+    KMARK(RCT_TK_BEGIN);
     CK(cudaMemsetAsync(p->hist, 0, 4 * p->L.hist_stride_u32 * nslots, st));
     p->cube_dirty = true;
+    KMARK(RCT_TK_MEMSET);
     if ((rc = mark(p, st))) return rc;
     PixArgs a = pix_args(p, f, mode, label, p_begin, p_end, nullptr);
     dim3 grid(pix_blocks(p, p_end - p_begin, nslots), nslots);
     if (p->resample) LAUNCH(k_hist<true>, grid, 256, st, a);
     else LAUNCH(k_hist<false>, grid, 256, st, a);
+    KMARK(RCT_TK_HIST);
     return mark(p, st);
 }
 
@@ -477,10 +508,12 @@ int phase_front(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
     int rc;
     if ((rc = mark(p, st))) return rc;
     CK(cudaMemsetAsync(p->ctrl, 0, sizeof(FrameCtrl) * nslots, st));
+    KMARK(RCT_TK_BEGIN);
     if (p->cube_dirty) {  // split buckets merge through windows of the cube and leave it zero again
         CK(cudaMemsetAsync(p->hist, 0, 4 * p->L.hist_stride_u32 * p->slots, st));
         p->cube_dirty = false;
     }
+    KMARK(RCT_TK_MEMSET);
     if ((rc = mark(p, st))) return rc;
     static thread_local int attr_dev = -1;
     int dev = 0;
@@ -509,13 +542,17 @@ int phase_front(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
         }                                                                          \
     } while (0)
     FRONT_DISPATCH(k_front_count, gcount, 256, a);
+    KMARK(RCT_TK_FRONT_COUNT);
     LAUNCH(k_front_scan, dim3(nslots), kNB, st, p->ctrl, fa);
+    KMARK(RCT_TK_FRONT_SCAN);
     FRONT_DISPATCH(k_front_part, gpart, kPartThreads, a, fa);
+    KMARK(RCT_TK_FRONT_PART);
 #undef FRONT_DISPATCH
     k_front_hist<<<dim3((unsigned)p->L.cmap_stride_u32, nslots), kFrontHistThreads, kSmemFrontHist, st>>>(
         p->ctrl, p->jobs, fa, p->hist, p->L.hist_stride_u32);
     ++t_launches;
     CK(cudaGetLastError());
+    KMARK(RCT_TK_FRONT_HIST);
     return mark(p, st);
 }
 
@@ -535,20 +572,26 @@ int ensure_kernel_attrs()
 }
 
 // exact sort of njobs key lists (keys + coarse histograms ready; zero zones cleared)
-int sort_jobs(const Job *jobs, int njobs, unsigned eblocks, size_t cap, size_t maxparts, unsigned part_cap,
+int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t cap, size_t maxparts, unsigned part_cap,
               cudaStream_t st)
 {
     int rc = ensure_kernel_attrs();
     if (rc) return rc;
     unsigned hblocks = (unsigned)((cap + kFineHistChunk - 1) / kFineHistChunk);
     LAUNCH(k_plan_fine, dim3(1, njobs), 1024, st, jobs);
+    KMARK(RCT_TK_PLAN_FINE);
     k_fine_hist<<<dim3(hblocks, njobs), 512, kSmemFineHist, st>>>(jobs);
+    KMARK(RCT_TK_FINE_HIST);
     k_plan_parts<<<dim3(1, njobs), 1024, 0, st>>>(jobs);
+    KMARK(RCT_TK_PLAN_PARTS);
     k_scatter<<<dim3(eblocks, njobs), 256, 0, st>>>(jobs);
+    KMARK(RCT_TK_SCATTER);
     k_part_sort<<<dim3((unsigned)maxparts, njobs), kSortThreads, kSmemPartSort, st>>>(jobs, part_cap);
+    KMARK(RCT_TK_PART_SORT);
     t_launches += 4;
     CK(cudaGetLastError());
     LAUNCH(k_part_scan, dim3(1, njobs), 1024, st, jobs);
+    KMARK(RCT_TK_PART_SCAN);
     return RCT_OK;
 }
 
@@ -556,15 +599,22 @@ int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)
 {
     unsigned eb = entry_blocks(p, nslots);
     CK(cudaMemsetAsync(p->ws + p->L.off_zero, 0, p->L.zero_bytes * 2 * (size_t)nslots, st));
-    if (from_cube)
+    KMARK(RCT_TK_MEMSET);
+    if (from_cube) {
         LAUNCH(k_compact, dim3(kCube / 1024, 2, nslots), 256, st, p->hist, p->L.hist_stride_u32, p->ctrl, p->jobs);
+        KMARK(RCT_TK_COMPACT);
+    }
     LAUNCH(k_lab_moments, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs);
+    KMARK(RCT_TK_LAB_MOMENTS);
     LAUNCH(k_pca, dim3((nslots + 31) / 32), 32, st, p->ctrl, nslots);
+    KMARK(RCT_TK_PCA);
     LAUNCH(k_keys, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs);
-    int rc = sort_jobs(p->jobs, 2 * nslots, eb, p->L.cap, p->L.maxparts, p->part_cap, st);
+    KMARK(RCT_TK_KEYS);
+    int rc = sort_jobs(p, p->jobs, 2 * nslots, eb, p->L.cap, p->L.maxparts, p->part_cap, st);
     if (rc) return rc;
     LAUNCH(k_match, dim3((unsigned)p->L.maxparts, nslots), kMatchThreads, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32,
            p->dbg_m, p->dbg_j, p->L.dbg_stride, p->match_interleave);
+    KMARK(RCT_TK_MATCH);
     return mark(p, st);
 }
 
@@ -582,10 +632,11 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
         CK(cudaGetDevice(&dev));
         if (attr_dev != dev) {
             CK(cudaFuncSetAttribute(k_apply_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ApSmem)));
-            CK(cudaFuncSetAttribute((k_apply_warp<true, 8>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
-            CK(cudaFuncSetAttribute((k_apply_warp<false, 8>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
-            CK(cudaFuncSetAttribute((k_apply_warp<true, 16>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<16>)));
-            CK(cudaFuncSetAttribute((k_apply_warp<true, 16>), cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+            CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
+            CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 5>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
+            CK(cudaFuncSetAttribute((k_apply_warp<false, 8, 4>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
+            CK(cudaFuncSetAttribute((k_apply_warp<true, 16, 3>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<16>)));
+            CK(cudaFuncSetAttribute((k_apply_warp<true, 16, 3>), cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             CK(cudaFuncSetAttribute(k_apply_tma, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             attr_dev = dev;
         }
@@ -599,16 +650,19 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
         } else if (p->apply_tma == 4) {  // one pipeline per warp, 512-pixel tiles, bulk-async loads
             const size_t tiles = (npix16 + AwCfg<16>::kTile - 1) / AwCfg<16>::kTile, total = tiles * (size_t)nslots;
             const size_t need = (total + AwCfg<16>::kWarps - 1) / AwCfg<16>::kWarps, maxb = (size_t)p->sm * AwCfg<16>::kMinBlocks;
-            k_apply_warp<true, 16><<<(unsigned)(need < maxb ? need : maxb), AwCfg<16>::kThreads, sizeof(AwSmem<16>), st>>>(
+            k_apply_warp<true, 16, 3><<<(unsigned)(need < maxb ? need : maxb), AwCfg<16>::kThreads, sizeof(AwSmem<16>), st>>>(
                 b, (unsigned)tiles, (unsigned)nslots);
         } else {  // one pipeline per warp, 256-pixel tiles: 1 = bulk-async (TMA 1-D) loads, 2 = cp.async (LDGSTS)
             const size_t tiles = (npix16 + AwCfg<8>::kTile - 1) / AwCfg<8>::kTile, total = tiles * (size_t)nslots;
-            const size_t need = (total + AwCfg<8>::kWarps - 1) / AwCfg<8>::kWarps, maxb = (size_t)p->sm * AwCfg<8>::kMinBlocks;
+            const size_t need = (total + AwCfg<8>::kWarps - 1) / AwCfg<8>::kWarps;
+            const size_t maxb = (size_t)p->sm * (p->apply_tma == 5 ? 5 : 4);
             const unsigned grid = (unsigned)(need < maxb ? need : maxb);
             if (p->apply_tma == 2)
-                k_apply_warp<false, 8><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
+                k_apply_warp<false, 8, 4><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
+            else if (p->apply_tma == 5)
+                k_apply_warp<true, 8, 5><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
             else
-                k_apply_warp<true, 8><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
+                k_apply_warp<true, 8, 4><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
         }
         ++t_launches;
         CK(cudaGetLastError());
@@ -617,11 +671,13 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
             c.p_begin = p_begin + npix16;
             LAUNCH(k_apply<false>, dim3(1, nslots), 256, st, c);
         }
+        KMARK(RCT_TK_APPLY);
         return mark(p, st);
     }
     dim3 grid(pix_blocks(p, p_end - p_begin, nslots), nslots);
     if (p->resample) LAUNCH(k_apply<true>, grid, 256, st, a);
     else LAUNCH(k_apply<false>, grid, 256, st, a);
+    KMARK(RCT_TK_APPLY);
     return mark(p, st);
 }
 
@@ -909,7 +965,7 @@ int rct_match_cdf(const double *target_proj, size_t nt, const double *source_pro
     LAUNCH(k_key_range_finish, 1, 32, st, hj[0].rc, hj[1].rc, (unsigned long long)nt, (unsigned long long)ns);
     LAUNCH(k_coarse_hist, dim3(eb, 2), 256, st, jobs);
     size_t mp = M.maxparts[0] > M.maxparts[1] ? M.maxparts[0] : M.maxparts[1];
-    rc = sort_jobs(jobs, 2, eb, nmax, mp, kPartCap, st);
+    rc = sort_jobs(nullptr, jobs, 2, eb, nmax, mp, kPartCap, st);
     if (rc) return rc;
     LAUNCH(k_match_generic, (unsigned)M.maxparts[0], kMatchThreads, st, jobs, matched, (long long *)j_index);
     return RCT_OK;
@@ -937,6 +993,39 @@ int rct_plan_timing(rct_plan *p, double *ms4, long long *groups, int reset)
     if (reset) {
         memset(p->phase_ms, 0, sizeof p->phase_ms);
         p->phase_groups = 0;
+    }
+    return RCT_OK;
+}
+
+static const char *const kTkNames[RCT_TK_COUNT] = {
+    "begin", "memset", "k_front_count", "k_front_scan", "k_front_part", "k_front_hist", "k_hist", "k_compact",
+    "k_lab_moments", "k_pca", "k_keys", "k_plan_fine", "k_fine_hist", "k_plan_parts", "k_scatter", "k_part_sort",
+    "k_part_scan", "k_match", "k_apply"};
+const char *rct_kernel_timing_name(int id) { return (id >= 0 && id < RCT_TK_COUNT) ? kTkNames[id] : nullptr; }
+
+int rct_plan_kernel_timing(rct_plan *p, double *ms, long long *groups, int reset)
+{
+    if (!p) return fail(RCT_ERR_ARG, "null plan");
+    CK(cudaSetDevice(p->device));
+    for (size_t i = 0; i < p->kev.size(); ++i) {
+        if (p->kev_id[i] == RCT_TK_BEGIN) {
+            ++p->kernel_groups;
+            continue;
+        }
+        if (i == 0) continue;
+        CK(cudaEventSynchronize(p->kev[i]));
+        float t = 0.f;
+        CK(cudaEventElapsedTime(&t, p->kev[i - 1], p->kev[i]));
+        p->kernel_ms[p->kev_id[i]] += (double)t;
+    }
+    for (cudaEvent_t e : p->kev) p->ev_free.push_back(e);
+    p->kev.clear();
+    p->kev_id.clear();
+    if (ms) memcpy(ms, p->kernel_ms, sizeof p->kernel_ms);
+    if (groups) *groups = p->kernel_groups;
+    if (reset) {
+        memset(p->kernel_ms, 0, sizeof p->kernel_ms);
+        p->kernel_groups = 0;
     }
     return RCT_OK;
 }

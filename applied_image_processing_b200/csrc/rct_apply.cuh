@@ -81,6 +81,40 @@ __device__ __forceinline__ uint32_t ldg_gather(const unsigned *p)
     asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
     return v;
 }
+// L2 eviction policies: the image streams are touched once (evict first), a frame's colour LUT is
+// gathered from again and again while the frame is walked (evict last)
+__device__ __forceinline__ unsigned long long l2_policy_evict_first()
+{
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ unsigned long long l2_policy_evict_last()
+{
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void *dst_smem, const void *src_gmem, unsigned bytes,
+                                              unsigned long long *bar, unsigned long long pol)
+{
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t ldg_hint(const unsigned *p, unsigned long long pol)
+{
+    uint32_t v;
+    asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ void stg8_hint(void *p, uint32_t x, uint32_t y, unsigned long long pol)
+{
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.v2.u32 [%0], {%1,%2}, %3;" ::"l"(p), "r"(x), "r"(y), "l"(pol)
+                 : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
@@ -270,8 +304,9 @@ __device__ __forceinline__ void cp_async_wait()
 }
 
 // 8 pixels: 6 words each of content / stylised, 2 words of mask -> 6 output words
+template <bool HINT>
 __device__ __forceinline__ void apply8(const uint32_t wc[6], const uint32_t ws[6], const uint32_t wm[2],
-                                       const unsigned *lut, int status, uint32_t wo[6])
+                                       const unsigned *lut, int status, uint32_t wo[6], unsigned long long pol_lut)
 {
     uint32_t c[8], s[8];
 #pragma unroll
@@ -292,7 +327,10 @@ __device__ __forceinline__ void apply8(const uint32_t wc[6], const uint32_t ws[6
     }
     uint32_t t[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) t[k] = __ldg(lut + (((want >> k) & 1u) ? c[k] : 0u));
+    for (int k = 0; k < 8; ++k) {
+        const unsigned *g = lut + (((want >> k) & 1u) ? c[k] : 0u);
+        t[k] = HINT ? ldg_hint(g, pol_lut) : __ldg(g);
+    }
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
         s[4 * q + 0] = ws[3 * q] & 0xffffffu;
@@ -318,8 +356,8 @@ __device__ __forceinline__ void stg_stream8(void *p, uint32_t x, uint32_t y)
     asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(x), "r"(y) : "memory");
 }
 
-template <bool BULK, int PXL>
-__global__ void __launch_bounds__(AwCfg<PXL>::kThreads, AwCfg<PXL>::kMinBlocks)
+template <bool BULK, int PXL, int MINB>
+__global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
     k_apply_warp(PixArgs a, unsigned tiles_per_frame, unsigned nslots)
 {
     constexpr int kWarps = AwCfg<PXL>::kWarps, kTile = AwCfg<PXL>::kTile;
@@ -341,6 +379,7 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, AwCfg<PXL>::kMinBlocks)
     }
     const unsigned GW = gridDim.x * kWarps, w0 = blockIdx.x * kWarps + warp;
     const unsigned cnt = w0 < total ? (total - w0 + GW - 1) / GW : 0u;
+    const unsigned long long pol_stream = l2_policy_evict_first(), pol_lut = l2_policy_evict_last();
 
     auto tile_geom = [&](unsigned i, unsigned &slot, size_t &p0, unsigned &n) {
         const unsigned T = w0 + i * GW;
@@ -361,9 +400,15 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, AwCfg<PXL>::kMinBlocks)
         if (BULK) {
             if (lane == 0) {
                 mbar_expect_tx(&S.full[warp][st], 7u * n);
-                bulk_g2s(W.c[st], gc, 3u * n, &S.full[warp][st]);
-                bulk_g2s(W.s[st], gs, 3u * n, &S.full[warp][st]);
-                bulk_g2s(W.m[st], gm, n, &S.full[warp][st]);
+                if (PXL == 8) {
+                    bulk_g2s_hint(W.c[st], gc, 3u * n, &S.full[warp][st], pol_stream);
+                    bulk_g2s_hint(W.s[st], gs, 3u * n, &S.full[warp][st], pol_stream);
+                    bulk_g2s_hint(W.m[st], gm, n, &S.full[warp][st], pol_stream);
+                } else {
+                    bulk_g2s(W.c[st], gc, 3u * n, &S.full[warp][st]);
+                    bulk_g2s(W.s[st], gs, 3u * n, &S.full[warp][st]);
+                    bulk_g2s(W.m[st], gm, n, &S.full[warp][st]);
+                }
             }
         } else {
             const unsigned n3 = 3u * n / 16u, n1 = n / 16u;  // 16-byte chunks
@@ -427,11 +472,17 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, AwCfg<PXL>::kMinBlocks)
             }
             __syncwarp();
             if (active) {
-                apply8(wc, ws, wm, lut, status, wo);
+                apply8<BULK>(wc, ws, wm, lut, status, wo, pol_lut);  // the cp.async flavour runs without L2 hints (A/B)
                 uint8_t *qo = a.out + (size_t)slot * a.out_stride + 3 * p0 + 24u * lane;
-                stg_stream8(qo, wo[0], wo[1]);
-                stg_stream8(qo + 8, wo[2], wo[3]);
-                stg_stream8(qo + 16, wo[4], wo[5]);
+                if (BULK) {
+                    stg8_hint(qo, wo[0], wo[1], pol_stream);
+                    stg8_hint(qo + 8, wo[2], wo[3], pol_stream);
+                    stg8_hint(qo + 16, wo[4], wo[5], pol_stream);
+                } else {
+                    stg_stream8(qo, wo[0], wo[1]);
+                    stg_stream8(qo + 8, wo[2], wo[3]);
+                    stg_stream8(qo + 16, wo[4], wo[5]);
+                }
             }
         }
     }

@@ -98,6 +98,17 @@ class Plan:
         check(_cabi.lib().rct_plan_timing(self.handle, ms, C.byref(groups), int(reset)))
         return dict(memset_ms=ms[0], hist_ms=ms[1], solve_ms=ms[2], apply_ms=ms[3], groups=groups.value)
 
+    def kernel_timing(self, reset=True):
+        """Per-kernel device time (ms) accumulated since the last reset (``set_option(OPT_TIMING, 2)``:
+        one CUDA event after every kernel, on the launching stream)."""
+        L = _cabi.lib()
+        ms = (C.c_double * _cabi.TK_COUNT)()
+        groups = C.c_longlong(0)
+        check(L.rct_plan_kernel_timing(self.handle, ms, C.byref(groups), int(reset)))
+        out = {L.rct_kernel_timing_name(i).decode(): ms[i] for i in range(1, _cabi.TK_COUNT) if ms[i] > 0.0}
+        out["groups"] = groups.value
+        return out
+
     # -- introspection (parity tests) -------------------------------------------------------
     def info(self, slot=0) -> dict:
         fi = _cabi.FrameInfo()

@@ -34,6 +34,17 @@ METRIC = "megapixels/sec region colour transfer"
 UNIT = "MP/s"
 H4K, W4K = 2160, 3840
 ALG_BYTES_PER_PIXEL = {"hist": 7.0, "apply": 10.0, "pipeline": 10.0}  # SURVEY.md 8(d), DESIGN.md
+# kernels that stream the pixels and their algorithmic bytes per pixel: content 3 + stylised 3 + mask 1
+# read (+ combined 3 written by the apply pass)
+PIXEL_KERNELS = {"k_front_count": 7.0, "k_front_part": 7.0, "k_hist": 7.0, "k_apply": 10.0}
+
+
+def load_traffic():
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    try:
+        return json.load(open(p))
+    except Exception:
+        return {}
 
 
 def parse_args():
@@ -56,7 +67,7 @@ def parse_args():
     ap.add_argument("--front", type=int, default=1, choices=[0, 1],
                     help="1: colour-partition front end (default); 0: colour-cube histograms (A/B runs)")
     ap.add_argument("--match", type=int, default=1, choices=[0, 1], help="k_match traversal (RCT_OPT_MATCH), A/B runs")
-    ap.add_argument("--apply", type=int, default=1, choices=[0, 1, 2, 3, 4],
+    ap.add_argument("--apply", type=int, default=1, choices=[0, 1, 2, 3, 4, 5],
                     help="apply kernel (RCT_OPT_APPLY): 1 per-warp bulk-async pipeline, 256-px tiles (default), 2 same with "
                          "cp.async, 4 per-warp bulk-async 512-px tiles, 3 CTA-wide bulk-async ring, 0 register-staged k_apply")
     a = ap.parse_args()
@@ -298,8 +309,6 @@ def run_gpu_arm(a):
     for _ in range(max(a.warmup, 3)):
         step()
     barrier()
-    plan.set_option(_cabi.OPT_TIMING, 1)
-    plan.timing(reset=True)
     sampler = ClockSampler(local)
     L.rct_launch_count(1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -312,8 +321,6 @@ def run_gpu_arm(a):
     clocks = sampler.stop()
     launches = int(L.rct_launch_count(0))
     ms_total = max_over_ranks(e0.elapsed_time(e1))
-    phases = plan.timing(reset=True)
-    plan.set_option(_cabi.OPT_TIMING, 0)
     status = np.zeros(n, np.int32)
     _cabi.check(L.rct_plan_status(plan.handle, status.ctypes.data, n, st))
     assert not status.any(), f"unexpected empty-region status {status}"
@@ -321,23 +328,45 @@ def run_gpu_arm(a):
     ms_step = ms_total / a.steps
     value = mp_step / (ms_step * 1e-3)
 
-    # ---- roofline of the dominant per-pixel kernel (events on the launching stream) -------------------
+    # ---- per-kernel device time: a second pass of the same steps with one CUDA event after every
+    # kernel on the launching stream (RCT_OPT_TIMING = 2); the value above is measured without them ----
+    plan.set_option(_cabi.OPT_TIMING, 2)
+    plan.kernel_timing(reset=True)
+    for _ in range(a.steps):
+        step()
+    barrier()
+    kt = plan.kernel_timing(reset=True)
+    plan.set_option(_cabi.OPT_TIMING, 0)
+    groups = max(1, kt.pop("groups"))
+    ms_launch = {k: v / groups for k, v in kt.items()}           # average duration of one launch
+    t_all = sum(ms_launch.values())
+    frames_launch = min(a.slots, n)
+    apply_name = {0: "k_apply", 1: "k_apply_warp<bulk,8>", 2: "k_apply_warp<cp.async,8>", 3: "k_apply_tma",
+                  4: "k_apply_warp<bulk,16>", 5: "k_apply_warp<bulk,8>"}[0 if labels else a.apply]
+
+    # ---- roofline: the per-pixel kernels stream the images (algorithmic bytes per pixel: SURVEY 8d /
+    # DESIGN.md section 5); the dominant one of them is the headline, every kernel's time is listed ----
     peak, peak_src = peaks()
-    groups = max(1, phases["groups"])
+    traffic_db = load_traffic()
     kern = {}
-    front_name = "k_front_count+scan+part+hist" if a.front else "k_hist"
-    apply_name = {0: "k_apply", 1: "k_apply_warp<bulk,8>", 2: "k_apply_warp<cp.async,8>", 3: "k_apply_tma", 4: "k_apply_warp<bulk,16>"}[0 if labels else a.apply]
-    for name, key in ((front_name, "hist"), (apply_name, "apply")):
-        ms_launch = phases[key + "_ms"] / groups
-        gb = ALG_BYTES_PER_PIXEL[key] * min(a.slots, n) * H * W / 1e9
-        kern[name] = {"ms_per_launch": ms_launch, "alg_bytes_per_pixel": ALG_BYTES_PER_PIXEL[key],
-                      "achieved_GBps": gb / (ms_launch * 1e-3) if ms_launch > 0 else None}
+    for kname, bpp in PIXEL_KERNELS.items():
+        if kname not in ms_launch:
+            continue
+        gb = bpp * frames_launch * H * W / 1e9
+        shown = apply_name if kname == "k_apply" else kname
+        tr = traffic_db.get(a.kind, {}).get(shown)
+        kern[shown] = {"ms_per_launch": ms_launch[kname], "alg_bytes_per_pixel": bpp,
+                       "achieved_GBps": gb / (ms_launch[kname] * 1e-3), "frac": gb / (ms_launch[kname] * 1e-3) / peak,
+                       "share_of_step": ms_launch[kname] / t_all,
+                       "ncu_dram_bytes_per_launch": (tr["dram_bytes_per_frame"] * frames_launch if tr else None)}
     dom = max(kern, key=lambda k: kern[k]["ms_per_launch"])
-    phase_share = {k: phases[k + "_ms"] / a.steps / ms_step for k in ("memset", "hist", "solve", "apply")}
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_GBps"], "peak": peak, "unit": "GB/s",
-        "frac": kern[dom]["achieved_GBps"] / peak, "traffic": None, "peak_source": peak_src,
-        "kernels": kern, "phase_share_of_step": phase_share,
+        "frac": kern[dom]["frac"], "traffic": kern[dom]["ncu_dram_bytes_per_launch"], "peak_source": peak_src,
+        "algorithmic_bytes_per_launch": kern[dom]["alg_bytes_per_pixel"] * frames_launch * H * W,
+        "traffic_source": "profiles/r01_traffic.json (ncu --set full, dram__bytes_read+write per launch, scaled by frames per launch)",
+        "pixel_kernels": kern,
+        "all_kernels_ms_per_launch": {k: round(v, 5) for k, v in sorted(ms_launch.items(), key=lambda kv: -kv[1])},
         "pipeline_achieved_GBps_per_gpu": ALG_BYTES_PER_PIXEL["pipeline"] * n * H * W / 1e9 / (ms_step * 1e-3),
     }
     roofline["pipeline_frac"] = roofline["pipeline_achieved_GBps_per_gpu"] / peak

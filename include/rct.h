@@ -78,7 +78,7 @@ int rct_plan_destroy(rct_plan *plan);
 /* tuning knobs; RCT_OPT_AGGREGATE (0/1): warp-aggregate equal colours before the histogram
  * atomic (pays off on flat / low-colour images, costs a MATCH per pixel otherwise) */
 #define RCT_OPT_AGGREGATE 0
-/* RCT_OPT_TIMING (0/1): bracket the phases of every launch group of rct_transfer_async /
+/* RCT_OPT_TIMING (0/1/2): 1 = bracket the phases of every launch group of rct_transfer_async /
  * rct_transfer_host with CUDA events on the launching stream; read with rct_plan_timing() */
 #define RCT_OPT_TIMING 1
 /* RCT_OPT_PART_CAP (1..4096): largest sort part handled in shared memory; lowering it forces the
@@ -102,6 +102,17 @@ int rct_plan_set_option(rct_plan *plan, int option, int value);
  * [1] k_hist (pixels -> colour histograms), [2] solve (compact .. match -> LUT), [3] k_apply
  * (pixels -> output); *groups = launch groups accumulated.  Synchronises the recorded events. */
 int rct_plan_timing(rct_plan *plan, double *ms4, long long *groups, int reset);
+/* RCT_OPT_TIMING = 2: one CUDA event after EVERY kernel of rct_transfer_async (on the launching
+ * stream); rct_plan_kernel_timing() returns the accumulated device time per kernel id since the
+ * last reset, ms[RCT_TK_COUNT], and the launch groups accumulated.  A group's first interval
+ * (id RCT_TK_BEGIN) is not counted; memsets are their own id. */
+enum {
+    RCT_TK_BEGIN = 0, RCT_TK_MEMSET, RCT_TK_FRONT_COUNT, RCT_TK_FRONT_SCAN, RCT_TK_FRONT_PART, RCT_TK_FRONT_HIST,
+    RCT_TK_HIST, RCT_TK_COMPACT, RCT_TK_LAB_MOMENTS, RCT_TK_PCA, RCT_TK_KEYS, RCT_TK_PLAN_FINE, RCT_TK_FINE_HIST,
+    RCT_TK_PLAN_PARTS, RCT_TK_SCATTER, RCT_TK_PART_SORT, RCT_TK_PART_SCAN, RCT_TK_MATCH, RCT_TK_APPLY, RCT_TK_COUNT
+};
+int rct_plan_kernel_timing(rct_plan *plan, double *ms, long long *groups, int reset);
+const char *rct_kernel_timing_name(int id);
 
 /* ---- the fused pipeline: LST:222-238 + color_transfer_foreground (LST:128-168) ----------
  * n_frames frames (any number; processed `slots` at a time), frame f at base + f*stride.

@@ -381,7 +381,7 @@ def test_front_ends_and_apply_kernels_agree(case):
     ref, st, d = orc.transfer(c, s, mask, debug=True)
     assert st == 0
     for front in (1, 0):
-        for apply_tma in (1, 2, 4, 3, 0):
+        for apply_tma in (1, 2, 5, 4, 3, 0):
             plan = _debug_plan(H, W, sh, sw)
             plan.set_option(_cabi.OPT_FRONTEND, front)
             plan.set_option(_cabi.OPT_APPLY, apply_tma)
