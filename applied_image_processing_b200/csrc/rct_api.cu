@@ -971,6 +971,41 @@ int rct_match_cdf(const double *target_proj, size_t nt, const double *source_pro
     return RCT_OK;
 }
 
+// ---- adjacent rows: AdaIN mask-blend tail, DeepLab post-processing ------------------
+int rct_adain_mask_blend(const float *content, const float *output, const float *mask, float *stylized,
+                         uint8_t *rgb8, int n, int H, int W, int oh, int ow, int mh, int mw, size_t mask_stride,
+                         void *stream)
+{
+    if (n <= 0 || H <= 0 || W <= 0 || oh <= 0 || ow <= 0 || mh <= 0 || mw <= 0) return fail(RCT_ERR_ARG, "bad geometry");
+    if (!content || !output || !mask || !stylized) return fail(RCT_ERR_ARG, "null pointer");
+    int dev, rc = ensure_device(&dev);
+    if (rc) return rc;
+    BlendArgs a{content, output, mask, stylized, rgb8, n, H, W, oh, ow, mh, mw, mask_stride};
+    LAUNCH(k_mask_blend, flat_blocks((size_t)n * H * W, dev), 256, (cudaStream_t)stream, a);
+    return RCT_OK;
+}
+
+int rct_softmax_threshold_mask(const float *logits, int n_classes, size_t npix, int cls, float threshold,
+                               uint8_t *mask, void *stream)
+{
+    if (npix == 0) return RCT_OK;
+    if (!logits || !mask || n_classes <= 0 || cls < 0 || cls >= n_classes) return fail(RCT_ERR_ARG, "bad argument");
+    int dev, rc = ensure_device(&dev);
+    if (rc) return rc;
+    LAUNCH(k_softmax_mask, flat_blocks(npix, dev), 256, (cudaStream_t)stream, logits, n_classes, npix, cls, threshold, mask);
+    return RCT_OK;
+}
+
+int rct_argmax_labels(const float *logits, int n_classes, size_t npix, uint8_t *labels, void *stream)
+{
+    if (npix == 0) return RCT_OK;
+    if (!logits || !labels || n_classes <= 0 || n_classes > 256) return fail(RCT_ERR_ARG, "bad argument");
+    int dev, rc = ensure_device(&dev);
+    if (rc) return rc;
+    LAUNCH(k_argmax_labels, flat_blocks(npix, dev), 256, (cudaStream_t)stream, logits, n_classes, npix, labels);
+    return RCT_OK;
+}
+
 // ---- phase timing (RCT_OPT_TIMING) -------------------------------------------------------------
 int rct_plan_timing(rct_plan *p, double *ms4, long long *groups, int reset)
 {

@@ -654,6 +654,7 @@ __global__ void __launch_bounds__(256) k_coarse_hist(const Job *jobs)
 #include "rct_front.cuh"
 #include "rct_apply.cuh"
 #include "rct_sort.cuh"
+#include "rct_adjacent.cuh"
 
 // ------------------------------------------------------------------------------------------
 // the reference's stand-alone element-wise functions

@@ -367,13 +367,25 @@ def regional_color_transfer_labels(content, stylized, labels, n_labels, slots=No
     return out
 
 
-def extract_foreground_deeplab(content_img, threshold=0.5):
-    """LST:171-188 -- out of scope: the north-star path starts after
-    the segmentation mask exists; DeepLabV3 stays stock torchvision."""
-    raise NotImplementedError(
-        "DeepLabV3 mask extraction is outside the accelerated path; pass background_mask= to "
-        "run_localized_style_transfer (weights are not available offline)"
-    )
+def extract_foreground_deeplab(content_img, threshold=0.5, model=None):
+    """LST:171-188.  The DeepLabV3 network itself is outside the accelerated path (SURVEY.md
+    section 2 #3; its weights are a network download the reference performs, LST:173): pass a loaded
+    ``torchvision.models.segmentation`` model as ``model=`` and it runs as stock PyTorch on the GPU,
+    followed by the fused softmax / threshold kernel (f-2, :mod:`.adjacent`).  Returns the
+    reference's uint8 ``[1,H,W]`` background mask."""
+    if model is None:
+        raise NotImplementedError(
+            "DeepLabV3 weights are not available offline: pass model= (a loaded torchvision "
+            "deeplabv3_resnet101) or pass background_mask= to run_localized_style_transfer"
+        )
+    from . import adjacent
+
+    dev = _require_cuda()
+    x = torch.from_numpy(np.ascontiguousarray(np.asarray(content_img))).to(dev)
+    x = x.permute(2, 0, 1).float().div(255).unsqueeze(0)  # torchvision F.to_tensor for uint8 HWC
+    with torch.no_grad():
+        logits = model.to(dev).eval()(x)["out"][0]
+    return adjacent.deeplab_background_mask(logits, threshold)
 
 
 def run_localized_style_transfer(

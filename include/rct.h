@@ -173,6 +173,22 @@ size_t rct_match_scratch_bytes(size_t nt, size_t ns);
 int rct_match_cdf(const double *target_proj, size_t nt, const double *source_proj, size_t ns,
                   double *matched, int64_t *j_index, void *scratch, void *stream);
 
+/* ---- the steps either side of the hot path --------------------------------
+ * f-1: mask-blend tail of AdaIN inference (Style_3DGS/AdaIN/test.py:222-236): mask [mh,mw] float32
+ * resized with torch's nearest rule, output [n,3,oh,ow] with torch's bilinear rule
+ * (align_corners=False), stylized = content * (1 - mask) + output * mask, planar float32 NCHW.
+ * rgb8 (optional) receives what torchvision.utils.save_image quantises, uint8 [n,H,W,3].
+ * mask_stride: elements between per-image masks, 0 = one mask for the batch (the reference). */
+int rct_adain_mask_blend(const float *content, const float *output, const float *mask, float *stylized,
+                         uint8_t *rgb8, int n, int H, int W, int oh, int ow, int mh, int mw,
+                         size_t mask_stride, void *stream);
+/* f-2: DeepLab post-processing (LST:178-188): softmax over n_classes planes of logits
+ * [n_classes, npix] float32, probability of class `cls` > threshold -> uint8 {0,1} */
+int rct_softmax_threshold_mask(const float *logits, int n_classes, size_t npix, int cls, float threshold,
+                               uint8_t *mask, void *stream);
+/* f-2 generalised to label maps (the 8-label configuration): per-pixel arg-max, first index on ties */
+int rct_argmax_labels(const float *logits, int n_classes, size_t npix, uint8_t *labels, void *stream);
+
 /* ---- introspection for parity tests (RCT_FLAG_DEBUG plans; all synchronise) -------------- */
 typedef struct {
     int64_t n_target, n_source;     /* region pixel counts (non-black, LST:134-138) */
