@@ -18,6 +18,7 @@ OPT_PART_CAP = 2
 OPT_FRONTEND = 3
 OPT_APPLY = 4
 OPT_MATCH = 5
+OPT_STAGE_SETS = 6
 TK_COUNT = 19
 
 _lib = None
@@ -68,6 +69,9 @@ SIGNATURES = {
     "rct_adain_mask_blend": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _sz, _vp]),
     "rct_softmax_threshold_mask": (_i, [_vp, _i, _sz, _i, C.c_float, _vp, _vp]),
     "rct_argmax_labels": (_i, [_vp, _i, _sz, _vp, _vp]),
+    "rct_warp_image": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "rct_blend_images": (_i, [_vp, _vp, C.c_double, _vp, _sz, _vp]),
+    "rct_warp_blend": (_i, [_vp, _vp, _vp, C.c_double, _vp, _i, _i, _i, _i, _vp]),
     "rct_plan_info": (_i, [_vp, _i, C.POINTER(FrameInfo)]),
     "rct_plan_debug_hist": (_i, [_vp, _i, _vp, _vp]),
     "rct_plan_debug_target": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp]),

@@ -158,6 +158,7 @@ Layout make_layout(int H, int W, int slots, unsigned flags)
 
 }  // namespace
 
+constexpr int kStageSetsMax = 4;
 struct rct_plan {
     int device, H, W, sh, sw, slots;
     unsigned flags;
@@ -185,7 +186,8 @@ struct rct_plan {
     size_t stage_bytes;
     cudaStream_t own_stream;            // compute stream of the host entry point
     cudaStream_t h2d_stream, d2h_stream; // copy streams of the host entry point (overlap with compute)
-    cudaEvent_t ev_in[2], ev_comp[2], ev_out[2];
+    cudaEvent_t ev_in[kStageSetsMax], ev_comp[kStageSetsMax], ev_out[kStageSetsMax];
+    int stage_sets;  // RCT_OPT_STAGE_SETS: staging sets of the host entry point (2..kStageSetsMax)
     // RCT_OPT_TIMING: five events per launch group (memset | k_hist | solve | k_apply)
     int timing;
     std::vector<cudaEvent_t> ev_busy, ev_free;
@@ -267,6 +269,7 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     p->apply_tma = 1;
     p->cube_dirty = true;
     p->part_cap = kPartCap;
+    p->stage_sets = 3;
     if (workspace) {
         if (workspace_bytes < p->L.total) {
             delete p;
@@ -337,7 +340,7 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->own_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->h2d_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->d2h_stream, cudaStreamNonBlocking);
-    for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+    for (int b = 0; b < kStageSetsMax && e == cudaSuccess; ++b) {
         e = cudaEventCreateWithFlags(&p->ev_in[b], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_comp[b], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_out[b], cudaEventDisableTiming);
@@ -358,7 +361,7 @@ int rct_plan_destroy(rct_plan *p)
     if (p->own_stream) cudaStreamDestroy(p->own_stream);
     if (p->h2d_stream) cudaStreamDestroy(p->h2d_stream);
     if (p->d2h_stream) cudaStreamDestroy(p->d2h_stream);
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < kStageSetsMax; ++b) {
         if (p->ev_in[b]) cudaEventDestroy(p->ev_in[b]);
         if (p->ev_comp[b]) cudaEventDestroy(p->ev_comp[b]);
         if (p->ev_out[b]) cudaEventDestroy(p->ev_out[b]);
@@ -381,6 +384,7 @@ int rct_plan_set_option(rct_plan *p, int option, int value)
     else if (option == RCT_OPT_FRONTEND) p->front = value ? 1 : 0;
     else if (option == RCT_OPT_MATCH) p->match_interleave = value ? 1 : 0;
     else if (option == RCT_OPT_APPLY) p->apply_tma = (value >= 0 && value <= 5) ? value : 1;
+    else if (option == RCT_OPT_STAGE_SETS) p->stage_sets = value < 2 ? 2 : (value > kStageSetsMax ? kStageSetsMax : value);
     else if (option == RCT_OPT_PART_CAP) p->part_cap = (value > 0 && value <= kPartCap) ? (unsigned)value : (unsigned)kPartCap;
     else return fail(RCT_ERR_ARG, "unknown option %d", option);
     return RCT_OK;
@@ -747,11 +751,14 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
     CK(cudaSetDevice(p->device));
     const size_t npix = (size_t)p->H * (size_t)p->W, spix = (size_t)p->sh * (size_t)p->sw;
     const size_t cb = align_up(npix * 3), sb = align_up(spix * 3), mb = align_up(npix);
-    // Two staging sets: while group k computes, group k+1 is copied in and group k-1 is copied
-    // out (three streams, events between them).  Frames are contiguous on the host; device
-    // staging keeps aligned per-slot strides.
+    // A ring of S staging sets (RCT_OPT_STAGE_SETS, default 3): group k is copied in on the H2D
+    // stream, computed on the plan's stream and copied out on the D2H stream; a set's inputs are
+    // free again once its compute is done, its output once the copy-out is done, so the H2D
+    // stream (the bottleneck: 7 of the 10 bytes per pixel) never waits for a copy-out.
+    // Frames are contiguous on the host; device staging keeps aligned per-slot strides.
+    const int S = p->stage_sets;
     const size_t per_set = (cb + sb + mb + cb) * (size_t)p->slots;
-    const size_t need = 2 * per_set;
+    const size_t need = (size_t)S * per_set;
     if (p->stage_bytes < need) {
         if (p->stage) CK(cudaFree(p->stage));
         p->stage = nullptr;
@@ -764,13 +771,14 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
     cudaStream_t st = p->own_stream, sin = p->h2d_stream, sout = p->d2h_stream;
     int k = 0;
     for (int f0 = 0; f0 < n_frames; f0 += p->slots, ++k) {
-        const int b = k & 1;
+        const int b = k % S;
         int ns = n_frames - f0 < p->slots ? n_frames - f0 : p->slots;
         uint8_t *d_c = p->stage + per_set * b, *d_s = d_c + cb * p->slots, *d_m = d_s + sb * p->slots,
                 *d_o = d_m + mb * p->slots;
-        if (k >= 2) {  // set b was last used by group k-2
+        if (k >= S) {  // set b was last used by group k-S
             CK(cudaStreamWaitEvent(sin, p->ev_comp[b], 0));
-            CK(cudaStreamWaitEvent(sin, p->ev_out[b], 0));
+            if (mode == RCT_MODE_LABEL) CK(cudaStreamWaitEvent(sin, p->ev_out[b], 0));
+            else CK(cudaStreamWaitEvent(st, p->ev_out[b], 0));
         }
         CK(cudaMemcpy2DAsync(d_c, cb, content_h + (size_t)f0 * npix * 3, npix * 3, npix * 3, ns, cudaMemcpyHostToDevice, sin));
         CK(cudaMemcpy2DAsync(d_s, sb, stylised_h + (size_t)f0 * spix * 3, spix * 3, spix * 3, ns, cudaMemcpyHostToDevice, sin));
@@ -1003,6 +1011,47 @@ int rct_argmax_labels(const float *logits, int n_classes, size_t npix, uint8_t *
     int dev, rc = ensure_device(&dev);
     if (rc) return rc;
     LAUNCH(k_argmax_labels, flat_blocks(npix, dev), 256, (cudaStream_t)stream, logits, n_classes, npix, labels);
+    return RCT_OK;
+}
+
+// ---- f-4: video temporal-consistency step (video/utils.py:89-105, 217-229) ------------------------
+static int warp_launch(const uint8_t *stylized, const uint8_t *prev, const float *flow, double alpha, uint8_t *out,
+                       int n, int H, int W, int channels, bool blend, void *stream)
+{
+    if (n <= 0 || H <= 0 || W <= 0 || channels <= 0 || channels > 4) return fail(RCT_ERR_ARG, "bad geometry");
+    if (H > 32767 || W > 32767) return fail(RCT_ERR_ARG, "cv2.remap addresses sources with 16-bit coordinates");
+    if (!prev || !flow || !out || (blend && !stylized)) return fail(RCT_ERR_ARG, "null pointer");
+    int dev, rc = ensure_device(&dev);
+    if (rc) return rc;
+    WarpArgs g{stylized, prev, flow, out, n, H, W, channels, (float)alpha, (float)(1.0 - alpha)};
+    const unsigned blocks = flat_blocks((size_t)n * H * W, dev);
+    if (blend) LAUNCH(k_warp_blend<true>, blocks, 256, (cudaStream_t)stream, g);
+    else LAUNCH(k_warp_blend<false>, blocks, 256, (cudaStream_t)stream, g);
+    return RCT_OK;
+}
+
+int rct_warp_image(const uint8_t *image, const float *flow, uint8_t *warped, int n, int H, int W, int channels,
+                   void *stream)
+{
+    return warp_launch(nullptr, image, flow, 0.0, warped, n, H, W, channels, false, stream);
+}
+
+int rct_warp_blend(const uint8_t *stylized, const uint8_t *prev_stylized, const float *flow, double alpha, uint8_t *out,
+                   int n, int H, int W, int channels, void *stream)
+{
+    return warp_launch(stylized, prev_stylized, flow, alpha, out, n, H, W, channels, true, stream);
+}
+
+int rct_blend_images(const uint8_t *stylized, const uint8_t *warped, double alpha, uint8_t *out, size_t nbytes,
+                     void *stream)
+{
+    if (nbytes == 0) return RCT_OK;
+    if (!stylized || !warped || !out) return fail(RCT_ERR_ARG, "null pointer");
+    int dev, rc = ensure_device(&dev);
+    if (rc) return rc;
+    const int vec = ((((uintptr_t)stylized) | ((uintptr_t)warped) | ((uintptr_t)out)) & 15) == 0;
+    LAUNCH(k_blend, flat_blocks((nbytes + 15) / 16, dev), 256, (cudaStream_t)stream, stylized, warped, out, nbytes,
+           (float)alpha, (float)(1.0 - alpha), vec);
     return RCT_OK;
 }
 

@@ -655,6 +655,7 @@ __global__ void __launch_bounds__(256) k_coarse_hist(const Job *jobs)
 #include "rct_apply.cuh"
 #include "rct_sort.cuh"
 #include "rct_adjacent.cuh"
+#include "rct_video.cuh"
 
 // ------------------------------------------------------------------------------------------
 // the reference's stand-alone element-wise functions

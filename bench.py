@@ -64,6 +64,8 @@ def parse_args():
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-slots", type=int, default=0, help="frames per copy/compute group of the host entry point (0 = its default)")
+    ap.add_argument("--stage-sets", type=int, default=0, help="RCT_OPT_STAGE_SETS of the host entry point (0 = default)")
     ap.add_argument("--front", type=int, default=1, choices=[0, 1],
                     help="1: colour-partition front end (default); 0: colour-cube histograms (A/B runs)")
     ap.add_argument("--match", type=int, default=1, choices=[0, 1], help="k_match traversal (RCT_OPT_MATCH), A/B runs")
@@ -376,11 +378,16 @@ def run_gpu_arm(a):
     if not a.no_e2e:
         hcn, hsn, hmn, hon = hc.numpy(), hs.numpy(), hm.numpy(), ho.numpy()
 
+        e2e_slots = a.e2e_slots or None
+        if a.stage_sets:
+            lst.get_plan(dev, H, W, H, W, slots=e2e_slots or max(1, min(8, (n + 3) // 4))).set_option(
+                _cabi.OPT_STAGE_SETS, a.stage_sets)
+
         def api_call():
             if labels:
-                hon[...] = aip.regional_color_transfer_labels(hcn, hsn, hmn, 8)
+                hon[...] = aip.regional_color_transfer_labels(hcn, hsn, hmn, 8, slots=e2e_slots)
             else:
-                aip.regional_color_transfer(hcn, hsn, hmn, out=hon)
+                aip.regional_color_transfer(hcn, hsn, hmn, out=hon, slots=e2e_slots)
 
         for _ in range(2):
             api_call()

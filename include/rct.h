@@ -97,6 +97,9 @@ int rct_plan_destroy(rct_plan *plan);
  * interleaved (coalesced, every search starts from an interpolated position); 0: one contiguous
  * run per thread with hinted searches.  Same results. */
 #define RCT_OPT_MATCH 5
+/* RCT_OPT_STAGE_SETS (2..4, default 3): device staging sets of rct_transfer_host; group k is copied
+   in while group k-1 computes and group k-2 is copied out. */
+#define RCT_OPT_STAGE_SETS 6
 int rct_plan_set_option(rct_plan *plan, int option, int value);
 /* accumulated device time per phase since the last reset, in ms: [0] workspace memsets,
  * [1] k_hist (pixels -> colour histograms), [2] solve (compact .. match -> LUT), [3] k_apply
@@ -188,6 +191,19 @@ int rct_softmax_threshold_mask(const float *logits, int n_classes, size_t npix, 
                                uint8_t *mask, void *stream);
 /* f-2 generalised to label maps (the 8-label configuration): per-pixel arg-max, first index on ties */
 int rct_argmax_labels(const float *logits, int n_classes, size_t npix, uint8_t *labels, void *stream);
+/* f-4: the temporal-consistency step of the video driver (video/utils.py:355-359).
+ * rct_warp_image = warp_image (video/utils.py:89-105): cv2.remap(image, x + flow[0], y + flow[1],
+ * INTER_LINEAR, BORDER_REFLECT) in OpenCV's own fixed-point arithmetic; image / warped uint8
+ * [n,H,W,channels] (channels 1..4), flow float32 [n,2,H,W].
+ * rct_blend_images = blend_images (video/utils.py:223-229) on uint8 inputs: float32
+ * alpha*s/255 + (1-alpha)*w/255, *255, clip, truncate; nbytes = number of uint8 elements.
+ * rct_warp_blend = blend_images(stylized, warp_image(prev_stylized, flow), alpha) in one pass. */
+int rct_warp_image(const uint8_t *image, const float *flow, uint8_t *warped, int n, int H, int W, int channels,
+                   void *stream);
+int rct_blend_images(const uint8_t *stylized, const uint8_t *warped, double alpha, uint8_t *out, size_t nbytes,
+                     void *stream);
+int rct_warp_blend(const uint8_t *stylized, const uint8_t *prev_stylized, const float *flow, double alpha,
+                   uint8_t *out, int n, int H, int W, int channels, void *stream);
 
 /* ---- introspection for parity tests (RCT_FLAG_DEBUG plans; all synchronise) -------------- */
 typedef struct {
