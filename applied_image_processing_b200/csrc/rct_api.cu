@@ -163,6 +163,7 @@ struct rct_plan {
     int device, H, W, sh, sw, slots;
     unsigned flags;
     bool resample, owns_ws;
+    bool rs_tma_ok;  // geometry admits k_apply_warp_rs (TMA-staged NEAREST resample)
     uint8_t *ws;
     Layout L;
     FrameCtrl *ctrl;
@@ -269,7 +270,7 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     p->apply_tma = 1;
     p->cube_dirty = true;
     p->part_cap = kPartCap;
-    p->stage_sets = 3;
+    p->stage_sets = 4;
     if (workspace) {
         if (workspace_bytes < p->L.total) {
             delete p;
@@ -331,6 +332,20 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     if (e == cudaSuccess && p->resample) {
         rct_resample_table(sw, W, tab);
         e = cudaMemcpy(p->xtab, tab, sizeof(int) * (size_t)W, cudaMemcpyHostToDevice);
+        // k_apply_warp_rs stages, per 256-pixel tile, the source spans of its (at most two) row
+        // segments: every pair must fit kRsCap bytes (3 bytes per source pixel, each span widened
+        // to 16-byte boundaries), the stylised frames must be whole 16-byte units, W >= 256
+        bool ok = W >= 256 && ((size_t)sh * (size_t)sw * 3) % 16 == 0;
+        auto seg_bytes = [&](int xa, int npx) -> size_t {
+            if (npx <= 0) return 0;
+            size_t span = (size_t)(tab[xa + npx - 1] - tab[xa] + 1);
+            return (3 * span + 15 + 15 + 15) & ~(size_t)15;
+        };
+        for (int x0 = 0; ok && x0 < W; ++x0) {
+            int na = W - x0 < 256 ? W - x0 : 256;
+            if (seg_bytes(x0, na) + seg_bytes(0, 256 - na) > (size_t)kRsCap) ok = false;
+        }
+        p->rs_tma_ok = ok;
         if (e == cudaSuccess) {
             rct_resample_table(sh, H, tab);
             e = cudaMemcpy(p->ytab, tab, sizeof(int) * (size_t)H, cudaMemcpyHostToDevice);
@@ -678,6 +693,32 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
         KMARK(RCT_TK_APPLY);
         return mark(p, st);
     }
+    if (p->apply_tma && mode == RCT_MODE_MASK && p->resample && p->rs_tma_ok && f.mask && npix16 > 0 &&
+        (((uintptr_t)f.content | (uintptr_t)f.sty | (uintptr_t)f.mask | (uintptr_t)f.out | (uintptr_t)p_begin |
+          (nslots > 1 ? (f.cs | f.ss | f.ms | f.os) : 0)) & 15) == 0) {
+        // the a-1 resample staged by bulk-async copies (k_apply_warp_rs): 256-pixel tiles, one pipeline per warp
+        static thread_local int attr_dev_rs = -1;
+        int dev = 0;
+        CK(cudaGetDevice(&dev));
+        if (attr_dev_rs != dev) {
+            CK(cudaFuncSetAttribute(k_apply_warp_rs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem)));
+            attr_dev_rs = dev;
+        }
+        PixArgs b = a;
+        b.p_end = p_begin + npix16;
+        const size_t tiles = (npix16 + 255) / 256, total = tiles * (size_t)nslots;
+        const size_t need = (total + 7) / 8, maxb = (size_t)p->sm * 4;
+        k_apply_warp_rs<<<(unsigned)(need < maxb ? need : maxb), 256, sizeof(RsSmem), st>>>(b, (unsigned)tiles, (unsigned)nslots);
+        ++t_launches;
+        CK(cudaGetLastError());
+        if (npix16 < p_end - p_begin) {
+            PixArgs c = a;
+            c.p_begin = p_begin + npix16;
+            LAUNCH(k_apply<true>, dim3(1, nslots), 256, st, c);
+        }
+        KMARK(RCT_TK_APPLY);
+        return mark(p, st);
+    }
     dim3 grid(pix_blocks(p, p_end - p_begin, nslots), nslots);
     if (p->resample) LAUNCH(k_apply<true>, grid, 256, st, a);
     else LAUNCH(k_apply<false>, grid, 256, st, a);
@@ -751,7 +792,7 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
     CK(cudaSetDevice(p->device));
     const size_t npix = (size_t)p->H * (size_t)p->W, spix = (size_t)p->sh * (size_t)p->sw;
     const size_t cb = align_up(npix * 3), sb = align_up(spix * 3), mb = align_up(npix);
-    // A ring of S staging sets (RCT_OPT_STAGE_SETS, default 3): group k is copied in on the H2D
+    // A ring of S staging sets (RCT_OPT_STAGE_SETS, default 4): group k is copied in on the H2D
     // stream, computed on the plan's stream and copied out on the D2H stream; a set's inputs are
     // free again once its compute is done, its output once the copy-out is done, so the H2D
     // stream (the bottleneck: 7 of the 10 bytes per pixel) never waits for a copy-out.

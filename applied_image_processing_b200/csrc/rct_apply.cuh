@@ -488,3 +488,164 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
     }
     if (!BULK) cp_async_wait<0>();
 }
+
+// ------------------------------------------------------------------------------------------
+// k_apply_warp_rs: the per-warp bulk-async pipeline WITH the a-1 NEAREST resample of the
+// stylised image (the reference's usual geometry: AdaIN output at 512-short-side scale, content
+// at any size).  A 256-pixel tile of the output covers at most two output rows (W >= 256); for
+// each, the pixels x in [xa, xb] read the contiguous source span xtab[xa] .. xtab[xb] of source
+// row ytab[y] -- staged by one cp.async.bulk per row segment (16-byte aligned outwards) next to
+// the content and mask tiles, on the same mbarrier.  The nearest gather then runs against shared
+// memory; the resized image is never materialised and every stylised byte crosses L2 -> SM once
+// per tile instead of once per output pixel.
+// Host guarantees (phase_apply): MASK mode, W >= 256, frame bases / strides / stylised frame size
+// 16-byte aligned, and every possible pair of segments fits kRsCap bytes.
+// ------------------------------------------------------------------------------------------
+constexpr int kRsCap = 2048;
+struct RsWarpSmem {
+    alignas(128) uint8_t c[kAwStages][256 * 3];
+    alignas(128) uint8_t s[kAwStages][kRsCap];
+    alignas(128) uint8_t m[kAwStages][256];
+};
+struct RsSmem {
+    RsWarpSmem w[8];
+    alignas(8) unsigned long long full[8][kAwStages];
+};
+
+struct RsSeg {  // one row segment of a tile
+    unsigned npx;       // output pixels in the segment (0 = none)
+    unsigned x_first;   // first output x
+    unsigned xs_first;  // xtab[x_first]
+    unsigned smem_off;  // where the staged span starts in the stage's s[] buffer ...
+    unsigned delta;     // ... and the byte offset of source pixel xs_first inside it
+    unsigned bytes;     // staged bytes (multiple of 16)
+    const uint8_t *g;   // 16-byte aligned global source address
+};
+
+__device__ __forceinline__ void rs_segment(const uint8_t *sty, const int *__restrict__ xtab, const int *__restrict__ ytab,
+                                           int sw, unsigned y, unsigned xa, unsigned npx, unsigned smem_off, RsSeg &sg)
+{
+    sg.npx = npx;
+    sg.x_first = xa;
+    sg.smem_off = smem_off;
+    if (npx == 0) {
+        sg.bytes = 0;
+        sg.delta = 0;
+        sg.xs_first = 0;
+        sg.g = sty;
+        return;
+    }
+    const unsigned xs0 = (unsigned)__ldg(xtab + xa), xs1 = (unsigned)__ldg(xtab + xa + npx - 1);
+    const size_t b0 = 3 * ((size_t)__ldg(ytab + y) * (size_t)sw + xs0), b1 = b0 + 3 * (size_t)(xs1 - xs0 + 1);
+    const size_t g0 = b0 & ~(size_t)15, g1 = (b1 + 15) & ~(size_t)15;
+    sg.xs_first = xs0;
+    sg.delta = (unsigned)(b0 - g0);
+    sg.bytes = (unsigned)(g1 - g0);
+    sg.g = sty + g0;
+}
+
+__global__ void __launch_bounds__(256, 4) k_apply_warp_rs(PixArgs a, unsigned tiles_per_frame, unsigned nslots)
+{
+    constexpr int kWarps = 8, kTile = 256;
+    extern __shared__ __align__(128) uint8_t rs_smem_raw[];
+    RsSmem &S = *reinterpret_cast<RsSmem *>(rs_smem_raw);
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    RsWarpSmem &Wm = S.w[warp];
+    const unsigned total = tiles_per_frame * nslots;
+    if (a.status_out && blockIdx.x == 0)
+        for (unsigned q = threadIdx.x; q < nslots; q += 256u) a.status_out[q] = a.ctrl[q].status;
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < kAwStages; ++s) mbar_init(&S.full[warp][s], 1u);
+        fence_mbar_init();
+        fence_proxy_async();
+    }
+    __syncwarp();
+    const unsigned GW = gridDim.x * kWarps, w0 = blockIdx.x * kWarps + warp;
+    const unsigned cnt = w0 < total ? (total - w0 + GW - 1) / GW : 0u;
+    const unsigned long long pol_stream = l2_policy_evict_first(), pol_lut = l2_policy_evict_last();
+    const unsigned Wd = (unsigned)a.W;
+
+    // tile i of this warp: frame, first pixel, pixel count, and its (at most two) row segments
+    auto tile_geom = [&](unsigned i, unsigned &slot, size_t &p0, unsigned &n, RsSeg &sa, RsSeg &sb) {
+        const unsigned T = w0 + i * GW;
+        slot = T / tiles_per_frame;
+        const unsigned t = T - slot * tiles_per_frame;
+        p0 = a.p_begin + (size_t)t * kTile;
+        const size_t left = a.p_end - p0;
+        n = left < (size_t)kTile ? (unsigned)left : (unsigned)kTile;
+        const unsigned y = (unsigned)(p0 / Wd), x = (unsigned)(p0 - (size_t)y * Wd);
+        const unsigned na = n < Wd - x ? n : Wd - x;
+        const uint8_t *sty = a.sty + (size_t)slot * a.sty_stride;
+        rs_segment(sty, a.xtab, a.ytab, a.sw, y, x, na, 0u, sa);
+        rs_segment(sty, a.xtab, a.ytab, a.sw, y + 1u, 0u, n - na, sa.bytes, sb);
+    };
+    auto issue = [&](unsigned i) {  // lane 0 only
+        unsigned slot, n;
+        size_t p0;
+        RsSeg sa, sb;
+        tile_geom(i, slot, p0, n, sa, sb);
+        const unsigned st = i % kAwStages;
+        unsigned long long *bar = &S.full[warp][st];
+        mbar_expect_tx(bar, 4u * n + sa.bytes + sb.bytes);
+        bulk_g2s_hint(Wm.c[st], a.content + (size_t)slot * a.content_stride + 3 * p0, 3u * n, bar, pol_stream);
+        bulk_g2s_hint(Wm.m[st], a.mask + (size_t)slot * a.mask_stride + p0, n, bar, pol_stream);
+        bulk_g2s(Wm.s[st] + sa.smem_off, sa.g, sa.bytes, bar);  // the (small) source image is re-read: default policy
+        if (sb.bytes) bulk_g2s(Wm.s[st] + sb.smem_off, sb.g, sb.bytes, bar);
+    };
+
+    if (cnt > 0 && lane == 0) issue(0);
+    for (unsigned i = 0; i < cnt; ++i) {
+        const unsigned st = i % kAwStages;
+        if (i + 1 < cnt && lane == 0) issue(i + 1);  // stage (i+1)%2 was released by the __syncwarp ending iteration i-1
+        unsigned slot, n;
+        size_t p0;
+        RsSeg sa, sb;
+        tile_geom(i, slot, p0, n, sa, sb);
+        const bool active = lane * 8u < n;
+        // source x of this lane's 8 pixels (the tables are L1-resident) while the tile is in flight
+        unsigned soff[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const unsigned q = lane * 8u + (unsigned)k;
+            unsigned off = 0u;
+            if (q < n) {
+                const bool in_a = q < sa.npx;
+                const RsSeg &sg = in_a ? sa : sb;
+                const unsigned x = sg.x_first + (in_a ? q : q - sa.npx);
+                off = sg.smem_off + sg.delta + 3u * ((unsigned)__ldg(a.xtab + x) - sg.xs_first);
+            }
+            soff[k] = off;
+        }
+        mbar_wait(&S.full[warp][st], (i / kAwStages) & 1u);
+        const unsigned *lut = a.lut + (size_t)slot * a.lut_stride;
+        const int status = a.ctrl[slot].status;
+        uint32_t wc[6], ws[6], wm[2], wo[6];
+        if (active) {
+            const uint2 *qc = reinterpret_cast<const uint2 *>(Wm.c[st] + 24u * lane);
+            const uint2 x0 = qc[0], x1 = qc[1], x2 = qc[2];
+            const uint2 z = *reinterpret_cast<const uint2 *>(Wm.m[st] + 8u * lane);
+            wc[0] = x0.x; wc[1] = x0.y; wc[2] = x1.x; wc[3] = x1.y; wc[4] = x2.x; wc[5] = x2.y;
+            wm[0] = z.x; wm[1] = z.y;
+            uint32_t sp[8];
+            const uint8_t *sb8 = Wm.s[st];
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                sp[k] = (uint32_t)sb8[soff[k]] | ((uint32_t)sb8[soff[k] + 1] << 8) | ((uint32_t)sb8[soff[k] + 2] << 16);
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {  // repack as the 6 little-endian words apply8 expects
+                ws[3 * q + 0] = sp[4 * q] | (sp[4 * q + 1] << 24);
+                ws[3 * q + 1] = (sp[4 * q + 1] >> 8) | (sp[4 * q + 2] << 16);
+                ws[3 * q + 2] = (sp[4 * q + 2] >> 16) | (sp[4 * q + 3] << 8);
+            }
+        }
+        __syncwarp();  // the stage is read: the next iteration may refill it
+        if (active) {
+            apply8<true>(wc, ws, wm, lut, status, wo, pol_lut);
+            uint8_t *qo = a.out + (size_t)slot * a.out_stride + 3 * p0 + 24u * lane;
+            stg8_hint(qo, wo[0], wo[1], pol_stream);
+            stg8_hint(qo + 8, wo[2], wo[3], pol_stream);
+            stg8_hint(qo + 16, wo[4], wo[5], pol_stream);
+        }
+    }
+}

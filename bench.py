@@ -64,6 +64,9 @@ def parse_args():
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--sty-short", type=int, default=0,
+                    help="stylised frames at this short-side size (512 = what AdaIN's Resize(512) hands the reference, "
+                         "LST:223-230), NEAREST-resampled inside the kernels; 0 = same size as the content")
     ap.add_argument("--e2e-slots", type=int, default=0, help="frames per copy/compute group of the host entry point (0 = its default)")
     ap.add_argument("--stage-sets", type=int, default=0, help="RCT_OPT_STAGE_SETS of the host entry point (0 = default)")
     ap.add_argument("--front", type=int, default=1, choices=[0, 1],
@@ -90,19 +93,33 @@ def workload_name(a):
         return (f"{a.width}x{a.height} synthetic frames with 8-label Voronoi masks, per-label exact transfer, image "
                 f"family {a.kind} (BASELINE.json configs[4], exact-rank mode); {a.frames} frames per step per GPU")
     cfg = "configs[1]" if a.workload == "4k" else "configs[2]"
-    return (f"{a.width}x{a.height} synthetic content/stylised pair, binary fg/bg ellipse mask (40% fg), "
+    rs = ""
+    if a.sty_short:
+        sh, sw = sty_size(a)
+        rs = f", stylised at {sw}x{sh} (short side {a.sty_short}) NEAREST-resampled in-kernel"
+    return (f"{a.width}x{a.height} synthetic content/stylised pair{rs}, binary fg/bg ellipse mask (40% fg), "
             f"image family {a.kind} (BASELINE.json {cfg}); {a.frames} distinct pairs per step per GPU")
+
+
+def sty_size(a):
+    """(sh, sw) of the stylised frames: torchvision Resize(short) keeps the aspect ratio (test.py:16-24)."""
+    if not a.sty_short or a.workload in ("16k", "labels"):
+        return a.height, a.width
+    short = min(a.height, a.width)
+    return (a.sty_short, int(a.sty_short * a.width / short)) if a.height <= a.width else (
+        int(a.sty_short * a.height / short), a.sty_short)
 
 
 def make_frames(a, n, seed0):
     from tests.synth import ellipse_mask, synth_image
 
+    sh, sw = sty_size(a)
     cs = np.empty((n, a.height, a.width, 3), np.uint8)
-    ss = np.empty((n, a.height, a.width, 3), np.uint8)
+    ss = np.empty((n, sh, sw, 3), np.uint8)
     ms = np.empty((n, a.height, a.width), np.uint8)
     for i in range(n):
         cs[i] = synth_image(a.height, a.width, seed0 + 2 * i, a.kind)
-        ss[i] = synth_image(a.height, a.width, seed0 + 2 * i + 1, a.kind)
+        ss[i] = synth_image(sh, sw, seed0 + 2 * i + 1, a.kind)
         if a.workload == "labels":
             from tests.synth import voronoi_labels
 
@@ -291,7 +308,8 @@ def run_gpu_arm(a):
     ho = torch.empty_like(hc).pin_memory()
     dc, ds, dm = hc.to(dev), hs.to(dev), hm.to(dev)
     do = torch.empty_like(dc)
-    plan = lst.get_plan(dev, H, W, H, W, slots=a.slots)
+    sh, sw = sty_size(a)
+    plan = lst.get_plan(dev, H, W, sh, sw, slots=a.slots)
     plan.set_option(_cabi.OPT_FRONTEND, a.front)
     plan.set_option(_cabi.OPT_APPLY, a.apply)
     plan.set_option(_cabi.OPT_MATCH, a.match)
@@ -301,11 +319,11 @@ def run_gpu_arm(a):
         if labels:  # configs[4]: every label is an independent exact transfer; untouched pixels keep the content
             do.copy_(dc)
             for lab in range(8):
-                _cabi.check(L.rct_transfer_async(plan.handle, dc.data_ptr(), H * W * 3, ds.data_ptr(), H * W * 3,
+                _cabi.check(L.rct_transfer_async(plan.handle, dc.data_ptr(), H * W * 3, ds.data_ptr(), sh * sw * 3,
                                                  dm.data_ptr(), H * W, do.data_ptr(), H * W * 3, n,
                                                  _cabi.MODE_LABEL, lab, st))
             return
-        _cabi.check(L.rct_transfer_async(plan.handle, dc.data_ptr(), H * W * 3, ds.data_ptr(), H * W * 3,
+        _cabi.check(L.rct_transfer_async(plan.handle, dc.data_ptr(), H * W * 3, ds.data_ptr(), sh * sw * 3,
                                          dm.data_ptr(), H * W, do.data_ptr(), H * W * 3, n, _cabi.MODE_MASK, 0, st))
 
     for _ in range(max(a.warmup, 3)):
@@ -345,6 +363,8 @@ def run_gpu_arm(a):
     frames_launch = min(a.slots, n)
     apply_name = {0: "k_apply", 1: "k_apply_warp<bulk,8>", 2: "k_apply_warp<cp.async,8>", 3: "k_apply_tma",
                   4: "k_apply_warp<bulk,16>", 5: "k_apply_warp<bulk,8>"}[0 if labels else a.apply]
+    if (sh, sw) != (H, W) and not labels:
+        apply_name = "k_apply_warp_rs" if a.apply else "k_apply<resample>"
 
     # ---- roofline: the per-pixel kernels stream the images (algorithmic bytes per pixel: SURVEY 8d /
     # DESIGN.md section 5); the dominant one of them is the headline, every kernel's time is listed ----
@@ -354,6 +374,7 @@ def run_gpu_arm(a):
     for kname, bpp in PIXEL_KERNELS.items():
         if kname not in ms_launch:
             continue
+        bpp = bpp - 3.0 * (1.0 - sh * sw / (H * W))  # stylised bytes counted at their true size
         gb = bpp * frames_launch * H * W / 1e9
         shown = apply_name if kname == "k_apply" else kname
         tr = traffic_db.get(a.kind, {}).get(shown)
@@ -369,7 +390,8 @@ def run_gpu_arm(a):
         "traffic_source": "profiles/r01_traffic.json (ncu --set full, dram__bytes_read+write per launch, scaled by frames per launch)",
         "pixel_kernels": kern,
         "all_kernels_ms_per_launch": {k: round(v, 5) for k, v in sorted(ms_launch.items(), key=lambda kv: -kv[1])},
-        "pipeline_achieved_GBps_per_gpu": ALG_BYTES_PER_PIXEL["pipeline"] * n * H * W / 1e9 / (ms_step * 1e-3),
+        "pipeline_achieved_GBps_per_gpu": (ALG_BYTES_PER_PIXEL["pipeline"] - 3.0 * (1.0 - sh * sw / (H * W)))
+        * n * H * W / 1e9 / (ms_step * 1e-3),
     }
     roofline["pipeline_frac"] = roofline["pipeline_achieved_GBps_per_gpu"] / peak
 
@@ -380,7 +402,7 @@ def run_gpu_arm(a):
 
         e2e_slots = a.e2e_slots or None
         if a.stage_sets:
-            lst.get_plan(dev, H, W, H, W, slots=e2e_slots or max(1, min(8, (n + 3) // 4))).set_option(
+            lst.get_plan(dev, H, W, sh, sw, slots=e2e_slots or lst.host_group_size(n)).set_option(
                 _cabi.OPT_STAGE_SETS, a.stage_sets)
 
         def api_call():

@@ -97,7 +97,7 @@ int rct_plan_destroy(rct_plan *plan);
  * interleaved (coalesced, every search starts from an interpolated position); 0: one contiguous
  * run per thread with hinted searches.  Same results. */
 #define RCT_OPT_MATCH 5
-/* RCT_OPT_STAGE_SETS (2..4, default 3): device staging sets of rct_transfer_host; group k is copied
+/* RCT_OPT_STAGE_SETS (2..4, default 4): device staging sets of rct_transfer_host; group k is copied
    in while group k-1 computes and group k-2 is copied out. */
 #define RCT_OPT_STAGE_SETS 6
 int rct_plan_set_option(rct_plan *plan, int option, int value);
