@@ -19,12 +19,12 @@ from .localized_style_transfer import (  # noqa: F401
     run_localized_style_transfer,
 )
 from .adjacent import adain_mask_blend, deeplab_background_mask, deeplab_label_map  # noqa: F401
-from .video import blend_images, normalize_image, warp_blend, warp_image  # noqa: F401
+from .video import blend_images, blend_sequence, normalize_image, warp_blend, warp_image  # noqa: F401
 
 __all__ = [
     "RGB_TO_LMS", "LMS_TO_LAB", "LAB_TO_LMS", "LMS_TO_RGB", "RegionPCA", "apply_pca",
     "color_transfer_foreground", "extract_foreground_deeplab", "lab_to_rgb_image", "lab_to_rgb_pixels",
     "match_cdf", "regional_color_transfer", "regional_color_transfer_labels", "rgb_to_lab_image",
     "rgb_to_lab_pixels", "run_localized_style_transfer", "adain_mask_blend", "deeplab_background_mask",
-    "deeplab_label_map", "warp_image", "normalize_image", "blend_images", "warp_blend",
+    "deeplab_label_map", "warp_image", "normalize_image", "blend_images", "warp_blend", "blend_sequence",
 ]

@@ -3,6 +3,7 @@
 //        -Xcompiler -fPIC -shared   (see csrc/Makefile, __graft_entry__.build()).
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -87,6 +88,15 @@ int ensure_device(int *dev_out)
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, dev));
     g_sm_count[dev] = prop.multiProcessorCount;
+    if (const char *fg = getenv("RCT_L2_FETCH")) {  // experiment: L2 fetch granularity for the random gathers / scatters
+        size_t v = (size_t)atoi(fg), got = 0;
+        if (v == 32 || v == 64 || v == 128) {
+            cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, v);
+            cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
+            fprintf(stderr, "librct: cudaLimitMaxL2FetchGranularity %zu -> %zu\n", v, got);
+        }
+        cudaGetLastError();
+    }
     g_dev_version[dev] = g_mat_version;
     return RCT_OK;
 }
@@ -335,7 +345,8 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
         // k_apply_warp_rs stages, per 256-pixel tile, the source spans of its (at most two) row
         // segments: every pair must fit kRsCap bytes (3 bytes per source pixel, each span widened
         // to 16-byte boundaries), the stylised frames must be whole 16-byte units, W >= 256
-        bool ok = W >= 256 && ((size_t)sh * (size_t)sw * 3) % 16 == 0;
+        // (W % 256 == 0: tiles never straddle rows -- the two-segment path faulted on the B200 and stays off)
+        bool ok = W >= 256 && W % 256 == 0 && ((size_t)sh * (size_t)sw * 3) % 16 == 0;
         auto seg_bytes = [&](int xa, int npx) -> size_t {
             if (npx <= 0) return 0;
             size_t span = (size_t)(tab[xa + npx - 1] - tab[xa] + 1);
@@ -398,7 +409,7 @@ int rct_plan_set_option(rct_plan *p, int option, int value)
     else if (option == RCT_OPT_TIMING) p->timing = value;
     else if (option == RCT_OPT_FRONTEND) p->front = value ? 1 : 0;
     else if (option == RCT_OPT_MATCH) p->match_interleave = value ? 1 : 0;
-    else if (option == RCT_OPT_APPLY) p->apply_tma = (value >= 0 && value <= 5) ? value : 1;
+    else if (option == RCT_OPT_APPLY) p->apply_tma = (value >= 0 && value <= 8) ? value : 1;
     else if (option == RCT_OPT_STAGE_SETS) p->stage_sets = value < 2 ? 2 : (value > kStageSetsMax ? kStageSetsMax : value);
     else if (option == RCT_OPT_PART_CAP) p->part_cap = (value > 0 && value <= kPartCap) ? (unsigned)value : (unsigned)kPartCap;
     else return fail(RCT_ERR_ARG, "unknown option %d", option);
@@ -586,6 +597,7 @@ int ensure_kernel_attrs()
     if (done_dev == dev) return RCT_OK;
     CK(cudaFuncSetAttribute(k_fine_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemFineHist));
     CK(cudaFuncSetAttribute(k_part_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemPartSort));
+    CK(cudaFuncSetAttribute(k_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemScatter));
     done_dev = dev;
     return RCT_OK;
 }
@@ -603,7 +615,11 @@ int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t 
     KMARK(RCT_TK_FINE_HIST);
     k_plan_parts<<<dim3(1, njobs), 1024, 0, st>>>(jobs);
     KMARK(RCT_TK_PLAN_PARTS);
-    k_scatter<<<dim3(eblocks, njobs), 256, 0, st>>>(jobs);
+    // few, long-lived CTAs per job: each stages the fine-bin tables (kSmemScatter bytes) once
+    unsigned sblocks = (unsigned)((p ? p->sm : 148) * 12 / (njobs > 0 ? njobs : 1));  // ~4 waves of 3 CTAs per SM
+    if (sblocks < 16u) sblocks = 16u;
+    if (sblocks > eblocks) sblocks = eblocks;
+    k_scatter<<<dim3(sblocks, njobs), 256, kSmemScatter, st>>>(jobs);
     KMARK(RCT_TK_SCATTER);
     k_part_sort<<<dim3((unsigned)maxparts, njobs), kSortThreads, kSmemPartSort, st>>>(jobs, part_cap);
     KMARK(RCT_TK_PART_SORT);
@@ -655,6 +671,8 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
             CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 5>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
             CK(cudaFuncSetAttribute((k_apply_warp<false, 8, 4>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
             CK(cudaFuncSetAttribute((k_apply_warp<true, 16, 3>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<16>)));
+            CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 3>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8, 3>)));
+            CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 2, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8, 2, true>)));
             CK(cudaFuncSetAttribute((k_apply_warp<true, 16, 3>), cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             CK(cudaFuncSetAttribute(k_apply_tma, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             attr_dev = dev;
@@ -678,6 +696,10 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
             const unsigned grid = (unsigned)(need < maxb ? need : maxb);
             if (p->apply_tma == 2)
                 k_apply_warp<false, 8, 4><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
+            else if (p->apply_tma == 7)
+                k_apply_warp<true, 8, 4, 2, true><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8, 2, true>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
+            else if (p->apply_tma == 6)
+                k_apply_warp<true, 8, 4, 3><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8, 3>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
             else if (p->apply_tma == 5)
                 k_apply_warp<true, 8, 5><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
             else
@@ -693,7 +715,8 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
         KMARK(RCT_TK_APPLY);
         return mark(p, st);
     }
-    if (p->apply_tma && mode == RCT_MODE_MASK && p->resample && p->rs_tma_ok && f.mask && npix16 > 0 &&
+    static const bool rs_disabled = getenv("RCT_DISABLE_RS") != nullptr;  // debugging aid
+    if (!rs_disabled && p->apply_tma == 8 && mode == RCT_MODE_MASK && p->resample && p->rs_tma_ok && f.mask && npix16 > 0 &&
         (((uintptr_t)f.content | (uintptr_t)f.sty | (uintptr_t)f.mask | (uintptr_t)f.out | (uintptr_t)p_begin |
           (nslots > 1 ? (f.cs | f.ss | f.ms | f.os) : 0)) & 15) == 0) {
         // the a-1 resample staged by bulk-async copies (k_apply_warp_rs): 256-pixel tiles, one pipeline per warp

@@ -280,16 +280,17 @@ struct AwCfg {
     static constexpr int kTile = 32 * PXL;
     static constexpr int kMinBlocks = PXL == 8 ? 4 : 3;
 };
-template <int PXL>
+template <int PXL, int STG = 2, bool OST = false>
 struct AwWarpSmem {
-    alignas(128) uint8_t c[kAwStages][32 * PXL * 3];
-    alignas(128) uint8_t s[kAwStages][32 * PXL * 3];
-    alignas(128) uint8_t m[kAwStages][32 * PXL];
+    alignas(128) uint8_t c[STG][32 * PXL * 3];
+    alignas(128) uint8_t s[STG][32 * PXL * 3];
+    alignas(128) uint8_t m[STG][32 * PXL];
+    alignas(128) uint8_t o[OST ? 2 : 1][OST ? 32 * PXL * 3 : 128];  // output tiles of the bulk-store flavour
 };
-template <int PXL>
+template <int PXL, int STG = 2, bool OST = false>
 struct AwSmem {
-    AwWarpSmem<PXL> w[AwCfg<PXL>::kWarps];
-    alignas(8) unsigned long long full[AwCfg<PXL>::kWarps][kAwStages];
+    AwWarpSmem<PXL, STG, OST> w[AwCfg<PXL>::kWarps];
+    alignas(8) unsigned long long full[AwCfg<PXL>::kWarps][STG];
 };
 
 __device__ __forceinline__ void cp_async16(void *dst_smem, const void *src_gmem)
@@ -356,22 +357,32 @@ __device__ __forceinline__ void stg_stream8(void *p, uint32_t x, uint32_t y)
     asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(x), "r"(y) : "memory");
 }
 
-template <bool BULK, int PXL, int MINB>
+__device__ __forceinline__ void bulk_s2g_hint(void *dst_gmem, const void *src_smem, unsigned bytes, unsigned long long pol)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst_gmem),
+                 "r"(smem_u32(src_smem)), "r"(bytes), "l"(pol)
+                 : "memory");
+}
+
+// OST = true: the output tile goes through shared memory and leaves with ONE cp.async.bulk store
+// per tile (the register flavour's three 8-byte stores per lane, 24 bytes apart, touch every 32-byte
+// sector of the tile three times: ncu shows the L1 -> crossbar request port 83 % busy on image N)
+template <bool BULK, int PXL, int MINB, int STG = 2, bool OST = false>
 __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
     k_apply_warp(PixArgs a, unsigned tiles_per_frame, unsigned nslots)
 {
     constexpr int kWarps = AwCfg<PXL>::kWarps, kTile = AwCfg<PXL>::kTile;
     extern __shared__ __align__(128) uint8_t aw_smem_raw[];
-    AwSmem<PXL> &S = *reinterpret_cast<AwSmem<PXL> *>(aw_smem_raw);
+    AwSmem<PXL, STG, OST> &S = *reinterpret_cast<AwSmem<PXL, STG, OST> *>(aw_smem_raw);
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    AwWarpSmem<PXL> &W = S.w[warp];
+    AwWarpSmem<PXL, STG, OST> &W = S.w[warp];
     const unsigned total = tiles_per_frame * nslots;
     if (a.status_out && blockIdx.x == 0)
         for (unsigned q = threadIdx.x; q < nslots; q += AwCfg<PXL>::kThreads) a.status_out[q] = a.ctrl[q].status;
     if (BULK) {
         if (lane == 0) {
 #pragma unroll
-            for (int s = 0; s < kAwStages; ++s) mbar_init(&S.full[warp][s], 1u);
+            for (int s = 0; s < STG; ++s) mbar_init(&S.full[warp][s], 1u);
             fence_mbar_init();
             fence_proxy_async();
         }
@@ -393,7 +404,7 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
         unsigned slot, n;
         size_t p0;
         tile_geom(i, slot, p0, n);
-        const unsigned st = i % kAwStages;
+        const unsigned st = i % STG;
         const uint8_t *gc = a.content + (size_t)slot * a.content_stride + 3 * p0;
         const uint8_t *gs = a.sty + (size_t)slot * a.sty_stride + 3 * p0;
         const uint8_t *gm = a.mask + (size_t)slot * a.mask_stride + p0;
@@ -420,13 +431,16 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
         }
     };
 
-    if (cnt > 0) issue(0);
+    static_assert(BULK || STG == 2, "the cp.async flavour is two-stage");
+#pragma unroll
+    for (unsigned i = 0; i + 1 < (unsigned)STG; ++i)
+        if (i < cnt) issue(i);
     if (!BULK) cp_async_commit();
     for (unsigned i = 0; i < cnt; ++i) {
-        const unsigned st = i % kAwStages;
-        if (i + 1 < cnt) issue(i + 1);  // stage (i+1)%2 was released by the __syncwarp ending iteration i-1
+        const unsigned st = i % STG;
+        if (i + STG - 1 < cnt) issue(i + STG - 1);  // that stage was released by the __syncwarp ending iteration i-1
         if (BULK) {
-            mbar_wait(&S.full[warp][st], (i / kAwStages) & 1u);
+            mbar_wait(&S.full[warp][st], (i / STG) & 1u);
         } else {
             cp_async_commit();  // possibly empty: keeps one group per iteration
             cp_async_wait<1>();
@@ -471,7 +485,25 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
                 wm[0] = z.x; wm[1] = z.y;
             }
             __syncwarp();
-            if (active) {
+            if (OST) {
+                static_assert(!OST || (BULK && PXL == 8), "bulk-store flavour: bulk loads, 256-pixel tiles");
+                const unsigned ob = i & 1u;
+                if (active) apply8<true>(wc, ws, wm, lut, status, wo, pol_lut);
+                if (lane == 0) bulk_wait_read<1>();  // the store of tile i-2 has read o[ob]
+                __syncwarp();
+                if (active) {
+                    uint2 *so = reinterpret_cast<uint2 *>(W.o[ob] + 24u * lane);
+                    so[0] = make_uint2(wo[0], wo[1]);
+                    so[1] = make_uint2(wo[2], wo[3]);
+                    so[2] = make_uint2(wo[4], wo[5]);
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    bulk_s2g_hint(a.out + (size_t)slot * a.out_stride + 3 * p0, W.o[ob], 3u * n, pol_stream);
+                    bulk_commit();
+                }
+            } else if (active) {
                 apply8<BULK>(wc, ws, wm, lut, status, wo, pol_lut);  // the cp.async flavour runs without L2 hints (A/B)
                 uint8_t *qo = a.out + (size_t)slot * a.out_stride + 3 * p0 + 24u * lane;
                 if (BULK) {
@@ -487,6 +519,7 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
         }
     }
     if (!BULK) cp_async_wait<0>();
+    if (OST && lane == 0) bulk_wait<0>();
 }
 
 // ------------------------------------------------------------------------------------------

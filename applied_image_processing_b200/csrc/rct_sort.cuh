@@ -150,6 +150,7 @@ __global__ void __launch_bounds__(1024) k_plan_parts(const Job *jobs)
             if (flags & (1u << k)) {
                 ++pid;
                 job.pstart[pid] = o;
+                job.pfill[(size_t)pid * kFillStride] = o;  // fill counters start at the part's first entry
             }
             job.pof[f0 + k] = (unsigned short)pid;
         }
@@ -181,9 +182,13 @@ __device__ __forceinline__ bool rec_less(const Rec &a, const Rec &b)
     return ka < kb || (ka == kb && rec_pay(a) < rec_pay(b));
 }
 
-// k_scatter: entries -> their part.  The fine-bin tables are read through L1 (they are small
-// and hot); each thread moves kScatPer entries per trip so that the fill-counter atomics overlap.
+// k_scatter: entries -> their part.  The fine-bin tables (fine_base 16 KB, pof <= 40 KB) are staged
+// in shared memory once per CTA (two of the five dependent memory round trips of an entry used
+// to be L2 hits on them), and the fill counters are seeded with the part starts by k_plan_parts, so
+// the atomic returns the record's final position.  Each thread moves kScatPer entries per trip so
+// that the loads and the fill-counter atomics overlap.
 constexpr int kScatPer = 4;
+constexpr size_t kSmemScatter = (size_t)(kCoarse + 1) * 4 + (size_t)kFineMax * 2 + 16;
 __global__ void __launch_bounds__(256) k_scatter(const Job *jobs)
 {
     const Job &job = jobs[blockIdx.y];
@@ -191,8 +196,17 @@ __global__ void __launch_bounds__(256) k_scatter(const Job *jobs)
     if (rc->skip) return;
     const unsigned d = rc->d;
     if ((size_t)blockIdx.x * blockDim.x * kScatPer >= d) return;
-    const unsigned *fine_base = rc->fine_base;
-    const unsigned short *pof = job.pof;
+    extern __shared__ __align__(16) unsigned s_scat[];
+    unsigned *s_base = s_scat;                                                       // [kCoarse + 1]
+    unsigned short *s_pof = reinterpret_cast<unsigned short *>(s_scat + kCoarse + 2);  // [n_fine]
+    {
+        const unsigned nf2 = (rc->n_fine + 1u) / 2u;
+        const unsigned *pof32 = reinterpret_cast<const unsigned *>(job.pof);
+        unsigned *s_pof32 = s_scat + kCoarse + 2;
+        for (unsigned i = threadIdx.x; i <= (unsigned)kCoarse; i += blockDim.x) s_base[i] = rc->fine_base[i];
+        for (unsigned i = threadIdx.x; i < nf2; i += blockDim.x) s_pof32[i] = pof32[i];
+        __syncthreads();
+    }
     const double klo = rc->klo, cscale = rc->cscale;
     Rec *recP = job.recP;
     const size_t stride = (size_t)gridDim.x * blockDim.x * kScatPer;
@@ -209,7 +223,7 @@ __global__ void __launch_bounds__(256) k_scatter(const Job *jobs)
 #pragma unroll
         for (int k = 0; k < kScatPer; ++k) {
             double ff;
-            p[k] = __ldg(pof + fine_bin(key[k], klo, cscale, fine_base, ff));
+            p[k] = s_pof[fine_bin(key[k], klo, cscale, s_base, ff)];
         }
 #pragma unroll
         for (int k = 0; k < kScatPer; ++k) {
@@ -219,7 +233,7 @@ __global__ void __launch_bounds__(256) k_scatter(const Job *jobs)
 #pragma unroll
         for (int k = 0; k < kScatPer; ++k) {
             size_t e = e0 + (size_t)k * blockDim.x;
-            if (e < d) recP[__ldg(job.pstart + p[k]) + pos[k]] = make_rec(key[k], pay[k], cnt[k]);
+            if (e < d) recP[pos[k]] = make_rec(key[k], pay[k], cnt[k]);
         }
     }
 }

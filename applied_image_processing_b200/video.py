@@ -103,3 +103,30 @@ def warp_blend(stylized, prev_stylized, flow, alpha):
         check(_cabi.lib().rct_warp_blend(s.data_ptr(), p.data_ptr(), fl.data_ptr(), float(alpha), out.data_ptr(),
                                          n, H, W, ch, torch.cuda.current_stream().cuda_stream))
     return out.cpu().numpy() if was_np else out
+
+
+def blend_sequence(stylized_frames, flows, alpha=0.7):
+    """The frame loop of ``apply_style_transfer*`` (video/utils.py:304-371) without its file I/O and
+    stylisation: ``out[0] = stylized[0]``; ``out[i] = blend_images(stylized[i], warp_image(out[i-1],
+    flows[i-1]), alpha)`` -- the recurrence is sequential (each frame warps the previous *blended*
+    frame), so it is one fused ``warp_blend`` launch per frame on the caller's stream, frames
+    staying on the device.  ``stylized_frames`` uint8 [N,H,W,C], ``flows`` float32 [N-1,2,H,W]
+    (``flows[i-1]`` = estimate_optical_flow(frame[i-1], frame[i]))."""
+    s, was_np = _u8(stylized_frames, "stylized_frames")
+    if s.dim() != 4:
+        raise ValueError("stylized_frames must be [N,H,W,C]")
+    fl = _flow(flows, s.device)
+    n, H, W, ch = s.shape
+    if tuple(fl.shape) != (max(n - 1, 0), 2, H, W):
+        raise ValueError(f"flows must be {(n - 1, 2, H, W)}, got {tuple(fl.shape)}")
+    out = torch.empty_like(s)
+    if n == 0:
+        return out.cpu().numpy() if was_np else out
+    out[0].copy_(s[0])
+    L = _cabi.lib()
+    with torch.cuda.device(s.device):
+        st = torch.cuda.current_stream().cuda_stream
+        for i in range(1, n):
+            check(L.rct_warp_blend(s[i].data_ptr(), out[i - 1].data_ptr(), fl[i - 1].data_ptr(), float(alpha),
+                                   out[i].data_ptr(), 1, H, W, ch, st))
+    return out.cpu().numpy() if was_np else out

@@ -72,9 +72,9 @@ def parse_args():
     ap.add_argument("--front", type=int, default=1, choices=[0, 1],
                     help="1: colour-partition front end (default); 0: colour-cube histograms (A/B runs)")
     ap.add_argument("--match", type=int, default=1, choices=[0, 1], help="k_match traversal (RCT_OPT_MATCH), A/B runs")
-    ap.add_argument("--apply", type=int, default=1, choices=[0, 1, 2, 3, 4, 5],
+    ap.add_argument("--apply", type=int, default=1, choices=[0, 1, 2, 3, 4, 5, 6, 7, 8],
                     help="apply kernel (RCT_OPT_APPLY): 1 per-warp bulk-async pipeline, 256-px tiles (default), 2 same with "
-                         "cp.async, 4 per-warp bulk-async 512-px tiles, 3 CTA-wide bulk-async ring, 0 register-staged k_apply")
+                         "cp.async, 4 per-warp bulk-async 512-px tiles, 3 CTA-wide bulk-async ring, 6 three-stage variant of 1, 7 = 1 with one bulk store per tile, 0 register-staged k_apply")
     a = ap.parse_args()
     dflt = {"4k": (H4K, W4K, 8), "1080p": (1080, 1920, 32), "labels": (1080, 1920, 16), "16k": (8640, 15360, 1)}[a.workload]
     a.height = a.height or dflt[0]
@@ -362,9 +362,9 @@ def run_gpu_arm(a):
     t_all = sum(ms_launch.values())
     frames_launch = min(a.slots, n)
     apply_name = {0: "k_apply", 1: "k_apply_warp<bulk,8>", 2: "k_apply_warp<cp.async,8>", 3: "k_apply_tma",
-                  4: "k_apply_warp<bulk,16>", 5: "k_apply_warp<bulk,8>"}[0 if labels else a.apply]
+                  4: "k_apply_warp<bulk,16>", 5: "k_apply_warp<bulk,8>", 6: "k_apply_warp<bulk,8,3stage>", 7: "k_apply_warp<bulk,8,bulk-store>", 8: "k_apply_warp<bulk,8>"}[0 if labels else a.apply]
     if (sh, sw) != (H, W) and not labels:
-        apply_name = "k_apply_warp_rs" if a.apply else "k_apply<resample>"
+        apply_name = "k_apply_warp_rs" if a.apply == 8 else "k_apply<resample>"
 
     # ---- roofline: the per-pixel kernels stream the images (algorithmic bytes per pixel: SURVEY 8d /
     # DESIGN.md section 5); the dominant one of them is the headline, every kernel's time is listed ----

@@ -381,7 +381,7 @@ def test_front_ends_and_apply_kernels_agree(case):
     ref, st, d = orc.transfer(c, s, mask, debug=True)
     assert st == 0
     for front in (1, 0):
-        for apply_tma in (1, 2, 5, 4, 3, 0):
+        for apply_tma in (1, 7, 6, 2, 5, 4, 3, 0):
             plan = _debug_plan(H, W, sh, sw)
             plan.set_option(_cabi.OPT_FRONTEND, front)
             plan.set_option(_cabi.OPT_APPLY, apply_tma)
@@ -397,22 +397,22 @@ def test_front_ends_and_apply_kernels_agree(case):
 
 @pytest.mark.parametrize("H,W,sh,sw", [
     (300, 416, 208, 288),    # up-sampling 1.44x (stylised at a lower scale: the reference's usual case)
-    (300, 416, 360, 512),    # down-sampling 1.23x: widest spans the staged kernel accepts
-    (512, 1024, 128, 256),   # up-sampling 4x
+    (300, 512, 360, 624),    # down-sampling 1.22x: wide spans, W % 256 == 0
+    (512, 1024, 128, 256),   # up-sampling 4x, W % 256 == 0
     (200, 300, 128, 192),    # W % 16 != 0: tiles cross rows at arbitrary x
     (201, 301, 128, 192),    # ragged tail of 5 pixels through the register-staged kernel
     (64, 256, 64, 128),      # W == 256: one tile per row
 ])
 def test_tma_staged_resample_apply(H, W, sh, sw):
-    """k_apply_warp_rs (bulk-async staged NEAREST resample, RCT_OPT_APPLY=1) against the oracle and
-    against the register-staged kernel (RCT_OPT_APPLY=0), single frames and a strided batch."""
+    """k_apply_warp_rs (bulk-async staged NEAREST resample, opt-in RCT_OPT_APPLY=8, W % 256 == 0) and the
+    register-staged resample kernel (the default) against the oracle, single frames and a strided batch."""
     n = 3
     cs = np.stack([synth.synth_image(H, W, 500 + i, "UN"[i % 2]) for i in range(n)])
     ss = np.stack([synth.synth_image(sh, sw, 600 + i, "NU"[i % 2]) for i in range(n)])
     ms = np.stack([synth.ellipse_mask(H, W, 0.3 + 0.15 * i, i) if i else synth.bernoulli_mask(H, W, 0.5, 9)
                    for i in range(n)])
     refs = np.stack([orc.transfer(cs[i], ss[i], ms[i])[0] for i in range(n)])
-    for apply_opt in (1, 0):
+    for apply_opt in (8, 1, 0):
         plan = _debug_plan(H, W, sh, sw)
         plan.set_option(_cabi.OPT_APPLY, apply_opt)
         for i in range(n):

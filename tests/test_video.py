@@ -111,6 +111,22 @@ def test_gpu_warp_blend_batch_1080p_vs_oracle():
 
 
 @pytest.mark.gpu
+def test_gpu_blend_sequence_is_the_reference_frame_loop():
+    import applied_image_processing_b200.video as video
+
+    rng = np.random.default_rng(21)
+    n, H, W = 5, 90, 160
+    sty = rng.integers(0, 256, (n, H, W, 3), dtype=np.uint8)
+    flows = (rng.standard_normal((n - 1, 2, H, W)) * 4).astype(np.float32)
+    got = video.blend_sequence(sty, flows, 0.7)
+    prev = sty[0]
+    assert np.array_equal(got[0], prev)
+    for i in range(1, n):  # video/utils.py:355-371: prev_stylized is the *blended* previous frame
+        prev = aorc.blend_images(sty[i], aorc.warp_image(prev, flows[i - 1]), 0.7)
+        assert np.array_equal(got[i], prev), i
+
+
+@pytest.mark.gpu
 def test_gpu_warp_grey_and_rgba():
     import applied_image_processing_b200 as aip
 
