@@ -19,6 +19,7 @@ OPT_FRONTEND = 3
 OPT_APPLY = 4
 OPT_MATCH = 5
 OPT_STAGE_SETS = 6
+OPT_LUT = 7
 TK_COUNT = 19
 
 _lib = None

@@ -86,18 +86,51 @@ __global__ void __launch_bounds__(256) k_mask_blend(BlendArgs a)
     }
 }
 
-// logits [C, npix] float32 (one image; the reference handles one image per call, LST:176)
+// logits [C, npix] float32 (one image; the reference handles one image per call, LST:176).
+// The decision is DEFINED as the float64 evaluation p_cls = 1 / sum_i exp(x_i - x_cls) > threshold
+// (it differs from a float32 softmax only inside a ~1e-7 band around the threshold).  Evaluating
+// 21 double-precision exponentials per pixel is 6x slower than streaming the 84 bytes, so the sum
+// is first taken in float32 (relative error < 1e-5) and only pixels whose float32 sum lands within
+// 1e-3 (relative) of 1/threshold are re-evaluated in float64: same decisions, HBM-bound.
+__device__ __forceinline__ uint8_t softmax_decide64(const float *logits, int C, size_t npix, size_t p, float xc,
+                                                    float threshold)
+{
+    double den = 0.0;
+    for (int c = 0; c < C; ++c) den += exp((double)logits[(size_t)c * npix + p] - (double)xc);
+    return (1.0 / den > (double)threshold) ? 1 : 0;
+}
+
 __global__ void __launch_bounds__(256) k_softmax_mask(const float *logits, int C, size_t npix, int cls, float threshold,
                                                       uint8_t *mask)
 {
-    for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += (size_t)gridDim.x * blockDim.x) {
-        const float xc = logits[(size_t)cls * npix + p];
-        // p_cls = 1 / sum_i exp(x_i - x_cls), evaluated in float64: the decision differs from a float32
-        // softmax only inside a ~1e-7 band around the threshold
-        double den = 0.0;
-        for (int c = 0; c < C; ++c) den += exp((double)logits[(size_t)c * npix + p] - (double)xc);
-        mask[p] = (1.0 / den > (double)threshold) ? 1 : 0;
+    const bool fast_ok = threshold > 1e-6f && threshold < 1.0f;
+    const float inv_thr = fast_ok ? 1.0f / threshold : 0.f;
+    const size_t nquad = ((((uintptr_t)logits | (uintptr_t)mask) & 15) == 0 && (npix & 3) == 0) ? npix / 4 : 0;
+    const size_t stride = (size_t)gridDim.x * blockDim.x, t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // four pixels per thread: one 16-byte load per class plane, one 4-byte store
+    for (size_t q = t0; q < nquad; q += stride) {
+        const float4 xc = __ldcs(reinterpret_cast<const float4 *>(logits + (size_t)cls * npix) + q);
+        float d0 = 0.f, d1 = 0.f, d2 = 0.f, d3 = 0.f;
+        for (int c = 0; c < C; ++c) {
+            const float4 x = __ldcs(reinterpret_cast<const float4 *>(logits + (size_t)c * npix) + q);
+            d0 += expf(x.x - xc.x);
+            d1 += expf(x.y - xc.y);
+            d2 += expf(x.z - xc.z);
+            d3 += expf(x.w - xc.w);
+        }
+        const float den[4] = {d0, d1, d2, d3}, xcs[4] = {xc.x, xc.y, xc.z, xc.w};
+        uint32_t packed = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint8_t m;
+            if (fast_ok && fabsf(den[k] - inv_thr) > 1e-3f * inv_thr) m = den[k] < inv_thr ? 1 : 0;  // also den = inf
+            else m = softmax_decide64(logits, C, npix, 4 * q + k, xcs[k], threshold);
+            packed |= (uint32_t)m << (8 * k);
+        }
+        reinterpret_cast<uint32_t *>(mask)[q] = packed;
     }
+    for (size_t p = nquad * 4 + t0; p < npix; p += stride)
+        mask[p] = softmax_decide64(logits, C, npix, p, logits[(size_t)cls * npix + p], threshold);
 }
 
 __global__ void __launch_bounds__(256) k_argmax_labels(const float *logits, int C, size_t npix, uint8_t *labels)

@@ -88,15 +88,6 @@ int ensure_device(int *dev_out)
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, dev));
     g_sm_count[dev] = prop.multiProcessorCount;
-    if (const char *fg = getenv("RCT_L2_FETCH")) {  // experiment: L2 fetch granularity for the random gathers / scatters
-        size_t v = (size_t)atoi(fg), got = 0;
-        if (v == 32 || v == 64 || v == 128) {
-            cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, v);
-            cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
-            fprintf(stderr, "librct: cudaLimitMaxL2FetchGranularity %zu -> %zu\n", v, got);
-        }
-        cudaGetLastError();
-    }
     g_dev_version[dev] = g_mat_version;
     return RCT_OK;
 }
@@ -198,6 +189,7 @@ struct rct_plan {
     cudaStream_t own_stream;            // compute stream of the host entry point
     cudaStream_t h2d_stream, d2h_stream; // copy streams of the host entry point (overlap with compute)
     cudaEvent_t ev_in[kStageSetsMax], ev_comp[kStageSetsMax], ev_out[kStageSetsMax];
+    int lut_mode;    // RCT_OPT_LUT: 1 = uint16 run indices + palette, 0 = uint32 RGB per colour
     int stage_sets;  // RCT_OPT_STAGE_SETS: staging sets of the host entry point (2..kStageSetsMax)
     // RCT_OPT_TIMING: five events per launch group (memset | k_hist | solve | k_apply)
     int timing;
@@ -281,6 +273,7 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     p->cube_dirty = true;
     p->part_cap = kPartCap;
     p->stage_sets = 4;
+    p->lut_mode = 0;
     if (workspace) {
         if (workspace_bytes < p->L.total) {
             delete p;
@@ -410,6 +403,7 @@ int rct_plan_set_option(rct_plan *p, int option, int value)
     else if (option == RCT_OPT_FRONTEND) p->front = value ? 1 : 0;
     else if (option == RCT_OPT_MATCH) p->match_interleave = value ? 1 : 0;
     else if (option == RCT_OPT_APPLY) p->apply_tma = (value >= 0 && value <= 8) ? value : 1;
+    else if (option == RCT_OPT_LUT) p->lut_mode = value ? 1 : 0;
     else if (option == RCT_OPT_STAGE_SETS) p->stage_sets = value < 2 ? 2 : (value > kStageSetsMax ? kStageSetsMax : value);
     else if (option == RCT_OPT_PART_CAP) p->part_cap = (value > 0 && value <= kPartCap) ? (unsigned)value : (unsigned)kPartCap;
     else return fail(RCT_ERR_ARG, "unknown option %d", option);
@@ -434,7 +428,7 @@ PixArgs pix_args(rct_plan *p, const FrameSet &f, int mode, int label, size_t p_b
     a.xtab = p->resample ? p->xtab : nullptr;
     a.ytab = p->resample ? p->ytab : nullptr;
     a.hist = p->hist; a.hist_stride = p->L.hist_stride_u32;
-    a.lut = p->lut; a.lut_stride = p->L.lut_stride_u32;
+    a.lut = p->lut; a.lut_stride = p->L.lut_stride_u32; a.lut_mode = p->lut_mode;
     a.ctrl = p->ctrl; a.status_out = status_out;
     a.W = p->W; a.sw = p->sw;
     a.p_begin = p_begin; a.p_end = p_end;
@@ -647,8 +641,17 @@ int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)
     KMARK(RCT_TK_KEYS);
     int rc = sort_jobs(p, p->jobs, 2 * nslots, eb, p->L.cap, p->L.maxparts, p->part_cap, st);
     if (rc) return rc;
-    LAUNCH(k_match, dim3((unsigned)p->L.maxparts, nslots), kMatchThreads, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32,
-           p->dbg_m, p->dbg_j, p->L.dbg_stride, p->match_interleave);
+    if (p->lut_mode)
+        LAUNCH(k_match_pal, dim3((unsigned)p->L.maxparts, nslots), kMatchThreads, st, p->ctrl, p->jobs, p->lut,
+               p->L.lut_stride_u32, p->dbg_m, p->dbg_j, p->L.dbg_stride, p->match_interleave);
+    else
+        LAUNCH(k_match, dim3((unsigned)p->L.maxparts, nslots), kMatchThreads, st, p->ctrl, p->jobs, p->lut,
+               p->L.lut_stride_u32, p->dbg_m, p->dbg_j, p->L.dbg_stride, p->match_interleave);
+    if (p->lut_mode) {  // palette LUT: runs of equal output colour along the sorted target -> uint16 indices + palette
+        LAUNCH(k_pal_count, dim3((unsigned)p->L.maxparts, nslots), kPalThreads, st, p->ctrl, p->jobs);
+        LAUNCH(k_pal_scan, dim3(nslots), 1024, st, p->ctrl, p->jobs);
+        LAUNCH(k_pal_write, dim3((unsigned)p->L.maxparts, nslots), kPalThreads, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32);
+    }
     KMARK(RCT_TK_MATCH);
     return mark(p, st);
 }
@@ -673,13 +676,19 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
             CK(cudaFuncSetAttribute((k_apply_warp<true, 16, 3>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<16>)));
             CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 3>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8, 3>)));
             CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 2, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8, 2, true>)));
+            CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 2, false, 1>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
             CK(cudaFuncSetAttribute((k_apply_warp<true, 16, 3>), cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             CK(cudaFuncSetAttribute(k_apply_tma, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             attr_dev = dev;
         }
         PixArgs b = a;
         b.p_end = p_begin + npix16;
-        if (p->apply_tma == 3) {  // CTA-wide ring (kept for A/B)
+        if (p->lut_mode) {  // palette LUT: the per-warp pipeline with the two-level lookup
+            const size_t tiles = (npix16 + AwCfg<8>::kTile - 1) / AwCfg<8>::kTile, total = tiles * (size_t)nslots;
+            const size_t need = (total + AwCfg<8>::kWarps - 1) / AwCfg<8>::kWarps, maxb = (size_t)p->sm * 4;
+            k_apply_warp<true, 8, 4, 2, false, 1><<<(unsigned)(need < maxb ? need : maxb), AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(
+                b, (unsigned)tiles, (unsigned)nslots);
+        } else if (p->apply_tma == 3) {  // CTA-wide ring (kept for A/B)
             const size_t tiles = (npix16 + kApTile - 1) / kApTile, total = tiles * (size_t)nslots;
             const size_t maxb = (size_t)p->sm * 2;
             k_apply_tma<<<(unsigned)(total < maxb ? total : maxb), kApThreads, sizeof(ApSmem), st>>>(b, (unsigned)tiles,
@@ -710,13 +719,14 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
         if (npix16 < p_end - p_begin) {  // ragged tail of < 16 pixels per frame
             PixArgs c = a;
             c.p_begin = p_begin + npix16;
-            LAUNCH(k_apply<false>, dim3(1, nslots), 256, st, c);
+            if (p->lut_mode) LAUNCH((k_apply<false, 1>), dim3(1, nslots), 256, st, c);
+            else LAUNCH(k_apply<false>, dim3(1, nslots), 256, st, c);
         }
         KMARK(RCT_TK_APPLY);
         return mark(p, st);
     }
     static const bool rs_disabled = getenv("RCT_DISABLE_RS") != nullptr;  // debugging aid
-    if (!rs_disabled && p->apply_tma == 8 && mode == RCT_MODE_MASK && p->resample && p->rs_tma_ok && f.mask && npix16 > 0 &&
+    if (!rs_disabled && !p->lut_mode && p->apply_tma == 8 && mode == RCT_MODE_MASK && p->resample && p->rs_tma_ok && f.mask && npix16 > 0 &&
         (((uintptr_t)f.content | (uintptr_t)f.sty | (uintptr_t)f.mask | (uintptr_t)f.out | (uintptr_t)p_begin |
           (nslots > 1 ? (f.cs | f.ss | f.ms | f.os) : 0)) & 15) == 0) {
         // the a-1 resample staged by bulk-async copies (k_apply_warp_rs): 256-pixel tiles, one pipeline per warp
@@ -743,7 +753,10 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
         return mark(p, st);
     }
     dim3 grid(pix_blocks(p, p_end - p_begin, nslots), nslots);
-    if (p->resample) LAUNCH(k_apply<true>, grid, 256, st, a);
+    if (p->lut_mode) {
+        if (p->resample) LAUNCH((k_apply<true, 1>), grid, 256, st, a);
+        else LAUNCH((k_apply<false, 1>), grid, 256, st, a);
+    } else if (p->resample) LAUNCH(k_apply<true>, grid, 256, st, a);
     else LAUNCH(k_apply<false>, grid, 256, st, a);
     KMARK(RCT_TK_APPLY);
     return mark(p, st);
@@ -1088,6 +1101,14 @@ static int warp_launch(const uint8_t *stylized, const uint8_t *prev, const float
     int dev, rc = ensure_device(&dev);
     if (rc) return rc;
     WarpArgs g{stylized, prev, flow, out, n, H, W, channels, (float)alpha, (float)(1.0 - alpha)};
+    const bool rgb4 = channels == 3 && W % 4 == 0 && (((uintptr_t)flow) & 15) == 0 &&
+                      ((((uintptr_t)prev) | ((uintptr_t)out) | ((uintptr_t)stylized)) & 3) == 0;
+    if (rgb4) {  // four pixels per thread, vector loads / stores
+        const unsigned blocks = flat_blocks((size_t)n * H * W / 4, dev);
+        if (blend) LAUNCH(k_warp_blend_rgb4<true>, blocks, 256, (cudaStream_t)stream, g);
+        else LAUNCH(k_warp_blend_rgb4<false>, blocks, 256, (cudaStream_t)stream, g);
+        return RCT_OK;
+    }
     const unsigned blocks = flat_blocks((size_t)n * H * W, dev);
     if (blend) LAUNCH(k_warp_blend<true>, blocks, 256, (cudaStream_t)stream, g);
     else LAUNCH(k_warp_blend<false>, blocks, 256, (cudaStream_t)stream, g);
@@ -1259,6 +1280,14 @@ int rct_plan_debug_lut(rct_plan *p, int slot, uint32_t *lut_host)
     CK(cudaSetDevice(p->device));
     CK(cudaDeviceSynchronize());
     CK(cudaMemcpy(lut_host, p->lut + (size_t)slot * p->L.lut_stride_u32, 4 * (size_t)kCube, cudaMemcpyDeviceToHost));
+    if (p->lut_mode) {  // expand run index + palette to the uint32 RGB per colour the caller expects
+        const uint16_t *idx = reinterpret_cast<const uint16_t *>(lut_host);
+        uint32_t *pal = new (std::nothrow) uint32_t[kPaletteCap];
+        if (!pal) return fail(RCT_ERR_NOMEM, "out of host memory");
+        memcpy(pal, lut_host + kPaletteOffsetU32, sizeof(uint32_t) * kPaletteCap);
+        for (size_t c = (size_t)kCube; c-- > 0;) lut_host[c] = pal[idx[c]];  // descending: idx[c] lies below lut_host[c]
+        delete[] pal;
+    }
     return RCT_OK;
 }
 

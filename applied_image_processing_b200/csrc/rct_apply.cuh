@@ -110,6 +110,12 @@ __device__ __forceinline__ uint32_t ldg_hint(const unsigned *p, unsigned long lo
     asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
     return v;
 }
+__device__ __forceinline__ uint32_t ldg_u16_hint(const unsigned short *p, unsigned long long pol)
+{
+    unsigned short v;
+    asm volatile("ld.global.nc.L2::cache_hint.u16 %0, [%1], %2;" : "=h"(v) : "l"(p), "l"(pol));
+    return (uint32_t)v;
+}
 __device__ __forceinline__ void stg8_hint(void *p, uint32_t x, uint32_t y, unsigned long long pol)
 {
     asm volatile("st.global.L1::no_allocate.L2::cache_hint.v2.u32 [%0], {%1,%2}, %3;" ::"l"(p), "r"(x), "r"(y), "l"(pol)
@@ -305,7 +311,7 @@ __device__ __forceinline__ void cp_async_wait()
 }
 
 // 8 pixels: 6 words each of content / stylised, 2 words of mask -> 6 output words
-template <bool HINT>
+template <bool HINT, int LUTM = 0>
 __device__ __forceinline__ void apply8(const uint32_t wc[6], const uint32_t ws[6], const uint32_t wm[2],
                                        const unsigned *lut, int status, uint32_t wo[6], unsigned long long pol_lut)
 {
@@ -327,10 +333,21 @@ __device__ __forceinline__ void apply8(const uint32_t wc[6], const uint32_t ws[6
         }
     }
     uint32_t t[8];
+    if (LUTM) {  // uint16 run index (L2-resident table), then the palette (L1-resident)
+        const unsigned short *l16 = reinterpret_cast<const unsigned short *>(lut);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const unsigned *g = lut + (((want >> k) & 1u) ? c[k] : 0u);
-        t[k] = HINT ? ldg_hint(g, pol_lut) : __ldg(g);
+        for (int k = 0; k < 8; ++k) {
+            const unsigned short *g = l16 + (((want >> k) & 1u) ? c[k] : 0u);
+            t[k] = HINT ? ldg_u16_hint(g, pol_lut) : (uint32_t)__ldg(g);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t[k] = __ldg(lut + kPaletteOffsetU32 + t[k]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const unsigned *g = lut + (((want >> k) & 1u) ? c[k] : 0u);
+            t[k] = HINT ? ldg_hint(g, pol_lut) : __ldg(g);
+        }
     }
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
@@ -367,7 +384,7 @@ __device__ __forceinline__ void bulk_s2g_hint(void *dst_gmem, const void *src_sm
 // OST = true: the output tile goes through shared memory and leaves with ONE cp.async.bulk store
 // per tile (the register flavour's three 8-byte stores per lane, 24 bytes apart, touch every 32-byte
 // sector of the tile three times: ncu shows the L1 -> crossbar request port 83 % busy on image N)
-template <bool BULK, int PXL, int MINB, int STG = 2, bool OST = false>
+template <bool BULK, int PXL, int MINB, int STG = 2, bool OST = false, int LUTM = 0>
 __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
     k_apply_warp(PixArgs a, unsigned tiles_per_frame, unsigned nslots)
 {
@@ -488,7 +505,7 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
             if (OST) {
                 static_assert(!OST || (BULK && PXL == 8), "bulk-store flavour: bulk loads, 256-pixel tiles");
                 const unsigned ob = i & 1u;
-                if (active) apply8<true>(wc, ws, wm, lut, status, wo, pol_lut);
+                if (active) apply8<true, LUTM>(wc, ws, wm, lut, status, wo, pol_lut);
                 if (lane == 0) bulk_wait_read<1>();  // the store of tile i-2 has read o[ob]
                 __syncwarp();
                 if (active) {
@@ -504,7 +521,7 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
                     bulk_commit();
                 }
             } else if (active) {
-                apply8<BULK>(wc, ws, wm, lut, status, wo, pol_lut);  // the cp.async flavour runs without L2 hints (A/B)
+                apply8<BULK, LUTM>(wc, ws, wm, lut, status, wo, pol_lut);  // the cp.async flavour runs without L2 hints (A/B)
                 uint8_t *qo = a.out + (size_t)slot * a.out_stride + 3 * p0 + 24u * lane;
                 if (BULK) {
                     stg8_hint(qo, wo[0], wo[1], pol_stream);

@@ -30,6 +30,8 @@ constexpr int kFineMax = kFineTarget + kCoarse;  // upper bound on fine bins per
 constexpr int kPartT = 2048;            // entries per part aimed at (part < kPartT + largest fine bin)
 constexpr int kPartCap = 4096;          // entries a part may have to be sorted in shared memory
 constexpr int kFillStride = 32;         // uint32 stride of the per-part fill counters (128 B apart)
+constexpr unsigned kPaletteCap = 65536;               // palette LUT: run indices are uint16
+constexpr size_t kPaletteOffsetU32 = (size_t)1 << 23;  // the palette sits behind the 2^24 uint16 indices of a slot's LUT
 
 struct RegionCtrl {
     unsigned long long n_pix;           // region pixel count N (non-black pixels)
@@ -66,7 +68,8 @@ struct FrontCtrl {
 struct FrameCtrl {
     RegionCtrl r[2];
     int status;
-    int pad_[3];
+    unsigned n_palette;  // runs of equal output colour along the sorted target (palette LUT)
+    int pad_[2];
     FrontCtrl front;
 };
 
@@ -202,8 +205,9 @@ struct PixArgs {
     const int *xtab, *ytab;                                      // NULL when no resample
     unsigned *hist;        // slot 0; slot s at + s*hist_stride (uint32 units): [2][2^24]
     size_t hist_stride;
-    const unsigned *lut;   // slot 0; [2^24] per slot
+    const unsigned *lut;   // slot 0; per slot [2^24] uint32 RGB, or (lut_mode 1) [2^24] uint16 run indices + palette
     size_t lut_stride;
+    int lut_mode;
     FrameCtrl *ctrl;       // [slots]
     int *status_out;       // [slots] or NULL
     int W, sw;
@@ -278,7 +282,7 @@ __global__ void __launch_bounds__(256) k_hist(PixArgs a)
 
 // k_apply: a-7..a-9 for pixels: target non-black -> LUT[colour]; target black -> black;
 // MASK mode non-target -> stylised pixel (background_np); LABEL mode non-target untouched.
-template <bool RESAMPLE>
+template <bool RESAMPLE, int LUTM = 0>
 __global__ void __launch_bounds__(256, 3) k_apply(PixArgs a)
 {
     const int slot = blockIdx.y;
@@ -319,7 +323,14 @@ __global__ void __launch_bounds__(256, 3) k_apply(PixArgs a)
         uint32_t t[16];
 #pragma unroll
         for (int k = 0; k < 16; ++k)
-            t[k] = __ldg(lut + ((((tgt >> k) & 1u) && status == 0 && k < nvalid) ? c[k] : 0u));
+        {
+            const uint32_t idx = (((tgt >> k) & 1u) && status == 0 && k < nvalid) ? c[k] : 0u;
+            t[k] = LUTM ? (uint32_t)__ldg(reinterpret_cast<const unsigned short *>(lut) + idx) : __ldg(lut + idx);
+        }
+        if (LUTM) {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) t[k] = __ldg(lut + kPaletteOffsetU32 + t[k]);
+        }
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
             uint32_t v = 0;

@@ -689,10 +689,108 @@ __device__ double match_one(const Sorted &t, const Sorted &s, unsigned p, unsign
     return m;
 }
 
+// ------------------------------------------------------------------------------------------
+// Palette LUT (RCT_OPT_LUT = 1).  Every recoloured target pixel lies on the one-dimensional curve
+// mean + m * component (a-7), and m is non-decreasing along the sorted target entries, so the
+// output colours along the sorted order form a few thousand runs of equal RGB (each channel is a
+// sum of three exponentials in m: at most three monotone pieces of at most 256 uint8 steps).
+// The colour -> RGB table therefore factors into a uint16 run index per colour (32 MiB instead of
+// 64 MiB per frame: it stays L2-resident while the apply pass walks the frame) and a palette of
+// the run colours (a few KB, L1-resident).
+//   k_match      writes the output colour of sorted entry i to rgb_sorted[i]
+//   k_pal_count  run starts per part          -> pfill[part] (the scatter counters are dead by now)
+//   k_pal_scan   exclusive scan over the parts -> run index of each part's first entry; n_palette
+//   k_pal_write  lut16[colour] = run index, palette[run] = colour
+// rgb_sorted lives in the target job's unsorted-key array (dead after k_scatter).
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned *pal_rgb_sorted(const Job &jt)
+{
+    return reinterpret_cast<unsigned *>(const_cast<double *>(jt.keyA));
+}
+__device__ __forceinline__ bool pal_run_start(const unsigned *rgb, unsigned i)
+{
+    return i == 0u || __ldg(rgb + i) != __ldg(rgb + i - 1);
+}
+
+constexpr int kPalThreads = 256;
+__global__ void __launch_bounds__(kPalThreads) k_pal_count(FrameCtrl *ctrl, const Job *jobs)
+{
+    const int slot = blockIdx.y;
+    if (ctrl[slot].status != 0) return;
+    const Job &jt = jobs[2 * slot];
+    const unsigned p = blockIdx.x;
+    if (p >= jt.rc->n_parts) return;
+    const unsigned ps = jt.pstart[p], pe = jt.pstart[p + 1];
+    const unsigned *rgb = pal_rgb_sorted(jt);
+    unsigned c = 0;
+    for (unsigned i = ps + threadIdx.x; i < pe; i += kPalThreads) c += pal_run_start(rgb, i) ? 1u : 0u;
+    __shared__ unsigned s_w[kPalThreads / 32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31u) == 0) s_w[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned t = 0;
+        for (int w = 0; w < kPalThreads / 32; ++w) t += s_w[w];
+        jt.pfill[(size_t)p * kFillStride] = t;
+    }
+}
+
+// one CTA of 1024 threads per slot
+__global__ void __launch_bounds__(1024) k_pal_scan(FrameCtrl *ctrl, const Job *jobs)
+{
+    const int slot = blockIdx.x;
+    if (ctrl[slot].status != 0) return;
+    const Job &jt = jobs[2 * slot];
+    __shared__ unsigned s_warp[33];
+    const unsigned np = jt.rc->n_parts;
+    unsigned carry = 0;
+    for (unsigned base = 0; base < np; base += 1024) {
+        const unsigned i = base + threadIdx.x;
+        unsigned v = i < np ? jt.pfill[(size_t)i * kFillStride] : 0u, total;
+        const unsigned ex = block_excl_scan(v, s_warp, total);
+        if (i < np) jt.pfill[(size_t)i * kFillStride] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) {
+        ctrl[slot].n_palette = carry;
+        if (carry > kPaletteCap) ctrl[slot].status = 3;  // cannot happen for a-7's curve; apply keeps the content, hosts raise
+    }
+}
+
+__global__ void __launch_bounds__(kPalThreads) k_pal_write(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0, size_t lut_stride)
+{
+    const int slot = blockIdx.y;
+    if (ctrl[slot].status != 0) return;
+    const Job &jt = jobs[2 * slot];
+    const unsigned p = blockIdx.x;
+    if (p >= jt.rc->n_parts) return;
+    const unsigned ps = jt.pstart[p], pe = jt.pstart[p + 1];
+    const unsigned *rgb = pal_rgb_sorted(jt);
+    unsigned short *lut16 = reinterpret_cast<unsigned short *>(lut0 + (size_t)slot * lut_stride);
+    unsigned *palette = lut0 + (size_t)slot * lut_stride + kPaletteOffsetU32;
+    __shared__ unsigned s_warp[33];
+    unsigned run = jt.pfill[(size_t)p * kFillStride];  // runs started before this part
+    for (unsigned i0 = ps; i0 < pe; i0 += kPalThreads) {
+        const unsigned i = i0 + threadIdx.x;
+        const bool live = i < pe;
+        const unsigned f = (live && pal_run_start(rgb, i)) ? 1u : 0u;
+        unsigned total;
+        const unsigned ex = block_excl_scan(f, s_warp, total);
+        if (live) {
+            const unsigned idx = run + ex + f - 1u;  // runs started up to and including i, minus one
+            lut16[rec_pay(__ldg(jt.recP + i))] = (unsigned short)idx;
+            if (f) palette[idx] = __ldg(rgb + i);
+        }
+        run += total;
+    }
+}
+
 // pipeline flavour: jobs[2*slot] = target, jobs[2*slot+1] = source; one CTA per target part.
 // Writes the colour -> output-RGB LUT (a-7: inverse_transform, lab -> rgb, clip, truncate).
 constexpr int kMatchThreads = 128;
-__global__ void __launch_bounds__(kMatchThreads) k_match(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0,
+template <int LUTM>
+__device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0,
                                                          size_t lut_stride, double *dbg_matched0, long long *dbg_j0,
                                                          size_t dbg_stride, int interleave)
 {
@@ -708,6 +806,7 @@ __global__ void __launch_bounds__(kMatchThreads) k_match(FrameCtrl *ctrl, const 
     stage_tabs(&T);
     const Pca pca = jt.rc->pca;
     unsigned *lut = lut0 + (size_t)slot * lut_stride;
+    unsigned *rgb_sorted = pal_rgb_sorted(jt);
     Hint ht{0, 0, false, false}, hs{0, 0, false, false};
     // interleave: the CTA sweeps the part 128 consecutive entries at a time, so neighbouring lanes
     // read neighbouring target and source records (coalesced, L1-resident) and every source
@@ -724,12 +823,29 @@ __global__ void __launch_bounds__(kMatchThreads) k_match(FrameCtrl *ctrl, const 
         double lab[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) lab[c] = m * pca.comp[c] + pca.mean[c];  // inverse_transform
-        lut[rec_pay(__ldg(t.rec + i))] = lab2rgb(lab, &T, nullptr);
+        // palette LUT: the colour goes to its sorted position (k_pal_* turn the runs of equal colours
+        // into indices); otherwise straight into the colour-indexed table
+        unsigned *dst = LUTM ? rgb_sorted + i : lut + rec_pay(__ldg(t.rec + i));
+        *dst = lab2rgb(lab, &T, nullptr);
         if (dbg_matched0) {
             dbg_matched0[(size_t)slot * dbg_stride + i] = m;
             dbg_j0[(size_t)slot * dbg_stride + i] = j;
         }
     }
+}
+
+__global__ void __launch_bounds__(kMatchThreads) k_match(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0, size_t lut_stride,
+                                                         double *dbg_matched0, long long *dbg_j0, size_t dbg_stride,
+                                                         int interleave)
+{
+    match_body<0>(ctrl, jobs, lut0, lut_stride, dbg_matched0, dbg_j0, dbg_stride, interleave);
+}
+// palette flavour (RCT_OPT_LUT = 1): output colours go to their sorted position, see k_pal_*
+__global__ void __launch_bounds__(kMatchThreads, 7) k_match_pal(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0,
+                                                                size_t lut_stride, double *dbg_matched0, long long *dbg_j0,
+                                                                size_t dbg_stride, int interleave)
+{
+    match_body<1>(ctrl, jobs, lut0, lut_stride, dbg_matched0, dbg_j0, dbg_stride, interleave);
 }
 
 // generic flavour (rct_match_cdf): jobs[0] = target, jobs[1] = source; payload = input index

@@ -59,6 +59,72 @@ __device__ __forceinline__ uint32_t blend_u8(uint32_t s, uint32_t w, const float
     return (uint32_t)(int)r;  // astype(uint8) of a value in [0,255]: truncation
 }
 
+// one bilinear sample of cv2.remap at map (mx, my): 3 interleaved channels packed r | g<<8 | b<<16
+__device__ __forceinline__ uint32_t remap3(const uint8_t *img, int H, int W, float mx, float my)
+{
+    const int sx = cv_fix5(mx), sy = cv_fix5(my);
+    const int ix = clamp_short(sx >> 5), iy = clamp_short(sy >> 5), fx = sx & 31, fy = sy & 31;
+    int x0 = ix, x1 = ix + 1, y0 = iy, y1 = iy + 1;
+    if ((unsigned)ix >= (unsigned)(W - 1) || (unsigned)iy >= (unsigned)(H - 1)) {  // a tap leaves the image
+        x0 = cv_reflect(ix, W); x1 = cv_reflect(ix + 1, W);
+        y0 = cv_reflect(iy, H); y1 = cv_reflect(iy + 1, H);
+    }
+    const int w00 = (32 - fx) * (32 - fy) * 32, w01 = fx * (32 - fy) * 32, w10 = (32 - fx) * fy * 32, w11 = fx * fy * 32;
+    const uint8_t *p00 = img + ((size_t)y0 * W + x0) * 3, *p01 = img + ((size_t)y0 * W + x1) * 3;
+    const uint8_t *p10 = img + ((size_t)y1 * W + x0) * 3, *p11 = img + ((size_t)y1 * W + x1) * 3;
+    uint32_t out = 0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const int v = (w00 * (int)__ldg(p00 + c) + w01 * (int)__ldg(p01 + c) + w10 * (int)__ldg(p10 + c) +
+                       w11 * (int)__ldg(p11 + c) + (1 << 14)) >> 15;
+        out |= (uint32_t)v << (8 * c);
+    }
+    return out;
+}
+
+// RGB fast path: W % 4 == 0, flow 16-byte aligned, images 4-byte aligned.  Four pixels per thread:
+// two float4 flow loads, three 32-bit stylised loads, three 32-bit stores; the taps go through
+// the read-only path (neighbouring pixels share cache lines).
+template <bool BLEND>
+__global__ void __launch_bounds__(256) k_warp_blend_rgb4(WarpArgs g)
+{
+    __shared__ float s_a[256], s_b[256];
+    if (BLEND) blend_tables(g.a, g.b, s_a, s_b);
+    const size_t plane = (size_t)g.H * g.W, quads = plane / 4, total = quads * (size_t)g.n;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int f = (int)(i / quads);
+        const size_t q = i - (size_t)f * quads, p = 4 * q;
+        const int y = (int)(p / g.W), x = (int)(p - (size_t)y * g.W);
+        const float *fl = g.flow + (size_t)f * 2 * plane;
+        const float4 fx4 = __ldcs(reinterpret_cast<const float4 *>(fl + p));
+        const float4 fy4 = __ldcs(reinterpret_cast<const float4 *>(fl + plane + p));
+        const float fxs[4] = {fx4.x, fx4.y, fx4.z, fx4.w}, fys[4] = {fy4.x, fy4.y, fy4.z, fy4.w};
+        const uint8_t *img = g.prev + (size_t)f * plane * 3;
+        uint32_t c[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            c[k] = remap3(img, g.H, g.W, (float)((double)(x + k) + (double)fxs[k]), (float)((double)y + (double)fys[k]));
+        if (BLEND) {
+            const uint32_t *sw = reinterpret_cast<const uint32_t *>(g.stylized + ((size_t)f * plane + p) * 3);
+            const uint32_t w0 = __ldcs(sw), w1 = __ldcs(sw + 1), w2 = __ldcs(sw + 2);
+            const uint32_t s[4] = {w0 & 0xffffffu, __funnelshift_r(w0, w1, 24) & 0xffffffu,
+                                   __funnelshift_r(w1, w2, 16) & 0xffffffu, w2 >> 8};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                uint32_t o = 0;
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch)
+                    o |= blend_u8((s[k] >> (8 * ch)) & 255u, (c[k] >> (8 * ch)) & 255u, s_a, s_b) << (8 * ch);
+                c[k] = o;
+            }
+        }
+        uint32_t *ow = reinterpret_cast<uint32_t *>(g.out + ((size_t)f * plane + p) * 3);
+        __stcs(ow, c[0] | (c[1] << 24));
+        __stcs(ow + 1, (c[1] >> 8) | (c[2] << 16));
+        __stcs(ow + 2, (c[2] >> 16) | (c[3] << 8));
+    }
+}
+
 template <bool BLEND>
 __global__ void __launch_bounds__(256) k_warp_blend(WarpArgs g)
 {

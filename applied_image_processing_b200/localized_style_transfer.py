@@ -162,6 +162,8 @@ def _warn(status: int):
         print("Warning: No foreground pixels found.")
     elif status == _cabi.RCT_EMPTY_SOURCE:
         print("Warning: No background pixels found for color transfer.")
+    elif status == 3:
+        raise _cabi.RctError("palette LUT overflow (> 65536 runs of output colour): set OPT_LUT to 0 for this plan")
 
 
 def _np_u8(a, name):

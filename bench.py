@@ -64,6 +64,8 @@ def parse_args():
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--lut", type=int, default=0, choices=[0, 1],
+                    help="RCT_OPT_LUT: 0 uint32 RGB per colour (default), 1 uint16 run index + palette (A/B runs)")
     ap.add_argument("--sty-short", type=int, default=0,
                     help="stylised frames at this short-side size (512 = what AdaIN's Resize(512) hands the reference, "
                          "LST:223-230), NEAREST-resampled inside the kernels; 0 = same size as the content")
@@ -313,6 +315,7 @@ def run_gpu_arm(a):
     plan.set_option(_cabi.OPT_FRONTEND, a.front)
     plan.set_option(_cabi.OPT_APPLY, a.apply)
     plan.set_option(_cabi.OPT_MATCH, a.match)
+    plan.set_option(_cabi.OPT_LUT, a.lut)
     st = torch.cuda.current_stream().cuda_stream
 
     def step():

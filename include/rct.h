@@ -100,6 +100,11 @@ int rct_plan_destroy(rct_plan *plan);
 /* RCT_OPT_STAGE_SETS (2..4, default 4): device staging sets of rct_transfer_host; group k is copied
    in while group k-1 computes and group k-2 is copied out. */
 #define RCT_OPT_STAGE_SETS 6
+/* RCT_OPT_LUT: layout of the per-frame colour -> output table.  0 (default): uint32 RGB per colour (64 MiB);
+ * 1: uint16 run index per colour (32 MiB, L2-resident during the apply pass) + palette of the run colours --
+ * the apply pass gets 1.5x faster on noisy images, the three extra solve kernels cost more than that
+ * (measured, profiles/r01_summary_v10.md), so it stays opt-in. */
+#define RCT_OPT_LUT 7
 int rct_plan_set_option(rct_plan *plan, int option, int value);
 /* accumulated device time per phase since the last reset, in ms: [0] workspace memsets,
  * [1] k_hist (pixels -> colour histograms), [2] solve (compact .. match -> LUT), [3] k_apply

@@ -115,6 +115,28 @@ def test_cuda_deeplab_postprocessing():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("thr", [0.5, 0.3, 0.9])
+def test_cuda_softmax_mask_fast_path_and_guard_band(thr):
+    """Vectorised float32 fast path (npix % 4 == 0) with the float64 re-evaluation inside the guard band:
+    a third of the pixels are constructed to sit within ~1e-6 of the threshold."""
+    from applied_image_processing_b200 import adjacent
+
+    rng = np.random.default_rng(9)
+    H, W = 212, 316
+    logits = rng.normal(0, 3, (21, H, W)).astype(np.float32)
+    # rows 0..69: 20 equal competitors a, class 0 at a + ln(20 thr / (1 - thr)) + tiny -> p0 = thr +- ~1e-7
+    a = rng.normal(0, 2, (70, W)).astype(np.float32)
+    logits[1:, :70] = a
+    logits[0, :70] = a + np.float32(np.log(20 * thr / (1 - thr))) + rng.normal(0, 2e-6, (70, W)).astype(np.float32)
+    want, p = aorc.softmax_mask(logits, thr)
+    got = adjacent.deeplab_background_mask(torch.from_numpy(logits).cuda(), thr)
+    decidable = np.abs(p - np.float64(np.float32(thr))) > 1e-12
+    assert (np.abs(p[:70] - thr) < 1e-4).mean() > 0.9          # the band really is populated
+    assert np.array_equal(got[0][decidable], want[0][decidable])
+    assert 0 < got[0, :70].mean() < 1
+
+
+@pytest.mark.gpu
 def test_blend_feeds_the_colour_transfer_without_a_file_round_trip():
     """f-1 -> hot path on the device: the uint8 image the blend emits is what save_image would have
     written (before JPEG), and goes straight into regional_color_transfer as the stylised input."""

@@ -423,6 +423,36 @@ def test_tma_staged_resample_apply(H, W, sh, sw):
     assert np.array_equal(out.cpu().numpy(), refs)
 
 
+@pytest.mark.parametrize("case", ["U", "N", "resample", "tiny_target"])
+def test_lut_layouts_agree(case):
+    """RCT_OPT_LUT: uint16 run indices + palette (opt-in) against the uint32 RGB table (default) and the
+    oracle, through the bulk-async and the register-staged apply kernels."""
+    H, W, sh, sw = 360, 640, 360, 640
+    fg = 0.4
+    if case == "resample":
+        sh, sw = 256, 448
+    if case == "tiny_target":
+        fg = 0.01
+    kind = "N" if case == "N" else "U"
+    c, s = synth.synth_image(H, W, 31, kind), synth.synth_image(sh, sw, 32, "N" if case == "resample" else kind)
+    mask = synth.ellipse_mask(H, W, fg, 4)
+    ref, st, _ = orc.transfer(c, s, mask)
+    assert st == 0
+    luts = []
+    for lut_mode in (1, 0):
+        for apply_opt in (1, 0):
+            plan = _debug_plan(H, W, sh, sw)
+            plan.set_option(_cabi.OPT_LUT, lut_mode)
+            plan.set_option(_cabi.OPT_APPLY, apply_opt)
+            out = _run_plan(plan, c, s, mask)
+            assert np.array_equal(out, ref), (lut_mode, apply_opt, int((out != ref).sum()))
+        luts.append(plan.debug_lut())
+    col = c[..., 0].astype(np.uint32) | (c[..., 1].astype(np.uint32) << 8) | (c[..., 2].astype(np.uint32) << 16)
+    sel = (mask == 0) & (col > 0)
+    assert np.array_equal(luts[0][col[sel]], luts[1][col[sel]])
+    assert len(np.unique(luts[0][col[sel]])) <= 3 * 3 * 256  # a-7: the outputs lie on one curve
+
+
 def test_partition_front_end_all_and_label_modes():
     """Two-pass item generation (a pixel feeds both regions) of the partition front end."""
     H, W = 200, 304
