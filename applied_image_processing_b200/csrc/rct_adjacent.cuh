@@ -86,6 +86,60 @@ __global__ void __launch_bounds__(256) k_mask_blend(BlendArgs a)
     }
 }
 
+// W % 4 == 0 and 16-byte aligned planes: four pixels of one row per thread -- the row's taps are
+// computed once, content / stylized move as float4, rgb8 as three 32-bit words.  Same arithmetic,
+// same order of operations as k_mask_blend.
+__global__ void __launch_bounds__(256) k_mask_blend4(BlendArgs a)
+{
+    const float sy_o = (float)a.oh / (float)a.H, sx_o = (float)a.ow / (float)a.W;
+    const float sy_m = (float)a.mh / (float)a.H, sx_m = (float)a.mw / (float)a.W;
+    const size_t plane = (size_t)a.H * a.W, oplane = (size_t)a.oh * a.ow, quads = plane / 4;
+    const size_t total = quads * (size_t)a.N;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int n = (int)(i / quads);
+        const size_t p = 4 * (i - (size_t)n * quads);
+        const int y = (int)(p / a.W), x = (int)(p - (size_t)y * a.W);
+        int y0, y1;
+        float ly0, ly1;
+        torch_linear_taps(y, sy_o, a.oh, y0, y1, ly0, ly1);
+        const float *mrow = a.mask + (size_t)n * a.mask_stride + (size_t)torch_nearest_idx(y, sy_m, a.mh) * a.mw;
+        int x0[4], x1[4];
+        float lx0[4], lx1[4], m[4], om[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            torch_linear_taps(x + k, sx_o, a.ow, x0[k], x1[k], lx0[k], lx1[k]);
+            m[k] = __ldg(mrow + torch_nearest_idx(x + k, sx_m, a.mw));
+            om[k] = __fsub_rn(1.f, m[k]);
+        }
+        uint32_t packed[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float *o = a.output + ((size_t)n * 3 + c) * oplane;
+            const float *r0 = o + (size_t)y0 * a.ow, *r1 = o + (size_t)y1 * a.ow;
+            const float4 cv4 = __ldcs(reinterpret_cast<const float4 *>(a.content + ((size_t)n * 3 + c) * plane + p));
+            const float cv[4] = {cv4.x, cv4.y, cv4.z, cv4.w};
+            float r[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float top = __fadd_rn(__fmul_rn(lx0[k], __ldg(r0 + x0[k])), __fmul_rn(lx1[k], __ldg(r0 + x1[k])));
+                const float bot = __fadd_rn(__fmul_rn(lx0[k], __ldg(r1 + x0[k])), __fmul_rn(lx1[k], __ldg(r1 + x1[k])));
+                const float up = __fadd_rn(__fmul_rn(ly0, top), __fmul_rn(ly1, bot));
+                r[k] = __fadd_rn(__fmul_rn(cv[k], om[k]), __fmul_rn(up, m[k]));
+                float q = __fadd_rn(__fmul_rn(r[k], 255.f), 0.5f);
+                q = q < 0.f ? 0.f : (q > 255.f ? 255.f : q);
+                packed[k] |= (uint32_t)(uint8_t)q << (8 * c);
+            }
+            __stcs(reinterpret_cast<float4 *>(a.stylized + ((size_t)n * 3 + c) * plane + p), make_float4(r[0], r[1], r[2], r[3]));
+        }
+        if (a.rgb8) {
+            uint32_t *d = reinterpret_cast<uint32_t *>(a.rgb8 + 3 * ((size_t)n * plane + p));
+            d[0] = packed[0] | (packed[1] << 24);
+            d[1] = (packed[1] >> 8) | (packed[2] << 16);
+            d[2] = (packed[2] >> 16) | (packed[3] << 8);
+        }
+    }
+}
+
 // logits [C, npix] float32 (one image; the reference handles one image per call, LST:176).
 // The decision is DEFINED as the float64 evaluation p_cls = 1 / sum_i exp(x_i - x_cls) > threshold
 // (it differs from a float32 softmax only inside a ~1e-7 band around the threshold).  Evaluating

@@ -1066,7 +1066,9 @@ int rct_adain_mask_blend(const float *content, const float *output, const float 
     int dev, rc = ensure_device(&dev);
     if (rc) return rc;
     BlendArgs a{content, output, mask, stylized, rgb8, n, H, W, oh, ow, mh, mw, mask_stride};
-    LAUNCH(k_mask_blend, flat_blocks((size_t)n * H * W, dev), 256, (cudaStream_t)stream, a);
+    const bool vec4 = W % 4 == 0 && ((((uintptr_t)content) | ((uintptr_t)stylized)) & 15) == 0 && (((uintptr_t)rgb8) & 3) == 0;
+    if (vec4) LAUNCH(k_mask_blend4, flat_blocks((size_t)n * H * W / 4, dev), 256, (cudaStream_t)stream, a);
+    else LAUNCH(k_mask_blend, flat_blocks((size_t)n * H * W, dev), 256, (cudaStream_t)stream, a);
     return RCT_OK;
 }
 

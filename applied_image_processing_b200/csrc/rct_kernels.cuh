@@ -182,14 +182,22 @@ __device__ __forceinline__ void gather16_rgb(const uint8_t *sty, const int *__re
     int y = (int)(p0 / (size_t)W);
     int x = (int)(p0 - (size_t)y * (size_t)W);
     size_t rowoff = (size_t)__ldg(ytab + y) * (size_t)sw;
+    int prev = -1;       // source x of the previous pixel: up-sampling repeats source pixels, which
+    uint32_t pv = 0;     // are then taken from the register instead of three more byte loads
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
         if (k < nvalid) {
-            const uint8_t *p = sty + 3 * (rowoff + (size_t)__ldg(xtab + x));
-            c[k] = (uint32_t)__ldg(p) | ((uint32_t)__ldg(p + 1) << 8) | ((uint32_t)__ldg(p + 2) << 16);
+            const int xs = __ldg(xtab + x);
+            if (xs != prev) {
+                const uint8_t *p = sty + 3 * (rowoff + (size_t)xs);
+                pv = (uint32_t)__ldg(p) | ((uint32_t)__ldg(p + 1) << 8) | ((uint32_t)__ldg(p + 2) << 16);
+                prev = xs;
+            }
+            c[k] = pv;
             if (++x == W) {
                 x = 0;
                 ++y;
+                prev = -1;
                 if (k + 1 < nvalid) rowoff = (size_t)__ldg(ytab + y) * (size_t)sw;
             }
         } else {

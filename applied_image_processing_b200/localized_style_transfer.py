@@ -370,6 +370,17 @@ def regional_color_transfer(content, stylized, background_mask, slots=None, out=
 def regional_color_transfer_labels(content, stylized, labels, n_labels, slots=None):
     """BASELINE.json config 5 (no counterpart in the reference): for every label l the content
     pixels with that label are matched to the stylised pixels with that label."""
+    if not _is_tensor(content):
+        # numpy calling convention: one upload, the n_labels passes on the device, one download
+        # (per-pass host round trips would move every image 2 * n_labels times over PCIe)
+        dev = _require_cuda()
+        c, s, l = (torch.from_numpy(_np_u8(x, nm)).to(dev, non_blocking=True)
+                   for x, nm in ((content, "content"), (stylized, "stylised"), (labels, "labels")))
+        if c.dim() == 4 and s.dim() == 3:
+            s = s.unsqueeze(0).expand(c.shape[0], -1, -1, -1).contiguous()
+        if c.dim() == 4 and l.dim() == 2:
+            l = l.unsqueeze(0).expand(c.shape[0], -1, -1).contiguous()
+        return regional_color_transfer_labels(c, s, l, n_labels, slots=slots).cpu().numpy()
     out = None
     for lab in range(n_labels):
         out = _transfer(content, stylized, labels, MODE_LABEL, label=lab, out=out, slots=slots, quiet=True)
