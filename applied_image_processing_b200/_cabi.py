@@ -54,6 +54,7 @@ SIGNATURES = {
     "rct_kernel_timing_name": (C.c_char_p, [_i]),
     "rct_transfer_async": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _sz, _vp, _sz, _i, _i, _i, _vp]),
     "rct_plan_status": (_i, [_vp, _vp, _i, _vp]),
+    "rct_transfer_labels_async": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _sz, _vp, _sz, _i, _i, _vp]),
     "rct_transfer_host": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "rct_shard_hist_async": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "rct_plan_hist_ptr": (_vp, [_vp]),

@@ -189,6 +189,7 @@ struct rct_plan {
     cudaStream_t own_stream;            // compute stream of the host entry point
     cudaStream_t h2d_stream, d2h_stream; // copy streams of the host entry point (overlap with compute)
     cudaEvent_t ev_in[kStageSetsMax], ev_comp[kStageSetsMax], ev_out[kStageSetsMax];
+    int lpf;         // labels per frame of the call in progress (rct_transfer_labels_async), else 1
     int lut_mode;    // RCT_OPT_LUT: 1 = uint16 run indices + palette, 0 = uint32 RGB per colour
     int stage_sets;  // RCT_OPT_STAGE_SETS: staging sets of the host entry point (2..kStageSetsMax)
     // RCT_OPT_TIMING: five events per launch group (memset | k_hist | solve | k_apply)
@@ -274,6 +275,7 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     p->part_cap = kPartCap;
     p->stage_sets = 4;
     p->lut_mode = 0;
+    p->lpf = 1;
     if (workspace) {
         if (workspace_bytes < p->L.total) {
             delete p;
@@ -432,7 +434,7 @@ PixArgs pix_args(rct_plan *p, const FrameSet &f, int mode, int label, size_t p_b
     a.ctrl = p->ctrl; a.status_out = status_out;
     a.W = p->W; a.sw = p->sw;
     a.p_begin = p_begin; a.p_end = p_end;
-    a.mode = mode; a.label = label;
+    a.mode = mode; a.label = label; a.lpf = p->lpf > 0 ? p->lpf : 1;
     a.aggregate = p->aggregate;
     return a;
 }
@@ -817,6 +819,37 @@ int rct_plan_status(rct_plan *p, int *status_host, int n_frames, void *stream)
     CK(cudaMemcpyAsync(status_host, p->status_frames, sizeof(int) * (size_t)n_frames, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     return RCT_OK;
+}
+
+// BASELINE.json configs[4]: every label of a label map is an independent exact transfer (target =
+// content pixels with that label, source = stylised pixels with that label).  One launch group carries
+// slots / n_labels frames x n_labels labels as virtual slots (slot = frame * n_labels + label): the
+// solve runs all labels of all frames of the group side by side instead of n_labels small passes.
+// `out` must hold the values pixels of labels >= n_labels keep (normally a copy of content).
+int rct_transfer_labels_async(rct_plan *p, const uint8_t *content, size_t content_stride, const uint8_t *stylised,
+                              size_t stylised_stride, const uint8_t *labels, size_t labels_stride, uint8_t *out,
+                              size_t out_stride, int n_frames, int n_labels, void *stream)
+{
+    if (!p || !content || !stylised || !labels || !out || n_frames <= 0) return fail(RCT_ERR_ARG, "null/invalid argument");
+    if (n_labels <= 0 || n_labels > 256 || n_labels > p->slots)
+        return fail(RCT_ERR_ARG, "n_labels %d needs a plan with at least as many slots (has %d)", n_labels, p->slots);
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = ensure_status_frames(p, n_frames * n_labels);
+    if (rc) return rc;
+    const size_t npix = (size_t)p->H * (size_t)p->W;
+    const int fpg = p->slots / n_labels;  // frames per launch group
+    p->lpf = n_labels;
+    for (int f0 = 0; f0 < n_frames && rc == RCT_OK; f0 += fpg) {
+        const int nf = n_frames - f0 < fpg ? n_frames - f0 : fpg, ns = nf * n_labels;
+        FrameSet f{content + (size_t)f0 * content_stride, stylised + (size_t)f0 * stylised_stride,
+                   labels + (size_t)f0 * labels_stride, out + (size_t)f0 * out_stride,
+                   content_stride, stylised_stride, labels_stride, out_stride};
+        rc = p->front ? phase_front(p, f, ns, RCT_MODE_LABEL, 0, 0, npix, st) : phase_hist(p, f, ns, RCT_MODE_LABEL, 0, 0, npix, st);
+        if (rc == RCT_OK) rc = phase_solve(p, ns, st, !p->front);
+        if (rc == RCT_OK) rc = phase_apply(p, f, ns, RCT_MODE_LABEL, 0, 0, npix, p->status_frames + (size_t)f0 * n_labels, st);
+    }
+    p->lpf = 1;
+    return rc;
 }
 
 int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *stylised_h, const uint8_t *mask_h,

@@ -102,9 +102,10 @@ template <bool RESAMPLE, bool TWO_PASS>
 __global__ void __launch_bounds__(256, 3) k_front_count(PixArgs a)
 {
     const int slot = blockIdx.y;
-    const uint8_t *content = a.content + (size_t)slot * a.content_stride;
-    const uint8_t *sty = a.sty + (size_t)slot * a.sty_stride;
-    const uint8_t *mask = a.mask ? a.mask + (size_t)slot * a.mask_stride : nullptr;
+    const int frame = slot / a.lpf, label = a.label + slot % a.lpf;  // fused label pass: slot = (frame, label)
+    const uint8_t *content = a.content + (size_t)frame * a.content_stride;
+    const uint8_t *sty = a.sty + (size_t)frame * a.sty_stride;
+    const uint8_t *mask = a.mask ? a.mask + (size_t)frame * a.mask_stride : nullptr;
     __shared__ unsigned s_cnt[2 * kNB];
     for (int i = threadIdx.x; i < 2 * kNB; i += blockDim.x) s_cnt[i] = 0;
     __syncthreads();
@@ -121,8 +122,8 @@ __global__ void __launch_bounds__(256, 3) k_front_count(PixArgs a)
         {
             uint32_t c[16], s[16], m[16];
             front_load<RESAMPLE>(a, content, sty, mask, p0, nvalid, vec_c, vec_s, vec_m, c, s, m);
-            front_items(a.mode, a.label, c, s, m, mask != nullptr, nvalid, 0, it0);
-            if (TWO_PASS) front_items(a.mode, a.label, c, s, m, mask != nullptr, nvalid, 1, it1);
+            front_items(a.mode, label, c, s, m, mask != nullptr, nvalid, 0, it0);
+            if (TWO_PASS) front_items(a.mode, label, c, s, m, mask != nullptr, nvalid, 1, it1);
         }
         count_runs(it0, item_runs(it0), s_cnt);
         if (TWO_PASS) count_runs(it1, item_runs(it1), s_cnt);
@@ -165,9 +166,10 @@ template <bool RESAMPLE, bool TWO_PASS>
 __global__ void __launch_bounds__(kPartThreads, 2) k_front_part(PixArgs a, FrontArgs f)
 {
     const int slot = blockIdx.y;
-    const uint8_t *content = a.content + (size_t)slot * a.content_stride;
-    const uint8_t *sty = a.sty + (size_t)slot * a.sty_stride;
-    const uint8_t *mask = a.mask ? a.mask + (size_t)slot * a.mask_stride : nullptr;
+    const int frame = slot / a.lpf, label = a.label + slot % a.lpf;  // fused label pass: slot = (frame, label)
+    const uint8_t *content = a.content + (size_t)frame * a.content_stride;
+    const uint8_t *sty = a.sty + (size_t)frame * a.sty_stride;
+    const uint8_t *mask = a.mask ? a.mask + (size_t)frame * a.mask_stride : nullptr;
     FrontCtrl &fc = a.ctrl[slot].front;
     unsigned *items_t = f.items0 + (size_t)(2 * slot) * f.items_stride;
     unsigned *items_s = items_t + f.items_stride;
@@ -189,8 +191,8 @@ __global__ void __launch_bounds__(kPartThreads, 2) k_front_part(PixArgs a, Front
         {
             uint32_t c[16], s[16], m[16];
             front_load<RESAMPLE>(a, content, sty, mask, p0, nvalid, vec_c, vec_s, vec_m, c, s, m);
-            front_items(a.mode, a.label, c, s, m, mask != nullptr, nvalid, 0, it0);
-            if (TWO_PASS) front_items(a.mode, a.label, c, s, m, mask != nullptr, nvalid, 1, it1);
+            front_items(a.mode, label, c, s, m, mask != nullptr, nvalid, 0, it0);
+            if (TWO_PASS) front_items(a.mode, label, c, s, m, mask != nullptr, nvalid, 1, it1);
         }
         for (int pass = 0; pass < npass; ++pass) {
             for (int i = threadIdx.x; i < 2 * kNB; i += kPartThreads) s_cnt[i] = 0;

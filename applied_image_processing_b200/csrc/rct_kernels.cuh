@@ -221,6 +221,7 @@ struct PixArgs {
     int W, sw;
     size_t p_begin, p_end; // pixel range within a frame (row sharding)
     int mode, label;
+    int lpf;               // labels per frame of a fused label pass (slot = frame * lpf + label offset); else 1
     int aggregate;         // warp-aggregate equal colours before the atomic
 };
 
@@ -254,9 +255,10 @@ template <bool RESAMPLE>
 __global__ void __launch_bounds__(256) k_hist(PixArgs a)
 {
     const int slot = blockIdx.y;
-    const uint8_t *content = a.content + (size_t)slot * a.content_stride;
-    const uint8_t *sty = a.sty + (size_t)slot * a.sty_stride;
-    const uint8_t *mask = a.mask ? a.mask + (size_t)slot * a.mask_stride : nullptr;
+    const int frame = slot / a.lpf, label = a.label + slot % a.lpf;  // fused label pass: slot = (frame, label)
+    const uint8_t *content = a.content + (size_t)frame * a.content_stride;
+    const uint8_t *sty = a.sty + (size_t)frame * a.sty_stride;
+    const uint8_t *mask = a.mask ? a.mask + (size_t)frame * a.mask_stride : nullptr;
     unsigned *hist_t = a.hist + (size_t)slot * a.hist_stride;
     unsigned *hist_s = hist_t + kCube;
     const size_t npix = a.p_end - a.p_begin;
@@ -280,7 +282,7 @@ __global__ void __launch_bounds__(256) k_hist(PixArgs a)
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
             bool in_t, in_s;
-            region_flags(a.mode, a.label, mask ? m[k] : 0u, in_t, in_s);
+            region_flags(a.mode, label, mask ? m[k] : 0u, in_t, in_s);
             bool ok = k < nvalid;
             hist_add(hist_t, c[k], ok && in_t && c[k] != 0u, a.aggregate);
             hist_add(hist_s, s[k], ok && in_s && s[k] != 0u, a.aggregate);
@@ -294,10 +296,11 @@ template <bool RESAMPLE, int LUTM = 0>
 __global__ void __launch_bounds__(256, 3) k_apply(PixArgs a)
 {
     const int slot = blockIdx.y;
-    const uint8_t *content = a.content + (size_t)slot * a.content_stride;
-    const uint8_t *sty = a.sty + (size_t)slot * a.sty_stride;
-    const uint8_t *mask = a.mask ? a.mask + (size_t)slot * a.mask_stride : nullptr;
-    uint8_t *out = a.out + (size_t)slot * a.out_stride;
+    const int frame = slot / a.lpf, label = a.label + slot % a.lpf;  // fused label pass: slot = (frame, label)
+    const uint8_t *content = a.content + (size_t)frame * a.content_stride;
+    const uint8_t *sty = a.sty + (size_t)frame * a.sty_stride;
+    const uint8_t *mask = a.mask ? a.mask + (size_t)frame * a.mask_stride : nullptr;
+    uint8_t *out = a.out + (size_t)frame * a.out_stride;
     const unsigned *lut = a.lut + (size_t)slot * a.lut_stride;
     const int status = a.ctrl[slot].status;
     if (a.status_out && blockIdx.x == 0 && threadIdx.x == 0) a.status_out[slot] = status;
@@ -324,7 +327,7 @@ __global__ void __launch_bounds__(256, 3) k_apply(PixArgs a)
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
             bool in_t, in_s;
-            region_flags(a.mode, a.label, mask ? m[k] : 0u, in_t, in_s);
+            region_flags(a.mode, label, mask ? m[k] : 0u, in_t, in_s);
             if (in_t) tgt |= 1u << k;
             if (in_t || a.mode == 0) keep |= 1u << k;
         }

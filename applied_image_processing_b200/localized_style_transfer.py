@@ -367,7 +367,7 @@ def regional_color_transfer(content, stylized, background_mask, slots=None, out=
     return _transfer(content, stylized, background_mask, MODE_MASK, slots=slots, out=out)
 
 
-def regional_color_transfer_labels(content, stylized, labels, n_labels, slots=None):
+def regional_color_transfer_labels(content, stylized, labels, n_labels, slots=None, fused=True):
     """BASELINE.json config 5 (no counterpart in the reference): for every label l the content
     pixels with that label are matched to the stylised pixels with that label."""
     if not _is_tensor(content):
@@ -380,10 +380,40 @@ def regional_color_transfer_labels(content, stylized, labels, n_labels, slots=No
             s = s.unsqueeze(0).expand(c.shape[0], -1, -1, -1).contiguous()
         if c.dim() == 4 and l.dim() == 2:
             l = l.unsqueeze(0).expand(c.shape[0], -1, -1).contiguous()
-        return regional_color_transfer_labels(c, s, l, n_labels, slots=slots).cpu().numpy()
+        return regional_color_transfer_labels(c, s, l, n_labels, slots=slots, fused=fused).cpu().numpy()
+    if fused and 0 < n_labels <= 64:
+        return _transfer_labels_fused(content, stylized, labels, n_labels, slots)
     out = None
     for lab in range(n_labels):
         out = _transfer(content, stylized, labels, MODE_LABEL, label=lab, out=out, slots=slots, quiet=True)
+    return out
+
+
+_LABEL_WS_BUDGET = 48 << 30  # bytes of workspace a fused label plan may take (of 180 GB)
+
+
+def _transfer_labels_fused(content, stylized, labels, n_labels, frames_per_group=None):
+    """All labels of a group of frames in one launch group: rct_transfer_labels_async with a plan of
+    frames_per_group * n_labels slots (slot = frame * n_labels + label)."""
+    L = _cabi.lib()
+    dev = content.device
+    for t in (content, stylized, labels):
+        if t.dtype != torch.uint8 or not t.is_contiguous() or t.device != dev or dev.type != "cuda":
+            raise TypeError("inputs must be contiguous uint8 tensors on one CUDA device")
+    batched = content.dim() == 4
+    n = content.shape[0] if batched else 1
+    H, W = content.shape[-3], content.shape[-2]
+    sh, sw = stylized.shape[-3], stylized.shape[-2]
+    sty_b, lab_b = stylized.dim() == 4, labels.dim() == 3
+    fpg = max(1, min(n, frames_per_group or 8))
+    while fpg > 1 and L.rct_plan_workspace_bytes(H, W, fpg * n_labels, 0) > _LABEL_WS_BUDGET:
+        fpg -= 1
+    plan = get_plan(dev, H, W, sh, sw, fpg * n_labels)
+    out = content.clone()  # pixels of labels >= n_labels keep the content
+    with torch.cuda.device(dev), plan.lock:
+        check(L.rct_transfer_labels_async(
+            plan.handle, content.data_ptr(), H * W * 3, stylized.data_ptr(), sh * sw * 3 if sty_b else 0,
+            labels.data_ptr(), H * W if lab_b else 0, out.data_ptr(), H * W * 3, n, n_labels, _stream_ptr()))
     return out
 
 

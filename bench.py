@@ -64,6 +64,9 @@ def parse_args():
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--labels-fused", type=int, default=1, choices=[0, 1],
+                    help="labels workload: 1 all labels of a frame group in one launch group (rct_transfer_labels_async), "
+                         "0 one pass per label (A/B runs)")
     ap.add_argument("--lut", type=int, default=0, choices=[0, 1],
                     help="RCT_OPT_LUT: 0 uint32 RGB per colour (default), 1 uint16 run index + palette (A/B runs)")
     ap.add_argument("--sty-short", type=int, default=0,
@@ -311,7 +314,8 @@ def run_gpu_arm(a):
     dc, ds, dm = hc.to(dev), hs.to(dev), hm.to(dev)
     do = torch.empty_like(dc)
     sh, sw = sty_size(a)
-    plan = lst.get_plan(dev, H, W, sh, sw, slots=a.slots)
+    fused = labels and a.labels_fused
+    plan = lst.get_plan(dev, H, W, sh, sw, slots=a.slots * (8 if fused else 1))
     plan.set_option(_cabi.OPT_FRONTEND, a.front)
     plan.set_option(_cabi.OPT_APPLY, a.apply)
     plan.set_option(_cabi.OPT_MATCH, a.match)
@@ -319,6 +323,11 @@ def run_gpu_arm(a):
     st = torch.cuda.current_stream().cuda_stream
 
     def step():
+        if fused:  # configs[4], all 8 labels of a.slots frames per launch group
+            do.copy_(dc)
+            _cabi.check(L.rct_transfer_labels_async(plan.handle, dc.data_ptr(), H * W * 3, ds.data_ptr(), sh * sw * 3,
+                                                    dm.data_ptr(), H * W, do.data_ptr(), H * W * 3, n, 8, st))
+            return
         if labels:  # configs[4]: every label is an independent exact transfer; untouched pixels keep the content
             do.copy_(dc)
             for lab in range(8):
@@ -344,8 +353,9 @@ def run_gpu_arm(a):
     clocks = sampler.stop()
     launches = int(L.rct_launch_count(0))
     ms_total = max_over_ranks(e0.elapsed_time(e1))
-    status = np.zeros(n, np.int32)
-    _cabi.check(L.rct_plan_status(plan.handle, status.ctypes.data, n, st))
+    n_status = n * 8 if fused else n
+    status = np.zeros(n_status, np.int32)
+    _cabi.check(L.rct_plan_status(plan.handle, status.ctypes.data, n_status, st))
     assert not status.any(), f"unexpected empty-region status {status}"
     mp_step = world * n * H * W / 1e6
     ms_step = ms_total / a.steps
@@ -410,7 +420,7 @@ def run_gpu_arm(a):
 
         def api_call():
             if labels:
-                hon[...] = aip.regional_color_transfer_labels(hcn, hsn, hmn, 8, slots=e2e_slots)
+                hon[...] = aip.regional_color_transfer_labels(hcn, hsn, hmn, 8, slots=e2e_slots, fused=bool(a.labels_fused))
             else:
                 aip.regional_color_transfer(hcn, hsn, hmn, out=hon, slots=e2e_slots)
 

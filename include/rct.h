@@ -133,6 +133,14 @@ int rct_transfer_async(rct_plan *plan, const uint8_t *content, size_t content_st
                        int mode, int label, void *stream);
 int rct_plan_status(rct_plan *plan, int *status_host, int n_frames, void *stream);
 
+/* BASELINE.json configs[4] (no counterpart in the reference, which knows one foreground / background pair): for every
+ * label l < n_labels of a uint8 label map, the content pixels with label l are matched to the stylised pixels with label
+ * l (LABEL mode of rct_transfer_async), all labels of slots / n_labels frames per launch group side by side.  The plan
+ * needs slots >= n_labels.  `out` must be pre-filled with the values untouched pixels keep (a copy of content).
+ * Status per (frame, label) lands in the plan's status array (rct_plan_status, n = n_frames * n_labels). */
+int rct_transfer_labels_async(rct_plan *plan, const uint8_t *content, size_t content_stride, const uint8_t *stylised,
+                              size_t stylised_stride, const uint8_t *labels, size_t labels_stride, uint8_t *out,
+                              size_t out_stride, int n_frames, int n_labels, void *stream);
 /* Same through HOST buffers (the reference's calling convention: numpy arrays in, numpy
  * array out).  Copies in, runs, copies out, synchronises; pinned host memory makes the
  * copies true DMA.  Returns the worst per-frame status. */

@@ -149,6 +149,32 @@ def test_label_mode_eight_regions():
     assert np.array_equal(out, ref)
 
 
+def test_fused_label_batch_equals_per_label_passes_and_oracle():
+    """rct_transfer_labels_async (all labels of a frame group side by side) against one pass per label and
+    against the oracle; a label that is absent from a frame, labels >= n_labels, shared stylised image."""
+    n, H, W, nl = 3, 150, 208, 5
+    cs = np.stack([synth.synth_image(H, W, 700 + i, "UN"[i % 2]) for i in range(n)])
+    ss = np.stack([synth.synth_image(H, W, 800 + i, "NU"[i % 2]) for i in range(n)])
+    ls = np.stack([synth.voronoi_labels(H, W, 7, 40 + i) for i in range(n)])  # labels 0..6: 5 and 6 stay content
+    ls[1][ls[1] == 2] = 3                                                      # frame 1 has no label 2
+    refs = cs.copy()
+    for i in range(n):
+        for lab in range(nl):
+            orc.transfer(cs[i], ss[i], ls[i], mode=orc.MODE_LABEL, label=lab, out=refs[i])
+    tc, ts, tl = (torch.from_numpy(x).cuda() for x in (cs, ss, ls))
+    fused = aip.regional_color_transfer_labels(tc, ts, tl, nl, slots=2)        # 2 frames per group: a ragged last group
+    seq = aip.regional_color_transfer_labels(tc, ts, tl, nl, fused=False)
+    assert np.array_equal(fused.cpu().numpy(), refs), int((fused.cpu().numpy() != refs).sum())
+    assert np.array_equal(seq.cpu().numpy(), refs)
+    # numpy in -> numpy out, one shared stylised image
+    refs1 = cs.copy()
+    for i in range(n):
+        for lab in range(nl):
+            orc.transfer(cs[i], ss[0], ls[i], mode=orc.MODE_LABEL, label=lab, out=refs1[i])
+    got = aip.regional_color_transfer_labels(cs, ss[0], ls, nl)
+    assert isinstance(got, np.ndarray) and np.array_equal(got, refs1)
+
+
 def test_row_sharded_phases_equal_single_pass():
     """per-shard histograms summed (what the NCCL all-reduce does) -> identical
     LUT -> per-shard apply == the unsharded result, for any split."""
