@@ -7,7 +7,7 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librct.so")
+LIB_PATH = os.environ.get("RCT_LIB") or os.path.join(_HERE, "librct.so")  # RCT_LIB: tuning builds (tools/)
 
 RCT_OK, RCT_EMPTY_TARGET, RCT_EMPTY_SOURCE = 0, 1, 2
 MODE_MASK, MODE_LABEL, MODE_ALL = 0, 1, 2

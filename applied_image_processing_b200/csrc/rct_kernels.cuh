@@ -27,7 +27,10 @@ constexpr int kCoarse = 4096;           // coarse key-histogram bins per region
 constexpr unsigned kCube = 1u << 24;    // colour-cube bins
 constexpr int kFineTarget = 16384;      // fine bins aimed at per sort job (equalised)
 constexpr int kFineMax = kFineTarget + kCoarse;  // upper bound on fine bins per job
-constexpr int kPartT = 2048;            // entries per part aimed at (part < kPartT + largest fine bin)
+#ifndef RCT_PARTT
+#define RCT_PARTT 3072
+#endif
+constexpr int kPartT = RCT_PARTT;            // entries per part aimed at (part < kPartT + largest fine bin)
 constexpr int kPartCap = 4096;          // entries a part may have to be sorted in shared memory
 constexpr int kFillStride = 32;         // uint32 stride of the per-part fill counters (128 B apart)
 constexpr unsigned kPaletteCap = 65536;               // palette LUT: run indices are uint16

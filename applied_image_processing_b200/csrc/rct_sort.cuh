@@ -7,8 +7,8 @@
 //   k_plan_fine              coarse bin with c keys -> ~c*F/d fine sub-bins (histogram
 //                            equalisation; F ~ d/256, at most 16384)
 //   k_fine_hist              exact fine-bin counts (shared-memory privatised)
-//   k_plan_parts             consecutive fine bins grouped into parts of ~2048 entries
-//                            (part = floor(exclusive offset / 2048), ids compacted)
+//   k_plan_parts             consecutive fine bins grouped into parts of ~kPartT (3072) entries
+//                            (part = floor(exclusive offset / kPartT), ids compacted)
 //   k_scatter                entries -> their part (one fill counter per part; the write
 //                            frontier is one sector per part, so L2 merges the stores)
 //   k_part_sort              one CTA per part: counting sort on the estimated rank in shared
@@ -187,7 +187,10 @@ __device__ __forceinline__ bool rec_less(const Rec &a, const Rec &b)
 // to be L2 hits on them), and the fill counters are seeded with the part starts by k_plan_parts, so
 // the atomic returns the record's final position.  Each thread moves kScatPer entries per trip so
 // that the loads and the fill-counter atomics overlap.
-constexpr int kScatPer = 4;
+#ifndef RCT_SCATPER
+#define RCT_SCATPER 4
+#endif
+constexpr int kScatPer = RCT_SCATPER;
 constexpr size_t kSmemScatter = (size_t)(kCoarse + 1) * 4 + (size_t)kFineMax * 2 + 16;
 __global__ void __launch_bounds__(256) k_scatter(const Job *jobs)
 {
