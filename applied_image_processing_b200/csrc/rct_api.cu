@@ -443,7 +443,10 @@ unsigned pix_blocks(rct_plan *p, size_t npix, int nslots)
 {
     size_t groups = (npix + 15) / 16;
     size_t blocks = (groups + 255) / 256;
-    size_t maxb = (size_t)p->sm * 8;
+#ifndef RCT_PB
+#define RCT_PB 8
+#endif
+    size_t maxb = (size_t)p->sm * RCT_PB;
     if (nslots > 1) maxb = (maxb + nslots - 1) / nslots < (size_t)p->sm ? (size_t)p->sm : (maxb + nslots - 1) / nslots;
     if (blocks > maxb) blocks = maxb;
     return (unsigned)(blocks ? blocks : 1);
@@ -452,7 +455,10 @@ unsigned pix_blocks(rct_plan *p, size_t npix, int nslots)
 unsigned entry_blocks(rct_plan *p, int nslots)
 {
     size_t blocks = (p->L.cap + 255) / 256;
-    size_t maxb = (size_t)p->sm * 4;
+#ifndef RCT_EB
+#define RCT_EB 8
+#endif
+    size_t maxb = (size_t)p->sm * RCT_EB;
     if (nslots > 1) maxb = maxb / nslots < 32 ? 32 : maxb / nslots;
     if (blocks > maxb) blocks = maxb;
     return (unsigned)(blocks ? blocks : 1);
@@ -553,7 +559,10 @@ int phase_front(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
     const size_t npix = p_end - p_begin;
     dim3 gcount(pix_blocks(p, npix, nslots), nslots);
     size_t ntiles = ((npix + 15) / 16 + kPartThreads - 1) / kPartThreads;
-    size_t maxb = ((size_t)p->sm * 4 + nslots - 1) / nslots;  // two waves of 2 CTAs per SM over all slots
+#ifndef RCT_FPG
+#define RCT_FPG 64
+#endif
+    size_t maxb = ((size_t)p->sm * RCT_FPG + nslots - 1) / nslots;  // two waves of 2 CTAs per SM over all slots
     if (ntiles < 1) ntiles = 1;
     dim3 gpart((unsigned)(ntiles < maxb ? ntiles : maxb), nslots);
     const bool two = mode != RCT_MODE_MASK;
@@ -612,9 +621,11 @@ int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t 
     k_plan_parts<<<dim3(1, njobs), 1024, 0, st>>>(jobs);
     KMARK(RCT_TK_PLAN_PARTS);
     // few, long-lived CTAs per job: each stages the fine-bin tables (kSmemScatter bytes) once
-    unsigned sblocks = (unsigned)((p ? p->sm : 148) * 12 / (njobs > 0 ? njobs : 1));  // ~4 waves of 3 CTAs per SM
+#ifndef RCT_SB
+#define RCT_SB 12
+#endif
+    unsigned sblocks = (unsigned)((p ? p->sm : 148) * RCT_SB / (njobs > 0 ? njobs : 1));  // ~4 waves of 3 CTAs per SM
     if (sblocks < 16u) sblocks = 16u;
-    if (sblocks > eblocks) sblocks = eblocks;
     k_scatter<<<dim3(sblocks, njobs), 256, kSmemScatter, st>>>(jobs);
     KMARK(RCT_TK_SCATTER);
     k_part_sort<<<dim3((unsigned)maxparts, njobs), kSortThreads, kSmemPartSort, st>>>(jobs, part_cap);
@@ -639,7 +650,10 @@ int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)
     KMARK(RCT_TK_LAB_MOMENTS);
     LAUNCH(k_pca, dim3((nslots + 31) / 32), 32, st, p->ctrl, nslots);
     KMARK(RCT_TK_PCA);
-    LAUNCH(k_keys, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs);
+#ifndef RCT_EBK
+#define RCT_EBK 2
+#endif
+    LAUNCH(k_keys, dim3(eb * RCT_EBK, 2, nslots), 256, st, p->ctrl, p->jobs);
     KMARK(RCT_TK_KEYS);
     int rc = sort_jobs(p, p->jobs, 2 * nslots, eb, p->L.cap, p->L.maxparts, p->part_cap, st);
     if (rc) return rc;

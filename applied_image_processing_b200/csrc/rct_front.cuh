@@ -161,9 +161,12 @@ __global__ void __launch_bounds__(kNB) k_front_scan(FrameCtrl *ctrl, FrontArgs f
     if (t == 0) fc.nchunks = chunk_carry < f.cmap_cap ? chunk_carry : f.cmap_cap;
 }
 
-constexpr int kPartThreads = 512;
+#ifndef RCT_FPT
+#define RCT_FPT 512
+#endif
+constexpr int kPartThreads = RCT_FPT;
 template <bool RESAMPLE, bool TWO_PASS>
-__global__ void __launch_bounds__(kPartThreads, 2) k_front_part(PixArgs a, FrontArgs f)
+__global__ void __launch_bounds__(kPartThreads, 1024 / kPartThreads) k_front_part(PixArgs a, FrontArgs f)
 {
     const int slot = blockIdx.y;
     const int frame = slot / a.lpf, label = a.label + slot % a.lpf;  // fused label pass: slot = (frame, label)
@@ -239,7 +242,10 @@ __global__ void __launch_bounds__(kPartThreads, 2) k_front_part(PixArgs a, Front
     }
 }
 
-constexpr int kFrontHistThreads = 256;
+#ifndef RCT_FHT
+#define RCT_FHT 512
+#endif
+constexpr int kFrontHistThreads = RCT_FHT;
 constexpr size_t kSmemFrontHist = (size_t)kBucketBins * 4;
 __global__ void __launch_bounds__(kFrontHistThreads) k_front_hist(FrameCtrl *ctrl, const Job *jobs, FrontArgs f,
                                                                   unsigned *hist0, size_t hist_stride)

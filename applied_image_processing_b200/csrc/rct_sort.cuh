@@ -74,7 +74,10 @@ __global__ void __launch_bounds__(1024) k_plan_fine(const Job *jobs)
 }
 
 // k_fine_hist: dynamic shared memory = (kFineMax + kCoarse + 1) * 4 bytes.
-constexpr int kFineHistChunk = 65536;  // entries per block
+#ifndef RCT_FHC
+#define RCT_FHC 65536
+#endif
+constexpr int kFineHistChunk = RCT_FHC;  // entries per block
 __global__ void __launch_bounds__(512) k_fine_hist(const Job *jobs)
 {
     const Job &job = jobs[blockIdx.y];
@@ -791,7 +794,10 @@ __global__ void __launch_bounds__(kPalThreads) k_pal_write(FrameCtrl *ctrl, cons
 
 // pipeline flavour: jobs[2*slot] = target, jobs[2*slot+1] = source; one CTA per target part.
 // Writes the colour -> output-RGB LUT (a-7: inverse_transform, lab -> rgb, clip, truncate).
-constexpr int kMatchThreads = 128;
+#ifndef RCT_MATCHT
+#define RCT_MATCHT 128
+#endif
+constexpr int kMatchThreads = RCT_MATCHT;
 template <int LUTM>
 __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0,
                                                          size_t lut_stride, double *dbg_matched0, long long *dbg_j0,
