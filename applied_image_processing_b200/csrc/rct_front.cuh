@@ -99,7 +99,10 @@ __device__ __forceinline__ void front_load(const PixArgs &a, const uint8_t *cont
 }
 
 template <bool RESAMPLE, bool TWO_PASS>
-__global__ void __launch_bounds__(256, 3) k_front_count(PixArgs a)
+#ifndef RCT_FCB
+#define RCT_FCB 4
+#endif
+__global__ void __launch_bounds__(256, RCT_FCB) k_front_count(PixArgs a)
 {
     const int slot = blockIdx.y;
     const int frame = slot / a.lpf, label = a.label + slot % a.lpf;  // fused label pass: slot = (frame, label)
@@ -166,7 +169,10 @@ __global__ void __launch_bounds__(kNB) k_front_scan(FrameCtrl *ctrl, FrontArgs f
 #endif
 constexpr int kPartThreads = RCT_FPT;
 template <bool RESAMPLE, bool TWO_PASS>
-__global__ void __launch_bounds__(kPartThreads, 1024 / kPartThreads) k_front_part(PixArgs a, FrontArgs f)
+#ifndef RCT_FPB
+#define RCT_FPB (1024 / kPartThreads)
+#endif
+__global__ void __launch_bounds__(kPartThreads, RCT_FPB) k_front_part(PixArgs a, FrontArgs f)
 {
     const int slot = blockIdx.y;
     const int frame = slot / a.lpf, label = a.label + slot % a.lpf;  // fused label pass: slot = (frame, label)

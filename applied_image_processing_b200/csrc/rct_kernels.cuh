@@ -437,7 +437,10 @@ __device__ __forceinline__ long long warp_sum_ll(long long v)
 // below 128 (virtually all of them) take the 64-bit fast path of rct_math.cuh; the rest, and
 // the rare overflow-guard flushes, go through 48-bit limbs in shared memory.  The next
 // entry is loaded before the current one is evaluated (the loop is latency-bound otherwise).
-__global__ void __launch_bounds__(256, 2) k_lab_moments(FrameCtrl *ctrl, const Job *jobs)
+#ifndef RCT_LMB
+#define RCT_LMB 2
+#endif
+__global__ void __launch_bounds__(256, RCT_LMB) k_lab_moments(FrameCtrl *ctrl, const Job *jobs)
 {
     const int region = blockIdx.y, slot = blockIdx.z;
     const Job &job = jobs[slot * 2 + region];

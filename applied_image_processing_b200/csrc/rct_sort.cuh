@@ -191,7 +191,7 @@ __device__ __forceinline__ bool rec_less(const Rec &a, const Rec &b)
 // the atomic returns the record's final position.  Each thread moves kScatPer entries per trip so
 // that the loads and the fill-counter atomics overlap.
 #ifndef RCT_SCATPER
-#define RCT_SCATPER 4
+#define RCT_SCATPER 6
 #endif
 constexpr int kScatPer = RCT_SCATPER;
 constexpr size_t kSmemScatter = (size_t)(kCoarse + 1) * 4 + (size_t)kFineMax * 2 + 16;
@@ -843,7 +843,15 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
     }
 }
 
-__global__ void __launch_bounds__(kMatchThreads) k_match(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0, size_t lut_stride,
+#ifndef RCT_MATCHB
+#define RCT_MATCHB 12
+#endif
+#if RCT_MATCHB > 0
+#define RCT_MATCH_LB __launch_bounds__(kMatchThreads, RCT_MATCHB)
+#else
+#define RCT_MATCH_LB __launch_bounds__(kMatchThreads)
+#endif
+__global__ void RCT_MATCH_LB k_match(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0, size_t lut_stride,
                                                          double *dbg_matched0, long long *dbg_j0, size_t dbg_stride,
                                                          int interleave)
 {
