@@ -18,7 +18,7 @@ def shown(name):
     name = name.replace("void ", "").replace("rct::", "")
     base = name.split("(")[0]
     base = re.sub(r"\(bool\)|\(int\)", "", base)
-    m = re.match(r"k_apply_warp<(\d), *(\d+)>", base)
+    m = re.match(r"k_apply_warp<(\d), *(\d+)", base)
     if m:
         return "k_apply_warp<%s,%s>" % ("bulk" if m.group(1) == "1" else "cp.async", m.group(2))
     return re.sub(r"<.*>", "", base)
