@@ -944,7 +944,19 @@ int rct_shard_hist_async(rct_plan *p, const uint8_t *content, const uint8_t *sty
     int rc = check_mode(mode, mask);
     if (rc) return rc;
     FrameSet f{content, stylised, mask, nullptr, 0, 0, 0, 0};
-    return phase_hist(p, f, 1, mode, label, (size_t)row0 * p->W, (size_t)(row0 + rows) * p->W, (cudaStream_t)stream);
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t pb = (size_t)row0 * p->W, pe = (size_t)(row0 + rows) * p->W;
+    if (!p->front) return phase_hist(p, f, 1, mode, label, pb, pe, st);
+    // Colour-partitioned front end on the band (streaming passes, no global atomics), then the band's
+    // (colour, count) lists are written into the zeroed colour cubes the ranks all-reduce: one plain
+    // store per distinct colour instead of one atomic per pixel (k_hist).
+    rc = phase_front(p, f, 1, mode, label, pb, pe, st);
+    if (rc) return rc;
+    LAUNCH(k_list_to_cube, (unsigned)p->sm * 8, 256, st, p->ctrl, p->jobs, 0, 0, p->hist);
+    LAUNCH(k_list_to_cube, (unsigned)p->sm * 8, 256, st, p->ctrl, p->jobs, 0, 1, p->hist + kCube);
+    p->cube_dirty = true;
+    CK(cudaMemsetAsync(p->ctrl, 0, sizeof(FrameCtrl), st));  // the solve rebuilds the lists from the reduced cubes
+    return mark(p, st);
 }
 void *rct_plan_hist_ptr(rct_plan *p) { return p ? (void *)p->hist : nullptr; }
 size_t rct_plan_hist_bytes(rct_plan *p) { return p ? 4 * p->L.hist_stride_u32 : 0; }
