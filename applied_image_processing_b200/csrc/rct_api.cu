@@ -616,7 +616,7 @@ int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t 
     unsigned hblocks = (unsigned)((cap + kFineHistChunk - 1) / kFineHistChunk);
     LAUNCH(k_plan_fine, dim3(1, njobs), 1024, st, jobs);
     KMARK(RCT_TK_PLAN_FINE);
-    k_fine_hist<<<dim3(hblocks, njobs), 512, kSmemFineHist, st>>>(jobs);
+    k_fine_hist<<<dim3(hblocks, njobs), RCT_FHTH, kSmemFineHist, st>>>(jobs);
     KMARK(RCT_TK_FINE_HIST);
     k_plan_parts<<<dim3(1, njobs), 1024, 0, st>>>(jobs);
     KMARK(RCT_TK_PLAN_PARTS);

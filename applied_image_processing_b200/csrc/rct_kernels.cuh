@@ -57,7 +57,10 @@ struct RegionCtrl {
 constexpr int kBucketShift = 14;
 constexpr int kBucketBins = 1 << kBucketShift;  // colours per bucket = bins of the shared-memory histogram
 constexpr int kNB = 1024;                       // buckets per region
-constexpr unsigned kChunk = 65536;              // items one CTA of k_front_hist accumulates
+#ifndef RCT_CHUNK
+#define RCT_CHUNK 65536
+#endif
+constexpr unsigned kChunk = RCT_CHUNK;              // items one CTA of k_front_hist accumulates
 
 struct FrontCtrl {
     unsigned bcnt[2 * kNB];      // items per (region, bucket)

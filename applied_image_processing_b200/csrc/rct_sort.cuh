@@ -48,7 +48,10 @@ __global__ void __launch_bounds__(1024) k_plan_fine(const Job *jobs)
     if (rc->skip) return;
     __shared__ unsigned s_warp[33];
     const unsigned d = rc->d;
-    unsigned F = d / 256u;
+#ifndef RCT_FDIV
+#define RCT_FDIV 256
+#endif
+    unsigned F = d / (unsigned)RCT_FDIV;
     if (F < 1u) F = 1u;
     if (F > (unsigned)kFineTarget) F = (unsigned)kFineTarget;
     unsigned nb[4], sum = 0;
@@ -78,7 +81,10 @@ __global__ void __launch_bounds__(1024) k_plan_fine(const Job *jobs)
 #define RCT_FHC 65536
 #endif
 constexpr int kFineHistChunk = RCT_FHC;  // entries per block
-__global__ void __launch_bounds__(512) k_fine_hist(const Job *jobs)
+#ifndef RCT_FHTH
+#define RCT_FHTH 1024
+#endif
+__global__ void __launch_bounds__(RCT_FHTH) k_fine_hist(const Job *jobs)
 {
     const Job &job = jobs[blockIdx.y];
     RegionCtrl *rc = job.rc;

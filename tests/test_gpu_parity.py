@@ -546,3 +546,42 @@ def test_match_traversals_agree(fg):
         pos = o[np.searchsorted(t["colour"][o], colour[sel])]
         assert np.array_equal(t["j"][pos], d["j"][sel]), order
         assert np.array_equal(t["matched"][pos], d["matched"][sel]), order
+
+
+def test_randomised_geometries_against_the_oracle():
+    """Seeded sweep over sizes (including < 16 pixels, odd rows, W around the 256-pixel tile), stylised
+    sizes (same / up- / down-sampled), mask kinds and image families: uint8 output bit-exact vs the
+    oracle, statuses equal (empty regions leave the content / stylised pixels alone)."""
+    rng = np.random.default_rng(2026)
+    kinds = ("U", "N")
+    for case in range(40):
+        H = int(rng.integers(1, 40)) if case % 5 == 0 else int(rng.integers(40, 320))
+        W = int(rng.choice([int(rng.integers(1, 64)), 255, 256, 257, int(rng.integers(64, 400))]))
+        if rng.random() < 0.5:
+            sh, sw = H, W
+        else:
+            sh, sw = max(1, int(H * rng.uniform(0.4, 1.6))), max(1, int(W * rng.uniform(0.4, 1.6)))
+        c = synth.synth_image(H, W, 9000 + case, kinds[case % 2], black_frac=float(rng.choice([0.0, 0.001, 0.2])))
+        s = synth.synth_image(sh, sw, 9500 + case, kinds[(case // 2) % 2], black_frac=float(rng.choice([0.0, 0.01])))
+        mk = case % 6
+        if mk == 0:
+            mask = synth.ellipse_mask(H, W, float(rng.uniform(0.05, 0.95)), case)
+        elif mk == 1:
+            mask = synth.bernoulli_mask(H, W, float(rng.uniform(0.1, 0.9)), case)
+        elif mk == 2:
+            mask = np.zeros((H, W), np.uint8)          # everything foreground: no source pixels
+        elif mk == 3:
+            mask = np.ones((H, W), np.uint8)           # everything background: no target pixels
+        elif mk == 4:
+            mask = (np.add.outer(np.arange(H) // 7, np.arange(W) // 5) % 2).astype(np.uint8)
+        else:
+            mask = np.ones((H, W), np.uint8)
+            mask[rng.integers(0, H), rng.integers(0, W)] = 0   # a single target pixel
+        ref, st, _ = orc.transfer(c, s, mask)
+        plan = lst.get_plan(_dev(), H, W, sh, sw, 1)
+        out = _run_plan(plan, c, s, mask)
+        status = np.zeros(1, np.int32)
+        _cabi.check(_cabi.lib().rct_plan_status(plan.handle, status.ctypes.data, 1, torch.cuda.current_stream().cuda_stream))
+        assert int(status[0]) == st, (case, H, W, sh, sw, mk, int(status[0]), st)
+        assert np.array_equal(out, ref), (case, H, W, sh, sw, mk, int((out != ref).sum()))
+    lst.clear_plans()
