@@ -626,7 +626,7 @@ int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t 
 #endif
     unsigned sblocks = (unsigned)((p ? p->sm : 148) * RCT_SB / (njobs > 0 ? njobs : 1));  // ~4 waves of 3 CTAs per SM
     if (sblocks < 16u) sblocks = 16u;
-    k_scatter<<<dim3(sblocks, njobs), 256, kSmemScatter, st>>>(jobs);
+    k_scatter<<<dim3(sblocks, njobs), RCT_SCT, kSmemScatter, st>>>(jobs);
     KMARK(RCT_TK_SCATTER);
     k_part_sort<<<dim3((unsigned)maxparts, njobs), kSortThreads, kSmemPartSort, st>>>(jobs, part_cap);
     KMARK(RCT_TK_PART_SORT);

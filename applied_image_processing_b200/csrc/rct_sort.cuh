@@ -197,11 +197,18 @@ __device__ __forceinline__ bool rec_less(const Rec &a, const Rec &b)
 // the atomic returns the record's final position.  Each thread moves kScatPer entries per trip so
 // that the loads and the fill-counter atomics overlap.
 #ifndef RCT_SCATPER
-#define RCT_SCATPER 6
+#define RCT_SCATPER 4
 #endif
 constexpr int kScatPer = RCT_SCATPER;
 constexpr size_t kSmemScatter = (size_t)(kCoarse + 1) * 4 + (size_t)kFineMax * 2 + 16;
-__global__ void __launch_bounds__(256) k_scatter(const Job *jobs)
+#ifndef RCT_SCT
+#define RCT_SCT 384
+#endif
+#ifndef RCT_SCTB
+#define RCT_SCTB 3
+#endif
+#define RCT_SCT_LB __launch_bounds__(RCT_SCT, RCT_SCTB)
+__global__ void RCT_SCT_LB k_scatter(const Job *jobs)
 {
     const Job &job = jobs[blockIdx.y];
     RegionCtrl *rc = job.rc;

@@ -11,7 +11,7 @@ for v in ${VARIANTS:-""}; do
 import json
 d=json.loads(open("gpurun_out/b_${k}_var$v.log").read().strip().splitlines()[-1])
 m=d["roofline"]["all_kernels_ms_per_launch"]
-print("  $k", round(d["value"]), {x:m[x] for x in ("k_fine_hist","k_part_sort","k_scatter","k_match","k_front_hist")})
+print("  $k", round(d["value"]), {x:m[x] for x in ("k_scatter","k_part_sort","k_match")})
 PY
   done
 done
