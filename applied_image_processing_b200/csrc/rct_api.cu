@@ -340,7 +340,9 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
         // k_apply_warp_rs stages, per 256-pixel tile, the source spans of its (at most two) row
         // segments: every pair must fit kRsCap bytes (3 bytes per source pixel, each span widened
         // to 16-byte boundaries), the stylised frames must be whole 16-byte units, W >= 256
-        // (W % 256 == 0: tiles never straddle rows -- the two-segment path faulted on the B200 and stays off)
+        // W % 256 == 0: tiles never straddle rows.  The two-segment path is correct in an instrumented build
+        // (tools/rs_debug.py, -DRCT_RS_DEBUG: 0 differing bytes) but faults in the optimised one -- the split
+        // `min(n, W - x)` comes out as n there -- so it stays off until that is understood.
         bool ok = W >= 256 && W % 256 == 0 && ((size_t)sh * (size_t)sw * 3) % 16 == 0;
         auto seg_bytes = [&](int xa, int npx) -> size_t {
             if (npx <= 0) return 0;
@@ -432,7 +434,7 @@ PixArgs pix_args(rct_plan *p, const FrameSet &f, int mode, int label, size_t p_b
     a.hist = p->hist; a.hist_stride = p->L.hist_stride_u32;
     a.lut = p->lut; a.lut_stride = p->L.lut_stride_u32; a.lut_mode = p->lut_mode;
     a.ctrl = p->ctrl; a.status_out = status_out;
-    a.W = p->W; a.sw = p->sw;
+    a.W = p->W; a.sw = p->sw; a.sh_dbg = p->sh;
     a.p_begin = p_begin; a.p_end = p_end;
     a.mode = mode; a.label = label; a.lpf = p->lpf > 0 ? p->lpf : 1;
     a.aggregate = p->aggregate;

@@ -625,7 +625,11 @@ __global__ void __launch_bounds__(256, 4) k_apply_warp_rs(PixArgs a, unsigned ti
         const size_t left = a.p_end - p0;
         n = left < (size_t)kTile ? (unsigned)left : (unsigned)kTile;
         const unsigned y = (unsigned)(p0 / Wd), x = (unsigned)(p0 - (size_t)y * Wd);
-        const unsigned na = n < Wd - x ? n : Wd - x;
+        const unsigned room = Wd - x;  // pixels left in the tile's first row
+        const unsigned na = n < room ? n : room;
+#ifdef RCT_RS_DEBUG
+        if (na + x > Wd) printf("RS GEOM Wd %u a.W %d x %u y %u n %u room %u na %u\n", Wd, a.W, x, y, n, room, na);
+#endif
         const uint8_t *sty = a.sty + (size_t)slot * a.sty_stride;
         rs_segment(sty, a.xtab, a.ytab, a.sw, y, x, na, 0u, sa);
         rs_segment(sty, a.xtab, a.ytab, a.sw, y + 1u, 0u, n - na, sa.bytes, sb);
@@ -637,6 +641,20 @@ __global__ void __launch_bounds__(256, 4) k_apply_warp_rs(PixArgs a, unsigned ti
         tile_geom(i, slot, p0, n, sa, sb);
         const unsigned st = i % kAwStages;
         unsigned long long *bar = &S.full[warp][st];
+#ifdef RCT_RS_DEBUG
+        {
+            const size_t sty_bytes = 3 * (size_t)a.sw * (size_t)a.sh_dbg;
+            const uint8_t *sty0 = a.sty + (size_t)slot * a.sty_stride;
+            const bool bad = sa.bytes == 0 || (sa.bytes & 15) || (sb.bytes & 15) || sa.bytes + sb.bytes > (unsigned)kRsCap ||
+                             (((uintptr_t)sa.g) & 15) || (((uintptr_t)sb.g) & 15) || sa.g < sty0 ||
+                             sa.g + sa.bytes > sty0 + sty_bytes || (sb.bytes && (sb.g < sty0 || sb.g + sb.bytes > sty0 + sty_bytes)) ||
+                             (n & 15) || n == 0 || n > 256 || p0 + n > a.p_end;
+            if (bad)
+                printf("RS BAD tile p0=%llu n=%u slot=%u A(npx %u x %u xs %u off %u d %u b %u g+%lld) B(npx %u b %u off %u g+%lld) sty_bytes %llu\n",
+                       (unsigned long long)p0, n, slot, sa.npx, sa.x_first, sa.xs_first, sa.smem_off, sa.delta, sa.bytes,
+                       (long long)(sa.g - sty0), sb.npx, sb.bytes, sb.smem_off, (long long)(sb.g - sty0), (unsigned long long)sty_bytes);
+        }
+#endif
         mbar_expect_tx(bar, 4u * n + sa.bytes + sb.bytes);
         bulk_g2s_hint(Wm.c[st], a.content + (size_t)slot * a.content_stride + 3 * p0, 3u * n, bar, pol_stream);
         bulk_g2s_hint(Wm.m[st], a.mask + (size_t)slot * a.mask_stride + p0, n, bar, pol_stream);
@@ -667,6 +685,11 @@ __global__ void __launch_bounds__(256, 4) k_apply_warp_rs(PixArgs a, unsigned ti
             }
             soff[k] = off;
         }
+#ifdef RCT_RS_DEBUG
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            if (soff[k] + 2u >= (unsigned)kRsCap) printf("RS BAD soff %u lane %u k %d p0 %llu n %u\n", soff[k], lane, k, (unsigned long long)p0, n);
+#endif
         mbar_wait(&S.full[warp][st], (i / kAwStages) & 1u);
         const unsigned *lut = a.lut + (size_t)slot * a.lut_stride;
         const int status = a.ctrl[slot].status;

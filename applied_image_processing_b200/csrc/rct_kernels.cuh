@@ -225,6 +225,7 @@ struct PixArgs {
     FrameCtrl *ctrl;       // [slots]
     int *status_out;       // [slots] or NULL
     int W, sw;
+    int sh_dbg;            // stylised height (RCT_RS_DEBUG builds only)
     size_t p_begin, p_end; // pixel range within a frame (row sharding)
     int mode, label;
     int lpf;               // labels per frame of a fused label pass (slot = frame * lpf + label offset); else 1
