@@ -340,10 +340,7 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
         // k_apply_warp_rs stages, per 256-pixel tile, the source spans of its (at most two) row
         // segments: every pair must fit kRsCap bytes (3 bytes per source pixel, each span widened
         // to 16-byte boundaries), the stylised frames must be whole 16-byte units, W >= 256
-        // W % 256 == 0: tiles never straddle rows.  The two-segment path is correct in an instrumented build
-        // (tools/rs_debug.py, -DRCT_RS_DEBUG: 0 differing bytes) but faults in the optimised one -- the split
-        // `min(n, W - x)` comes out as n there -- so it stays off until that is understood.
-        bool ok = W >= 256 && W % 256 == 0 && ((size_t)sh * (size_t)sw * 3) % 16 == 0;
+        bool ok = W >= 256 && ((size_t)sh * (size_t)sw * 3) % 16 == 0;
         auto seg_bytes = [&](int xa, int npx) -> size_t {
             if (npx <= 0) return 0;
             size_t span = (size_t)(tab[xa + npx - 1] - tab[xa] + 1);

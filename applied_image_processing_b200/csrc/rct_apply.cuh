@@ -625,10 +625,13 @@ __global__ void __launch_bounds__(256, 4) k_apply_warp_rs(PixArgs a, unsigned ti
         const size_t left = a.p_end - p0;
         n = left < (size_t)kTile ? (unsigned)left : (unsigned)kTile;
         const unsigned y = (unsigned)(p0 / Wd), x = (unsigned)(p0 - (size_t)y * Wd);
-        const unsigned room = Wd - x;  // pixels left in the tile's first row
-        const unsigned na = n < room ? n : room;
+        // pixels of the tile that lie in its first row.  64-bit on purpose: written as min(n, W - x) in
+        // 32-bit arithmetic the optimised build produced na == n for row-crossing tiles (illegal address on
+        // the B200; an instrumented build was correct) -- tools/rs_debug.py reproduces it
+        const size_t row_end = ((size_t)y + 1u) * (size_t)Wd;
+        const unsigned na = (p0 + (size_t)n <= row_end) ? n : (unsigned)(row_end - p0);
 #ifdef RCT_RS_DEBUG
-        if (na + x > Wd) printf("RS GEOM Wd %u a.W %d x %u y %u n %u room %u na %u\n", Wd, a.W, x, y, n, room, na);
+        if (na + x > Wd) printf("RS GEOM Wd %u a.W %d x %u y %u n %u na %u\n", Wd, a.W, x, y, n, na);
 #endif
         const uint8_t *sty = a.sty + (size_t)slot * a.sty_stride;
         rs_segment(sty, a.xtab, a.ytab, a.sw, y, x, na, 0u, sa);

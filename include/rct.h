@@ -90,8 +90,13 @@ int rct_plan_destroy(rct_plan *plan);
 #define RCT_OPT_FRONTEND 3
 /* RCT_OPT_APPLY: the apply pass when the call is MASK mode, not resampled and 16-byte aligned.
  * 1 (default): one bulk-async (TMA 1-D, cp.async.bulk + mbarrier) staged pipeline per warp;
- * 2: the same pipeline fed by cp.async (LDGSTS); 3: one CTA-wide bulk-async ring; 0: always the
- * register-staged kernel (which also serves every other geometry). */
+ * 2: the same pipeline fed by cp.async (LDGSTS); 3: one CTA-wide bulk-async ring; 4: 512-pixel tiles;
+ * 5: five CTAs per SM; 6: three stages; 7: output through shared memory + one bulk store per tile
+ * (A/B variants, all measured slower or equal: profiles/r01_summary_v10.md); 0: always the register-staged
+ * kernel (which also serves every other geometry).
+ * 8: as 1, and when the stylised image is resampled (W >= 256, 16-byte aligned frames) the NEAREST
+ * resample is staged per tile by bulk copies of the source row spans (k_apply_warp_rs); measured slower
+ * than the register-staged gather (the source image is L2-resident), hence opt-in. */
 #define RCT_OPT_APPLY 4
 /* RCT_OPT_MATCH: traversal of a sorted target part by the CDF-match kernel.  1 (default): lanes
  * interleaved (coalesced, every search starts from an interpolated position); 0: one contiguous

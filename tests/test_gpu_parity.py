@@ -430,7 +430,7 @@ def test_front_ends_and_apply_kernels_agree(case):
     (64, 256, 64, 128),      # W == 256: one tile per row
 ])
 def test_tma_staged_resample_apply(H, W, sh, sw):
-    """k_apply_warp_rs (bulk-async staged NEAREST resample, opt-in RCT_OPT_APPLY=8, W % 256 == 0) and the
+    """k_apply_warp_rs (bulk-async staged NEAREST resample, opt-in RCT_OPT_APPLY=8, W >= 256) and the
     register-staged resample kernel (the default) against the oracle, single frames and a strided batch."""
     n = 3
     cs = np.stack([synth.synth_image(H, W, 500 + i, "UN"[i % 2]) for i in range(n)])
