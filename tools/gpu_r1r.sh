@@ -16,5 +16,8 @@ CMD="python bench.py --steps 1 --warmup 3 --frames 4 --kind U --no-cpu --no-e2e"
 $CMD > gpurun_out/plain_U.log 2>&1 || exit 1
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_U.csv $CMD > gpurun_out/ncu_list_U.log 2>&1
 echo "ncu list exit $?"
-true
-
+# the ncu --set full pass (about a minute of box time); skip with NO_NCU_FULL=1
+if [ -z "$NO_NCU_FULL" ]; then
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"k_" -s 45 -c 15 -f -o gpurun_out/prof_r01_full_U $CMD > gpurun_out/ncu_full_U.log 2>&1
+  echo "ncu full exit $?"
+fi
