@@ -74,6 +74,9 @@ SIGNATURES = {
     "rct_warp_image": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "rct_blend_images": (_i, [_vp, _vp, C.c_double, _vp, _sz, _vp]),
     "rct_warp_blend": (_i, [_vp, _vp, _vp, C.c_double, _vp, _i, _i, _i, _i, _vp]),
+    "rct_jpeg_workspace_bytes": (_sz, [_i, _i, _i]),
+    "rct_jpeg_max_bytes": (_sz, [_i, _i]),
+    "rct_jpeg_encode_async": (_i, [_vp, _sz, _i, _i, _i, _i, _vp, _vp, _sz, _sz, _vp, _vp]),
     "rct_plan_info": (_i, [_vp, _i, C.POINTER(FrameInfo)]),
     "rct_plan_debug_hist": (_i, [_vp, _i, _vp, _vp]),
     "rct_plan_debug_target": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp]),

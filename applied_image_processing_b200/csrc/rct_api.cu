@@ -12,6 +12,7 @@
 
 #include "../../include/rct.h"
 #include "rct_kernels.cuh"
+#include "rct_jpeg.cuh"
 
 using namespace rct;
 
@@ -1197,6 +1198,42 @@ int rct_blend_images(const uint8_t *stylized, const uint8_t *warped, double alph
     const int vec = ((((uintptr_t)stylized) | ((uintptr_t)warped) | ((uintptr_t)out)) & 15) == 0;
     LAUNCH(k_blend, flat_blocks((nbytes + 15) / 16, dev), 256, (cudaStream_t)stream, stylized, warped, out, nbytes,
            (float)alpha, (float)(1.0 - alpha), vec);
+    return RCT_OK;
+}
+
+// ---- f-3: baseline JPEG encoder (rct_jpeg.cuh) -------------------------------------------------
+size_t rct_jpeg_workspace_bytes(int H, int W, int n)
+{
+    if (H <= 0 || W <= 0 || n <= 0 || H > 65535 || W > 65535) return 0;
+    return jpeg::carve(jpeg::make_geom(H, W, 0), n, nullptr).bytes;
+}
+
+size_t rct_jpeg_max_bytes(int H, int W)
+{
+    if (H <= 0 || W <= 0 || H > 65535 || W > 65535) return 0;
+    const jpeg::Geom g = jpeg::make_geom(H, W, 0);
+    // header + every entropy-coded byte stuffed + EOI
+    return (size_t)jpeg::kHeaderMax + 2u * (((size_t)g.nblk * jpeg::kBlockBitsMax + 7u) / 8u) + 2u;
+}
+
+int rct_jpeg_encode_async(const uint8_t *rgb, size_t frame_stride, int n, int H, int W, int quality, void *workspace,
+                          uint8_t *out, size_t out_stride, size_t out_cap, unsigned long long *nbytes, void *stream)
+{
+    if (n == 0) return RCT_OK;
+    if (!rgb || !workspace || !out || !nbytes) return fail(RCT_ERR_ARG, "null pointer");
+    if (n < 0 || H <= 0 || W <= 0 || H > 65535 || W > 65535) return fail(RCT_ERR_ARG, "JPEG frames are 1..65535 pixels a side");
+    if (quality < 1 || quality > 100) return fail(RCT_ERR_ARG, "quality %d outside 1..100", quality);
+    if (((uintptr_t)workspace & 255u) != 0) return fail(RCT_ERR_ARG, "workspace must be 256-byte aligned");
+    if (out_cap > out_stride && n > 1) return fail(RCT_ERR_ARG, "out_cap exceeds out_stride");
+    int dev, rc = ensure_device(&dev);
+    if (rc) return rc;
+    const jpeg::Geom g = jpeg::make_geom(H, W, frame_stride);
+    const jpeg::Workspace ws = jpeg::carve(g, n, workspace);
+    int launches = 0;
+    cudaError_t e = jpeg::encode_launch(rgb, g, n, quality, ws, out, out_stride, out_cap, nbytes, g_sm_count[dev],
+                                        (cudaStream_t)stream, &launches);
+    t_launches += launches;
+    if (e != cudaSuccess) return fail(RCT_ERR_CUDA, "JPEG encoder launch failed: %s", cudaGetErrorString(e));
     return RCT_OK;
 }
 

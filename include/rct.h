@@ -223,6 +223,18 @@ int rct_blend_images(const uint8_t *stylized, const uint8_t *warped, double alph
 int rct_warp_blend(const uint8_t *stylized, const uint8_t *prev_stylized, const float *flow, double alpha,
                    uint8_t *out, int n, int H, int W, int channels, void *stream);
 
+/* f-3: the write at the end of the pipeline, `Image.fromarray(combined_image).save(".../result.jpg")`
+ * (LST:241-243; Pillow defaults = libjpeg baseline, 4:2:0, Annex-K Huffman tables, islow DCT), on the device:
+ * rgb uint8 [n] frames of H x W x 3, frame_stride bytes apart (0 = packed); out [n][out_stride] receives the
+ * complete JFIF files, byte for byte what Pillow writes at the same quality (1..100; the reference uses 75);
+ * nbytes[n] (device) = bytes of each file.  A value above out_cap means that file was truncated at out_cap:
+ * retry with rct_jpeg_max_bytes(H, W).  workspace: rct_jpeg_workspace_bytes(H, W, n) bytes of device memory,
+ * 256-byte aligned, contents irrelevant.  Everything is enqueued on `stream`; nothing synchronises. */
+size_t rct_jpeg_workspace_bytes(int H, int W, int n);
+size_t rct_jpeg_max_bytes(int H, int W);
+int rct_jpeg_encode_async(const uint8_t *rgb, size_t frame_stride, int n, int H, int W, int quality, void *workspace,
+                          uint8_t *out, size_t out_stride, size_t out_cap, unsigned long long *nbytes, void *stream);
+
 /* ---- introspection for parity tests (RCT_FLAG_DEBUG plans; all synchronise) -------------- */
 typedef struct {
     int64_t n_target, n_source;     /* region pixel counts (non-black, LST:134-138) */
