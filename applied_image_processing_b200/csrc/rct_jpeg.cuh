@@ -6,10 +6,12 @@
 //
 // Pipeline per frame (blocks in scan order: MCU-major, Y00 Y01 Y10 Y11 Cb Cr inside a 16x16 MCU):
 //   k_jpeg_dct      thread per block: RGB -> component samples (edge rules of jcprepct.c/jcsample.c),
-//                   islow DCT, quantise -> int16[64] in zigzag order                       (3 B/px written)
-//   k_jpeg_bits     thread per block: length in bits of the block's Huffman code
-//   k_jpeg_scan     one CTA per frame: exclusive scan -> bit offset of every block, total bits
-//   k_jpeg_emit     thread per block: codes OR-ed into the (zeroed) unstuffed bit stream at its offset
+//                   islow DCT, quantise -> int16[64] in zigzag order (3 B/px written), plus per block
+//                   (bits of its AC codes, DC) for the bit count
+//   k_jpeg_bits     thread per block: length in bits of the block's Huffman code; sum per group of 256 blocks
+//   k_jpeg_scan     one CTA per frame: exclusive scan over the groups -> bit offset of each group, total bits
+//   k_jpeg_emit     thread per block: offset = group offset + scan inside the CTA; codes OR-ed into the
+//                   (zeroed) unstuffed bit stream
 //   k_jpeg_ff_count / k_jpeg_ff_scan / k_jpeg_ff_write   byte stuffing (0xFF -> 0xFF 0x00) as a
 //                   count / scan / scatter over 4 KiB tiles, header in front, EOI behind, byte count out
 // The per-block bodies are __host__ __device__ so that tools/jpeg_selftest.cu can run the same arithmetic
@@ -52,6 +54,7 @@ inline Geom make_geom(int H, int W, size_t frame_stride)
 // derived tables, passed to the kernels by value (2.4 KB of kernel parameters)
 struct Tables {
     unsigned short q8[2][64];   // 8 * quantiser, indexed by ZIGZAG POSITION (the order the blocks are stored in)
+    unsigned rq[2][64];         // ceil(2^32 / q8): floor(n / q8) == mulhi(n, rq) for every n < 2^20 (q8 <= 2040)
     unsigned dc[2][12];         // (code << 5) | length
     unsigned ac[2][256];
 };
@@ -78,6 +81,28 @@ JHD bool is_dummy(const Geom &g, unsigned mcu, int b)
     return (2 * myi + (b >> 1)) >= g.by || (2 * mxi + (b & 1)) >= g.bx;
 }
 
+// NPX pixels of one image row starting at x0, as packed little-endian words; pixels right of the image repeat the
+// last column.  Spans inside the image whose first byte is 4-byte aligned are read as words.
+template <int NPX>
+JHD void load_span(const uint8_t *row, int x0, int W, unsigned *wv)
+{
+    const uint8_t *p = row + (size_t)x0 * 3u;
+    if (x0 + NPX <= W && ((uintptr_t)p & 3u) == 0) {
+        const unsigned *pw = reinterpret_cast<const unsigned *>(p);
+#pragma unroll
+        for (int k = 0; k < NPX * 3 / 4; ++k) wv[k] = pw[k];
+        return;
+    }
+#pragma unroll
+    for (int k = 0; k < NPX * 3 / 4; ++k) wv[k] = 0u;
+#pragma unroll
+    for (int j = 0; j < NPX * 3; ++j) {
+        const int x = x0 + j / 3 < W ? x0 + j / 3 : W - 1;
+        wv[j >> 2] |= (unsigned)row[(size_t)x * 3u + (unsigned)(j % 3)] << (8 * (j & 3));
+    }
+}
+JHD int span_byte(const unsigned *wv, int j) { return (int)((wv[j >> 2] >> (8 * (j & 3))) & 255u); }
+
 // level-shifted samples of block b of one MCU.  Luma: edge pixels replicated.  Chroma: the right edge is
 // replicated at full resolution before the 2x2 box filter (bias 1, 2, 1, 2 ... along a row), an odd last row
 // is doubled, and rows below the image repeat the last DOWNSAMPLED row (jcprepct.c pre_process_data).
@@ -87,34 +112,35 @@ JHD void block_samples(const uint8_t *rgb, const Geom &g, unsigned mcu, int b, i
     const size_t rowb = (size_t)g.W * 3u;
     if (b < 4) {
         const int y0 = myi * 16 + (b >> 1) * 8, x0 = mxi * 16 + (b & 1) * 8;
+#pragma unroll
         for (int r = 0; r < 8; ++r) {
             const int y = y0 + r < g.H ? y0 + r : g.H - 1;
-            const uint8_t *row = rgb + (size_t)y * rowb;
-            for (int c = 0; c < 8; ++c) {
-                const int x = x0 + c < g.W ? x0 + c : g.W - 1;
-                const uint8_t *p = row + (size_t)x * 3u;
-                blk[r * 8 + c] = ycc_y(p[0], p[1], p[2]) - 128;
-            }
+            unsigned wv[6];
+            load_span<8>(rgb + (size_t)y * rowb, x0 < g.W ? x0 : g.W - 1, g.W, wv);
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                blk[r * 8 + c] = ycc_y(span_byte(wv, 3 * c), span_byte(wv, 3 * c + 1), span_byte(wv, 3 * c + 2)) - 128;
         }
         return;
     }
+#pragma unroll
     for (int r = 0; r < 8; ++r) {
         int cr = myi * 8 + r;
         if (cr > g.ch - 1) cr = g.ch - 1;
         const int ya = 2 * cr, yb = 2 * cr + 1 < g.H ? 2 * cr + 1 : g.H - 1;
-        const uint8_t *ra = rgb + (size_t)ya * rowb, *rb = rgb + (size_t)yb * rowb;
+        unsigned wa[12], wb[12];
+        load_span<16>(rgb + (size_t)ya * rowb, mxi * 16, g.W, wa);
+        load_span<16>(rgb + (size_t)yb * rowb, mxi * 16, g.W, wb);
+#pragma unroll
         for (int c = 0; c < 8; ++c) {
-            const int xa0 = mxi * 16 + 2 * c, xb0 = xa0 + 1;
-            const int xa = xa0 < g.W ? xa0 : g.W - 1, xb = xb0 < g.W ? xb0 : g.W - 1;
-            const uint8_t *p0 = ra + (size_t)xa * 3u, *p1 = ra + (size_t)xb * 3u;
-            const uint8_t *p2 = rb + (size_t)xa * 3u, *p3 = rb + (size_t)xb * 3u;
-            int s;
-            if (b == 4)
-                s = ycc_cb(p0[0], p0[1], p0[2]) + ycc_cb(p1[0], p1[1], p1[2]) + ycc_cb(p2[0], p2[1], p2[2]) +
-                    ycc_cb(p3[0], p3[1], p3[2]);
-            else
-                s = ycc_cr(p0[0], p0[1], p0[2]) + ycc_cr(p1[0], p1[1], p1[2]) + ycc_cr(p2[0], p2[1], p2[2]) +
-                    ycc_cr(p3[0], p3[1], p3[2]);
+            int s = 0;
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const int j = 3 * (2 * c + k);
+                const int r0 = span_byte(wa, j), g0 = span_byte(wa, j + 1), b0 = span_byte(wa, j + 2);
+                const int r1 = span_byte(wb, j), g1 = span_byte(wb, j + 1), b1 = span_byte(wb, j + 2);
+                s += b == 4 ? ycc_cb(r0, g0, b0) + ycc_cb(r1, g1, b1) : ycc_cr(r0, g0, b0) + ycc_cr(r1, g1, b1);
+            }
             blk[r * 8 + c] = ((s + 1 + (c & 1)) >> 2) - 128;
         }
     }
@@ -154,8 +180,18 @@ JHD void fdct8(int *d, int s)
     d[s] = descale(t7 + z1 + z4, sh);
 }
 
-// jcdctmgr.c forward_DCT: rows, columns, then |c| + q8/2 over q8 with the sign put back; zigzag order out
-JHD void fdct_quantise(int *blk, const unsigned short *q8zz, short *out)
+JHD unsigned mulhi32(unsigned a, unsigned b)
+{
+#ifdef __CUDA_ARCH__
+    return __umulhi(a, b);
+#else
+    return (unsigned)(((unsigned long long)a * (unsigned long long)b) >> 32);
+#endif
+}
+
+// jcdctmgr.c forward_DCT: rows, columns, then (|c| + q8/2) / q8 with the sign put back; zigzag order out.
+// The division is a multiplication by ceil(2^32 / q8): exact while n * q8 < 2^32, and |c| < 2^16 here.
+JHD void fdct_quantise(int *blk, const unsigned short *q8zz, const unsigned *rqzz, short *out)
 {
 #pragma unroll
     for (int r = 0; r < 8; ++r) fdct8<true>(blk + 8 * r, 1);
@@ -164,7 +200,7 @@ JHD void fdct_quantise(int *blk, const unsigned short *q8zz, short *out)
 #pragma unroll
     for (int k = 0; k < 64; ++k) {
         const int v = blk[zigzag_natural(k)], q = (int)q8zz[k];
-        const int m = ((v < 0 ? -v : v) + (q >> 1)) / q;
+        const int m = (int)mulhi32((unsigned)((v < 0 ? -v : v) + (q >> 1)), rqzz[k]);
         out[k] = (short)(v < 0 ? -m : m);
     }
 }
@@ -209,6 +245,7 @@ JHD void encode_block(SINK &sink, const short *zz, bool dummy, int dc_diff, cons
     }
     int run = 0;
     if (!dummy) {
+#pragma unroll
         for (int k = 1; k < 64; ++k) {
             const int v = zz[k];
             if (v == 0) {
@@ -240,6 +277,31 @@ struct CountSink {
     unsigned bits = 0;
     JHD void put(unsigned, int len) { bits += (unsigned)len; }
 };
+
+// what k_jpeg_dct leaves per block for the bit count: (bits of the AC codes << 16) | (DC & 0xffff)
+JHD unsigned ac_code_bits(const short *zz, bool dummy, const unsigned *dc_tab, const unsigned *ac_tab)
+{
+    CountSink sink;
+    encode_block(sink, zz, dummy, 0, dc_tab, ac_tab);
+    return sink.bits - (dc_tab[0] & 31u);
+}
+JHD unsigned dc_code_bits(int diff, const unsigned *dc_tab)
+{
+    const int nb = bit_length((unsigned)(diff < 0 ? -diff : diff));
+    return (dc_tab[nb] & 31u) + (unsigned)nb;
+}
+JHD int meta_dc(unsigned m) { return (int)(short)(unsigned short)(m & 0xffffu); }
+JHD int resolved_dc_meta(const unsigned *meta, const Geom &g, unsigned mcu, int b)
+{
+    while (b > 0 && is_dummy(g, mcu, b)) --b;
+    return meta_dc(meta[(size_t)mcu * 6u + (unsigned)b]);
+}
+JHD int dc_predictor_meta(const unsigned *meta, const Geom &g, unsigned mcu, int b)
+{
+    if (b >= 1 && b <= 3) return resolved_dc_meta(meta, g, mcu, b - 1);
+    if (mcu == 0) return 0;
+    return b == 0 ? resolved_dc_meta(meta, g, mcu - 1, 3) : meta_dc(meta[(size_t)(mcu - 1) * 6u + (unsigned)b]);
+}
 
 JHD unsigned bswap32(unsigned v)
 {
@@ -288,6 +350,7 @@ struct StreamSink {
 
 // ---- host side: tables, header, workspace layout --------------------------------------------
 constexpr unsigned kTile = 4096;         // bytes of unstuffed stream per stuffing tile
+constexpr int kEntThreads = 256;         // blocks per CTA of the entropy kernels = one group of the offset scan
 constexpr unsigned kBlockBitsMax = 1664; // >= 20 (DC) + 63 * 26 (AC) bits: the worst block
 constexpr int kHeaderMax = 640;
 
@@ -369,7 +432,10 @@ inline void make_tables(int quality, Tables *t, Header *h, int H, int W)
     unsigned char q[2][64];
     quant_tables(quality, q[0], q[1]);
     for (int c = 0; c < 2; ++c)
-        for (int i = 0; i < 64; ++i) t->q8[c][i] = (unsigned short)(q[c][i] * 8);
+        for (int i = 0; i < 64; ++i) {
+            t->q8[c][i] = (unsigned short)(q[c][i] * 8);
+            t->rq[c][i] = (unsigned)(((1ull << 32) + t->q8[c][i] - 1u) / t->q8[c][i]);
+        }
     memset(t->dc, 0, sizeof t->dc);
     memset(t->ac, 0, sizeof t->ac);
     const int ids[4] = {0x00, 0x10, 0x01, 0x11};
@@ -423,12 +489,14 @@ inline void make_tables(int quality, Tables *t, Header *h, int H, int W)
 // device scratch of one call (n frames).  Every array is 256-byte aligned.
 struct Workspace {
     short *coef;                  // [n][nblk][64] zigzag order
+    unsigned *meta;               // [n][nblk] (AC code bits << 16) | DC
     unsigned *bits;               // [n][nblk]
-    unsigned long long *offs;     // [n][nblk] bit offset of each block in its frame's stream
+    unsigned *part;               // [n][nparts] bits of each group of kEntThreads consecutive blocks
+    unsigned long long *pbase;    // [n][nparts] bit offset of each group in its frame's stream
     unsigned long long *total;    // [n] bits of entropy-coded data before padding
     unsigned *stream;             // [n][stream_words] unstuffed, zeroed by the caller of the kernels
     unsigned *tile_ff;            // [n][ntiles] 0xFF bytes per tile, then their exclusive scan
-    size_t stream_words, ntiles, bytes;
+    size_t stream_words, ntiles, nparts, bytes;
 };
 inline size_t align256(size_t v) { return (v + 255u) & ~(size_t)255u; }
 inline Workspace carve(const Geom &g, int n, void *base)
@@ -445,8 +513,11 @@ inline Workspace carve(const Geom &g, int n, void *base)
         return (void *)r;
     };
     w.coef = (short *)take((size_t)n * g.nblk * 64u * sizeof(short));
+    w.meta = (unsigned *)take((size_t)n * g.nblk * sizeof(unsigned));
     w.bits = (unsigned *)take((size_t)n * g.nblk * sizeof(unsigned));
-    w.offs = (unsigned long long *)take((size_t)n * g.nblk * sizeof(unsigned long long));
+    w.nparts = ((size_t)g.nblk + kEntThreads - 1u) / kEntThreads;
+    w.part = (unsigned *)take((size_t)n * w.nparts * sizeof(unsigned));
+    w.pbase = (unsigned long long *)take((size_t)n * w.nparts * sizeof(unsigned long long));
     w.total = (unsigned long long *)take((size_t)n * sizeof(unsigned long long));
     w.stream = (unsigned *)take((size_t)n * stream_bytes);
     w.tile_ff = (unsigned *)take((size_t)n * w.ntiles * sizeof(unsigned));
@@ -490,28 +561,7 @@ __device__ __forceinline__ T jblock_excl_scan(T v, T *s_warp, T &block_total)
     return ex + s_warp[warp];
 }
 
-constexpr int kDctThreads = 128, kEntThreads = 128, kFfThreads = kTile / 16;
-
-__global__ void __launch_bounds__(kDctThreads) k_jpeg_dct(const uint8_t *rgb, Geom g, int n, Tables tab, short *coef)
-{
-    const size_t i = (size_t)blockIdx.x * kDctThreads + threadIdx.x;
-    if (i >= (size_t)n * g.nblk) return;
-    const unsigned frame = (unsigned)(i / g.nblk), r = (unsigned)(i % g.nblk), mcu = r / 6u;
-    const int b = (int)(r % 6u);
-    __align__(16) short out[64];
-    if (is_dummy(g, mcu, b)) {
-#pragma unroll
-        for (int k = 0; k < 64; ++k) out[k] = 0;
-    } else {
-        int blk[64];
-        block_samples(rgb + (size_t)frame * g.frame_stride, g, mcu, b, blk);
-        fdct_quantise(blk, tab.q8[b < 4 ? 0 : 1], out);
-    }
-    uint4 *dst = reinterpret_cast<uint4 *>(coef + i * 64u);
-    const uint4 *src = reinterpret_cast<const uint4 *>(out);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) dst[k] = src[k];
-}
+constexpr int kDctThreads = 192, kFfThreads = kTile / 16;
 
 __device__ __forceinline__ void load_tables(const Tables &tab, unsigned (*s_dc)[12], unsigned (*s_ac)[256])
 {
@@ -527,42 +577,78 @@ __device__ __forceinline__ void load_block(const short *coef, size_t block, shor
     for (int k = 0; k < 8; ++k) dst[k] = __ldg(src + k);
 }
 
-__global__ void __launch_bounds__(kEntThreads) k_jpeg_bits(const short *coef, Geom g, int n, Tables tab, unsigned *bits)
+// 192-thread CTAs over 32 consecutive MCUs: warps 0-3 take the 128 luma blocks, warp 4 the Cb and warp 5 the Cr
+// blocks (a chroma block reads four times the pixels of a luma block: warps of one kind finish together)
+#ifndef RCT_JDB
+#define RCT_JDB 3
+#endif
+__global__ void __launch_bounds__(kDctThreads, RCT_JDB) k_jpeg_dct(const uint8_t *rgb, Geom g, Tables tab, short *coef, unsigned *meta)
 {
     __shared__ unsigned s_dc[2][12], s_ac[2][256];
     load_tables(tab, s_dc, s_ac);
-    const size_t i = (size_t)blockIdx.x * kEntThreads + threadIdx.x;
-    if (i >= (size_t)n * g.nblk) return;
-    const unsigned frame = (unsigned)(i / g.nblk), r = (unsigned)(i % g.nblk), mcu = r / 6u;
-    const int b = (int)(r % 6u), c = b < 4 ? 0 : 1;
-    const short *fc = coef + (size_t)frame * g.nblk * 64u;
-    __align__(16) short zz[64];
-    load_block(coef, i, zz);
-    const int diff = resolved_dc(fc, g, mcu, b) - dc_predictor(fc, g, mcu, b);
-    CountSink sink;
-    encode_block(sink, zz, is_dummy(g, mcu, b), diff, s_dc[c], s_ac[c]);
-    bits[i] = sink.bits;
+    const unsigned frame = blockIdx.y, t = threadIdx.x;
+    const unsigned mcu = blockIdx.x * 32u + (t < 128u ? t >> 2 : (t - 128u) & 31u);
+    const int b = t < 128u ? (int)(t & 3u) : 4 + (int)((t - 128u) >> 5);
+    if (mcu >= g.nmcu) return;
+    __align__(16) short out[64];
+    if (is_dummy(g, mcu, b)) {
+#pragma unroll
+        for (int k = 0; k < 64; ++k) out[k] = 0;
+    } else {
+        int blk[64];
+        block_samples(rgb + (size_t)frame * g.frame_stride, g, mcu, b, blk);
+        fdct_quantise(blk, tab.q8[b < 4 ? 0 : 1], tab.rq[b < 4 ? 0 : 1], out);
+    }
+    const size_t blk_index = (size_t)frame * g.nblk + (size_t)mcu * 6u + (unsigned)b;
+    const int c = b < 4 ? 0 : 1;
+    meta[blk_index] = (ac_code_bits(out, is_dummy(g, mcu, b), s_dc[c], s_ac[c]) << 16) | (unsigned)(unsigned short)out[0];
+    uint4 *dst = reinterpret_cast<uint4 *>(coef + blk_index * 64u);
+    const uint4 *src = reinterpret_cast<const uint4 *>(out);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) dst[k] = src[k];
 }
 
-// one CTA of 1024 threads per frame: bit offset of every block; total[frame]
-__global__ void __launch_bounds__(1024) k_jpeg_scan(const unsigned *bits, Geom g, unsigned long long *offs,
+// grid (nparts, n): thread per block -> bits[] = AC bits + bits of the DC difference, and the sum over the CTA's
+// blocks -> part[]
+__global__ void __launch_bounds__(kEntThreads) k_jpeg_bits(const unsigned *meta, Geom g, Tables tab, unsigned *bits,
+                                                           unsigned *part, size_t nparts)
+{
+    __shared__ unsigned s_dc[2][12], s_warp[33];
+    if (threadIdx.x < 24) s_dc[threadIdx.x / 12][threadIdx.x % 12] = tab.dc[threadIdx.x / 12][threadIdx.x % 12];
+    __syncthreads();
+    const unsigned frame = blockIdx.y, r = blockIdx.x * kEntThreads + threadIdx.x;
+    unsigned mine = 0;
+    if (r < g.nblk) {
+        const unsigned mcu = r / 6u;
+        const int b = (int)(r % 6u);
+        const unsigned *fm = meta + (size_t)frame * g.nblk;
+        const int diff = resolved_dc_meta(fm, g, mcu, b) - dc_predictor_meta(fm, g, mcu, b);
+        mine = (fm[r] >> 16) + dc_code_bits(diff, s_dc[b < 4 ? 0 : 1]);
+        bits[(size_t)frame * g.nblk + r] = mine;
+    }
+    unsigned all;
+    jblock_excl_scan(mine, s_warp, all);
+    if (threadIdx.x == 0) part[(size_t)frame * nparts + blockIdx.x] = all;
+}
+
+// one CTA of 1024 threads per frame: bit offset of every group of blocks; total[frame]
+__global__ void __launch_bounds__(1024) k_jpeg_scan(const unsigned *part, size_t nparts, unsigned long long *pbase,
                                                     unsigned long long *total)
 {
-    __shared__ unsigned long long s_warp[33];
+    __shared__ unsigned s_warp[33];
     const unsigned frame = blockIdx.x;
-    const unsigned *fb = bits + (size_t)frame * g.nblk;
-    unsigned long long *fo = offs + (size_t)frame * g.nblk;
-    const unsigned chunk = (g.nblk + 1023u) / 1024u;
-    const unsigned lo = min(threadIdx.x * chunk, g.nblk), hi = min(lo + chunk, g.nblk);
-    unsigned long long sum = 0;
-    for (unsigned j = lo; j < hi; ++j) sum += fb[j];
-    unsigned long long all;
-    unsigned long long run = jblock_excl_scan(sum, s_warp, all);
-    for (unsigned j = lo; j < hi; ++j) {
-        fo[j] = run;
-        run += fb[j];
+    const unsigned *fp = part + (size_t)frame * nparts;
+    unsigned long long *fb = pbase + (size_t)frame * nparts;
+    unsigned long long carry = 0;
+    for (size_t base = 0; base < nparts; base += 1024u) {   // 1024 groups hold < 2^32 bits
+        const size_t i = base + threadIdx.x;
+        const unsigned v = i < nparts ? fp[i] : 0u;
+        unsigned all;
+        const unsigned ex = jblock_excl_scan(v, s_warp, all);
+        if (i < nparts) fb[i] = carry + ex;
+        carry += all;
     }
-    if (threadIdx.x == 0) total[frame] = all;
+    if (threadIdx.x == 0) total[frame] = carry;
 }
 
 // zero the words of each frame's stream that the entropy coder will OR into
@@ -574,21 +660,25 @@ __global__ void __launch_bounds__(256) k_jpeg_zero(unsigned *stream, size_t stre
     for (size_t k = (size_t)blockIdx.x * 256u + threadIdx.x; k < words; k += (size_t)gridDim.x * 256u) s[k] = 0u;
 }
 
-__global__ void __launch_bounds__(kEntThreads) k_jpeg_emit(const short *coef, Geom g, int n, Tables tab,
-                                                           const unsigned long long *offs, unsigned *stream,
-                                                           size_t stream_words)
+// grid (nparts, n): offset of a block = offset of its group + exclusive scan of bits[] inside the CTA
+__global__ void __launch_bounds__(kEntThreads) k_jpeg_emit(const short *coef, Geom g, Tables tab, const unsigned *bits,
+                                                           const unsigned long long *pbase, size_t nparts,
+                                                           unsigned *stream, size_t stream_words)
 {
-    __shared__ unsigned s_dc[2][12], s_ac[2][256];
+    __shared__ unsigned s_dc[2][12], s_ac[2][256], s_warp[33];
     load_tables(tab, s_dc, s_ac);
-    const size_t i = (size_t)blockIdx.x * kEntThreads + threadIdx.x;
-    if (i >= (size_t)n * g.nblk) return;
-    const unsigned frame = (unsigned)(i / g.nblk), r = (unsigned)(i % g.nblk), mcu = r / 6u;
+    const unsigned frame = blockIdx.y, r = blockIdx.x * kEntThreads + threadIdx.x;
+    const bool live = r < g.nblk;
+    unsigned all;
+    const unsigned ex = jblock_excl_scan(live ? bits[(size_t)frame * g.nblk + r] : 0u, s_warp, all);
+    if (!live) return;
+    const unsigned mcu = r / 6u;
     const int b = (int)(r % 6u), c = b < 4 ? 0 : 1;
     const short *fc = coef + (size_t)frame * g.nblk * 64u;
     __align__(16) short zz[64];
-    load_block(coef, i, zz);
+    load_block(fc, r, zz);
     const int diff = resolved_dc(fc, g, mcu, b) - dc_predictor(fc, g, mcu, b);
-    StreamSink sink(stream + (size_t)frame * stream_words, offs[i]);
+    StreamSink sink(stream + (size_t)frame * stream_words, pbase[(size_t)frame * nparts + blockIdx.x] + ex);
     encode_block(sink, zz, is_dummy(g, mcu, b), diff, s_dc[c], s_ac[c]);
     if (r == g.nblk - 1u) {  // jchuff.c flush_bits: pad the last byte with 1-bits
         const int k = (int)((8ull - (sink.position() & 7ull)) & 7ull);
@@ -696,15 +786,14 @@ inline cudaError_t encode_launch(const uint8_t *rgb, const Geom &g, int n, int q
     Tables tab;
     Header hdr;
     make_tables(quality, &tab, &hdr, g.H, g.W);
-    const size_t nb = (size_t)n * g.nblk;
     const unsigned wide = (unsigned)(sm_count > 0 ? sm_count : 148) * 8u;
     const unsigned gx = (unsigned)(ws.ntiles < wide ? ws.ntiles : wide);
-    k_jpeg_dct<<<(unsigned)((nb + kDctThreads - 1) / kDctThreads), kDctThreads, 0, st>>>(rgb, g, n, tab, ws.coef);
-    k_jpeg_bits<<<(unsigned)((nb + kEntThreads - 1) / kEntThreads), kEntThreads, 0, st>>>(ws.coef, g, n, tab, ws.bits);
-    k_jpeg_scan<<<n, 1024, 0, st>>>(ws.bits, g, ws.offs, ws.total);
+    k_jpeg_dct<<<dim3((g.nmcu + 31u) / 32u, (unsigned)n), kDctThreads, 0, st>>>(rgb, g, tab, ws.coef, ws.meta);
+    const dim3 ent((unsigned)ws.nparts, (unsigned)n);
+    k_jpeg_bits<<<ent, kEntThreads, 0, st>>>(ws.meta, g, tab, ws.bits, ws.part, ws.nparts);
+    k_jpeg_scan<<<n, 1024, 0, st>>>(ws.part, ws.nparts, ws.pbase, ws.total);
     k_jpeg_zero<<<dim3(wide, n), 256, 0, st>>>(ws.stream, ws.stream_words, ws.total);
-    k_jpeg_emit<<<(unsigned)((nb + kEntThreads - 1) / kEntThreads), kEntThreads, 0, st>>>(ws.coef, g, n, tab, ws.offs,
-                                                                                        ws.stream, ws.stream_words);
+    k_jpeg_emit<<<ent, kEntThreads, 0, st>>>(ws.coef, g, tab, ws.bits, ws.pbase, ws.nparts, ws.stream, ws.stream_words);
     k_jpeg_ff_count<<<dim3(gx, n), kFfThreads, 0, st>>>(ws.stream, ws.stream_words, ws.ntiles, ws.total, ws.tile_ff);
     k_jpeg_ff_scan<<<n, 1024, 0, st>>>(ws.tile_ff, ws.ntiles, ws.total, hdr, out, out_stride, out_cap, nbytes);
     k_jpeg_ff_write<<<dim3(gx, n), kFfThreads, 0, st>>>(ws.stream, ws.stream_words, ws.ntiles, ws.total, ws.tile_ff,

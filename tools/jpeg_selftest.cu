@@ -30,8 +30,15 @@ inline size_t encode_host_emulation(const uint8_t *rgb, int H, int W, int qualit
         } else {
             int blk[64];
             block_samples(rgb, g, mcu, b, blk);
-            fdct_quantise(blk, tab.q8[b < 4 ? 0 : 1], o);
+            fdct_quantise(blk, tab.q8[b < 4 ? 0 : 1], tab.rq[b < 4 ? 0 : 1], o);
         }
+    }
+    // as k_jpeg_dct / k_jpeg_bits split it: AC bits + DC per block first, then the DC differences
+    unsigned *meta = new unsigned[g.nblk];
+    for (unsigned i = 0; i < g.nblk; ++i) {
+        const int b = (int)(i % 6u), c = b < 4 ? 0 : 1;
+        const short *o = coef + (size_t)i * 64u;
+        meta[i] = (ac_code_bits(o, is_dummy(g, i / 6u, b), tab.dc[c], tab.ac[c]) << 16) | (unsigned)(unsigned short)o[0];
     }
     unsigned long long run = 0;
     for (unsigned i = 0; i < g.nblk; ++i) {
@@ -40,9 +47,15 @@ inline size_t encode_host_emulation(const uint8_t *rgb, int H, int W, int qualit
         CountSink sink;
         encode_block(sink, coef + (size_t)i * 64u, is_dummy(g, mcu, b), resolved_dc(coef, g, mcu, b) - dc_predictor(coef, g, mcu, b),
                      tab.dc[c], tab.ac[c]);
+        const unsigned fast = (meta[i] >> 16) + dc_code_bits(resolved_dc_meta(meta, g, mcu, b) - dc_predictor_meta(meta, g, mcu, b), tab.dc[c]);
+        if (fast != sink.bits) {
+            fprintf(stderr, "bit count of block %u: %u from (AC bits, DC), %u from the coefficients\n", i, fast, sink.bits);
+            exit(5);
+        }
         offs[i] = run;
-        run += sink.bits;
+        run += fast;
     }
+    delete[] meta;
     for (unsigned k = g.nblk; k-- > 0;) {  // any order: the blocks only OR into the stream
         const unsigned mcu = k / 6u;
         const int b = (int)(k % 6u), c = b < 4 ? 0 : 1;
