@@ -1,7 +1,8 @@
 """TEST INFRASTRUCTURE -- numpy restatement of the baseline JPEG encoder behind the reference's
 `Image.fromarray(combined_image).save(".../localized_style_transfer_result.jpg")` (LST:241-243;
 SURVEY.md 8f row f-3): Pillow defaults = libjpeg(-turbo) baseline, quality 75, 4:2:0, standard
-Huffman tables, JDCT_ISLOW.  Groundwork for the device encoder (not built yet): only tests/ may
+Huffman tables, JDCT_ISLOW -- and, further down, of the baseline decoder behind `Image.open` (LST:200, 219).
+The device encoder is csrc/rct_jpeg.cuh; the decoder half is the oracle only so far.  Only tests/ may
 import this; the product never does.
 
 The arithmetic is the published libjpeg algorithm (jccolor.c, jcsample.c, jfdctint.c,
@@ -245,3 +246,222 @@ def encode_jpeg(rgb, quality=75):
     out += entropy_scan(*component_blocks(rgb, quality))
     out += b"\xff\xd9"
     return bytes(out)
+
+
+# ---------------------------------------------------------------------------------------------
+# Decoder: the other half of row f-3, `Image.open(path)` of the content / stylised images
+# (localized_style_transfer.py:200, 219).  Baseline sequential JPEG, 8-bit, Huffman, 1 or 3 components with
+# luma sampling 1x1, 2x1, 1x2 or 2x2; libjpeg's defaults as Pillow uses them: islow IDCT (jidctint.c), fancy
+# (triangle) chroma upsampling (jdsample.c), table-driven YCbCr -> RGB (jdcolor.c).  Pinned to Pillow's decode
+# in tests/test_jpeg_oracle.py.
+# ---------------------------------------------------------------------------------------------
+def _idct_pass(d, first):
+    """One pass of jidctint.c jpeg_idct_islow along the last axis."""
+    i0, i1, i2, i3, i4, i5, i6, i7 = (d[..., k] for k in range(8))
+    z1 = (i2 + i6) * 4433
+    t2 = z1 - i6 * 15137
+    t3 = z1 + i2 * 6270
+    t0, t1 = (i0 + i4) << 13, (i0 - i4) << 13
+    t10, t13, t11, t12 = t0 + t3, t0 - t3, t1 + t2, t1 - t2
+    o0, o1, o2, o3 = i7, i5, i3, i1
+    z1, z2, z3, z4 = o0 + o3, o1 + o2, o0 + o2, o1 + o3
+    z5 = (z3 + z4) * 9633
+    o0, o1, o2, o3 = o0 * 2446, o1 * 16819, o2 * 25172, o3 * 12299
+    z1, z2, z3, z4 = z1 * -7373, z2 * -20995, z3 * -16069 + z5, z4 * -3196 + z5
+    o0, o1, o2, o3 = o0 + z1 + z3, o1 + z2 + z4, o2 + z2 + z3, o3 + z1 + z4
+    sh = 13 - 2 if first else 13 + 2 + 3
+    out = [t10 + o3, t11 + o2, t12 + o1, t13 + o0, t13 - o0, t12 - o1, t11 - o2, t10 - o3]
+    return np.stack([_descale(v, sh) for v in out], axis=-1)
+
+
+def idct_blocks(coef, zz_table):
+    """coef (..., 64) quantised, natural order -> samples (..., 8, 8) in 0..255 (dequantise, columns, rows, range limit)."""
+    q = np.empty(64, np.int64)
+    q[ZIGZAG] = zz_table
+    blk = (coef.astype(np.int64) * q).reshape(coef.shape[:-1] + (8, 8))
+    blk = _idct_pass(blk.swapaxes(-1, -2), True).swapaxes(-1, -2)   # columns
+    blk = _idct_pass(blk, False)                                     # rows
+    return np.clip(blk + 128, 0, 255)
+
+
+class _BitReader:
+    def __init__(self, data, pos):
+        self.d, self.p, self.acc, self.n = data, pos, 0, 0
+
+    def _fill(self):
+        b = self.d[self.p]
+        if b == 0xFF:
+            nxt = self.d[self.p + 1]
+            if nxt == 0:
+                self.p += 2
+            else:                       # a marker: feed zeros (libjpeg's behaviour at the end of the scan)
+                b = 0
+        else:
+            self.p += 1
+        self.acc = (self.acc << 8) | b
+        self.n += 8
+
+    def bits(self, k):
+        if k == 0:
+            return 0
+        while self.n < k:
+            self._fill()
+        self.n -= k
+        v = (self.acc >> self.n) & ((1 << k) - 1)
+        self.acc &= (1 << self.n) - 1
+        return v
+
+    def symbol(self, lookup):
+        code, length = 0, 0
+        while True:
+            code = (code << 1) | self.bits(1)
+            length += 1
+            s = lookup.get((length, code))
+            if s is not None:
+                return s
+            if length > 16:
+                raise ValueError("bad Huffman code")
+
+    def restart(self):
+        self.acc = self.n = 0
+        assert self.d[self.p] == 0xFF and 0xD0 <= self.d[self.p + 1] <= 0xD7, "restart marker expected"
+        self.p += 2
+
+
+def _extend(v, nbits):
+    return v if nbits == 0 or v >= (1 << (nbits - 1)) else v - (1 << nbits) + 1
+
+
+def _fancy_h2(row_sums, bias_a, bias_b, shift):
+    """jdsample.c triangle filter along a row: 3/4 nearer + 1/4 further sample; edges use the sample alone."""
+    this = row_sums
+    last = np.concatenate([this[:, :1], this[:, :-1]], axis=1)
+    nxt = np.concatenate([this[:, 1:], this[:, -1:]], axis=1)
+    out = np.empty((this.shape[0], this.shape[1] * 2), np.int64)
+    out[:, 0::2] = (this * 3 + last + bias_a) >> shift
+    out[:, 1::2] = (this * 3 + nxt + bias_b) >> shift
+    return out
+
+
+def upsample(plane, hs, vs):
+    """Chroma plane (real downsampled size) -> (rows*vs, cols*hs), jdsample.c with do_fancy_upsampling."""
+    p = plane.astype(np.int64)
+    if hs == 1 and vs == 1:
+        return p
+    if hs == 2 and p.shape[1] <= 2:                            # jinit_upsampler: fancy only if downsampled_width > 2
+        return np.repeat(np.repeat(p, 2, axis=1), vs, axis=0)  # h2v1_upsample / h2v2_upsample: replication
+    if hs == 2 and vs == 1:                                    # h2v1_fancy_upsample
+        out = _fancy_h2(p, 1, 2, 2)
+        out[:, 0], out[:, -1] = p[:, 0], p[:, -1]
+        return out
+    if hs == 2 and vs == 2:                                    # h2v2_fancy_upsample
+        above = np.concatenate([p[:1], p[:-1]], axis=0)
+        below = np.concatenate([p[1:], p[-1:]], axis=0)
+        rows = np.empty((p.shape[0] * 2, p.shape[1]), np.int64)
+        rows[0::2], rows[1::2] = p * 3 + above, p * 3 + below
+        out = _fancy_h2(rows, 8, 7, 4)
+        out[:, 0], out[:, -1] = (rows[:, 0] * 4 + 8) >> 4, (rows[:, -1] * 4 + 7) >> 4
+        return out
+    if hs == 1 and vs == 2:                                    # h1v2_fancy_upsample (libjpeg-turbo)
+        above = np.concatenate([p[:1], p[:-1]], axis=0)
+        below = np.concatenate([p[1:], p[-1:]], axis=0)
+        out = np.empty((p.shape[0] * 2, p.shape[1]), np.int64)
+        out[0::2], out[1::2] = (p * 3 + above + 1) >> 2, (p * 3 + below + 2) >> 2
+        return out
+    raise NotImplementedError((hs, vs))
+
+
+def ycc_to_rgb(y, cb, cr):
+    """jdcolor.c build_ycc_rgb_table + ycc_rgb_convert."""
+    xb, xr = cb - 128, cr - 128
+    r = y + ((91881 * xr + 32768) >> 16)
+    g = y + ((-22554 * xb + 32768 - 46802 * xr) >> 16)
+    b = y + ((116130 * xb + 32768) >> 16)
+    return np.clip(np.stack([r, g, b], -1), 0, 255).astype(np.uint8)
+
+
+def decode_jpeg(data):
+    """bytes of a baseline JFIF/JPEG file -> uint8 (H, W, 3) (or (H, W) for one component), as Pillow decodes it."""
+    data = bytes(data)
+    assert data[:2] == b"\xff\xd8", "not a JPEG"
+    pos, qt, huff, restart_interval = 2, {}, {}, 0
+    frame = None
+    while True:
+        assert data[pos] == 0xFF, "marker expected"
+        marker = data[pos + 1]
+        pos += 2
+        if marker == 0xFF:
+            pos -= 1
+            continue
+        length = int.from_bytes(data[pos:pos + 2], "big")
+        seg = data[pos + 2:pos + length]
+        if marker == 0xDB:
+            k = 0
+            while k < len(seg):
+                assert seg[k] >> 4 == 0, "16-bit quantisation tables are not baseline"
+                qt[seg[k] & 15] = list(seg[k + 1:k + 65])
+                k += 65
+        elif marker == 0xC4:
+            k = 0
+            while k < len(seg):
+                bits = list(seg[k + 1:k + 17])
+                n = sum(bits)
+                vals = list(seg[k + 17:k + 17 + n])
+                huff[seg[k]] = {(ln, code): sym for sym, (code, ln) in huffman_codes(bits, vals).items()}
+                k += 17 + n
+        elif marker == 0xC0 or marker == 0xC1:
+            assert seg[0] == 8, "8-bit samples only"
+            h, w = int.from_bytes(seg[1:3], "big"), int.from_bytes(seg[3:5], "big")
+            comps = [(seg[6 + 3 * i], seg[7 + 3 * i] >> 4, seg[7 + 3 * i] & 15, seg[8 + 3 * i]) for i in range(seg[5])]
+            frame = (h, w, comps)
+        elif marker in (0xC2, 0xC3, 0xC5, 0xC6, 0xC7, 0xC9, 0xCA, 0xCB, 0xCD, 0xCE, 0xCF):
+            raise NotImplementedError("only baseline sequential Huffman JPEG (SOF0/SOF1)")
+        elif marker == 0xDD:
+            restart_interval = int.from_bytes(seg[:2], "big")
+        elif marker == 0xDA:
+            ns = seg[0]
+            scan = {seg[1 + 2 * i]: (seg[2 + 2 * i] >> 4, seg[2 + 2 * i] & 15) for i in range(ns)}
+            pos += length
+            break
+        pos += length
+    h, w, comps = frame
+    assert len(scan) == len(comps), "one interleaved scan expected"
+    hmax, vmax = max(c[1] for c in comps), max(c[2] for c in comps)
+    mx, my = -(-w // (8 * hmax)), -(-h // (8 * vmax))
+    coef = [np.zeros((my * c[2], mx * c[1], 64), np.int64) for c in comps]
+    br, pred = _BitReader(data, pos), [0] * len(comps)
+    for m in range(mx * my):
+        if restart_interval and m and m % restart_interval == 0:
+            br.restart()
+            pred = [0] * len(comps)
+        j, i = divmod(m, mx)
+        for ci, (cid, hs, vs, _tq) in enumerate(comps):
+            dc_tab, ac_tab = huff[scan[cid][0]], huff[0x10 | scan[cid][1]]
+            for dy in range(vs):
+                for dx in range(hs):
+                    blk = coef[ci][j * vs + dy, i * hs + dx]
+                    s = br.symbol(dc_tab)
+                    pred[ci] += _extend(br.bits(s), s)
+                    blk[0] = pred[ci]
+                    k = 1
+                    while k < 64:
+                        rs = br.symbol(ac_tab)
+                        r, s = rs >> 4, rs & 15
+                        if s == 0:
+                            if r != 15:
+                                break
+                            k += 16
+                            continue
+                        k += r
+                        blk[ZIGZAG[k]] = _extend(br.bits(s), s)
+                        k += 1
+    planes = []
+    for ci, (cid, hs, vs, tq) in enumerate(comps):
+        px = idct_blocks(coef[ci], qt[tq])                                   # (by, bx, 8, 8)
+        full = px.transpose(0, 2, 1, 3).reshape(px.shape[0] * 8, px.shape[1] * 8)
+        ch, cw = -(-h * vs // vmax), -(-w * hs // hmax)                       # downsampled_height / _width
+        fh, fv = hmax // hs, vmax // vs
+        planes.append(upsample(full[:ch, :cw], fh, fv)[:h, :w])
+    if len(planes) == 1:
+        return planes[0].astype(np.uint8)
+    return ycc_to_rgb(*planes)

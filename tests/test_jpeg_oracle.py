@@ -58,3 +58,40 @@ def test_reference_geometry_frame():
     rng = np.random.default_rng(3)
     a = np.clip(_image("smooth", 270, 480, 0).astype(int) + rng.integers(-20, 20, (270, 480, 3)), 0, 255).astype(np.uint8)
     assert jo.encode_jpeg(a) == _pillow(a)
+
+
+# ---- decoder half (Image.open of the content / stylised files, LST:200, 219) -----------------------------------
+def _pillow_decode(data, mode="RGB"):
+    return np.asarray(PIL.open(io.BytesIO(data)).convert(mode))
+
+
+@pytest.mark.parametrize("h,w", [(16, 16), (1, 1), (2, 2), (3, 2), (2, 3), (5, 1), (1, 5), (17, 23), (33, 65), (9, 40),
+                                 (40, 9), (64, 48), (100, 75)])
+@pytest.mark.parametrize("subsampling", [2, 1, 0])      # 4:2:0 (Pillow's default), 4:2:2, 4:4:4
+def test_decoder_is_bit_exact_against_pillow(h, w, subsampling):
+    for kind, q in (("noise", 75), ("smooth", 95), ("noise", 30)):
+        a = _image(kind, h, w, h * 31 + w + q)
+        data = _pillow(a, quality=q, subsampling=subsampling)
+        assert np.array_equal(jo.decode_jpeg(data), _pillow_decode(data)), (kind, q)
+
+
+def test_decoder_grayscale_restart_markers_and_optimised_tables():
+    rng = np.random.default_rng(5)
+    g = rng.integers(0, 256, (37, 53), dtype=np.uint8)
+    data = _pillow(g)
+    assert np.array_equal(jo.decode_jpeg(data), _pillow_decode(data, "L"))
+    a = _image("noise", 70, 90, 1)
+    for kw in ({"restart_marker_blocks": 3}, {"restart_marker_rows": 1}, {"optimize": True}):
+        data = _pillow(a, **kw)
+        assert np.array_equal(jo.decode_jpeg(data), _pillow_decode(data)), kw
+
+
+def test_encode_then_decode_through_the_oracle_equals_pillow_round_trip():
+    a = _image("smooth", 45, 70, 2)
+    assert np.array_equal(jo.decode_jpeg(jo.encode_jpeg(a)), _pillow_decode(_pillow(a)))
+
+
+def test_decoder_rejects_progressive_files():
+    data = _pillow(_image("noise", 16, 16, 0), progressive=True)
+    with pytest.raises(NotImplementedError):
+        jo.decode_jpeg(data)
