@@ -13,6 +13,7 @@
 #include "../../include/rct.h"
 #include "rct_kernels.cuh"
 #include "rct_jpeg.cuh"
+#include "rct_jpeg_dec.cuh"
 
 using namespace rct;
 
@@ -1235,6 +1236,40 @@ int rct_jpeg_encode_async(const uint8_t *rgb, size_t frame_stride, int n, int H,
     t_launches += launches;
     if (e != cudaSuccess) return fail(RCT_ERR_CUDA, "JPEG encoder launch failed: %s", cudaGetErrorString(e));
     return RCT_OK;
+}
+
+// ---- f-3, decode half (rct_jpeg_dec.cuh) ----------------------------------------------------------
+int rct_jpeg_decode_info(const uint8_t *file_host, size_t nbytes, int *H, int *W, int *channels, size_t *workspace_bytes)
+{
+    if (!file_host) return fail(RCT_ERR_ARG, "null pointer");
+    jpeg::DecPlan pl;
+    if (!jpeg::parse_jpeg(file_host, nbytes, &pl)) return fail(RCT_ERR_ARG, "JPEG decoder: %s", pl.error);
+    if (H) *H = pl.f.H;
+    if (W) *W = pl.f.W;
+    if (channels) *channels = pl.f.ncomp == 3 ? 3 : 1;
+    if (workspace_bytes) *workspace_bytes = jpeg::carve_dec(pl.f, nullptr).bytes;
+    jpeg::free_plan(&pl);
+    return RCT_OK;
+}
+
+int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspace, size_t workspace_bytes, uint8_t *pixels,
+                          void *stream)
+{
+    if (!file_host || !workspace || !pixels) return fail(RCT_ERR_ARG, "null pointer");
+    if (((uintptr_t)workspace & 255u) != 0) return fail(RCT_ERR_ARG, "workspace must be 256-byte aligned");
+    jpeg::DecPlan pl;
+    if (!jpeg::parse_jpeg(file_host, nbytes, &pl)) return fail(RCT_ERR_ARG, "JPEG decoder: %s", pl.error);
+    int dev, rc = ensure_device(&dev);
+    if (rc == RCT_OK && jpeg::carve_dec(pl.f, nullptr).bytes > workspace_bytes)
+        rc = fail(RCT_ERR_ARG, "workspace of %zu bytes is too small", workspace_bytes);
+    if (rc == RCT_OK) {
+        int launches = 0;
+        cudaError_t e = jpeg::decode_launch(file_host, pl, jpeg::carve_dec(pl.f, workspace), pixels, (cudaStream_t)stream, &launches);
+        t_launches += launches;
+        if (e != cudaSuccess) rc = fail(RCT_ERR_CUDA, "JPEG decoder launch failed: %s", cudaGetErrorString(e));
+    }
+    jpeg::free_plan(&pl);
+    return rc;
 }
 
 // ---- phase timing (RCT_OPT_TIMING) -------------------------------------------------------------

@@ -1,0 +1,443 @@
+// SURVEY.md 8f row f-3, decode half: `Image.open(path)` of the content / stylised files
+// (Style_3DGS/localized_style_transfer.py:200, 219) -- baseline sequential Huffman JPEG, 8-bit, grayscale or
+// YCbCr with 4:4:4 / 4:2:2 / 4:2:0 sampling -> uint8 RGB (or gray) on the device, bit for bit what Pillow decodes
+// (libjpeg defaults: islow IDCT, fancy chroma upsampling, table-equivalent YCbCr -> RGB).
+//   host       parses the header (tables, frame, scan, restart interval) and the restart-marker positions
+//   k_jdec_huff  thread per restart interval (one thread for a file without restart markers: correct, serial --
+//                the self-synchronising parallel decode is the planned replacement) -> int16 coefficients
+//   k_jdec_idct  thread per 8x8 block: dequantise, jidctint islow, range limit -> uint8 component planes
+//   k_jdec_rgb   thread per output pixel: jdsample fancy upsampling (replication for chroma widths <= 2),
+//                jdcolor arithmetic -> interleaved RGB
+// The bodies are __host__ __device__; tools/jpeg_selftest --host-decode runs them serially on the CPU.
+#pragma once
+#include "rct_jpeg.cuh"
+
+namespace jpeg {
+
+struct DecFrame {
+    int H, W, ncomp;
+    int hs[3], vs[3], tq[3], td[3], ta[3];   // sampling factors, quantiser / DC / AC table of each component
+    int hmax, vmax, mx, my;                   // MCUs across / down
+    int bw[3], bh[3];                         // blocks across / down of each component (whole MCUs)
+    int cw[3], ch[3];                         // real (downsampled) size of each component
+    size_t coef_off[3];                       // first block of each component in the coefficient array
+    size_t plane_off[3];                      // first sample of each component plane
+    size_t nblocks, nsamples;
+    int restart_interval;                     // MCUs per restart interval, 0 = none
+    unsigned nintervals;
+    size_t scan_bytes;
+};
+
+struct DecTables {
+    unsigned short q[4][64];                  // natural order
+    // canonical Huffman decoding (jdhuff.c slow path): for length l, codes <= maxcode[l] have that length
+    int maxcode[4][18];                       // [table: 0,1 = DC 0/1; 2,3 = AC 0/1][length], -1 = none
+    int valptr[4][17];                        // index into vals of the first code of each length, minus its code
+    unsigned char vals[4][256];
+};
+
+// ---- bit reader over the entropy-coded segment (0xFF 0x00 unstuffed; a marker feeds zero bits) ----------
+struct BitReader {
+    const unsigned char *d;
+    size_t p, end;
+    unsigned long long acc;
+    int n;
+    JHD BitReader(const unsigned char *data, size_t begin, size_t end_) : d(data), p(begin), end(end_), acc(0ull), n(0) {}
+    JHD void fill()
+    {
+        unsigned b = 0;
+        if (p < end) {
+            b = d[p];
+            if (b == 0xFFu) {
+                const unsigned nx = p + 1 < end ? d[p + 1] : 0xD9u;
+                if (nx == 0u)
+                    p += 2;
+                else
+                    b = 0u;  // marker: stay in front of it
+            } else {
+                ++p;
+            }
+        }
+        acc = (acc << 8) | b;
+        n += 8;
+    }
+    JHD unsigned bits(int k)
+    {
+        if (k == 0) return 0u;
+        while (n < k) fill();
+        n -= k;
+        const unsigned v = (unsigned)(acc >> n) & ((1u << k) - 1u);
+        acc &= (1ull << n) - 1ull;
+        return v;
+    }
+};
+
+JHD int huff_symbol(BitReader &br, const DecTables &t, int table)
+{
+    int code = (int)br.bits(1), l = 1;
+    while (l <= 16 && code > t.maxcode[table][l]) {
+        code = (code << 1) | (int)br.bits(1);
+        ++l;
+    }
+    if (l > 16) return 0;  // corrupt data: libjpeg warns and returns 0
+    return t.vals[table][(t.valptr[table][l] + code) & 255];
+}
+JHD int huff_extend(unsigned v, int s) { return s == 0 || (int)v >= (1 << (s - 1)) ? (int)v : (int)v - (1 << s) + 1; }
+
+// decode MCUs [m0, m1) of one restart interval; coef must be zero beforehand (natural order, int16)
+JHD void decode_interval(const unsigned char *scan, size_t begin, size_t end, const DecFrame &f, const DecTables &t,
+                         unsigned m0, unsigned m1, short *coef)
+{
+    BitReader br(scan, begin, end);
+    int pred[3] = {0, 0, 0};
+    for (unsigned m = m0; m < m1; ++m) {
+        const int j = (int)(m / (unsigned)f.mx), i = (int)(m % (unsigned)f.mx);
+        for (int c = 0; c < f.ncomp; ++c)
+            for (int dy = 0; dy < f.vs[c]; ++dy)
+                for (int dx = 0; dx < f.hs[c]; ++dx) {
+                    short *blk = coef + (f.coef_off[c] + (size_t)(j * f.vs[c] + dy) * (size_t)f.bw[c] + (size_t)(i * f.hs[c] + dx)) * 64u;
+                    int s = huff_symbol(br, t, f.td[c]);
+                    pred[c] += huff_extend(br.bits(s), s);
+                    blk[0] = (short)pred[c];
+                    for (int k = 1; k < 64;) {
+                        const int rs = huff_symbol(br, t, 2 + f.ta[c]), r = rs >> 4;
+                        s = rs & 15;
+                        if (s == 0) {
+                            if (r != 15) break;
+                            k += 16;
+                            continue;
+                        }
+                        k += r;
+                        if (k > 63) break;  // corrupt data
+                        blk[zigzag_natural(k)] = (short)huff_extend(br.bits(s), s);
+                        ++k;
+                    }
+                }
+    }
+}
+
+// ---- IDCT (jidctint.c jpeg_idct_islow) ---------------------------------------------------------
+template <bool FIRST>
+JHD void idct8(int *d, int s)
+{
+    const int i0 = d[0], i1 = d[s], i2 = d[2 * s], i3 = d[3 * s], i4 = d[4 * s], i5 = d[5 * s], i6 = d[6 * s], i7 = d[7 * s];
+    int z1 = (i2 + i6) * 4433;
+    const int t2 = z1 - i6 * 15137, t3 = z1 + i2 * 6270;
+    const int t0 = (i0 + i4) * 8192, t1 = (i0 - i4) * 8192;
+    const int t10 = t0 + t3, t13 = t0 - t3, t11 = t1 + t2, t12 = t1 - t2;
+    int o0 = i7, o1 = i5, o2 = i3, o3 = i1;
+    z1 = o0 + o3;
+    int z2 = o1 + o2, z3 = o0 + o2, z4 = o1 + o3;
+    const int z5 = (z3 + z4) * 9633;
+    o0 *= 2446, o1 *= 16819, o2 *= 25172, o3 *= 12299;
+    z1 *= -7373, z2 *= -20995;
+    z3 = z3 * -16069 + z5;
+    z4 = z4 * -3196 + z5;
+    o0 += z1 + z3, o1 += z2 + z4, o2 += z2 + z3, o3 += z1 + z4;
+    constexpr int sh = FIRST ? 13 - 2 : 13 + 2 + 3;
+    d[0] = descale(t10 + o3, sh), d[7 * s] = descale(t10 - o3, sh);
+    d[s] = descale(t11 + o2, sh), d[6 * s] = descale(t11 - o2, sh);
+    d[2 * s] = descale(t12 + o1, sh), d[5 * s] = descale(t12 - o1, sh);
+    d[3 * s] = descale(t13 + o0, sh), d[4 * s] = descale(t13 - o0, sh);
+}
+
+// one block: coefficients (natural order) -> 64 samples 0..255 written into the component plane (row stride `stride`)
+JHD void idct_block(const short *coef, const unsigned short *q, unsigned char *dst, size_t stride)
+{
+    int blk[64];
+#pragma unroll
+    for (int k = 0; k < 64; ++k) blk[k] = (int)coef[k] * (int)q[k];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) idct8<true>(blk + c, 8);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) idct8<false>(blk + 8 * r, 1);
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const int v = blk[r * 8 + c] + 128;
+            dst[(size_t)r * stride + (size_t)c] = (unsigned char)(v < 0 ? 0 : v > 255 ? 255 : v);
+        }
+}
+
+// ---- upsampling + colour ---------------------------------------------------------------------
+// sample of a chroma plane at full-resolution position (y, x); fh, fv = hmax / hs, vmax / vs of the component
+JHD int upsampled(const unsigned char *P, size_t stride, int cw, int ch, int fh, int fv, int y, int x)
+{
+    if (fh == 1 && fv == 1) return P[(size_t)y * stride + (size_t)x];
+    const int c = fh == 2 ? x >> 1 : x, r = fv == 2 ? y >> 1 : y;
+    if (fh == 2 && cw <= 2) return P[(size_t)r * stride + (size_t)c];   // jinit_upsampler: fancy needs downsampled_width > 2
+    if (fv == 1) {                                                       // h2v1_fancy_upsample
+        const int v = P[(size_t)r * stride + (size_t)c];
+        if ((x & 1) == 0) return c == 0 ? v : (3 * v + P[(size_t)r * stride + (size_t)(c - 1)] + 1) >> 2;
+        return c == cw - 1 ? v : (3 * v + P[(size_t)r * stride + (size_t)(c + 1)] + 2) >> 2;
+    }
+    const int rn = (y & 1) == 0 ? (r > 0 ? r - 1 : 0) : (r < ch - 1 ? r + 1 : ch - 1);
+    const unsigned char *a = P + (size_t)r * stride, *b = P + (size_t)rn * stride;
+    const int cur = 3 * a[c] + b[c];
+    if ((x & 1) == 0) return c == 0 ? (cur * 4 + 8) >> 4 : (cur * 3 + 3 * a[c - 1] + b[c - 1] + 8) >> 4;
+    return c == cw - 1 ? (cur * 4 + 7) >> 4 : (cur * 3 + 3 * a[c + 1] + b[c + 1] + 7) >> 4;
+}
+
+JHD int clamp255(int v) { return v < 0 ? 0 : v > 255 ? 255 : v; }
+JHD void ycc_rgb(int y, int cb, int cr, unsigned char *rgb)
+{
+    const int xb = cb - 128, xr = cr - 128;
+    rgb[0] = (unsigned char)clamp255(y + ((91881 * xr + 32768) >> 16));
+    rgb[1] = (unsigned char)clamp255(y + ((-22554 * xb + 32768 - 46802 * xr) >> 16));
+    rgb[2] = (unsigned char)clamp255(y + ((116130 * xb + 32768) >> 16));
+}
+
+JHD void output_pixel(const unsigned char *planes, const DecFrame &f, int y, int x, unsigned char *out)
+{
+    const int Y = planes[f.plane_off[0] + (size_t)y * (size_t)(f.bw[0] * 8) + (size_t)x];
+    if (f.ncomp == 1) {
+        out[(size_t)y * (size_t)f.W + (size_t)x] = (unsigned char)Y;
+        return;
+    }
+    int cc[2];
+#pragma unroll
+    for (int c = 1; c < 3; ++c)
+        cc[c - 1] = upsampled(planes + f.plane_off[c], (size_t)(f.bw[c] * 8), f.cw[c], f.ch[c], f.hmax / f.hs[c],
+                              f.vmax / f.vs[c], y, x);
+    ycc_rgb(Y, cc[0], cc[1], out + ((size_t)y * (size_t)f.W + (size_t)x) * 3u);
+}
+
+// ---- host: header parse -------------------------------------------------------------------------
+struct DecPlan {
+    DecFrame f;
+    DecTables t;
+    size_t scan_begin, scan_end;                         // entropy-coded bytes of the file: [scan_begin, scan_end)
+    unsigned long long *intervals;                       // malloc'ed [nintervals][2]: byte range of each restart interval,
+                                                         // relative to scan_begin
+    const char *error;
+};
+inline void free_plan(DecPlan *p)
+{
+    free(p->intervals);
+    p->intervals = nullptr;
+}
+
+// returns false with p->error set for anything that is not a baseline file of the supported layouts
+inline bool parse_jpeg(const unsigned char *d, size_t n, DecPlan *p)
+{
+    memset(p, 0, sizeof *p);
+    auto bad = [&](const char *why) {
+        p->error = why;
+        return false;
+    };
+    if (n < 4 || d[0] != 0xFF || d[1] != 0xD8) return bad("not a JPEG file");
+    size_t pos = 2;
+    bool have_frame = false, have_q[4] = {false, false, false, false}, have_h[4] = {false, false, false, false};
+    DecFrame &f = p->f;
+    for (;;) {
+        if (pos + 4 > n) return bad("truncated file");
+        if (d[pos] != 0xFF) return bad("marker expected");
+        const unsigned marker = d[pos + 1];
+        if (marker == 0xFF) {
+            ++pos;
+            continue;
+        }
+        pos += 2;
+        const size_t len = ((size_t)d[pos] << 8) | d[pos + 1];
+        if (len < 2 || pos + len > n) return bad("truncated segment");
+        const unsigned char *seg = d + pos + 2;
+        const size_t sl = len - 2;
+        if (marker == 0xDB) {
+            for (size_t k = 0; k + 65 <= sl; k += 65) {
+                if (seg[k] >> 4) return bad("16-bit quantisation table");
+                const int id = seg[k] & 15;
+                if (id > 3) return bad("quantisation table id");
+                for (int i = 0; i < 64; ++i) p->t.q[id][zigzag_natural(i)] = seg[k + 1 + i];
+                have_q[id] = true;
+            }
+        } else if (marker == 0xC4) {
+            size_t k = 0;
+            while (k + 17 <= sl) {
+                const int tc = seg[k] >> 4, th = seg[k] & 15;
+                if (tc > 1 || th > 1) return bad("Huffman table id (baseline allows 0 and 1)");
+                const int tab = tc * 2 + th;
+                int total = 0;
+                for (int l = 1; l <= 16; ++l) total += seg[k + l];
+                if (total > 256 || k + 17 + (size_t)total > sl) return bad("bad Huffman table");
+                int code = 0, q = 0;
+                for (int l = 1; l <= 16; ++l) {  // jdhuff.c jpeg_make_d_derived_tbl
+                    const int cnt = seg[k + l];
+                    if (cnt) {
+                        p->t.valptr[tab][l] = q - code;
+                        q += cnt;
+                        code += cnt;
+                        p->t.maxcode[tab][l] = code - 1;
+                    } else {
+                        p->t.valptr[tab][l] = 0;
+                        p->t.maxcode[tab][l] = -1;
+                    }
+                    code <<= 1;
+                }
+                p->t.maxcode[tab][17] = 0x7fffffff;
+                memcpy(p->t.vals[tab], seg + k + 17, (size_t)total);
+                have_h[tab] = true;
+                k += 17 + (size_t)total;
+            }
+        } else if (marker == 0xC0 || marker == 0xC1) {
+            if (sl < 6 || seg[0] != 8) return bad("8-bit samples only");
+            f.H = (seg[1] << 8) | seg[2], f.W = (seg[3] << 8) | seg[4], f.ncomp = seg[5];
+            if (f.H <= 0 || f.W <= 0) return bad("empty frame");
+            if (f.ncomp != 1 && f.ncomp != 3) return bad("1 or 3 components only");
+            if (sl < 6 + 3 * (size_t)f.ncomp) return bad("truncated frame header");
+            for (int c = 0; c < f.ncomp; ++c) {
+                f.hs[c] = seg[7 + 3 * c] >> 4, f.vs[c] = seg[7 + 3 * c] & 15, f.tq[c] = seg[8 + 3 * c];
+                if (f.tq[c] > 3) return bad("quantisation table id");
+            }
+            if (f.ncomp == 1) f.hs[0] = f.vs[0] = 1;  // a single component is never interleaved
+            have_frame = true;
+        } else if (marker >= 0xC2 && marker <= 0xCF && marker != 0xC4 && marker != 0xC8 && marker != 0xCC) {
+            return bad("only baseline sequential Huffman JPEG (SOF0/SOF1)");
+        } else if (marker == 0xDD) {
+            if (sl < 2) return bad("truncated DRI");
+            f.restart_interval = (seg[0] << 8) | seg[1];
+        } else if (marker == 0xDA) {
+            if (!have_frame) return bad("scan before frame header");
+            if (sl < 1 || seg[0] != f.ncomp || sl < 1 + 2 * (size_t)f.ncomp + 3) return bad("one interleaved scan of all components expected");
+            for (int c = 0; c < f.ncomp; ++c) {
+                f.td[c] = seg[2 + 2 * c] >> 4, f.ta[c] = seg[2 + 2 * c] & 15;
+                if (f.td[c] > 1 || f.ta[c] > 1 || !have_h[f.td[c]] || !have_h[2 + f.ta[c]]) return bad("missing Huffman table");
+                if (!have_q[f.tq[c]]) return bad("missing quantisation table");
+            }
+            pos += len;
+            break;
+        }
+        pos += len;
+    }
+    if (f.ncomp == 3) {
+        if (f.hs[1] != 1 || f.vs[1] != 1 || f.hs[2] != 1 || f.vs[2] != 1) return bad("chroma sampling factors other than 1x1");
+        if (!((f.hs[0] == 1 || f.hs[0] == 2) && (f.vs[0] == 1 || f.vs[0] == 2)) || (f.hs[0] == 1 && f.vs[0] == 2))
+            return bad("luma sampling other than 1x1, 2x1, 2x2");
+    }
+    f.hmax = f.hs[0], f.vmax = f.vs[0];
+    f.mx = (f.W + 8 * f.hmax - 1) / (8 * f.hmax), f.my = (f.H + 8 * f.vmax - 1) / (8 * f.vmax);
+    size_t blocks = 0, samples = 0;
+    for (int c = 0; c < f.ncomp; ++c) {
+        f.bw[c] = f.mx * f.hs[c], f.bh[c] = f.my * f.vs[c];
+        f.cw[c] = (f.W * f.hs[c] + f.hmax - 1) / f.hmax, f.ch[c] = (f.H * f.vs[c] + f.vmax - 1) / f.vmax;
+        f.coef_off[c] = blocks, f.plane_off[c] = samples;
+        blocks += (size_t)f.bw[c] * (size_t)f.bh[c];
+        samples += (size_t)f.bw[c] * (size_t)f.bh[c] * 64u;
+    }
+    f.nblocks = blocks, f.nsamples = samples;
+    // the entropy-coded segment and its restart intervals
+    p->scan_begin = pos;
+    const unsigned nmcu = (unsigned)f.mx * (unsigned)f.my;
+    const unsigned want = f.restart_interval ? (nmcu + (unsigned)f.restart_interval - 1u) / (unsigned)f.restart_interval : 1u;
+    p->intervals = (unsigned long long *)malloc(sizeof(unsigned long long) * 2u * want);
+    if (!p->intervals) return bad("out of host memory");
+    unsigned found = 0;
+    size_t start = pos, q = pos;
+    while (q < n) {
+        const unsigned char *hit = (const unsigned char *)memchr(d + q, 0xFF, n - q);
+        if (!hit) {
+            q = n;
+            break;
+        }
+        q = (size_t)(hit - d);
+        const unsigned nx = q + 1 < n ? d[q + 1] : 0xD9u;
+        if (nx == 0x00 || nx == 0xFF) {
+            q += nx == 0x00 ? 2 : 1;
+            continue;
+        }
+        if (nx >= 0xD0 && nx <= 0xD7 && f.restart_interval && found + 1 < want) {
+            p->intervals[2 * found] = start - pos, p->intervals[2 * found + 1] = q - pos;
+            ++found;
+            q += 2;
+            start = q;
+            continue;
+        }
+        break;  // EOI or another marker: end of the scan
+    }
+    p->intervals[2 * found] = start - pos, p->intervals[2 * found + 1] = q - pos;
+    ++found;
+    if (found != want) {
+        free_plan(p);
+        return bad("restart markers do not match the restart interval");
+    }
+    f.nintervals = found;
+    p->scan_end = q;
+    f.scan_bytes = q - pos;
+    return true;
+}
+
+struct DecWorkspace {
+    unsigned char *scan;
+    unsigned long long *intervals;
+    short *coef;
+    unsigned char *planes;
+    size_t bytes;
+};
+inline DecWorkspace carve_dec(const DecFrame &f, void *base)
+{
+    DecWorkspace w;
+    char *p = (char *)base;
+    size_t o = 0;
+    auto take = [&](size_t bytes) {
+        char *r = p ? p + o : nullptr;
+        o += align256(bytes);
+        return (void *)r;
+    };
+    w.scan = (unsigned char *)take(f.scan_bytes + 16u);
+    w.intervals = (unsigned long long *)take((size_t)f.nintervals * 16u);
+    w.coef = (short *)take(f.nblocks * 64u * sizeof(short));
+    w.planes = (unsigned char *)take(f.nsamples);
+    w.bytes = o;
+    return w;
+}
+
+#ifdef __CUDACC__
+__global__ void __launch_bounds__(64) k_jdec_huff(const unsigned char *scan, const unsigned long long *intervals, DecFrame f,
+                                                  DecTables t, short *coef)
+{
+    const unsigned k = blockIdx.x * 64u + threadIdx.x;
+    if (k >= f.nintervals) return;
+    const unsigned nmcu = (unsigned)f.mx * (unsigned)f.my;
+    const unsigned ri = f.restart_interval ? (unsigned)f.restart_interval : nmcu;
+    const unsigned m0 = k * ri, m1 = min(m0 + ri, nmcu);
+    decode_interval(scan, (size_t)intervals[2 * k], (size_t)intervals[2 * k + 1], f, t, m0, m1, coef);
+}
+
+__global__ void __launch_bounds__(128) k_jdec_idct(const short *coef, DecFrame f, DecTables t, unsigned char *planes)
+{
+    const size_t i = (size_t)blockIdx.x * 128u + threadIdx.x;
+    if (i >= f.nblocks) return;
+    const int c = (f.ncomp == 3 && i >= f.coef_off[2]) ? 2 : (f.ncomp == 3 && i >= f.coef_off[1]) ? 1 : 0;
+    const size_t local = i - f.coef_off[c], stride = (size_t)f.bw[c] * 8u;
+    const size_t br = local / (size_t)f.bw[c], bc = local % (size_t)f.bw[c];
+    idct_block(coef + i * 64u, t.q[f.tq[c]], planes + f.plane_off[c] + br * 8u * stride + bc * 8u, stride);
+}
+
+__global__ void __launch_bounds__(256) k_jdec_rgb(const unsigned char *planes, DecFrame f, unsigned char *out)
+{
+    const size_t i = (size_t)blockIdx.x * 256u + threadIdx.x;
+    if (i >= (size_t)f.H * (size_t)f.W) return;
+    output_pixel(planes, f, (int)(i / (size_t)f.W), (int)(i % (size_t)f.W), out);
+}
+
+// file bytes on the host -> pixels on the device (H x W x 3, or H x W for a one-component file), enqueued on `st`
+inline cudaError_t decode_launch(const unsigned char *file_host, const DecPlan &pl, const DecWorkspace &ws, unsigned char *out,
+                                 cudaStream_t st, int *launches)
+{
+    const DecFrame &f = pl.f;
+    cudaError_t e = cudaMemcpyAsync(ws.scan, file_host + pl.scan_begin, f.scan_bytes, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    e = cudaMemcpyAsync(ws.intervals, pl.intervals, (size_t)f.nintervals * 16u, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(ws.coef, 0, f.nblocks * 64u * sizeof(short), st);
+    if (e != cudaSuccess) return e;
+    k_jdec_huff<<<(f.nintervals + 63u) / 64u, 64, 0, st>>>(ws.scan, ws.intervals, f, pl.t, ws.coef);
+    k_jdec_idct<<<(unsigned)((f.nblocks + 127u) / 128u), 128, 0, st>>>(ws.coef, f, pl.t, ws.planes);
+    const size_t px = (size_t)f.H * (size_t)f.W;
+    k_jdec_rgb<<<(unsigned)((px + 255u) / 256u), 256, 0, st>>>(ws.planes, f, out);
+    if (launches) *launches += 3;
+    return cudaGetLastError();
+}
+#endif
+
+}  // namespace jpeg

@@ -5,6 +5,10 @@
 ``encode_jpeg(image, quality=75)``    uint8 HWC (or NHWC batch) -> bytes (list of bytes for a batch), byte for
                                       byte what Pillow's ``save(..., "JPEG", quality=quality)`` writes
 ``save_jpeg(image, path, quality=75)`` the reference's call, file on disk
+``decode_jpeg(data, device=False)``    bytes / path of a baseline JPEG -> uint8 [H,W,3] ([H,W] for a gray file), the
+                                      pixels ``np.asarray(Image.open(path))`` gives (LST:200, 219), decoded on the GPU;
+                                      ``device=True`` returns the CUDA tensor instead of a numpy array
+``jpeg_info(data)``                   (H, W, channels) from the header, host only
 
 A frame that was transferred on the GPU leaves it as a JFIF stream (about a tenth of H*W*3 bytes at quality 75)
 instead of raw pixels, which is what the PCIe-bound end-to-end path wants.  numpy or CUDA tensors in.
@@ -70,3 +74,44 @@ def save_jpeg(image, path, quality: int = 75):
         raise ValueError("save_jpeg takes one image; use encode_jpeg for a batch")
     with open(path, "wb") as f:
         f.write(data)
+
+
+def _file_bytes(data) -> bytes:
+    if isinstance(data, (bytes, bytearray, memoryview)):
+        return bytes(data)
+    with open(data, "rb") as f:
+        return f.read()
+
+
+def jpeg_info(data):
+    """(H, W, channels) of a baseline JPEG; raises ValueError for files the decoder does not take (progressive, CMYK ...)."""
+    import ctypes as C
+
+    raw = _file_bytes(data)
+    h, w, ch, ws = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()
+    buf = (C.c_ubyte * len(raw)).from_buffer_copy(raw)
+    lib = _cabi.lib()
+    if lib.rct_jpeg_decode_info(buf, len(raw), C.byref(h), C.byref(w), C.byref(ch), C.byref(ws)) != 0:
+        raise ValueError(lib.rct_last_error().decode())
+    return h.value, w.value, ch.value
+
+
+def decode_jpeg(data, device: bool = False):
+    """LST:200, 219 (`Image.open`): file bytes or path -> pixels, decoded on the GPU, bit-exact with Pillow."""
+    import ctypes as C
+
+    raw = _file_bytes(data)
+    lib = _cabi.lib()
+    h, w, ch, ws = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()
+    buf = (C.c_ubyte * len(raw)).from_buffer_copy(raw)
+    if lib.rct_jpeg_decode_info(buf, len(raw), C.byref(h), C.byref(w), C.byref(ch), C.byref(ws)) != 0:
+        raise ValueError(lib.rct_last_error().decode())
+    dev = _dev()
+    work = torch.empty(ws.value, dtype=torch.uint8, device=dev)
+    shape = (h.value, w.value, 3) if ch.value == 3 else (h.value, w.value)
+    out = torch.empty(shape, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.rct_jpeg_decode_async(buf, len(raw), work.data_ptr(), ws.value, out.data_ptr(),
+                                        torch.cuda.current_stream().cuda_stream))
+        torch.cuda.current_stream().synchronize()   # `work` and `buf` are released on return
+    return out if device else out.cpu().numpy()

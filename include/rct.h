@@ -235,6 +235,19 @@ size_t rct_jpeg_max_bytes(int H, int W);
 int rct_jpeg_encode_async(const uint8_t *rgb, size_t frame_stride, int n, int H, int W, int quality, void *workspace,
                           uint8_t *out, size_t out_stride, size_t out_cap, unsigned long long *nbytes, void *stream);
 
+/* f-3, decode half: `Image.open(path)` of the content / stylised files (LST:200, 219).  Baseline sequential Huffman
+ * JPEG, 8-bit, one component or YCbCr at 4:4:4 / 4:2:2 / 4:2:0, with or without restart markers -> the pixels Pillow
+ * decodes (libjpeg defaults: islow IDCT, fancy upsampling), bit for bit.  Anything else (progressive, arithmetic,
+ * CMYK, 12-bit) returns RCT_ERR_ARG with the reason in rct_last_error(): nothing is decoded approximately.
+ * rct_jpeg_decode_info parses the header on the host (no GPU needed).  rct_jpeg_decode_async takes the FILE BYTES IN
+ * HOST MEMORY, copies the entropy-coded segment to the device and enqueues the decoder on `stream`; pixels (device)
+ * receives uint8 [H,W,3] (or [H,W] for one component).  The host bytes may be released when the call returns.
+ * Huffman decoding runs one thread per restart interval: a file without restart markers decodes serially (correct,
+ * slow). */
+int rct_jpeg_decode_info(const uint8_t *file_host, size_t nbytes, int *H, int *W, int *channels, size_t *workspace_bytes);
+int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspace, size_t workspace_bytes, uint8_t *pixels,
+                          void *stream);
+
 /* ---- introspection for parity tests (RCT_FLAG_DEBUG plans; all synchronise) -------------- */
 typedef struct {
     int64_t n_target, n_source;     /* region pixel counts (non-black, LST:134-138) */

@@ -4,10 +4,12 @@
 // Test infrastructure: tests/test_jpeg_device_core.py compares the output with oracle/jpeg_oracle.py and Pillow.
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <string>
 #include <vector>
 #include <cuda_runtime.h>
 #include "../applied_image_processing_b200/csrc/rct_jpeg.cuh"
+#include "../applied_image_processing_b200/csrc/rct_jpeg_dec.cuh"
 
 // the kernels' __host__ __device__ bodies run serially on the host (test infrastructure, never a product path)
 namespace jpeg {
@@ -99,6 +101,68 @@ inline size_t encode_host_emulation(const uint8_t *rgb, int H, int W, int qualit
 
 int main(int argc, char **argv)
 {
+    if (argc >= 4 && (std::string(argv[1]) == "--host-decode" || std::string(argv[1]) == "--gpu-decode")) {
+        // jpeg_selftest --host-decode|--gpu-decode in.jpg out.raw   (prints "H W channels")
+        FILE *fi = fopen(argv[2], "rb");
+        if (!fi) return 1;
+        std::vector<unsigned char> file;
+        unsigned char buf[65536];
+        for (size_t got; (got = fread(buf, 1, sizeof buf, fi)) > 0;) file.insert(file.end(), buf, buf + got);
+        fclose(fi);
+        jpeg::DecPlan pl;
+        if (!jpeg::parse_jpeg(file.data(), file.size(), &pl)) {
+            fprintf(stderr, "unsupported: %s\n", pl.error);
+            return 6;
+        }
+        const jpeg::DecFrame &f = pl.f;
+        const size_t outb = (size_t)f.H * f.W * (f.ncomp == 3 ? 3 : 1);
+        std::vector<unsigned char> out(outb);
+        if (std::string(argv[1]) == "--host-decode") {
+            std::vector<short> coef(f.nblocks * 64, 0);
+            std::vector<unsigned char> planes(f.nsamples);
+            const unsigned nmcu = (unsigned)f.mx * f.my, ri = f.restart_interval ? f.restart_interval : nmcu;
+            for (unsigned k = 0; k < f.nintervals; ++k)
+                jpeg::decode_interval(file.data() + pl.scan_begin, (size_t)pl.intervals[2 * k], (size_t)pl.intervals[2 * k + 1], f, pl.t,
+                                      k * ri, std::min(k * ri + ri, nmcu), coef.data());
+            for (size_t i = 0; i < f.nblocks; ++i) {
+                const int c = (f.ncomp == 3 && i >= f.coef_off[2]) ? 2 : (f.ncomp == 3 && i >= f.coef_off[1]) ? 1 : 0;
+                const size_t local = i - f.coef_off[c], stride = (size_t)f.bw[c] * 8;
+                jpeg::idct_block(coef.data() + i * 64, pl.t.q[f.tq[c]],
+                                 planes.data() + f.plane_off[c] + (local / f.bw[c]) * 8 * stride + (local % f.bw[c]) * 8, stride);
+            }
+            for (int y = 0; y < f.H; ++y)
+                for (int x = 0; x < f.W; ++x) jpeg::output_pixel(planes.data(), f, y, x, out.data());
+        } else {
+            const jpeg::DecWorkspace lay = jpeg::carve_dec(f, nullptr);
+            void *d_ws;
+            unsigned char *d_out;
+            CK(cudaMalloc(&d_ws, lay.bytes));
+            CK(cudaMalloc(&d_out, outb));
+            CK(cudaMemset(d_ws, 0xA5, lay.bytes));
+            const jpeg::DecWorkspace ws = jpeg::carve_dec(f, d_ws);
+            cudaEvent_t e0, e1;
+            CK(cudaEventCreate(&e0));
+            CK(cudaEventCreate(&e1));
+            float best = 1e30f;
+            for (int rep = 0; rep < 3; ++rep) {
+                CK(cudaEventRecord(e0));
+                CK(jpeg::decode_launch(file.data(), pl, ws, d_out, 0, nullptr));
+                CK(cudaEventRecord(e1));
+                CK(cudaDeviceSynchronize());
+                float ms;
+                CK(cudaEventElapsedTime(&ms, e0, e1));
+                best = ms < best ? ms : best;
+            }
+            CK(cudaMemcpy(out.data(), d_out, outb, cudaMemcpyDeviceToHost));
+            fprintf(stderr, "gpu decode: %dx%d, %u restart intervals, %.3f ms\n", f.H, f.W, f.nintervals, best);
+        }
+        printf("%d %d %d\n", f.H, f.W, f.ncomp == 3 ? 3 : 1);
+        jpeg::free_plan(&pl);
+        FILE *fo = fopen(argv[3], "wb");
+        if (!fo || fwrite(out.data(), 1, outb, fo) != outb) return 1;
+        fclose(fo);
+        return 0;
+    }
     if (argc < 6) {
         fprintf(stderr, "usage: %s --host|--gpu H W in.rgb out.jpg [quality] [frames]\n", argv[0]);
         return 1;
