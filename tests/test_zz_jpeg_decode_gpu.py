@@ -20,7 +20,7 @@ def _file(h, w, seed, mode="RGB", **kw):
 
 
 def _pillow(data, mode="RGB"):
-    return np.asarray(PIL.open(io.BytesIO(data)).convert(mode))
+    return np.array(PIL.open(io.BytesIO(data)).convert(mode))
 
 
 @pytest.mark.parametrize("h,w", [(16, 16), (1, 1), (2, 2), (2, 3), (5, 1), (17, 23), (33, 65), (40, 9), (100, 75)])
