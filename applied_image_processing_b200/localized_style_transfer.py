@@ -453,7 +453,7 @@ def run_localized_style_transfer(
     """LST:191-245 with the two out-of-scope producers injected: ``background_mask`` (uint8
     [1,H,W] or [H,W], what extract_foreground_deeplab returns) and ``stylized_image`` (path or
     uint8 array, what adain_inference writes).  The in-scope tail (LST:218-243) is unchanged:
-    resize -> masks -> colour transfer -> combine -> save JPEG; returns the saved path."""
+    resize -> masks -> colour transfer -> combine -> save JPEG (device encoder); returns the saved path."""
     from PIL import Image
 
     content_np = np.array(Image.open(content_img_path).convert("RGB"))
@@ -470,5 +470,8 @@ def run_localized_style_transfer(
         stylized_np = np.asarray(stylized_image, np.uint8)
     combined_image = regional_color_transfer(content_np, stylized_np, background_mask)
     save_path = f"{output_path}/localized_style_transfer_result.jpg"
-    Image.fromarray(combined_image.astype(np.uint8)).save(save_path)
+    # LST:243 `Image.fromarray(combined_image.astype(np.uint8)).save(save_path)`: the same bytes, encoded on the GPU
+    from .jpeg import save_jpeg
+
+    save_jpeg(combined_image.astype(np.uint8), save_path)
     return save_path

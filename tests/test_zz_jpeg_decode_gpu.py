@@ -67,3 +67,24 @@ def test_unsupported_files_raise():
         aip.decode_jpeg(_file(16, 16, 0, progressive=True))
     with pytest.raises(ValueError):
         aip.decode_jpeg(b"not a jpeg at all")
+
+
+def test_pipeline_tail_writes_the_file_the_reference_would(tmp_path):
+    # LST:191-245 with the mask and the stylised image injected: open -> transfer -> combine -> save JPEG
+    import applied_image_processing_b200 as aip
+    from applied_image_processing_b200.localized_style_transfer import run_localized_style_transfer
+    from oracle import oracle as orc
+    from tests.synth import ellipse_mask, synth_image
+
+    H, W = 270, 480
+    content, sty, mask = synth_image(H, W, 0, "N"), synth_image(200, 300, 1, "N"), ellipse_mask(H, W, 0.4, 4)
+    PIL.fromarray(content).save(tmp_path / "content.png")
+    path = run_localized_style_transfer(str(tmp_path / "content.png"), None, output_path=str(tmp_path),
+                                        background_mask=mask[None], stylized_image=sty)
+    assert path.endswith("localized_style_transfer_result.jpg")
+    ref, status, _ = orc.transfer(content, sty, mask)
+    assert status == 0
+    buf = io.BytesIO()
+    PIL.fromarray(ref).save(buf, "JPEG")
+    assert open(path, "rb").read() == buf.getvalue()
+    assert np.array_equal(aip.decode_jpeg(path), _pillow(buf.getvalue()))
