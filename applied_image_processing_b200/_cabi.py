@@ -77,6 +77,7 @@ SIGNATURES = {
     "rct_jpeg_workspace_bytes": (_sz, [_i, _i, _i]),
     "rct_jpeg_max_bytes": (_sz, [_i, _i]),
     "rct_jpeg_encode_async": (_i, [_vp, _sz, _i, _i, _i, _i, _vp, _vp, _sz, _sz, _vp, _vp]),
+    "rct_jpeg_decode_set_parallel": (_i, [_i]),
     "rct_jpeg_decode_info": (_i, [_vp, _sz, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_sz)]),
     "rct_jpeg_decode_async": (_i, [_vp, _sz, _vp, _sz, _vp, _vp]),
     "rct_plan_info": (_i, [_vp, _i, C.POINTER(FrameInfo)]),

@@ -1252,6 +1252,14 @@ int rct_jpeg_decode_info(const uint8_t *file_host, size_t nbytes, int *H, int *W
     return RCT_OK;
 }
 
+static int g_jpeg_parallel = 0;
+int rct_jpeg_decode_set_parallel(int on)
+{
+    const int before = g_jpeg_parallel;
+    g_jpeg_parallel = on ? 1 : 0;
+    return before;
+}
+
 int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspace, size_t workspace_bytes, uint8_t *pixels,
                           void *stream)
 {
@@ -1264,7 +1272,8 @@ int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspa
         rc = fail(RCT_ERR_ARG, "workspace of %zu bytes is too small", workspace_bytes);
     if (rc == RCT_OK) {
         int launches = 0;
-        cudaError_t e = jpeg::decode_launch(file_host, pl, jpeg::carve_dec(pl.f, workspace), pixels, (cudaStream_t)stream, &launches);
+        cudaError_t e = jpeg::decode_launch(file_host, pl, jpeg::carve_dec(pl.f, workspace), pixels, (cudaStream_t)stream, &launches,
+                                            g_jpeg_parallel != 0);
         t_launches += launches;
         if (e != cudaSuccess) rc = fail(RCT_ERR_CUDA, "JPEG decoder launch failed: %s", cudaGetErrorString(e));
     }

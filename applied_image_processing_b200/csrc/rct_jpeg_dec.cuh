@@ -116,6 +116,178 @@ JHD void decode_interval(const unsigned char *scan, size_t begin, size_t end, co
     }
 }
 
+// ---- self-synchronising parallel Huffman decode (files without restart markers) -----------------------
+// The scan is cut into subsequences of kSubBytes stuffed bytes.  A decoder state is (p, n, acc, bi, k): next byte to
+// load, buffered bits, their value, block inside the MCU, next zigzag index (0 = a DC code comes next); its position
+// label is 8p - n.  Subsequence i owns the code units that START at a label in [8 s_i, 8 s_{i+1}).
+//   speculative pass  thread i decodes subsequence i from (s_i, 0, 0, 0, 0) -- wrong in general -- and keeps the state
+//                     in which it leaves the subsequence, E[i].  Thread 0 starts from the true state.
+//   rounds            E'[i] = state after decoding subsequence i from E[i-1].  Huffman codes resynchronise within a
+//                     few dozen code units, so after a few rounds E' == E (measured on Pillow files at 256 bytes per
+//                     subsequence: 1-2 rounds).  E' == E for every i is a proof, not a heuristic: E[0] is exact and every
+//                     E[i] follows from E[i-1] by a real decode.  Without a fixed point after kSyncRounds the serial
+//                     kernel takes over.
+//   count / scan      blocks that start in each subsequence -> ordinal of its first block
+//   write             decode once more from the exact entry states, coefficients to their blocks, DC as differences
+//   DC prefix         running sum of the DC differences per component
+constexpr unsigned kSubBytes = 256;
+#ifndef RCT_JSYNC
+#define RCT_JSYNC 32
+#endif
+constexpr int kSyncRounds = RCT_JSYNC;
+
+struct HState {
+    unsigned long long p;
+    unsigned n, acc, bi, k;
+};
+JHD bool same_state(const HState &a, const HState &b) { return a.p == b.p && a.n == b.n && a.bi == b.bi && a.k == b.k; }
+
+struct SpanReader {
+    const unsigned char *d;
+    size_t p, end;
+    unsigned long long acc;
+    int n;
+    bool over;
+    JHD SpanReader(const unsigned char *data, size_t end_, const HState &s)
+        : d(data), p((size_t)s.p), end(end_), acc(s.acc), n((int)s.n), over(false) {}
+    JHD void fill()
+    {
+        unsigned b = 0;
+        if (p < end) {
+            b = d[p];
+            if (b == 0xFFu) {
+                if (p + 1 < end && d[p + 1] == 0u) {
+                    p += 2;
+                } else {
+                    b = 0u;
+                    p = end;
+                }
+            } else {
+                ++p;
+            }
+        } else {
+            over = true;
+        }
+        acc = (acc << 8) | b;
+        n += 8;
+    }
+    JHD unsigned bits(int k)
+    {
+        if (k == 0) return 0u;
+        while (n < k) fill();
+        n -= k;
+        const unsigned v = (unsigned)(acc >> n) & ((1u << k) - 1u);
+        acc &= (1ull << n) - 1ull;
+        return v;
+    }
+    JHD long long label() const { return 8ll * (long long)p - (long long)n; }
+};
+
+template <class R>
+JHD int huff_symbol_r(R &br, const DecTables &t, int table)
+{
+    int code = (int)br.bits(1), l = 1;
+    while (l <= 16 && code > t.maxcode[table][l]) {
+        code = (code << 1) | (int)br.bits(1);
+        ++l;
+    }
+    if (l > 16) return 0;
+    return t.vals[table][(t.valptr[table][l] + code) & 255];
+}
+
+// component of block `bi` of an MCU
+JHD int mcu_component(const DecFrame &f, unsigned bi)
+{
+    const unsigned n0 = (unsigned)(f.hs[0] * f.vs[0]);
+    return f.ncomp == 1 || bi < n0 ? 0 : (int)(bi - n0) + 1;
+}
+JHD unsigned blocks_per_mcu(const DecFrame &f) { return f.ncomp == 1 ? 1u : (unsigned)(f.hs[0] * f.vs[0]) + 2u; }
+
+// first byte of subsequence i (a stuffed 0x00 belongs to the 0xFF in front of it)
+JHD size_t sub_start(const unsigned char *scan, size_t nbytes, unsigned i)
+{
+    size_t p = (size_t)i * kSubBytes;
+    if (i && p < nbytes && scan[p] == 0u && scan[p - 1] == 0xFFu) ++p;
+    return p < nbytes ? p : nbytes;
+}
+
+struct NoSink {
+    JHD void dc(unsigned long long, int) {}
+    JHD void ac(unsigned long long, int, int) {}
+};
+// coefficient block of the ord-th block of the scan
+JHD short *scan_block(short *coef, const DecFrame &f, unsigned long long ord)
+{
+    const unsigned bpm = blocks_per_mcu(f);
+    const unsigned m = (unsigned)(ord / bpm), bi = (unsigned)(ord % bpm);
+    const int c = mcu_component(f, bi);
+    const unsigned within = c == 0 ? bi : 0u;
+    const int j = (int)(m / (unsigned)f.mx), i = (int)(m % (unsigned)f.mx);
+    const int dy = (int)within / f.hs[c], dx = (int)within % f.hs[c];
+    return coef + (f.coef_off[c] + (size_t)(j * f.vs[c] + dy) * (size_t)f.bw[c] + (size_t)(i * f.hs[c] + dx)) * 64u;
+}
+struct CoefSink {
+    short *coef;
+    const DecFrame *f;
+    unsigned long long total;
+    JHD void dc(unsigned long long ord, int diff)
+    {
+        if (ord < total) scan_block(coef, *f, ord)[0] = (short)diff;
+    }
+    JHD void ac(unsigned long long ord, int k, int v)
+    {
+        if (ord < total) scan_block(coef, *f, ord)[zigzag_natural(k)] = (short)v;
+    }
+};
+
+// decode the code units that start before `limit` (a label), from state `s`; `first_ord` = ordinal of the first block
+// that STARTS here (a unit continuing an earlier block belongs to first_ord - 1).  Returns the blocks started.
+template <class SINK>
+JHD unsigned decode_span(const unsigned char *scan, size_t nbytes, HState &s, long long limit, const DecFrame &f,
+                         const DecTables &t, unsigned long long first_ord, SINK &sink)
+{
+    SpanReader br(scan, nbytes, s);
+    const unsigned bpm = blocks_per_mcu(f);
+    unsigned bi = s.bi, k = s.k, started = 0;
+    while (br.label() < limit && !br.over) {
+        const int c = mcu_component(f, bi);
+        if (k == 0) {
+            const int sz = huff_symbol_r(br, t, f.td[c]);
+            const int diff = huff_extend(br.bits(sz), sz);
+            sink.dc(first_ord + started, diff);
+            ++started;
+            k = 1;
+        } else {
+            const int rs = huff_symbol_r(br, t, 2 + f.ta[c]), r = rs >> 4, sz = rs & 15;
+            if (sz == 0) {
+                k = r == 15 ? k + 16 : 64;
+            } else {
+                k += (unsigned)r;
+                const int v = huff_extend(br.bits(sz), sz);
+                if (k < 64) sink.ac(first_ord + started - 1ull, (int)k, v);
+                ++k;
+            }
+        }
+        if (k >= 64) {
+            k = 0;
+            bi = bi + 1 == bpm ? 0 : bi + 1;
+        }
+    }
+    s.p = br.p, s.n = (unsigned)br.n, s.acc = (unsigned)br.acc, s.bi = bi, s.k = k;
+    return started;
+}
+JHD long long sub_limit(const unsigned char *scan, size_t nbytes, unsigned i, unsigned nsub)
+{
+    return i + 1 < nsub ? 8ll * (long long)sub_start(scan, nbytes, i + 1) : 0x7fffffffffffffffll;
+}
+JHD HState sub_entry(const unsigned char *scan, size_t nbytes, unsigned i, const HState *E)
+{
+    if (i) return E[i - 1];
+    HState s;
+    s.p = 0, s.n = 0, s.acc = 0, s.bi = 0, s.k = 0;
+    return s;
+}
+
 // ---- IDCT (jidctint.c jpeg_idct_islow) ---------------------------------------------------------
 template <bool FIRST>
 JHD void idct8(int *d, int s)
@@ -371,6 +543,12 @@ struct DecWorkspace {
     unsigned long long *intervals;
     short *coef;
     unsigned char *planes;
+    // self-synchronising decode (files without restart markers)
+    HState *E0, *E1;
+    unsigned *flags;              // [kSyncRounds] 1 = that round still changed a state
+    unsigned *nb;                 // [nsub] blocks started per subsequence
+    unsigned long long *base;     // [nsub] ordinal of the first block started in the subsequence
+    unsigned nsub;
     size_t bytes;
 };
 inline DecWorkspace carve_dec(const DecFrame &f, void *base)
@@ -387,6 +565,12 @@ inline DecWorkspace carve_dec(const DecFrame &f, void *base)
     w.intervals = (unsigned long long *)take((size_t)f.nintervals * 16u);
     w.coef = (short *)take(f.nblocks * 64u * sizeof(short));
     w.planes = (unsigned char *)take(f.nsamples);
+    w.nsub = (unsigned)((f.scan_bytes + kSubBytes - 1u) / kSubBytes);
+    w.E0 = (HState *)take((size_t)w.nsub * sizeof(HState));
+    w.E1 = (HState *)take((size_t)w.nsub * sizeof(HState));
+    w.flags = (unsigned *)take((size_t)kSyncRounds * sizeof(unsigned));
+    w.nb = (unsigned *)take((size_t)w.nsub * sizeof(unsigned));
+    w.base = (unsigned long long *)take((size_t)w.nsub * sizeof(unsigned long long));
     w.bytes = o;
     return w;
 }
@@ -420,9 +604,108 @@ __global__ void __launch_bounds__(256) k_jdec_rgb(const unsigned char *planes, D
     output_pixel(planes, f, (int)(i / (size_t)f.W), (int)(i % (size_t)f.W), out);
 }
 
+// ---- self-synchronising decode: kernels (thread per subsequence) ------------------------------------
+constexpr int kSyncThreads = 64;
+__global__ void __launch_bounds__(kSyncThreads) k_jsync_spec(const unsigned char *scan, size_t nbytes, unsigned nsub, DecFrame f,
+                                                             DecTables t, HState *E)
+{
+    const unsigned i = blockIdx.x * kSyncThreads + threadIdx.x;
+    if (i >= nsub) return;
+    HState s;
+    s.p = sub_start(scan, nbytes, i), s.n = 0, s.acc = 0, s.bi = 0, s.k = 0;
+    NoSink none;
+    decode_span(scan, nbytes, s, sub_limit(scan, nbytes, i, nsub), f, t, 0ull, none);
+    E[i] = s;
+}
+
+// round r: Eout[i] = state after subsequence i entered in Ein[i-1]; flags[r] = 1 if any state but the last changed.
+// Once a round changed nothing the states are exact and the remaining rounds only copy.
+__global__ void __launch_bounds__(kSyncThreads) k_jsync_round(const unsigned char *scan, size_t nbytes, unsigned nsub, DecFrame f,
+                                                              DecTables t, const HState *Ein, HState *Eout, unsigned *flags, int r)
+{
+    const unsigned i = blockIdx.x * kSyncThreads + threadIdx.x;
+    if (i >= nsub) return;
+    if (r > 0 && flags[r - 1] == 0u) {
+        Eout[i] = Ein[i];
+        return;
+    }
+    HState s = sub_entry(scan, nbytes, i, Ein);
+    NoSink none;
+    decode_span(scan, nbytes, s, sub_limit(scan, nbytes, i, nsub), f, t, 0ull, none);
+    if (i + 1u < nsub && !same_state(s, Ein[i])) flags[r] = 1u;
+    Eout[i] = s;
+}
+
+__global__ void __launch_bounds__(kSyncThreads) k_jsync_count(const unsigned char *scan, size_t nbytes, unsigned nsub, DecFrame f,
+                                                              DecTables t, const HState *E, const unsigned *flags, unsigned *nb)
+{
+    const unsigned i = blockIdx.x * kSyncThreads + threadIdx.x;
+    if (i >= nsub || flags[kSyncRounds - 1] != 0u) return;
+    HState s = sub_entry(scan, nbytes, i, E);
+    NoSink none;
+    nb[i] = decode_span(scan, nbytes, s, sub_limit(scan, nbytes, i, nsub), f, t, 0ull, none);
+}
+
+// one CTA of 1024 threads: exclusive scan of nb[] -> base[]
+__global__ void __launch_bounds__(1024) k_jsync_scan(const unsigned *nb, unsigned nsub, const unsigned *flags, unsigned long long *base)
+{
+    __shared__ unsigned long long s_warp[33];
+    if (flags[kSyncRounds - 1] != 0u) return;
+    const unsigned chunk = (nsub + 1023u) / 1024u;
+    const unsigned lo = min(threadIdx.x * chunk, nsub), hi = min(lo + chunk, nsub);
+    unsigned long long sum = 0;
+    for (unsigned j = lo; j < hi; ++j) sum += nb[j];
+    unsigned long long all;
+    unsigned long long run = jblock_excl_scan(sum, s_warp, all);
+    for (unsigned j = lo; j < hi; ++j) {
+        base[j] = run;
+        run += nb[j];
+    }
+}
+
+__global__ void __launch_bounds__(kSyncThreads) k_jsync_write(const unsigned char *scan, size_t nbytes, unsigned nsub, DecFrame f,
+                                                              DecTables t, const HState *E, const unsigned *flags,
+                                                              const unsigned long long *base, short *coef)
+{
+    const unsigned i = blockIdx.x * kSyncThreads + threadIdx.x;
+    if (i >= nsub || flags[kSyncRounds - 1] != 0u) return;
+    HState s = sub_entry(scan, nbytes, i, E);
+    CoefSink sink;
+    sink.coef = coef, sink.f = &f, sink.total = (unsigned long long)((unsigned)f.mx * (unsigned)f.my) * blocks_per_mcu(f);
+    decode_span(scan, nbytes, s, sub_limit(scan, nbytes, i, nsub), f, t, base[i], sink);
+}
+
+// grid = components, 1024 threads: running sum of the DC differences of one component in scan order
+__global__ void __launch_bounds__(1024) k_jsync_dc(short *coef, DecFrame f, const unsigned *flags)
+{
+    __shared__ int s_warp[33];
+    if (flags[kSyncRounds - 1] != 0u) return;
+    const int c = blockIdx.x;
+    const unsigned nmcu = (unsigned)f.mx * (unsigned)f.my, bpm = blocks_per_mcu(f);
+    const unsigned per = c == 0 ? (unsigned)(f.hs[0] * f.vs[0]) : 1u, first = c == 0 ? 0u : (unsigned)(f.hs[0] * f.vs[0]) + (unsigned)c - 1u;
+    const unsigned n = nmcu * per, chunk = (n + 1023u) / 1024u;
+    const unsigned lo = min(threadIdx.x * chunk, n), hi = min(lo + chunk, n);
+    int sum = 0;
+    for (unsigned j = lo; j < hi; ++j) sum += scan_block(coef, f, (unsigned long long)(j / per) * bpm + first + j % per)[0];
+    int all;
+    int run = jblock_excl_scan(sum, s_warp, all);
+    for (unsigned j = lo; j < hi; ++j) {
+        short *b = scan_block(coef, f, (unsigned long long)(j / per) * bpm + first + j % per);
+        run += b[0];
+        b[0] = (short)run;
+    }
+}
+
+// the serial decoder as the fallback of the parallel one: runs only if the rounds did not reach a fixed point
+__global__ void k_jdec_huff_fallback(const unsigned char *scan, size_t nbytes, DecFrame f, DecTables t, const unsigned *flags, short *coef)
+{
+    if (flags[kSyncRounds - 1] == 0u) return;
+    decode_interval(scan, 0, nbytes, f, t, 0u, (unsigned)f.mx * (unsigned)f.my, coef);
+}
+
 // file bytes on the host -> pixels on the device (H x W x 3, or H x W for a one-component file), enqueued on `st`
 inline cudaError_t decode_launch(const unsigned char *file_host, const DecPlan &pl, const DecWorkspace &ws, unsigned char *out,
-                                 cudaStream_t st, int *launches)
+                                 cudaStream_t st, int *launches, bool parallel = false)
 {
     const DecFrame &f = pl.f;
     cudaError_t e = cudaMemcpyAsync(ws.scan, file_host + pl.scan_begin, f.scan_bytes, cudaMemcpyHostToDevice, st);
@@ -431,11 +714,29 @@ inline cudaError_t decode_launch(const unsigned char *file_host, const DecPlan &
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(ws.coef, 0, f.nblocks * 64u * sizeof(short), st);
     if (e != cudaSuccess) return e;
-    k_jdec_huff<<<(f.nintervals + 63u) / 64u, 64, 0, st>>>(ws.scan, ws.intervals, f, pl.t, ws.coef);
+    if (parallel && f.nintervals == 1 && ws.nsub >= 4u) {
+        e = cudaMemsetAsync(ws.flags, 0, (size_t)kSyncRounds * sizeof(unsigned), st);
+        if (e != cudaSuccess) return e;
+        const unsigned g = (ws.nsub + kSyncThreads - 1u) / kSyncThreads;
+        k_jsync_spec<<<g, kSyncThreads, 0, st>>>(ws.scan, f.scan_bytes, ws.nsub, f, pl.t, ws.E0);
+        for (int r = 0; r < kSyncRounds; ++r)
+            k_jsync_round<<<g, kSyncThreads, 0, st>>>(ws.scan, f.scan_bytes, ws.nsub, f, pl.t, (r & 1) ? ws.E1 : ws.E0,
+                                                     (r & 1) ? ws.E0 : ws.E1, ws.flags, r);
+        const HState *E = (kSyncRounds & 1) ? ws.E1 : ws.E0;
+        k_jsync_count<<<g, kSyncThreads, 0, st>>>(ws.scan, f.scan_bytes, ws.nsub, f, pl.t, E, ws.flags, ws.nb);
+        k_jsync_scan<<<1, 1024, 0, st>>>(ws.nb, ws.nsub, ws.flags, ws.base);
+        k_jsync_write<<<g, kSyncThreads, 0, st>>>(ws.scan, f.scan_bytes, ws.nsub, f, pl.t, E, ws.flags, ws.base, ws.coef);
+        k_jsync_dc<<<f.ncomp, 1024, 0, st>>>(ws.coef, f, ws.flags);
+        k_jdec_huff_fallback<<<1, 1, 0, st>>>(ws.scan, f.scan_bytes, f, pl.t, ws.flags, ws.coef);
+        if (launches) *launches += 6 + kSyncRounds;
+    } else {
+        k_jdec_huff<<<(f.nintervals + 63u) / 64u, 64, 0, st>>>(ws.scan, ws.intervals, f, pl.t, ws.coef);
+        if (launches) *launches += 1;
+    }
     k_jdec_idct<<<(unsigned)((f.nblocks + 127u) / 128u), 128, 0, st>>>(ws.coef, f, pl.t, ws.planes);
     const size_t px = (size_t)f.H * (size_t)f.W;
     k_jdec_rgb<<<(unsigned)((px + 255u) / 256u), 256, 0, st>>>(ws.planes, f, out);
-    if (launches) *launches += 3;
+    if (launches) *launches += 2;
     return cudaGetLastError();
 }
 #endif

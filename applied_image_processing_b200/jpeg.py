@@ -96,8 +96,9 @@ def jpeg_info(data):
     return h.value, w.value, ch.value
 
 
-def decode_jpeg(data, device: bool = False):
-    """LST:200, 219 (`Image.open`): file bytes or path -> pixels, decoded on the GPU, bit-exact with Pillow."""
+def decode_jpeg(data, device: bool = False, parallel: bool = False):
+    """LST:200, 219 (`Image.open`): file bytes or path -> pixels, decoded on the GPU, bit-exact with Pillow.
+    ``parallel=True`` selects the self-synchronising Huffman decoder for files without restart markers (same pixels)."""
     import ctypes as C
 
     raw = _file_bytes(data)
@@ -111,7 +112,11 @@ def decode_jpeg(data, device: bool = False):
     shape = (h.value, w.value, 3) if ch.value == 3 else (h.value, w.value)
     out = torch.empty(shape, dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
-        check(lib.rct_jpeg_decode_async(buf, len(raw), work.data_ptr(), ws.value, out.data_ptr(),
-                                        torch.cuda.current_stream().cuda_stream))
+        before = lib.rct_jpeg_decode_set_parallel(1 if parallel else 0)
+        try:
+            check(lib.rct_jpeg_decode_async(buf, len(raw), work.data_ptr(), ws.value, out.data_ptr(),
+                                            torch.cuda.current_stream().cuda_stream))
+        finally:
+            lib.rct_jpeg_decode_set_parallel(before)
         torch.cuda.current_stream().synchronize()   # `work` and `buf` are released on return
     return out if device else out.cpu().numpy()

@@ -244,6 +244,11 @@ int rct_jpeg_encode_async(const uint8_t *rgb, size_t frame_stride, int n, int H,
  * receives uint8 [H,W,3] (or [H,W] for one component).  The host bytes may be released when the call returns.
  * Huffman decoding runs one thread per restart interval: a file without restart markers decodes serially (correct,
  * slow). */
+/* rct_jpeg_decode_set_parallel(1): files without restart markers are decoded by the self-synchronising parallel
+ * Huffman decoder (subsequences of 256 bytes decoded speculatively, states iterated to a fixed point, which proves them
+ * exact; the serial kernel takes over on the device if 32 rounds do not converge).  Same pixels, orders of magnitude
+ * faster on large files.  Off by default until its kernels have had their first GPU run; returns the old setting. */
+int rct_jpeg_decode_set_parallel(int on);
 int rct_jpeg_decode_info(const uint8_t *file_host, size_t nbytes, int *H, int *W, int *channels, size_t *workspace_bytes);
 int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspace, size_t workspace_bytes, uint8_t *pixels,
                           void *stream);

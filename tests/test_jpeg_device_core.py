@@ -102,3 +102,26 @@ def test_jpeg_entry_points_fail_loudly_without_a_gpu():
         aip.encode_jpeg(np.zeros((8, 8, 3), np.uint8))
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         aip.decode_jpeg(buf.getvalue())
+
+
+@pytest.mark.parametrize("h,w,kw,noise", [(270, 480, {}, False), (270, 480, {"quality": 95}, True), (100, 75, {"optimize": True}, True),
+                                          (96, 128, {"subsampling": 0}, False), (64, 200, {"subsampling": 1}, True), (37, 53, {}, None)])
+def test_self_synchronising_decoder_core_on_host_is_bit_exact(selftest, tmp_path, h, w, kw, noise):
+    # the parallel Huffman decoder's bodies (speculative pass, rounds to a fixed point, count, write, DC prefix) run serially
+    rng = np.random.default_rng(h + w)
+    yy, xx = np.mgrid[0:h, 0:w]
+    a = np.stack([(xx * 5 + yy) % 256, (yy * 3) % 256, (xx + yy * 2) % 256], -1) + rng.integers(-12, 12, (h, w, 3))
+    if noise:
+        a = rng.integers(0, 256, (h, w, 3))
+    img = PIL.fromarray(np.clip(a, 0, 255).astype(np.uint8))
+    if noise is None:
+        img = img.convert("L")
+    buf = io.BytesIO()
+    img.save(buf, "JPEG", **kw)
+    (tmp_path / "i.jpg").write_bytes(buf.getvalue())
+    p = subprocess.run([selftest, "--host-decode", str(tmp_path / "i.jpg"), str(tmp_path / "o.raw"), "par"], check=True,
+                       capture_output=True, text=True)
+    assert "converged" in p.stderr and "NOT" not in p.stderr
+    ref = np.asarray(PIL.open(io.BytesIO(buf.getvalue())))
+    got = np.fromfile(tmp_path / "o.raw", np.uint8).reshape(ref.shape)
+    assert np.array_equal(got, ref)

@@ -102,7 +102,7 @@ inline size_t encode_host_emulation(const uint8_t *rgb, int H, int W, int qualit
 int main(int argc, char **argv)
 {
     if (argc >= 4 && (std::string(argv[1]) == "--host-decode" || std::string(argv[1]) == "--gpu-decode")) {
-        // jpeg_selftest --host-decode|--gpu-decode in.jpg out.raw   (prints "H W channels")
+        // jpeg_selftest --host-decode|--gpu-decode in.jpg out.raw [par]   (prints "H W channels"; par = self-synchronising decode)
         FILE *fi = fopen(argv[2], "rb");
         if (!fi) return 1;
         std::vector<unsigned char> file;
@@ -121,6 +121,50 @@ int main(int argc, char **argv)
             std::vector<short> coef(f.nblocks * 64, 0);
             std::vector<unsigned char> planes(f.nsamples);
             const unsigned nmcu = (unsigned)f.mx * f.my, ri = f.restart_interval ? f.restart_interval : nmcu;
+            const bool par = argc > 4 && std::string(argv[4]) == "par" && f.nintervals == 1;
+            if (par) {  // the self-synchronising decode, serially: same bodies and the same order of passes as the kernels
+                const unsigned char *scan = file.data() + pl.scan_begin;
+                const size_t nb = f.scan_bytes;
+                const unsigned nsub = (unsigned)((nb + jpeg::kSubBytes - 1) / jpeg::kSubBytes);
+                std::vector<jpeg::HState> E(nsub), E2(nsub);
+                jpeg::NoSink none;
+                for (unsigned i = 0; i < nsub; ++i) {
+                    jpeg::HState s = {jpeg::sub_start(scan, nb, i), 0, 0, 0, 0};
+                    jpeg::decode_span(scan, nb, s, jpeg::sub_limit(scan, nb, i, nsub), f, pl.t, 0, none);
+                    E[i] = s;
+                }
+                int rounds = 0, changed = 1;
+                for (; rounds < jpeg::kSyncRounds && changed; ++rounds) {
+                    changed = 0;
+                    for (unsigned i = 0; i < nsub; ++i) {
+                        jpeg::HState s = jpeg::sub_entry(scan, nb, i, E.data());
+                        jpeg::decode_span(scan, nb, s, jpeg::sub_limit(scan, nb, i, nsub), f, pl.t, 0, none);
+                        if (i + 1 < nsub && !jpeg::same_state(s, E[i])) changed = 1;
+                        E2[i] = s;
+                    }
+                    E.swap(E2);
+                }
+                fprintf(stderr, "parallel decode: %u subsequences, %d rounds, %s\n", nsub, rounds, changed ? "NOT converged" : "converged");
+                if (changed) return 7;
+                std::vector<unsigned long long> base(nsub + 1, 0);
+                for (unsigned i = 0; i < nsub; ++i) {
+                    jpeg::HState s = jpeg::sub_entry(scan, nb, i, E.data());
+                    base[i + 1] = base[i] + jpeg::decode_span(scan, nb, s, jpeg::sub_limit(scan, nb, i, nsub), f, pl.t, 0, none);
+                }
+                const unsigned long long total = (unsigned long long)nmcu * jpeg::blocks_per_mcu(f);
+                jpeg::CoefSink sink = {coef.data(), &f, total};
+                for (unsigned i = nsub; i-- > 0;) {
+                    jpeg::HState s = jpeg::sub_entry(scan, nb, i, E.data());
+                    jpeg::decode_span(scan, nb, s, jpeg::sub_limit(scan, nb, i, nsub), f, pl.t, base[i], sink);
+                }
+                int pred[3] = {0, 0, 0};
+                for (unsigned long long o = 0; o < total; ++o) {
+                    const int c = jpeg::mcu_component(f, (unsigned)(o % jpeg::blocks_per_mcu(f)));
+                    short *b = jpeg::scan_block(coef.data(), f, o);
+                    pred[c] += b[0];
+                    b[0] = (short)pred[c];
+                }
+            } else
             for (unsigned k = 0; k < f.nintervals; ++k)
                 jpeg::decode_interval(file.data() + pl.scan_begin, (size_t)pl.intervals[2 * k], (size_t)pl.intervals[2 * k + 1], f, pl.t,
                                       k * ri, std::min(k * ri + ri, nmcu), coef.data());
@@ -146,7 +190,7 @@ int main(int argc, char **argv)
             float best = 1e30f;
             for (int rep = 0; rep < 3; ++rep) {
                 CK(cudaEventRecord(e0));
-                CK(jpeg::decode_launch(file.data(), pl, ws, d_out, 0, nullptr));
+                CK(jpeg::decode_launch(file.data(), pl, ws, d_out, 0, nullptr, argc > 4 && std::string(argv[4]) == "par"));
                 CK(cudaEventRecord(e1));
                 CK(cudaDeviceSynchronize());
                 float ms;
