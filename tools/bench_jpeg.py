@@ -45,6 +45,7 @@ def main():
     ap.add_argument("--size", default="2160x3840")
     ap.add_argument("--quality", type=int, default=75)
     ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--parallel", action="store_true", help="also time the self-synchronising decoder (decode_jpeg(parallel=True))")
     a = ap.parse_args()
     H, W = (int(v) for v in a.size.split("x"))
     dev = torch.device("cuda", 0)
@@ -106,6 +107,22 @@ def main():
         ok = bool(np.array_equal(got.cpu().numpy(), np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))))
         out["decode"][name] = {"H": 1080, "W": 1920, "file_bytes": len(data), "ms": ms,
                                "MP_per_s": 1080 * 1920 / 1e6 / (ms * 1e-3), "bit_exact_vs_pillow": ok}
+    if a.parallel:
+        for name, (h, w) in (("1080p", (1080, 1920)), ("4k", (2160, 3840))):
+            buf = io.BytesIO()
+            Image.fromarray(frames_like_photos(1, h, w, dev)[0].cpu().numpy()).save(buf, "JPEG", quality=a.quality)
+            data = buf.getvalue()
+            aip.decode_jpeg(data, parallel=True)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(5):
+                got = aip.decode_jpeg(data, device=True, parallel=True)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 5
+            ok = bool(np.array_equal(got.cpu().numpy(), np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))))
+            out["decode"]["self_synchronising_" + name] = {"H": h, "W": w, "file_bytes": len(data), "ms": ms,
+                                                           "MP_per_s": h * w / 1e6 / (ms * 1e-3), "bit_exact_vs_pillow": ok}
     print(json.dumps(out))
 
 
