@@ -233,7 +233,7 @@ JHD int dc_predictor(const short *coef, const Geom &g, unsigned mcu, int b)
 
 // jchuff.c encode_one_block; SINK::put(code, length).  zz = the block's 64 coefficients in zigzag order
 // (zz[0] is ignored: the DC difference is passed in), dummy = AC all zero.
-template <class SINK>
+template <class SINK, bool UNROLL = true>
 JHD void encode_block(SINK &sink, const short *zz, bool dummy, int dc_diff, const unsigned *dc_tab, const unsigned *ac_tab)
 {
     {
@@ -245,7 +245,7 @@ JHD void encode_block(SINK &sink, const short *zz, bool dummy, int dc_diff, cons
     }
     int run = 0;
     if (!dummy) {
-#pragma unroll
+#pragma unroll(UNROLL ? 63 : 1)
         for (int k = 1; k < 64; ++k) {
             const int v = zz[k];
             if (v == 0) {
@@ -350,7 +350,13 @@ struct StreamSink {
 
 // ---- host side: tables, header, workspace layout --------------------------------------------
 constexpr unsigned kTile = 4096;         // bytes of unstuffed stream per stuffing tile
-constexpr int kEntThreads = 256;         // blocks per CTA of the entropy kernels = one group of the offset scan
+#ifndef RCT_JENT
+#define RCT_JENT 256
+#endif
+#ifndef RCT_JEMIT_UNROLL
+#define RCT_JEMIT_UNROLL 1               // 0: k_jpeg_emit walks the 63 AC coefficients in a rolled loop (A/B knob)
+#endif
+constexpr int kEntThreads = RCT_JENT;    // blocks per CTA of the entropy kernels = one group of the offset scan
 constexpr unsigned kBlockBitsMax = 1664; // >= 20 (DC) + 63 * 26 (AC) bits: the worst block
 constexpr int kHeaderMax = 640;
 
@@ -679,7 +685,7 @@ __global__ void __launch_bounds__(kEntThreads) k_jpeg_emit(const short *coef, Ge
     load_block(fc, r, zz);
     const int diff = resolved_dc(fc, g, mcu, b) - dc_predictor(fc, g, mcu, b);
     StreamSink sink(stream + (size_t)frame * stream_words, pbase[(size_t)frame * nparts + blockIdx.x] + ex);
-    encode_block(sink, zz, is_dummy(g, mcu, b), diff, s_dc[c], s_ac[c]);
+    encode_block<StreamSink, (RCT_JEMIT_UNROLL != 0)>(sink, zz, is_dummy(g, mcu, b), diff, s_dc[c], s_ac[c]);
     if (r == g.nblk - 1u) {  // jchuff.c flush_bits: pad the last byte with 1-bits
         const int k = (int)((8ull - (sink.position() & 7ull)) & 7ull);
         if (k) sink.put((1u << k) - 1u, k);

@@ -10,10 +10,18 @@ yy, xx = np.mgrid[0:h, 0:w]
 a = np.clip(np.stack([(xx * 5 + yy) % 256, (yy * 3) % 256, (xx + yy * 2) % 256], -1) + rng.integers(-12, 12, (h, w, 3)), 0, 255).astype(np.uint8)
 a.tofile("/tmp/in4k.rgb")
 PY
-for v in v1 vb2 vb3 vb4; do
-  [ -x tools/jpeg_selftest_$v ] || continue
-  echo -n "$v: "; timeout 20 tools/jpeg_selftest_$v --gpu 2160 3840 /tmp/in4k.rgb /tmp/o_$v.jpg 75 8 2>&1 | tail -1
-  cmp -s /tmp/o_$v.jpg /tmp/o_v1.jpg && echo "   same bytes as v1" || echo "   DIFFERS from v1"
+# builds from tools/build_jpeg_variants.sh; the reference bytes come from Pillow
+python - <<'PY'
+import numpy as np
+from PIL import Image
+a = np.fromfile("/tmp/in4k.rgb", np.uint8).reshape(2160, 3840, 3)
+Image.fromarray(a).save("/tmp/ref4k.jpg")
+PY
+for exe in tools/jpeg_selftest_v*; do
+  [ -x $exe ] || continue
+  v=${exe#tools/jpeg_selftest_}
+  echo -n "$v: "; timeout 20 $exe --gpu 2160 3840 /tmp/in4k.rgb /tmp/o_$v.jpg 75 8 2>&1 | tail -1
+  cmp -s /tmp/o_$v.jpg /tmp/ref4k.jpg && echo "   same bytes as Pillow" || echo "   DIFFERS from Pillow"
 done 2>&1 | tee gpurun_out/jpeg_ab.log
 timeout 40 python -m pytest tests/test_jpeg_gpu.py -m gpu -x -q -p no:cacheprovider > gpurun_out/jpeg_pytest.log 2>&1; echo "pytest exit $?"; tail -2 gpurun_out/jpeg_pytest.log
 echo "elapsed $SECONDS"
