@@ -13,6 +13,7 @@ from .localized_style_transfer import (  # noqa: F401
     lab_to_rgb_pixels,
     match_cdf,
     regional_color_transfer,
+    regional_color_transfer_binned,
     regional_color_transfer_labels,
     rgb_to_lab_image,
     rgb_to_lab_pixels,
@@ -25,7 +26,7 @@ from .jpeg import decode_jpeg, encode_jpeg, jpeg_info, save_jpeg  # noqa: F401
 __all__ = [
     "RGB_TO_LMS", "LMS_TO_LAB", "LAB_TO_LMS", "LMS_TO_RGB", "RegionPCA", "apply_pca",
     "color_transfer_foreground", "extract_foreground_deeplab", "lab_to_rgb_image", "lab_to_rgb_pixels",
-    "match_cdf", "regional_color_transfer", "regional_color_transfer_labels", "rgb_to_lab_image",
+    "match_cdf", "regional_color_transfer", "regional_color_transfer_binned", "regional_color_transfer_labels", "rgb_to_lab_image",
     "rgb_to_lab_pixels", "run_localized_style_transfer", "adain_mask_blend", "deeplab_background_mask",
     "deeplab_label_map", "warp_image", "normalize_image", "blend_images", "warp_blend", "blend_sequence",
 ]

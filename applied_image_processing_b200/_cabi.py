@@ -61,6 +61,11 @@ SIGNATURES = {
     "rct_plan_hist_bytes": (_sz, [_vp]),
     "rct_shard_solve_async": (_i, [_vp, _vp]),
     "rct_shard_apply_async": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "rct_transfer_binned_async": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _sz, _vp, _sz, _i, _i, _i, _i, _vp]),
+    "rct_shard_binned_phase_async": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "rct_plan_xchg_ptr": (_vp, [_vp]),
+    "rct_plan_xchg_bytes": (_sz, [_i, _i]),
+    "rct_plan_debug_binned": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "rct_rgb_to_lab": (_i, [_vp, _vp, _sz, _vp]),
     "rct_lab_to_rgb": (_i, [_vp, _vp, _vp, _sz, _vp]),
     "rct_pca_scratch_bytes": (_sz, []),

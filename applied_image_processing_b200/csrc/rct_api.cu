@@ -96,6 +96,22 @@ int ensure_device(int *dev_out)
 
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
+// Switches to `device` for the scope and restores the caller's current device afterwards
+// (a plan of another GPU must not change the calling thread's device: multi-GPU processes).
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    explicit DeviceGuard(int device)
+    {
+        if (cudaGetDevice(&prev) == cudaSuccess && prev != device) switched = cudaSetDevice(device) == cudaSuccess;
+    }
+    ~DeviceGuard()
+    {
+        if (switched) cudaSetDevice(prev);
+    }
+};
+
+constexpr size_t kXchgBytes = 64 << 10;
 struct Layout {
     size_t cap, maxparts;
     size_t off_ctrl, off_jobs, off_status, off_xtab, off_ytab;
@@ -105,6 +121,7 @@ struct Layout {
     size_t off_cmap, cmap_stride_u32;  // [slots] chunk maps of k_front_hist
     size_t off_zero, zero_bytes, z_fcnt, z_pfill;  // [slots][2] blocks zeroed before every sort
     size_t off_dbg_m, off_dbg_j, dbg_stride;
+    size_t off_xchg;  // exchange buffer of the row-sharded binned path (kXchgBytes)
     size_t total;
 };
 
@@ -155,6 +172,7 @@ Layout make_layout(int H, int W, int slots, unsigned flags)
         L.off_dbg_m = o; o = align_up(o + 8 * L.cap * slots);
         L.off_dbg_j = o; o = align_up(o + 8 * L.cap * slots);
     }
+    L.off_xchg = o; o = align_up(o + kXchgBytes);
     L.total = o;
     return L;
 }
@@ -191,6 +209,11 @@ struct rct_plan {
     cudaStream_t own_stream;            // compute stream of the host entry point
     cudaStream_t h2d_stream, d2h_stream; // copy streams of the host entry point (overlap with compute)
     cudaEvent_t ev_in[kStageSetsMax], ev_comp[kStageSetsMax], ev_out[kStageSetsMax];
+    // The workspace (ctrl, lists, LUT) is shared by every call on this plan: each entry point makes its
+    // stream wait for the previous call's last kernel (ev_last) and records it again when it has enqueued
+    // its own work, so calls from different streams (or the host entry point's own stream) never overlap.
+    cudaEvent_t ev_last;
+    bool ev_last_valid;
     int lpf;         // labels per frame of the call in progress (rct_transfer_labels_async), else 1
     int lut_mode;    // RCT_OPT_LUT: 1 = uint16 run indices + palette, 0 = uint32 RGB per colour
     int stage_sets;  // RCT_OPT_STAGE_SETS: staging sets of the host entry point (2..kStageSetsMax)
@@ -260,7 +283,12 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     if (H <= 0 || W <= 0 || sh <= 0 || sw <= 0 || slots <= 0 || slots > 4096)
         return fail(RCT_ERR_ARG, "bad geometry H=%d W=%d sh=%d sw=%d slots=%d", H, W, sh, sw, slots);
     if ((size_t)H * (size_t)W >= ((size_t)1 << 32)) return fail(RCT_ERR_ARG, "image too large (>= 2^32 pixels)");
-    CK(cudaSetDevice(device));
+    DeviceGuard guard(device);
+    {
+        int cur = -1;
+        CK(cudaGetDevice(&cur));
+        if (cur != device) return fail(RCT_ERR_CUDA, "cannot switch to device %d", device);
+    }
     int rc = ensure_device(nullptr);
     if (rc) return rc;
     rct_plan *p = new (std::nothrow) rct_plan();
@@ -359,6 +387,7 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
         }
     }
     delete[] tab;
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_last, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->own_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->h2d_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->d2h_stream, cudaStreamNonBlocking);
@@ -379,7 +408,8 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
 int rct_plan_destroy(rct_plan *p)
 {
     if (!p) return RCT_OK;
-    cudaSetDevice(p->device);
+    DeviceGuard guard(p->device);
+    if (p->ev_last) cudaEventDestroy(p->ev_last);
     if (p->own_stream) cudaStreamDestroy(p->own_stream);
     if (p->h2d_stream) cudaStreamDestroy(p->h2d_stream);
     if (p->d2h_stream) cudaStreamDestroy(p->d2h_stream);
@@ -618,8 +648,10 @@ int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t 
     LAUNCH(k_plan_fine, dim3(1, njobs), 1024, st, jobs);
     KMARK(RCT_TK_PLAN_FINE);
     k_fine_hist<<<dim3(hblocks, njobs), RCT_FHTH, kSmemFineHist, st>>>(jobs);
+    ++t_launches;
+    CK(cudaGetLastError());
     KMARK(RCT_TK_FINE_HIST);
-    k_plan_parts<<<dim3(1, njobs), 1024, 0, st>>>(jobs);
+    LAUNCH(k_plan_parts, dim3(1, njobs), 1024, st, jobs);
     KMARK(RCT_TK_PLAN_PARTS);
     // few, long-lived CTAs per job: each stages the fine-bin tables (kSmemScatter bytes) once
 #ifndef RCT_SB
@@ -628,11 +660,13 @@ int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t 
     unsigned sblocks = (unsigned)((p ? p->sm : 148) * RCT_SB / (njobs > 0 ? njobs : 1));  // ~4 waves of 3 CTAs per SM
     if (sblocks < 16u) sblocks = 16u;
     k_scatter<<<dim3(sblocks, njobs), RCT_SCT, kSmemScatter, st>>>(jobs);
+    ++t_launches;
+    CK(cudaGetLastError());
     KMARK(RCT_TK_SCATTER);
     k_part_sort<<<dim3((unsigned)maxparts, njobs), kSortThreads, kSmemPartSort, st>>>(jobs, part_cap);
-    KMARK(RCT_TK_PART_SORT);
-    t_launches += 4;
+    ++t_launches;
     CK(cudaGetLastError());
+    KMARK(RCT_TK_PART_SORT);
     LAUNCH(k_part_scan, dim3(1, njobs), 1024, st, jobs);
     KMARK(RCT_TK_PART_SCAN);
     return RCT_OK;
@@ -779,6 +813,19 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
     return mark(p, st);
 }
 
+// ordering between successive users of a plan's workspace (see rct_plan::ev_last)
+int plan_enter(rct_plan *p, cudaStream_t st)
+{
+    if (p->ev_last_valid) CK(cudaStreamWaitEvent(st, p->ev_last, 0));
+    return RCT_OK;
+}
+int plan_leave(rct_plan *p, cudaStream_t st)
+{
+    CK(cudaEventRecord(p->ev_last, st));
+    p->ev_last_valid = true;
+    return RCT_OK;
+}
+
 int check_mode(int mode, const void *mask)
 {
     if (mode < 0 || mode > 2) return fail(RCT_ERR_ARG, "bad mode %d", mode);
@@ -812,6 +859,7 @@ int rct_transfer_async(rct_plan *p, const uint8_t *content, size_t content_strid
     cudaStream_t st = (cudaStream_t)stream;
     rc = ensure_status_frames(p, n_frames);
     if (rc) return rc;
+    if ((rc = plan_enter(p, st))) return rc;
     const size_t npix = (size_t)p->H * (size_t)p->W;
     for (int f0 = 0; f0 < n_frames; f0 += p->slots) {
         int ns = n_frames - f0 < p->slots ? n_frames - f0 : p->slots;
@@ -823,7 +871,7 @@ int rct_transfer_async(rct_plan *p, const uint8_t *content, size_t content_strid
         if ((rc = phase_solve(p, ns, st, !p->front))) return rc;
         if ((rc = phase_apply(p, f, ns, mode, label, 0, npix, p->status_frames + f0, st))) return rc;
     }
-    return RCT_OK;
+    return plan_leave(p, st);
 }
 
 int rct_plan_status(rct_plan *p, int *status_host, int n_frames, void *stream)
@@ -853,6 +901,7 @@ int rct_transfer_labels_async(rct_plan *p, const uint8_t *content, size_t conten
     if (rc) return rc;
     const size_t npix = (size_t)p->H * (size_t)p->W;
     const int fpg = p->slots / n_labels;  // frames per launch group
+    if ((rc = plan_enter(p, st))) return rc;
     p->lpf = n_labels;
     for (int f0 = 0; f0 < n_frames && rc == RCT_OK; f0 += fpg) {
         const int nf = n_frames - f0 < fpg ? n_frames - f0 : fpg, ns = nf * n_labels;
@@ -864,6 +913,7 @@ int rct_transfer_labels_async(rct_plan *p, const uint8_t *content, size_t conten
         if (rc == RCT_OK) rc = phase_apply(p, f, ns, RCT_MODE_LABEL, 0, 0, npix, p->status_frames + (size_t)f0 * n_labels, st);
     }
     p->lpf = 1;
+    if (rc == RCT_OK) rc = plan_leave(p, st);
     return rc;
 }
 
@@ -873,7 +923,7 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
     if (!p || !content_h || !stylised_h || !out_h || n_frames <= 0) return fail(RCT_ERR_ARG, "null/invalid argument");
     int rc = check_mode(mode, mask_h);
     if (rc) return rc;
-    CK(cudaSetDevice(p->device));
+    DeviceGuard guard(p->device);
     const size_t npix = (size_t)p->H * (size_t)p->W, spix = (size_t)p->sh * (size_t)p->sw;
     const size_t cb = align_up(npix * 3), sb = align_up(spix * 3), mb = align_up(npix);
     // A ring of S staging sets (RCT_OPT_STAGE_SETS, default 4): group k is copied in on the H2D
@@ -894,6 +944,7 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
     rc = ensure_status_frames(p, n_frames);
     if (rc) return rc;
     cudaStream_t st = p->own_stream, sin = p->h2d_stream, sout = p->d2h_stream;
+    if ((rc = plan_enter(p, st))) return rc;
     int k = 0;
     for (int f0 = 0; f0 < n_frames; f0 += p->slots, ++k) {
         const int b = k % S;
@@ -933,6 +984,7 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
             if (tmp[i] > worst) worst = tmp[i];
     if (!status_host) delete[] tmp;
     if (e != cudaSuccess) return fail(RCT_ERR_CUDA, "host transfer failed: %s", cudaGetErrorString(e));
+    if ((rc = plan_leave(p, st))) return rc;
     return worst;
 }
 
@@ -947,7 +999,11 @@ int rct_shard_hist_async(rct_plan *p, const uint8_t *content, const uint8_t *sty
     FrameSet f{content, stylised, mask, nullptr, 0, 0, 0, 0};
     cudaStream_t st = (cudaStream_t)stream;
     const size_t pb = (size_t)row0 * p->W, pe = (size_t)(row0 + rows) * p->W;
-    if (!p->front) return phase_hist(p, f, 1, mode, label, pb, pe, st);
+    if ((rc = plan_enter(p, st))) return rc;
+    if (!p->front) {
+        rc = phase_hist(p, f, 1, mode, label, pb, pe, st);
+        return rc ? rc : plan_leave(p, st);
+    }
     // Colour-partitioned front end on the band (streaming passes, no global atomics), then the band's
     // (colour, count) lists are written into the zeroed colour cubes the ranks all-reduce: one plain
     // store per distinct colour instead of one atomic per pixel (k_hist).
@@ -957,14 +1013,17 @@ int rct_shard_hist_async(rct_plan *p, const uint8_t *content, const uint8_t *sty
     LAUNCH(k_list_to_cube, (unsigned)p->sm * 8, 256, st, p->ctrl, p->jobs, 0, 1, p->hist + kCube);
     p->cube_dirty = true;
     CK(cudaMemsetAsync(p->ctrl, 0, sizeof(FrameCtrl), st));  // the solve rebuilds the lists from the reduced cubes
-    return mark(p, st);
+    if ((rc = mark(p, st))) return rc;
+    return plan_leave(p, st);
 }
 void *rct_plan_hist_ptr(rct_plan *p) { return p ? (void *)p->hist : nullptr; }
 size_t rct_plan_hist_bytes(rct_plan *p) { return p ? 4 * p->L.hist_stride_u32 : 0; }
 int rct_shard_solve_async(rct_plan *p, void *stream)
 {
     if (!p) return fail(RCT_ERR_ARG, "null plan");
-    return phase_solve(p, 1, (cudaStream_t)stream, true);
+    int rc = plan_enter(p, (cudaStream_t)stream);
+    if (rc == RCT_OK) rc = phase_solve(p, 1, (cudaStream_t)stream, true);
+    return rc ? rc : plan_leave(p, (cudaStream_t)stream);
 }
 int rct_shard_apply_async(rct_plan *p, const uint8_t *content, const uint8_t *stylised, const uint8_t *mask,
                           uint8_t *out, int mode, int label, int row0, int rows, void *stream)
@@ -976,8 +1035,171 @@ int rct_shard_apply_async(rct_plan *p, const uint8_t *content, const uint8_t *st
     rc = ensure_status_frames(p, 1);
     if (rc) return rc;
     FrameSet f{content, stylised, mask, out, 0, 0, 0, 0};
-    return phase_apply(p, f, 1, mode, label, (size_t)row0 * p->W, (size_t)(row0 + rows) * p->W, p->status_frames,
-                       (cudaStream_t)stream);
+    if ((rc = plan_enter(p, (cudaStream_t)stream))) return rc;
+    rc = phase_apply(p, f, 1, mode, label, (size_t)row0 * p->W, (size_t)(row0 + rows) * p->W, p->status_frames,
+                     (cudaStream_t)stream);
+    return rc ? rc : plan_leave(p, (cudaStream_t)stream);
+}
+
+
+// ---- BINNED mode (approximation; rct_binned.cuh) ---------------------------------------------------
+namespace {
+int binned_solve(rct_plan *p, int nslots, int bins, cudaStream_t st, int first_phase, int last_phase)
+{
+    // phases: 0 moments | 1 pca + keys + key range | 2 histograms | 3 CDF build / inverse lookup -> LUT
+    const unsigned eb = entry_blocks(p, nslots);
+    if (first_phase <= 0 && last_phase >= 0) {
+        LAUNCH(k_lab_moments, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs);
+        KMARK(RCT_TK_LAB_MOMENTS);
+    }
+    if (first_phase <= 1 && last_phase >= 1) {
+        LAUNCH(k_pca, dim3((nslots + 31) / 32), 32, st, p->ctrl, nslots);
+        KMARK(RCT_TK_PCA);
+        LAUNCH(k_bin_keys, dim3(eb * RCT_EBK, 2, nslots), 256, st, p->ctrl, p->jobs);
+        KMARK(RCT_TK_KEYS);
+    }
+    if (first_phase <= 2 && last_phase >= 2) {
+        LAUNCH(k_bin_hist, dim3(eb, 2, nslots), 256, st, p->ctrl, p->jobs, bins);
+        KMARK(RCT_TK_FINE_HIST);
+    }
+    if (first_phase <= 3 && last_phase >= 3) {
+        LAUNCH(k_bin_match, dim3(eb * 2, nslots), 256, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32, bins, p->dbg_m,
+               p->dbg_j, p->L.dbg_stride);
+        KMARK(RCT_TK_MATCH);
+    }
+    return RCT_OK;
+}
+int check_bins(int bins)
+{
+    if (bins < 2 || bins > kBinMax) return fail(RCT_ERR_ARG, "bins %d outside 2..%d", bins, kBinMax);
+    return RCT_OK;
+}
+}  // namespace
+
+int rct_transfer_binned_async(rct_plan *p, const uint8_t *content, size_t content_stride, const uint8_t *stylised,
+                              size_t stylised_stride, const uint8_t *mask, size_t mask_stride, uint8_t *out,
+                              size_t out_stride, int n_frames, int mode, int label, int bins, void *stream)
+{
+    if (!p || !content || !stylised || !out || n_frames <= 0) return fail(RCT_ERR_ARG, "null/invalid argument");
+    int rc = check_mode(mode, mask);
+    if (rc == RCT_OK) rc = check_bins(bins);
+    if (rc) return rc;
+    if (p->lut_mode) return fail(RCT_ERR_ARG, "the binned mode writes the uint32 colour LUT: set RCT_OPT_LUT to 0");
+    cudaStream_t st = (cudaStream_t)stream;
+    rc = ensure_status_frames(p, n_frames);
+    if (rc) return rc;
+    if ((rc = plan_enter(p, st))) return rc;
+    const size_t npix = (size_t)p->H * (size_t)p->W;
+    const int front_saved = p->front;
+    p->front = 1;  // the colour-partition front end produces the (colour, count) lists directly
+    for (int f0 = 0; f0 < n_frames && rc == RCT_OK; f0 += p->slots) {
+        int ns = n_frames - f0 < p->slots ? n_frames - f0 : p->slots;
+        FrameSet f{content + (size_t)f0 * content_stride, stylised + (size_t)f0 * stylised_stride,
+                   mask ? mask + (size_t)f0 * mask_stride : nullptr, out + (size_t)f0 * out_stride,
+                   content_stride, stylised_stride, mask_stride, out_stride};
+        rc = phase_front(p, f, ns, mode, label, 0, npix, st);
+        if (rc == RCT_OK) rc = binned_solve(p, ns, bins, st, 0, 3);
+        if (rc == RCT_OK) rc = mark(p, st);
+        if (rc == RCT_OK) rc = phase_apply(p, f, ns, mode, label, 0, npix, p->status_frames + f0, st);
+    }
+    p->front = front_saved;
+    return rc ? rc : plan_leave(p, st);
+}
+
+/* Row-sharded binned path (one image, rows [row0, row0+rows) on this rank; slot 0).  Between the phases the caller
+ * all-reduces the exchange buffer (rct_plan_xchg_ptr):
+ *   phase 0: band -> colour lists -> exact moments          -> xchg 0: int64[56]   SUM
+ *   phase 1: PCA (global moments) -> keys -> key range      -> xchg 1: double[4]   MAX
+ *   phase 2: histograms over the global range               -> xchg 2: uint32[2*bins] SUM
+ *   phase 3: CDFs -> LUT of the band's colours -> apply the band's rows */
+int rct_shard_binned_phase_async(rct_plan *p, int phase, const uint8_t *content, const uint8_t *stylised,
+                                 const uint8_t *mask, uint8_t *out, int mode, int label, int row0, int rows, int bins,
+                                 void *stream)
+{
+    if (!p || !content || !stylised || row0 < 0 || rows < 0 || row0 + rows > p->H || phase < 0 || phase > 3)
+        return fail(RCT_ERR_ARG, "bad shard arguments");
+    int rc = check_mode(mode, mask);
+    if (rc == RCT_OK) rc = check_bins(bins);
+    if (rc) return rc;
+    if (p->lut_mode) return fail(RCT_ERR_ARG, "the binned mode writes the uint32 colour LUT: set RCT_OPT_LUT to 0");
+    cudaStream_t st = (cudaStream_t)stream;
+    void *xchg = p->ws + p->L.off_xchg;
+    const size_t pb = (size_t)row0 * p->W, pe = (size_t)(row0 + rows) * p->W;
+    if ((rc = plan_enter(p, st))) return rc;
+    if (phase == 0) {
+        FrameSet f{content, stylised, mask, nullptr, 0, 0, 0, 0};
+        const int front_saved = p->front;
+        p->front = 1;
+        rc = phase_front(p, f, 1, mode, label, pb, pe, st);
+        p->front = front_saved;
+        if (rc == RCT_OK) rc = binned_solve(p, 1, bins, st, 0, 0);
+        if (rc) return rc;
+        LAUNCH(k_xchg_pack, 1, 64, st, p->ctrl, xchg, 0, bins);
+    } else if (phase == 1) {
+        LAUNCH(k_xchg_unpack, 1, 64, st, p->ctrl, xchg, 0, bins);
+        if ((rc = binned_solve(p, 1, bins, st, 1, 1))) return rc;
+        LAUNCH(k_xchg_pack, 1, 64, st, p->ctrl, xchg, 1, bins);
+    } else if (phase == 2) {
+        LAUNCH(k_xchg_unpack, 1, 64, st, p->ctrl, xchg, 1, bins);
+        if ((rc = binned_solve(p, 1, bins, st, 2, 2))) return rc;
+        LAUNCH(k_xchg_pack, (2 * bins + 255) / 256, 256, st, p->ctrl, xchg, 2, bins);
+    } else {
+        if (!out) return fail(RCT_ERR_ARG, "null output");
+        LAUNCH(k_xchg_unpack, (2 * bins + 255) / 256, 256, st, p->ctrl, xchg, 2, bins);
+        if ((rc = binned_solve(p, 1, bins, st, 3, 3))) return rc;
+        if ((rc = ensure_status_frames(p, 1))) return rc;
+        FrameSet f{content, stylised, mask, out, 0, 0, 0, 0};
+        if ((rc = phase_apply(p, f, 1, mode, label, pb, pe, p->status_frames, st))) return rc;
+    }
+    return plan_leave(p, st);
+}
+void *rct_plan_xchg_ptr(rct_plan *p) { return p ? (void *)(p->ws + p->L.off_xchg) : nullptr; }
+size_t rct_plan_xchg_bytes(int which, int bins)
+{
+    if (which == 0) return 56 * sizeof(long long);
+    if (which == 1) return 4 * sizeof(double);
+    if (which == 2 && bins >= 2 && bins <= kBinMax) return 2 * (size_t)bins * sizeof(unsigned);
+    return 0;
+}
+
+/* binned introspection (parity tests): the two B-bin histograms, the key ranges (lo_t hi_t lo_s hi_s) and -- with
+ * RCT_FLAG_DEBUG -- per entry of slot's target list its colour, CDF index pair b*65536+b' and matched value */
+int rct_plan_debug_binned(rct_plan *p, int slot, int bins, uint32_t *hist_t, uint32_t *hist_s, double *range4,
+                          uint32_t *colour, int64_t *code, double *matched)
+{
+    if (!p || slot < 0 || slot >= p->slots) return fail(RCT_ERR_ARG, "bad slot");
+    int rc = check_bins(bins);
+    if (rc) return rc;
+    DeviceGuard guard(p->device);
+    CK(cudaDeviceSynchronize());
+    FrameCtrl *h = new (std::nothrow) FrameCtrl;
+    if (!h) return fail(RCT_ERR_NOMEM, "out of host memory");
+    cudaError_t e = cudaMemcpy(h, p->ctrl + slot, sizeof(FrameCtrl), cudaMemcpyDeviceToHost);
+    size_t d = 0;
+    if (e == cudaSuccess) {
+        if (hist_t) memcpy(hist_t, h->r[0].coarse, 4 * (size_t)bins);
+        if (hist_s) memcpy(hist_s, h->r[1].coarse, 4 * (size_t)bins);
+        if (range4)
+            for (int r = 0; r < 2; ++r) {
+                unsigned long long mx = h->r[r].lab_max[0], mn = ~h->r[r].lab_min[0];
+                unsigned long long umx = (mx & 0x8000000000000000ULL) ? (mx & 0x7fffffffffffffffULL) : ~mx;
+                unsigned long long umn = (mn & 0x8000000000000000ULL) ? (mn & 0x7fffffffffffffffULL) : ~mn;
+                memcpy(&range4[2 * r], &umn, 8);
+                memcpy(&range4[2 * r + 1], &umx, 8);
+            }
+        d = h->status == 0 ? h->r[0].d : 0;
+    }
+    delete h;
+    if (e != cudaSuccess) return fail(RCT_ERR_CUDA, "debug copy failed: %s", cudaGetErrorString(e));
+    if (d && (colour || code || matched)) {
+        if (!(p->flags & RCT_FLAG_DEBUG)) return fail(RCT_ERR_ARG, "plan was not created with RCT_FLAG_DEBUG");
+        const Layout &L = p->L;
+        uint8_t *b = p->ws + L.off_region + L.region_bytes * (size_t)(2 * slot);
+        if (colour) CK(cudaMemcpy(colour, b + L.r_col, 4 * d, cudaMemcpyDeviceToHost));
+        if (code) CK(cudaMemcpy(code, p->dbg_j + (size_t)slot * L.dbg_stride, 8 * d, cudaMemcpyDeviceToHost));
+        if (matched) CK(cudaMemcpy(matched, p->dbg_m + (size_t)slot * L.dbg_stride, 8 * d, cudaMemcpyDeviceToHost));
+    }
+    return RCT_OK;
 }
 
 // ---- stand-alone functions -----------------------------------------------------------------
@@ -1285,7 +1507,7 @@ int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspa
 int rct_plan_timing(rct_plan *p, double *ms4, long long *groups, int reset)
 {
     if (!p) return fail(RCT_ERR_ARG, "null plan");
-    CK(cudaSetDevice(p->device));
+    DeviceGuard guard(p->device);
     if (p->ev_busy.size() % 5 != 0) return fail(RCT_ERR_ARG, "timing events out of step (mixed entry points?)");
     for (size_t g = 0; g + 5 <= p->ev_busy.size(); g += 5) {
         CK(cudaEventSynchronize(p->ev_busy[g + 4]));
@@ -1316,7 +1538,7 @@ const char *rct_kernel_timing_name(int id) { return (id >= 0 && id < RCT_TK_COUN
 int rct_plan_kernel_timing(rct_plan *p, double *ms, long long *groups, int reset)
 {
     if (!p) return fail(RCT_ERR_ARG, "null plan");
-    CK(cudaSetDevice(p->device));
+    DeviceGuard guard(p->device);
     for (size_t i = 0; i < p->kev.size(); ++i) {
         if (p->kev_id[i] == RCT_TK_BEGIN) {
             ++p->kernel_groups;
@@ -1344,7 +1566,7 @@ int rct_plan_kernel_timing(rct_plan *p, double *ms, long long *groups, int reset
 int rct_plan_info(rct_plan *p, int slot, rct_frame_info *info)
 {
     if (!p || !info || slot < 0 || slot >= p->slots) return fail(RCT_ERR_ARG, "bad info request");
-    CK(cudaSetDevice(p->device));
+    DeviceGuard guard(p->device);
     CK(cudaDeviceSynchronize());
     FrameCtrl *h = new (std::nothrow) FrameCtrl;
     if (!h) return fail(RCT_ERR_NOMEM, "out of host memory");
@@ -1364,7 +1586,7 @@ int rct_plan_info(rct_plan *p, int slot, rct_frame_info *info)
 int rct_plan_debug_hist(rct_plan *p, int slot, uint32_t *ht, uint32_t *hs)
 {
     if (!p || slot < 0 || slot >= p->slots) return fail(RCT_ERR_ARG, "bad slot");
-    CK(cudaSetDevice(p->device));
+    DeviceGuard guard(p->device);
     CK(cudaDeviceSynchronize());
     unsigned *h = p->hist + (size_t)slot * p->L.hist_stride_u32;
     if (!p->cube_dirty) {  // partition front end: the cube is all zero; rebuild it from the colour lists
@@ -1418,7 +1640,7 @@ int rct_plan_debug_target(rct_plan *p, int slot, uint32_t *colour, double *key, 
 int rct_plan_debug_lut(rct_plan *p, int slot, uint32_t *lut_host)
 {
     if (!p || !lut_host || slot < 0 || slot >= p->slots) return fail(RCT_ERR_ARG, "bad slot");
-    CK(cudaSetDevice(p->device));
+    DeviceGuard guard(p->device);
     CK(cudaDeviceSynchronize());
     CK(cudaMemcpy(lut_host, p->lut + (size_t)slot * p->L.lut_stride_u32, 4 * (size_t)kCube, cudaMemcpyDeviceToHost));
     if (p->lut_mode) {  // expand run index + palette to the uint32 RGB per colour the caller expects

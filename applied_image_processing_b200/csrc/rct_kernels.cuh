@@ -686,6 +686,7 @@ __global__ void __launch_bounds__(256) k_coarse_hist(const Job *jobs)
 #include "rct_front.cuh"
 #include "rct_apply.cuh"
 #include "rct_sort.cuh"
+#include "rct_binned.cuh"
 #include "rct_adjacent.cuh"
 #include "rct_video.cuh"
 

@@ -137,6 +137,69 @@ class ShardedTransfer:
         self._timed = timed
         return out_band
 
+    # ---- binned mode: the only cross-GPU state is 56 integers, 4 doubles and 2 x bins counters ----------
+    def _xchg(self, which, bins):
+        L = _cabi.lib()
+        ptr = L.rct_plan_xchg_ptr(self.plan.handle)
+        nbytes = L.rct_plan_xchg_bytes(which, bins)
+        n, typestr = {0: (nbytes // 8, "<i8"), 1: (nbytes // 8, "<f8"), 2: (nbytes // 4, "<i4")}[which]
+
+        class _Buf:
+            __cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 3}
+
+        return torch.as_tensor(_Buf(), device=self.plan.device)
+
+    def _allreduce_small(self, t, op):
+        if self.world == 1:
+            return
+        if self._via_host:
+            h = t.cpu()
+            dist.all_reduce(h, op=op, group=self.group)
+            t.copy_(h)
+        else:
+            dist.all_reduce(t, op=op, group=self.group)
+
+    def binned(self, content_band, stylised_band, mask_band, out_band=None, bins=1024, mode=MODE_MASK, label=0,
+               timed=False):
+        """Row-sharded BINNED transfer (``rct_shard_binned_phase_async``): three tiny all-reduces (exact integer
+        moments, key ranges, key histograms) instead of the 128 MiB colour cubes, no redundant solve -- every rank
+        builds the LUT of its own band's colours only.  Same band conventions as ``__call__``.  An approximation of
+        the exact path (see ``regional_color_transfer_binned``), bit-identical for any number of ranks."""
+        L = _cabi.lib()
+        W, sw = self.W, self.sw
+        if out_band is None:
+            out_band = torch.empty_like(content_band)
+        c_ptr = content_band.data_ptr() - self.row0 * W * 3
+        m_ptr = mask_band.data_ptr() - self.row0 * W
+        o_ptr = out_band.data_ptr() - self.row0 * W * 3
+        s_ptr = stylised_band.data_ptr() - self.s0 * sw * 3
+        st = torch.cuda.current_stream()
+        sp = st.cuda_stream
+        ops = (dist.ReduceOp.SUM, dist.ReduceOp.MAX, dist.ReduceOp.SUM)
+        if not hasattr(self, "_evb"):
+            self._evb = [torch.cuda.Event(enable_timing=True) for _ in range(8)]
+        ev = self._evb
+        with torch.cuda.device(self.device), self.plan.lock:
+            for phase in range(4):
+                if timed:
+                    ev[2 * phase].record(st)
+                check(L.rct_shard_binned_phase_async(self.plan.handle, phase, c_ptr, s_ptr, m_ptr, o_ptr, mode, label,
+                                                     self.row0, self.rows, int(bins), sp))
+                if timed:
+                    ev[2 * phase + 1].record(st)
+                if phase < 3:
+                    self._allreduce_small(self._xchg(phase, bins), ops[phase])
+        return out_band
+
+    def binned_phase_ms(self):
+        """Device time of the last timed binned call: compute of the four phases and the three exchanges (ms)."""
+        ev = self._evb
+        ev[7].synchronize()
+        comp = [ev[2 * k].elapsed_time(ev[2 * k + 1]) for k in range(4)]
+        comm = [ev[2 * k + 1].elapsed_time(ev[2 * k + 2]) for k in range(3)]
+        return {"front_moments_ms": comp[0], "keys_ms": comp[1], "hist_ms": comp[2], "match_apply_ms": comp[3],
+                "allreduce_ms": sum(comm)}
+
     def phase_ms(self):
         """Device time of the last timed call: hist / all-reduce / solve / apply (ms)."""
         self._ev[4].synchronize()
@@ -150,10 +213,10 @@ class ShardedTransfer:
         return int(s[0])
 
 
-def regional_color_transfer_sharded(content, stylized, background_mask, group=None):
+def regional_color_transfer_sharded(content, stylized, background_mask, group=None, bins=0):
     """Convenience wrapper for callers that hold the FULL numpy images on every rank: slices
     this rank's band, runs the sharded protocol and returns this rank's output rows
-    (numpy, [rows, W, 3]) together with (row0, rows)."""
+    (numpy, [rows, W, 3]) together with (row0, rows).  bins > 0 selects the binned mode."""
     content = np.ascontiguousarray(content, np.uint8)
     stylized = np.ascontiguousarray(stylized, np.uint8)
     mask = np.ascontiguousarray(background_mask, np.uint8)
@@ -162,8 +225,9 @@ def regional_color_transfer_sharded(content, stylized, background_mask, group=No
     dev = torch.device("cuda", torch.cuda.current_device())
     t = ShardedTransfer(H, W, sh, sw, dev, group)
     r0, r1 = t.row0, t.row0 + t.rows
-    out = t(torch.from_numpy(content[r0:r1]).to(dev), torch.from_numpy(stylized[t.s0:t.s1]).to(dev),
+    args = (torch.from_numpy(content[r0:r1]).to(dev), torch.from_numpy(stylized[t.s0:t.s1]).to(dev),
             torch.from_numpy(mask[r0:r1]).to(dev))
+    out = t.binned(*args, bins=bins) if bins else t(*args)
     st = t.status()
     lst._warn(st)
     return out.cpu().numpy(), (t.row0, t.rows)

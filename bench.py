@@ -77,6 +77,10 @@ def parse_args():
     ap.add_argument("--sty-short", type=int, default=0,
                     help="stylised frames at this short-side size (512 = what AdaIN's Resize(512) hands the reference, "
                          "LST:223-230), NEAREST-resampled inside the kernels; 0 = same size as the content")
+    ap.add_argument("--bins", type=int, default=0,
+                    help="0 (default): the reference's exact CDF matching (the parity path); > 0: the BINNED approximation with "
+                         "this many histogram bins (BASELINE.json configs[4] '1024-bin histograms'; reported separately, never "
+                         "the headline).  Workloads 4k / 1080p / 16k")
     ap.add_argument("--e2e-slots", type=int, default=0, help="frames per copy/compute group of the host entry point (0 = its default)")
     ap.add_argument("--stage-sets", type=int, default=0, help="RCT_OPT_STAGE_SETS of the host entry point (0 = default)")
     ap.add_argument("--front", type=int, default=1, choices=[0, 1],
@@ -95,6 +99,11 @@ def parse_args():
 
 
 def workload_name(a):
+    if a.bins:
+        a_bins, a.bins = a.bins, 0
+        name = workload_name(a)
+        a.bins = a_bins
+        return name + f"; BINNED APPROXIMATION, {a_bins}-bin key histograms + CDF inverse lookup instead of the exact match_cdf"
     if a.workload == "16k":
         return (f"one {a.width}x{a.height} synthetic content/stylised pair, binary fg/bg ellipse mask (40% fg), image "
                 f"family {a.kind}, row-sharded over the ranks with an all-reduce of the colour histograms "
@@ -163,7 +172,7 @@ def host_threads():
         return os.cpu_count() or 1
 
 
-def cpu_pass(frames, threads, labels=False, keep=False):
+def cpu_pass(frames, threads, labels=False, keep=False, bins=0):
     """Run every frame through the oracle, `threads` at a time (ctypes releases the GIL).
     keep=True: returns (seconds, outputs) so the GPU arm can assert parity on the same frames."""
     from concurrent.futures import ThreadPoolExecutor
@@ -179,7 +188,7 @@ def cpu_pass(frames, threads, labels=False, keep=False):
             for lab in range(8):
                 orc.transfer(cs[i], ss[i], ms[i], mode=orc.MODE_LABEL, label=lab, out=out)
             return out if keep else None
-        out = orc.transfer(cs[i], ss[i], ms[i])[0]
+        out = (orc.transfer_binned(cs[i], ss[i], ms[i], bins) if bins else orc.transfer(cs[i], ss[i], ms[i]))[0]
         return out if keep else None
 
     t0 = time.perf_counter()
@@ -207,8 +216,8 @@ def run_reference_arm(a):
     frames = make_frames(a, n, 1000)
     labels = a.workload == "labels"
     for _ in range(a.warmup):
-        cpu_pass(frames, threads, labels)
-    times = [cpu_pass(frames, threads, labels) for _ in range(a.steps)]
+        cpu_pass(frames, threads, labels, bins=a.bins)
+    times = [cpu_pass(frames, threads, labels, bins=a.bins) for _ in range(a.steps)]
     mp = n * a.height * a.width / 1e6
     band_note = f" (each a {a.height}-row band of the {full_h}-row image)" if a.workload == "16k" else ""
     a.height = full_h
@@ -360,6 +369,11 @@ def run_gpu_arm(a):
                                                  dm.data_ptr(), H * W, do.data_ptr(), H * W * 3, n,
                                                  _cabi.MODE_LABEL, lab, st))
             return
+        if a.bins:
+            _cabi.check(L.rct_transfer_binned_async(plan.handle, dc.data_ptr(), H * W * 3, ds.data_ptr(), sh * sw * 3,
+                                                    dm.data_ptr(), H * W, do.data_ptr(), H * W * 3, n, _cabi.MODE_MASK, 0,
+                                                    a.bins, st))
+            return
         _cabi.check(L.rct_transfer_async(plan.handle, dc.data_ptr(), H * W * 3, ds.data_ptr(), sh * sw * 3,
                                          dm.data_ptr(), H * W, do.data_ptr(), H * W * 3, n, _cabi.MODE_MASK, 0, st))
 
@@ -450,6 +464,8 @@ def run_gpu_arm(a):
         def api_call():
             if labels:
                 hon[...] = aip.regional_color_transfer_labels(hcn, hsn, hmn, 8, slots=e2e_slots, fused=bool(a.labels_fused))
+            elif a.bins:
+                aip.regional_color_transfer_binned(hcn, hsn, hmn, a.bins, out=hon)
             else:
                 aip.regional_color_transfer(hcn, hsn, hmn, out=hon, slots=e2e_slots)
 
@@ -468,7 +484,7 @@ def run_gpu_arm(a):
         assert np.array_equal(hon, do.cpu().numpy()), "host path and device path disagree"
         # the same call with plain (pageable) numpy arrays: what the reference's caller holds
         # (np.array(Image.open(...)), LST:200-219); the driver stages such copies itself
-        if not labels:
+        if not labels and not a.bins:
             pc, ps, pm, po = cs, ss, ms, np.empty_like(cs)
 
             def api_call_pageable():
@@ -494,7 +510,7 @@ def run_gpu_arm(a):
         nc, threads = cpu_sample_size(a)
         nc = min(nc, n)
         threads = min(threads, nc)
-        t, cpu_outs = cpu_pass((cs[:nc], ss[:nc], ms[:nc]), threads, labels, keep=True)
+        t, cpu_outs = cpu_pass((cs[:nc], ss[:nc], ms[:nc]), threads, labels, keep=True, bins=a.bins)
         cpu = {"value": nc * H * W / 1e6 / t, "unit": UNIT, "cores": threads, "kind": "port",
                "sample": f"{nc} frame(s) of the step's batch, {threads} thread(s), one pass ({t:.1f} s)"}
         # parity at the benchmarked size: the GPU output of the same frames equals the oracle's byte for byte
@@ -536,18 +552,21 @@ def run_gpu_16k(a, torch, dist, world, rank, local, dev, barrier, max_over_ranks
     ho = torch.empty_like(hc).pin_memory()
     dc, ds, dm = hc.to(dev), hs.to(dev), hm.to(dev)
     do = torch.empty_like(dc)
+    run = (lambda timed=False: tr.binned(dc, ds, dm, do, bins=a.bins, timed=timed)) if a.bins else (
+        lambda timed=False: tr(dc, ds, dm, do, timed=timed))
     for _ in range(max(a.warmup, 3)):
-        tr(dc, ds, dm, do)
+        run()
     barrier()
     sampler = ClockSampler(local)
     L.rct_launch_count(1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    acc = {"hist_ms": 0.0, "allreduce_ms": 0.0, "solve_ms": 0.0, "apply_ms": 0.0}
+    acc = ({"front_moments_ms": 0.0, "keys_ms": 0.0, "hist_ms": 0.0, "match_apply_ms": 0.0, "allreduce_ms": 0.0} if a.bins
+           else {"hist_ms": 0.0, "allreduce_ms": 0.0, "solve_ms": 0.0, "apply_ms": 0.0})
     sampler.start()
     e0.record()
     for _ in range(a.steps):
-        tr(dc, ds, dm, do, timed=True)
-        for k, v in tr.phase_ms().items():  # syncs this step's last event: steps are serial anyway
+        run(timed=True)
+        for k, v in (tr.binned_phase_ms() if a.bins else tr.phase_ms()).items():  # syncs this step's last event
             acc[k] += v
     e1.record()
     barrier()
@@ -560,14 +579,23 @@ def run_gpu_16k(a, torch, dist, world, rank, local, dev, barrier, max_over_ranks
     phases = {k: max_over_ranks(v / a.steps) for k, v in acc.items()}
     peak, peak_src = peaks()
     npix_rank = (H + world - 1) // world * W
-    kern = {
-        "k_hist": {"ms_per_launch": phases["hist_ms"], "alg_bytes_per_pixel": 7.0,
-                   "achieved_GBps": 7.0 * npix_rank / 1e9 / (phases["hist_ms"] * 1e-3)},
-        "k_apply": {"ms_per_launch": phases["apply_ms"], "alg_bytes_per_pixel": 10.0,
-                    "achieved_GBps": 10.0 * npix_rank / 1e9 / (phases["apply_ms"] * 1e-3)},
-    }
+    if a.bins:  # phase 0 = front end + moments (7 B/px), phase 3 = LUT build + apply (10 B/px)
+        kern = {
+            "front+moments": {"ms_per_launch": phases["front_moments_ms"], "alg_bytes_per_pixel": 7.0,
+                              "achieved_GBps": 7.0 * npix_rank / 1e9 / (phases["front_moments_ms"] * 1e-3)},
+            "match+apply": {"ms_per_launch": phases["match_apply_ms"], "alg_bytes_per_pixel": 10.0,
+                            "achieved_GBps": 10.0 * npix_rank / 1e9 / (phases["match_apply_ms"] * 1e-3)},
+        }
+    else:
+        kern = {
+            "k_hist": {"ms_per_launch": phases["hist_ms"], "alg_bytes_per_pixel": 7.0,
+                       "achieved_GBps": 7.0 * npix_rank / 1e9 / (phases["hist_ms"] * 1e-3)},
+            "k_apply": {"ms_per_launch": phases["apply_ms"], "alg_bytes_per_pixel": 10.0,
+                        "achieved_GBps": 10.0 * npix_rank / 1e9 / (phases["apply_ms"] * 1e-3)},
+        }
     dom = max(kern, key=lambda k: kern[k]["ms_per_launch"])
-    hist_bytes = int(L.rct_plan_hist_bytes(tr.plan.handle))
+    hist_bytes = (sum(int(L.rct_plan_xchg_bytes(w, a.bins)) for w in range(3)) if a.bins
+                  else int(L.rct_plan_hist_bytes(tr.plan.handle)))
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_GBps"], "peak": peak, "unit": "GB/s",
         "frac": kern[dom]["achieved_GBps"] / peak, "traffic": None, "peak_source": peak_src, "kernels": kern,
@@ -582,7 +610,7 @@ def run_gpu_16k(a, torch, dist, world, rank, local, dev, barrier, max_over_ranks
             dc.copy_(hc, non_blocking=True)
             ds.copy_(hs, non_blocking=True)
             dm.copy_(hm, non_blocking=True)
-            tr(dc, ds, dm, do)
+            run()
             ho.copy_(do, non_blocking=True)
             torch.cuda.synchronize()
 
@@ -603,7 +631,7 @@ def run_gpu_16k(a, torch, dist, world, rank, local, dev, barrier, max_over_ranks
         cs = np.stack([hc.numpy()[i * hb:(i + 1) * hb] for i in range(threads)])
         ss = np.stack([hs.numpy()[i * hb:(i + 1) * hb] for i in range(threads)])
         ms_ = np.stack([hm.numpy()[i * hb:(i + 1) * hb] for i in range(threads)])
-        t = cpu_pass((cs, ss, ms_), threads)
+        t = cpu_pass((cs, ss, ms_), threads, bins=a.bins)
         cpu = {"value": threads * hb * W / 1e6 / t, "unit": UNIT, "cores": threads, "kind": "port",
                "sample": f"{threads} bands of {hb} rows of the image, one per thread, one pass ({t:.1f} s)"}
     if rank == 0:

@@ -172,6 +172,35 @@ int rct_shard_apply_async(rct_plan *plan, const uint8_t *content, const uint8_t 
                           const uint8_t *mask, uint8_t *out, int mode, int label, int row0,
                           int rows, void *stream);
 
+/* ---- BINNED mode: B-bin key histograms + CDF build / inverse lookup (BASELINE.json configs[4] "1024-bin
+ * histograms"; north_star subsystems 2-3) ---------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: match_cdf (LST:99-125) is exact and sort-based, and rct_transfer_async reproduces
+ * it exactly.  This mode replaces only that step by classic histogram matching (equal-width bins over the region's
+ * key range, in-bin rank lerp, inverse lookup in the source CDF; definition in csrc/rct_binned.cuh and
+ * oracle/rct_oracle.c:orc_match_binned); everything else (a-1..a-5, a-7..a-9) is the exact path's arithmetic.  It is an
+ * APPROXIMATION (measured: within 1 uint8 LSB of the exact result on all but isolated tail pixels, max 3; 0.5-5 % of the pixels differ), bit-exact against its own
+ * oracle, never the parity path.  2 <= bins <= 4096.  Same arguments as rct_transfer_async otherwise. */
+int rct_transfer_binned_async(rct_plan *plan, const uint8_t *content, size_t content_stride, const uint8_t *stylised,
+                              size_t stylised_stride, const uint8_t *mask, size_t mask_stride, uint8_t *out,
+                              size_t out_stride, int n_frames, int mode, int label, int bins, void *stream);
+/* Row-sharded binned path ("the binned approximate mode ... two tiny all-reduces"): the only cross-GPU
+ * state is the exchange buffer rct_plan_xchg_ptr(), which the caller all-reduces between the phases:
+ *   phase 0: band -> colour lists -> exact integer moments     then SUM  over int64  [56]       (which = 0)
+ *   phase 1: PCA from the global moments -> keys -> key range  then MAX  over double [4]        (which = 1)
+ *   phase 2: histograms over the global range                  then SUM  over uint32 [2*bins]   (which = 2)
+ *   phase 3: CDFs -> LUT of the band's colours -> the band's rows of `out`
+ * Integer sums and float max are order-independent: the result is bit-identical for any number of ranks. */
+int rct_shard_binned_phase_async(rct_plan *plan, int phase, const uint8_t *content, const uint8_t *stylised,
+                                 const uint8_t *mask, uint8_t *out, int mode, int label, int row0, int rows, int bins,
+                                 void *stream);
+void *rct_plan_xchg_ptr(rct_plan *plan);
+size_t rct_plan_xchg_bytes(int which, int bins);
+/* introspection for the parity tests: histograms [bins], key ranges (lo_t hi_t lo_s hi_s) and, for plans created with
+ * RCT_FLAG_DEBUG, per entry of the target colour list its colour, CDF index pair b * 65536 + b' and matched value
+ * (arrays of rct_frame_info.d_target entries; any pointer may be NULL) */
+int rct_plan_debug_binned(rct_plan *plan, int slot, int bins, uint32_t *hist_t, uint32_t *hist_s, double *range4,
+                          uint32_t *colour, int64_t *code, double *matched);
+
 /* ---- the reference's individual functions ------------------------------------------------ */
 /* rgb_to_lab_pixels / rgb_to_lab_image (LST:67-77, 22-40): uint8 [n,3] -> float64 [n,3] */
 int rct_rgb_to_lab(const uint8_t *rgb, double *lab, size_t n, void *stream);

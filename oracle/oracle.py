@@ -57,6 +57,7 @@ def lib():
         _LIB.orc_pow10.restype = C.c_double
         _LIB.orc_pow10.argtypes = [C.c_double]
         _LIB.orc_transfer.restype = C.c_int
+        _LIB.orc_transfer_binned.restype = C.c_int
         _LIB.orc_match_cdf.restype = C.c_int
         _LIB.orc_apply_pca.restype = C.c_int
         m = reference_matrices()
@@ -116,6 +117,18 @@ def transfer(content, stylised, mask=None, mode=MODE_MASK, label=0, out=None, de
     """Run the oracle pipeline.  Returns (out, status, info dict)."""
     content = np.ascontiguousarray(content, np.uint8)
     stylised = np.ascontiguousarray(stylised, np.uint8)
+    if mode == MODE_ALL and mask is None and content.shape[:2] != stylised.shape[:2] and out is None and not debug:
+        # color_transfer_foreground(fg, bg) with different shapes (LST:134-139): the reference gathers
+        # all non-black pixels of each image and never resizes.  Black pixels are excluded from everything,
+        # so padding both pixel lists with black to one length restates exactly that.
+        nf, nb = content.shape[0] * content.shape[1], stylised.shape[0] * stylised.shape[1]
+        n = max(nf, nb)
+        f = np.zeros((1, n, 3), np.uint8)
+        b = np.zeros((1, n, 3), np.uint8)
+        f[0, :nf] = content.reshape(nf, 3)
+        b[0, :nb] = stylised.reshape(nb, 3)
+        o, st, d = transfer(f, b, None, mode=MODE_ALL)
+        return np.ascontiguousarray(o[0, :nf].reshape(content.shape)), st, d
     H, W = content.shape[:2]
     sh, sw = stylised.shape[:2]
     if mask is not None:
@@ -139,6 +152,41 @@ def transfer(content, stylised, mask=None, mode=MODE_MASK, label=0, out=None, de
         C.c_int(mode), C.c_int(label), _p(out), C.byref(info),
         _p(d.get("key")), _p(d.get("j")), _p(d.get("matched")), _p(d.get("hist_t")),
         _p(d.get("hist_s")), _p(d.get("rgbf")),
+    )
+    d.update(
+        n_t=info.n_t, n_s=info.n_s,
+        t_mean=np.array(info.t_mean), t_comp=np.array(info.t_comp),
+        s_mean=np.array(info.s_mean), s_comp=np.array(info.s_comp),
+    )
+    return out, st, d
+
+
+def transfer_binned(content, stylised, mask=None, bins=1024, mode=MODE_MASK, label=0, out=None, debug=False):
+    """The pipeline with the BINNED CDF match (orc_match_binned in rct_oracle.c): an approximation
+    with no counterpart in the reference, whose definition this oracle and the CUDA path share.
+    Returns (out, status, info); debug adds key / code (= b * 65536 + b') / matched per pixel and
+    the two `bins`-bin histograms + key ranges."""
+    content = np.ascontiguousarray(content, np.uint8)
+    stylised = np.ascontiguousarray(stylised, np.uint8)
+    H, W = content.shape[:2]
+    sh, sw = stylised.shape[:2]
+    if mask is not None:
+        mask = np.ascontiguousarray(mask, np.uint8)
+        assert mask.shape == (H, W)
+    elif mode != MODE_ALL:
+        raise ValueError("mask required")
+    if out is None:
+        out = np.zeros((H, W, 3), np.uint8)
+    info = _Info()
+    d = {"hist_t": np.zeros(bins, np.uint32), "hist_s": np.zeros(bins, np.uint32), "range": np.zeros(4, np.float64)}
+    if debug:
+        d["key"] = np.empty((H, W), np.float64)
+        d["code"] = np.empty((H, W), np.int64)
+        d["matched"] = np.empty((H, W), np.float64)
+    st = lib().orc_transfer_binned(
+        _p(content), C.c_int(H), C.c_int(W), _p(stylised), C.c_int(sh), C.c_int(sw), _p(mask),
+        C.c_int(mode), C.c_int(label), C.c_int(bins), _p(out), C.byref(info),
+        _p(d.get("key")), _p(d.get("code")), _p(d.get("matched")), _p(d["hist_t"]), _p(d["hist_s"]), _p(d["range"]),
     )
     d.update(
         n_t=info.n_t, n_s=info.n_s,

@@ -72,3 +72,20 @@ def load_config1():
            for k in ("brad_pitt_jpg", "brushstrokes_jpg", "cat_jpg")}
     return [(tag, np.ascontiguousarray(c), np.ascontiguousarray(s), m, g[f"{tag}_combined"])
             for tag, c, s, m in config1_cases(dec)], g
+
+
+# color_transfer_foreground with fg.shape != bg.shape: tag -> (fg H, fg W, bg H, bg W, fg kind, bg kind)
+CTF_SHAPE_CASES = {
+    "bg_smaller": (40, 50, 23, 31, "U", "N"),
+    "bg_larger": (20, 30, 64, 48, "N", "U"),
+    "same_count_other_shape": (24, 36, 36, 24, "U", "U"),
+    "bg_much_larger": (17, 19, 200, 320, "N", "N"),
+}
+
+
+def ctf_inputs(fh, fw, bh, bw, fk, bk):
+    return synth.synth_image(fh, fw, 41, fk, 0.05), synth.synth_image(bh, bw, 42, bk, 0.02)
+
+
+def load_ctf_shapes():
+    return dict(np.load(os.path.join(GOLDEN_DIR, "ctf_shapes.npz"), allow_pickle=False))

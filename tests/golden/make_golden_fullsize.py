@@ -127,6 +127,16 @@ def main():
         arrays[f"{tag}_combined"] = comb
         arrays[f"{tag}_oracle_bytes_differing"] = np.int64(nd)
     np.savez_compressed(os.path.join(HERE, "config1.npz"), **arrays)
+
+    # ---- color_transfer_foreground(fg, bg) with fg.shape != bg.shape: the reference gathers all
+    # non-black pixels of both images and never resizes (LST:134-139)
+    shapes = {}
+    for tag, (fh, fw, bh, bw, fk, bk) in fullsize.CTF_SHAPE_CASES.items():
+        fg, bg = fullsize.ctf_inputs(fh, fw, bh, bw, fk, bk)
+        shapes[tag] = lst.color_transfer_foreground(fg, bg)
+        o, st, _ = orc.transfer(fg, bg, None, mode=orc.MODE_ALL)
+        print("ctf", tag, fg.shape, bg.shape, "oracle diff bytes", int((o != shapes[tag]).sum()))
+    np.savez_compressed(os.path.join(HERE, "ctf_shapes.npz"), **shapes)
     print("full-size fixtures written")
 
 

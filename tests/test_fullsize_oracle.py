@@ -47,3 +47,12 @@ def test_oracle_config1_literal():
         out, st, _ = orc.transfer(c, s, mask)
         assert st == 0
         assert np.array_equal(out, combined), f"config 1 ({tag}): {(out != combined).sum()} bytes differ from the reference"
+
+
+@pytest.mark.parametrize("tag", list(fullsize.CTF_SHAPE_CASES))
+def test_color_transfer_foreground_with_different_shapes(tag):
+    """LST:128-168 called with fg.shape != bg.shape: all non-black pixels of each image, no resize."""
+    fg, bg = fullsize.ctf_inputs(*fullsize.CTF_SHAPE_CASES[tag])
+    want = fullsize.load_ctf_shapes()[tag]
+    out, st, _ = orc.transfer(fg, bg, None, mode=orc.MODE_ALL)
+    assert st == 0 and out.shape == fg.shape and np.array_equal(out, want)

@@ -141,3 +141,56 @@ def test_16k_row_sharded_three_way_vs_oracle():
         for k in ("t_mean", "t_comp", "s_mean", "s_comp"):
             assert np.array_equal(info[k], d[k]), k
         assert np.array_equal(got, ref), f"{(got != ref).sum()} bytes differ from the oracle"
+
+
+@pytest.mark.parametrize("tag", list(fullsize.CTF_SHAPE_CASES))
+def test_color_transfer_foreground_with_different_shapes(tag):
+    """fg.shape != bg.shape must use ALL non-black bg pixels (the reference never resizes here)."""
+    fg, bg = fullsize.ctf_inputs(*fullsize.CTF_SHAPE_CASES[tag])
+    want = fullsize.load_ctf_shapes()[tag]
+    out = aip.color_transfer_foreground(fg, bg)
+    assert out.shape == fg.shape and np.array_equal(out, want), int((out != want).sum())
+    out_t = aip.color_transfer_foreground(torch.from_numpy(fg).cuda(), torch.from_numpy(bg).cuda())
+    assert np.array_equal(out_t.cpu().numpy(), want)
+
+
+def test_one_plan_used_from_two_streams_and_the_host_entry():
+    """a cached plan's workspace is shared; calls enqueued from different streams (and the host
+    entry point's own stream) must be ordered by the library, not corrupt each other."""
+    H, W = 540, 960
+    frames = [(synth.synth_image(H, W, 50 + i, "U"), synth.synth_image(H, W, 60 + i, "N"), synth.ellipse_mask(H, W, 0.3 + 0.1 * i, i))
+              for i in range(4)]
+    refs = [orc.transfer(*f)[0] for f in frames]
+    dev = [tuple(torch.from_numpy(x).cuda() for x in f) for f in frames]
+    streams = [torch.cuda.Stream() for _ in range(2)]
+    torch.cuda.synchronize()
+    outs = [None] * 4
+    for rep in range(3):
+        for i in range(4):
+            with torch.cuda.stream(streams[i % 2]):
+                outs[i] = aip.regional_color_transfer(*dev[i], slots=1)    # same geometry -> same cached plan
+        host = aip.regional_color_transfer(*frames[rep], slots=1)          # numpy path on the plan's own stream
+        torch.cuda.synchronize()
+        for i in range(4):
+            assert np.array_equal(outs[i].cpu().numpy(), refs[i]), (rep, i)
+        assert np.array_equal(host, refs[rep])
+
+
+def test_plan_cache_is_bounded_and_status_reaches_the_tensor_path(capsys):
+    old = lst.PLAN_CACHE_BYTES
+    lst.clear_plans()
+    try:
+        lst.PLAN_CACHE_BYTES = 1 << 30
+        for k in range(12):                                                # 12 geometries, ~0.2 GB each
+            H, W = 64 + 8 * k, 96
+            c, s = synth.synth_image(H, W, k, "U"), synth.synth_image(H, W, k + 1, "U")
+            aip.regional_color_transfer(c, s, synth.ellipse_mask(H, W, 0.4, k))
+            assert lst.cached_plan_bytes() <= (1 << 30) + (1 << 28)
+    finally:
+        lst.PLAN_CACHE_BYTES = old
+        lst.clear_plans()
+    H, W = 48, 64
+    c, s = torch.from_numpy(synth.synth_image(H, W, 1, "U")).cuda(), torch.from_numpy(synth.synth_image(H, W, 2, "U")).cuda()
+    out, status = aip.regional_color_transfer(c, s, torch.ones((H, W), dtype=torch.uint8, device="cuda"), return_status=True)
+    assert status.tolist() == [1] and "No foreground pixels" in capsys.readouterr().out
+    assert torch.equal(out, s)
