@@ -20,7 +20,8 @@ OPT_APPLY = 4
 OPT_MATCH = 5
 OPT_STAGE_SETS = 6
 OPT_LUT = 7
-TK_COUNT = 19
+OPT_KEYTAB = 8
+TK_COUNT = 20
 
 _lib = None
 _lock = threading.Lock()
@@ -89,6 +90,7 @@ SIGNATURES = {
     "rct_plan_debug_hist": (_i, [_vp, _i, _vp, _vp]),
     "rct_plan_debug_target": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp]),
     "rct_plan_debug_lut": (_i, [_vp, _i, _vp]),
+    "rct_plan_debug_keytab": (_i, [_vp, _i, _vp, _vp]),
     "rct_launch_count": (C.c_longlong, [_i]),
 }
 

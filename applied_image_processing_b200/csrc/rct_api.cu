@@ -122,6 +122,7 @@ struct Layout {
     size_t off_zero, zero_bytes, z_fcnt, z_pfill;  // [slots][2] blocks zeroed before every sort
     size_t off_dbg_m, off_dbg_j, dbg_stride;
     size_t off_xchg;  // exchange buffer of the row-sharded binned path (kXchgBytes)
+    size_t off_kt;    // [slots] key tables (rct_keytab.cuh)
     size_t total;
 };
 
@@ -173,6 +174,7 @@ Layout make_layout(int H, int W, int slots, unsigned flags)
         L.off_dbg_j = o; o = align_up(o + 8 * L.cap * slots);
     }
     L.off_xchg = o; o = align_up(o + kXchgBytes);
+    L.off_kt = o; o = align_up(o + kKtBytes * (size_t)slots);
     L.total = o;
     return L;
 }
@@ -216,6 +218,8 @@ struct rct_plan {
     bool ev_last_valid;
     int lpf;         // labels per frame of the call in progress (rct_transfer_labels_async), else 1
     int lut_mode;    // RCT_OPT_LUT: 1 = uint16 run indices + palette, 0 = uint32 RGB per colour
+    int keytab;      // RCT_OPT_KEYTAB: 1 = key table in front of the colour LUT (rct_keytab.cuh)
+    bool kt_live;    // the tables of the launch group in flight were built (exact path, interleaved match)
     int stage_sets;  // RCT_OPT_STAGE_SETS: staging sets of the host entry point (2..kStageSetsMax)
     // RCT_OPT_TIMING: five events per launch group (memset | k_hist | solve | k_apply)
     int timing;
@@ -305,6 +309,7 @@ int rct_plan_create(int device, int H, int W, int sh, int sw, int slots, unsigne
     p->part_cap = kPartCap;
     p->stage_sets = 4;
     p->lut_mode = 0;
+    p->keytab = 1;
     p->lpf = 1;
     if (workspace) {
         if (workspace_bytes < p->L.total) {
@@ -437,6 +442,7 @@ int rct_plan_set_option(rct_plan *p, int option, int value)
     else if (option == RCT_OPT_MATCH) p->match_interleave = value ? 1 : 0;
     else if (option == RCT_OPT_APPLY) p->apply_tma = (value >= 0 && value <= 8) ? value : 1;
     else if (option == RCT_OPT_LUT) p->lut_mode = value ? 1 : 0;
+    else if (option == RCT_OPT_KEYTAB) p->keytab = value ? 1 : 0;
     else if (option == RCT_OPT_STAGE_SETS) p->stage_sets = value < 2 ? 2 : (value > kStageSetsMax ? kStageSetsMax : value);
     else if (option == RCT_OPT_PART_CAP) p->part_cap = (value > 0 && value <= kPartCap) ? (unsigned)value : (unsigned)kPartCap;
     else return fail(RCT_ERR_ARG, "unknown option %d", option);
@@ -462,6 +468,7 @@ PixArgs pix_args(rct_plan *p, const FrameSet &f, int mode, int label, size_t p_b
     a.ytab = p->resample ? p->ytab : nullptr;
     a.hist = p->hist; a.hist_stride = p->L.hist_stride_u32;
     a.lut = p->lut; a.lut_stride = p->L.lut_stride_u32; a.lut_mode = p->lut_mode;
+    a.kt = p->kt_live ? p->ws + p->L.off_kt : nullptr;
     a.ctrl = p->ctrl; a.status_out = status_out;
     a.W = p->W; a.sw = p->sw; a.sh_dbg = p->sh;
     a.p_begin = p_begin; a.p_end = p_end;
@@ -623,6 +630,7 @@ int phase_front(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
 }
 
 constexpr size_t kSmemFineHist = (size_t)(kFineMax + kCoarse + 1) * 4;
+constexpr size_t kKtSortSmem = (size_t)kKtRunCap * 12;
 constexpr size_t kSmemPartSort = (size_t)kPartCap * 16 + ((size_t)kPartCap + kPartCap / 32 + 2) * 4;  // records + padded counters
 
 int ensure_kernel_attrs()
@@ -697,13 +705,30 @@ int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)
                p->L.lut_stride_u32, p->dbg_m, p->dbg_j, p->L.dbg_stride, p->match_interleave);
     else
         LAUNCH(k_match, dim3((unsigned)p->L.maxparts, nslots), kMatchThreads, st, p->ctrl, p->jobs, p->lut,
-               p->L.lut_stride_u32, p->dbg_m, p->dbg_j, p->L.dbg_stride, p->match_interleave);
+               p->L.lut_stride_u32, p->dbg_m, p->dbg_j, p->L.dbg_stride, p->match_interleave,
+               p->keytab ? p->ws + p->L.off_kt : nullptr);
     if (p->lut_mode) {  // palette LUT: runs of equal output colour along the sorted target -> uint16 indices + palette
         LAUNCH(k_pal_count, dim3((unsigned)p->L.maxparts, nslots), kPalThreads, st, p->ctrl, p->jobs);
         LAUNCH(k_pal_scan, dim3(nslots), 1024, st, p->ctrl, p->jobs);
         LAUNCH(k_pal_write, dim3((unsigned)p->L.maxparts, nslots), kPalThreads, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32);
     }
     KMARK(RCT_TK_MATCH);
+    p->kt_live = false;
+    if (p->keytab && !p->lut_mode) {  // key table: runs -> sorted thresholds + cell directory -> cells
+        static thread_local int attr_dev_kt = -1;
+        int dev = 0;
+        CK(cudaGetDevice(&dev));
+        if (attr_dev_kt != dev) {
+            CK(cudaFuncSetAttribute(k_kt_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKtSortSmem));
+            attr_dev_kt = dev;
+        }
+        k_kt_sort<<<nslots, 1024, kKtSortSmem, st>>>(p->ctrl, p->ws + p->L.off_kt, p->match_interleave);
+        ++t_launches;
+        CK(cudaGetLastError());
+        LAUNCH(k_kt_cells, dim3(64, nslots), 256, st, p->ctrl, p->ws + p->L.off_kt);
+        KMARK(RCT_TK_KEYTAB);
+        p->kt_live = true;
+    }
     return mark(p, st);
 }
 
@@ -728,6 +753,7 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
             CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 3>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8, 3>)));
             CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 2, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8, 2, true>)));
             CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 2, false, 1>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
+            CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 2, false, 2>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
             CK(cudaFuncSetAttribute((k_apply_warp<true, 16, 3>), cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             CK(cudaFuncSetAttribute(k_apply_tma, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             attr_dev = dev;
@@ -762,6 +788,8 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
                 k_apply_warp<true, 8, 4, 3><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8, 3>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
             else if (p->apply_tma == 5)
                 k_apply_warp<true, 8, 5><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
+            else if (b.kt)
+                k_apply_warp<true, 8, 4, 2, false, 2><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
             else
                 k_apply_warp<true, 8, 4><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
         }
@@ -1063,6 +1091,7 @@ int binned_solve(rct_plan *p, int nslots, int bins, cudaStream_t st, int first_p
         KMARK(RCT_TK_FINE_HIST);
     }
     if (first_phase <= 3 && last_phase >= 3) {
+        p->kt_live = false;  // the key table belongs to the exact path
         LAUNCH(k_bin_match, dim3(eb * 2, nslots), 256, st, p->ctrl, p->jobs, p->lut, p->L.lut_stride_u32, bins, p->dbg_m,
                p->dbg_j, p->L.dbg_stride);
         KMARK(RCT_TK_MATCH);
@@ -1532,7 +1561,7 @@ int rct_plan_timing(rct_plan *p, double *ms4, long long *groups, int reset)
 static const char *const kTkNames[RCT_TK_COUNT] = {
     "begin", "memset", "k_front_count", "k_front_scan", "k_front_part", "k_front_hist", "k_hist", "k_compact",
     "k_lab_moments", "k_pca", "k_keys", "k_plan_fine", "k_fine_hist", "k_plan_parts", "k_scatter", "k_part_sort",
-    "k_part_scan", "k_match", "k_apply"};
+    "k_part_scan", "k_match", "k_apply", "k_keytab"};
 const char *rct_kernel_timing_name(int id) { return (id >= 0 && id < RCT_TK_COUNT) ? kTkNames[id] : nullptr; }
 
 int rct_plan_kernel_timing(rct_plan *p, double *ms, long long *groups, int reset)
@@ -1634,6 +1663,39 @@ int rct_plan_debug_target(rct_plan *p, int slot, uint32_t *colour, double *key, 
     }
     if (j) CK(cudaMemcpy(j, p->dbg_j + (size_t)slot * L.dbg_stride, 8 * d, cudaMemcpyDeviceToHost));
     if (matched) CK(cudaMemcpy(matched, p->dbg_m + (size_t)slot * L.dbg_stride, 8 * d, cudaMemcpyDeviceToHost));
+    return RCT_OK;
+}
+
+int rct_plan_debug_keytab(rct_plan *p, int slot, unsigned long long *stats10, double *max_key_err)
+{
+    if (!p || !stats10 || slot < 0 || slot >= p->slots) return fail(RCT_ERR_ARG, "bad slot");
+    DeviceGuard guard(p->device);
+    CK(cudaDeviceSynchronize());
+    memset(stats10, 0, 10 * sizeof(unsigned long long));
+    if (max_key_err) *max_key_err = 0.0;
+    if (!p->kt_live) return RCT_OK;
+    const uint8_t *kt0 = p->ws + p->L.off_kt;
+    KtParams hp;
+    CK(cudaMemcpy(&hp, kt0 + (size_t)slot * kKtBytes, sizeof hp, cudaMemcpyDeviceToHost));
+    stats10[0] = hp.valid;
+    stats10[1] = hp.n_runs;
+    stats10[2] = hp.n_cells;
+    stats10[3] = hp.n_flagged;
+    if (!hp.valid) return RCT_OK;
+    unsigned long long *d_counts = nullptr;
+    CK(cudaMalloc((void **)&d_counts, 8 * sizeof(unsigned long long)));
+    cudaError_t e = cudaMemset(d_counts, 0, 8 * sizeof(unsigned long long));
+    if (e == cudaSuccess) {
+        k_kt_verify<<<p->sm * 4, 256>>>(p->ctrl, p->jobs, kt0, p->lut, p->L.lut_stride_u32, slot, d_counts);
+        if (max_key_err) k_kt_keyerr<<<p->sm * 8, 256>>>(p->ctrl, kt0, slot, reinterpret_cast<double *>(d_counts + 6));
+        e = cudaDeviceSynchronize();
+    }
+    unsigned long long h[8] = {0};
+    if (e == cudaSuccess) e = cudaMemcpy(h, d_counts, sizeof h, cudaMemcpyDeviceToHost);
+    cudaFree(d_counts);
+    if (e != cudaSuccess) return fail(RCT_ERR_CUDA, "key-table check failed: %s", cudaGetErrorString(e));
+    for (int k = 0; k < 6; ++k) stats10[4 + k] = h[k];
+    if (max_key_err) memcpy(max_key_err, &h[6], 8);
     return RCT_OK;
 }
 

@@ -311,9 +311,12 @@ __device__ __forceinline__ void cp_async_wait()
 }
 
 // 8 pixels: 6 words each of content / stylised, 2 words of mask -> 6 output words
+// LUTM: 0 colour -> RGB table, 1 uint16 run index + palette, 2 key table in front of the colour table
+// (rct_keytab.cuh: fp32 key -> cell -> colour, flagged cells fall back to the table)
 template <bool HINT, int LUTM = 0>
 __device__ __forceinline__ void apply8(const uint32_t wc[6], const uint32_t ws[6], const uint32_t wm[2],
-                                       const unsigned *lut, int status, uint32_t wo[6], unsigned long long pol_lut)
+                                       const unsigned *lut, int status, uint32_t wo[6], unsigned long long pol_lut,
+                                       const KtRegs *kr = nullptr, const KtView *kv = nullptr)
 {
     uint32_t c[8], s[8];
 #pragma unroll
@@ -333,7 +336,19 @@ __device__ __forceinline__ void apply8(const uint32_t wc[6], const uint32_t ws[6
         }
     }
     uint32_t t[8];
-    if (LUTM) {  // uint16 run index (L2-resident table), then the palette (L1-resident)
+    if (LUTM == 2) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t[k] = kt_lookup(*kr, *kv, c[k]);
+        // flagged cells: the exact table.  Every lane issues the gather (entry 0 where none is wanted: one
+        // broadcast sector per instruction), a gather inside a divergent branch would serialise on its latency
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const bool fb = ((want >> k) & 1u) && (t[k] & kKtFlag);
+            const unsigned *g = lut + (fb ? c[k] : 0u);
+            const uint32_t v = HINT ? ldg_hint(g, pol_lut) : __ldg(g);
+            if (fb) t[k] = v;
+        }
+    } else if (LUTM) {  // uint16 run index (L2-resident table), then the palette (L1-resident)
         const unsigned short *l16 = reinterpret_cast<const unsigned short *>(lut);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -449,6 +464,10 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
     };
 
     static_assert(BULK || STG == 2, "the cp.async flavour is two-stage");
+    unsigned kt_slot = 0xffffffffu;
+    bool kt_ok = false;
+    KtRegs kr{};
+    KtView kv{};
 #pragma unroll
     for (unsigned i = 0; i + 1 < (unsigned)STG; ++i)
         if (i < cnt) issue(i);
@@ -469,6 +488,12 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
         const bool active = lane * (unsigned)PXL < n;
         const unsigned *lut = a.lut + (size_t)slot * a.lut_stride;
         const int status = a.ctrl[slot].status;
+        if (LUTM == 2 && slot != kt_slot) {  // a new frame: its key-table parameters (warp-uniform)
+            kt_slot = slot;
+            kv = kt_view(a.kt, slot);
+            kt_ok = a.kt != nullptr && __ldg(&kv.par->valid) != 0u;
+            if (kt_ok) kr = kt_load(kv.par);
+        }
         if (PXL == 16) {
             uint32_t wc[12], ws[12], wm[4], wo[12];
             if (active) {
@@ -505,7 +530,7 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
             if (OST) {
                 static_assert(!OST || (BULK && PXL == 8), "bulk-store flavour: bulk loads, 256-pixel tiles");
                 const unsigned ob = i & 1u;
-                if (active) apply8<true, LUTM>(wc, ws, wm, lut, status, wo, pol_lut);
+                if (active) apply8<true, (LUTM == 2 ? 0 : LUTM)>(wc, ws, wm, lut, status, wo, pol_lut);
                 if (lane == 0) bulk_wait_read<1>();  // the store of tile i-2 has read o[ob]
                 __syncwarp();
                 if (active) {
@@ -521,7 +546,8 @@ __global__ void __launch_bounds__(AwCfg<PXL>::kThreads, MINB)
                     bulk_commit();
                 }
             } else if (active) {
-                apply8<BULK, LUTM>(wc, ws, wm, lut, status, wo, pol_lut);  // the cp.async flavour runs without L2 hints (A/B)
+                if (LUTM == 2 && kt_ok) apply8<BULK, 2>(wc, ws, wm, lut, status, wo, pol_lut, &kr, &kv);
+                else apply8<BULK, (LUTM == 2 ? 0 : LUTM)>(wc, ws, wm, lut, status, wo, pol_lut);  // the cp.async flavour runs without L2 hints (A/B)
                 uint8_t *qo = a.out + (size_t)slot * a.out_stride + 3 * p0 + 24u * lane;
                 if (BULK) {
                     stg8_hint(qo, wo[0], wo[1], pol_stream);

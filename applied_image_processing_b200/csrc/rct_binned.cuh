@@ -3,7 +3,7 @@
 // Included by rct_kernels.cuh inside namespace rct.
 //
 // NO COUNTERPART IN THE REFERENCE (match_cdf, LST:99-125, is exact and sort-based): an approximation with its own
-// written-down definition, shared with the oracle (oracle/rct_oracle.c, orc_match_binned) and compared with it
+// written-down definition, shared with the C oracle (orc_match_binned) and compared with it
 // bit for bit (histograms, CDF indices, uint8 output).  Never the parity path.  Its point: the only cross-GPU
 // state of a row-sharded image is 2 x 28 integers (exact moments), 4 doubles (key ranges) and 2 x B counters.
 //

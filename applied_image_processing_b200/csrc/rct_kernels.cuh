@@ -75,7 +75,8 @@ struct FrameCtrl {
     RegionCtrl r[2];
     int status;
     unsigned n_palette;  // runs of equal output colour along the sorted target (palette LUT)
-    int pad_[2];
+    unsigned n_runs;     // run starts k_match recorded for the key table (rct_keytab.cuh)
+    int pad_[1];
     FrontCtrl front;
 };
 
@@ -222,6 +223,7 @@ struct PixArgs {
     const unsigned *lut;   // slot 0; per slot [2^24] uint32 RGB, or (lut_mode 1) [2^24] uint16 run indices + palette
     size_t lut_stride;
     int lut_mode;
+    const uint8_t *kt;     // key tables of the slots (rct_keytab.cuh), or NULL
     FrameCtrl *ctrl;       // [slots]
     int *status_out;       // [slots] or NULL
     int W, sw;
@@ -684,8 +686,10 @@ __global__ void __launch_bounds__(256) k_coarse_hist(const Job *jobs)
 }
 
 #include "rct_front.cuh"
-#include "rct_apply.cuh"
+#include "rct_keytab_layout.cuh"
 #include "rct_sort.cuh"
+#include "rct_keytab.cuh"
+#include "rct_apply.cuh"
 #include "rct_binned.cuh"
 #include "rct_adjacent.cuh"
 #include "rct_video.cuh"

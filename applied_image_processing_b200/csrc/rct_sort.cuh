@@ -814,7 +814,7 @@ constexpr int kMatchThreads = RCT_MATCHT;
 template <int LUTM>
 __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0,
                                                          size_t lut_stride, double *dbg_matched0, long long *dbg_j0,
-                                                         size_t dbg_stride, int interleave)
+                                                         size_t dbg_stride, int interleave, uint8_t *kt0)
 {
     const int slot = blockIdx.y;
     if (ctrl[slot].status != 0) return;
@@ -835,11 +835,7 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
     // search starts from the position interpolated inside the source part.  Otherwise every
     // thread takes one contiguous run of entries and carries its search position along.
     hs.fresh = interleave != 0;
-    const unsigned per = (pe - ps + kMatchThreads - 1) / kMatchThreads;
-    const unsigned first = interleave ? ps + threadIdx.x : ps + threadIdx.x * per;
-    const unsigned step = interleave ? (unsigned)kMatchThreads : 1u;
-    const unsigned last = interleave ? pe : ((first + per < pe) ? first + per : pe);
-    for (unsigned i = first; i < last; i += step) {
+    auto one = [&](unsigned i) -> unsigned {
         long long j;
         double m = match_one(t, s, p, i, ht, hs, j);
         double lab[3];
@@ -848,10 +844,52 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
         // palette LUT: the colour goes to its sorted position (k_pal_* turn the runs of equal colours
         // into indices); otherwise straight into the colour-indexed table
         unsigned *dst = LUTM ? rgb_sorted + i : lut + rec_pay(__ldg(t.rec + i));
-        *dst = lab2rgb(lab, &T, nullptr);
+        const unsigned rgb = lab2rgb(lab, &T, nullptr);
+        *dst = rgb;
         if (dbg_matched0) {
             dbg_matched0[(size_t)slot * dbg_stride + i] = m;
             dbg_j0[(size_t)slot * dbg_stride + i] = j;
+        }
+        return rgb;
+    };
+    if (!interleave) {
+        const unsigned per = (pe - ps + kMatchThreads - 1) / kMatchThreads;
+        const unsigned first = ps + threadIdx.x * per;
+        const unsigned last = (first + per < pe) ? first + per : pe;
+        for (unsigned i = first; i < last; ++i) one(i);
+        return;
+    }
+    // Run starts for the key table (rct_keytab.cuh): wherever the output colour differs from the previous sorted
+    // entry's, (key, colour) is appended to the slot's run list; every part opens a run, so parts are independent.
+    double *run_key = nullptr;
+    unsigned *run_col = nullptr;
+    if (!LUTM && kt0) {
+        uint8_t *blk = kt0 + (size_t)slot * kKtBytes;
+        run_key = reinterpret_cast<double *>(blk + kKtOffRunKey);
+        run_col = reinterpret_cast<unsigned *>(blk + kKtOffRunCol);
+    }
+    __shared__ unsigned s_tail[kMatchThreads / 32];
+    __shared__ unsigned s_carry;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    for (unsigned base = ps; base < pe; base += kMatchThreads) {
+        const unsigned i = base + threadIdx.x;
+        const bool live = i < pe;
+        unsigned rgb = 0xffffffffu;
+        if (live) rgb = one(i);
+        if (run_key) {  // uniform across the CTA
+            unsigned prev = __shfl_up_sync(0xffffffffu, rgb, 1);
+            if (lane == 31) s_tail[warp] = rgb;
+            __syncthreads();
+            if (lane == 0) prev = warp ? s_tail[warp - 1] : (base == ps ? 0xffffffffu : s_carry);
+            if (live && rgb != prev) {
+                const unsigned idx = atomicAdd(&ctrl[slot].n_runs, 1u);
+                if (idx < (unsigned)kKtRunCap) {
+                    run_key[idx] = key_at(t, i);
+                    run_col[idx] = rgb;
+                }
+            }
+            __syncthreads();
+            if (threadIdx.x == kMatchThreads - 1) s_carry = rgb;
         }
     }
 }
@@ -866,16 +904,16 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
 #endif
 __global__ void RCT_MATCH_LB k_match(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0, size_t lut_stride,
                                                          double *dbg_matched0, long long *dbg_j0, size_t dbg_stride,
-                                                         int interleave)
+                                                         int interleave, uint8_t *kt0)
 {
-    match_body<0>(ctrl, jobs, lut0, lut_stride, dbg_matched0, dbg_j0, dbg_stride, interleave);
+    match_body<0>(ctrl, jobs, lut0, lut_stride, dbg_matched0, dbg_j0, dbg_stride, interleave, kt0);
 }
 // palette flavour (RCT_OPT_LUT = 1): output colours go to their sorted position, see k_pal_*
 __global__ void __launch_bounds__(kMatchThreads, 7) k_match_pal(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0,
                                                                 size_t lut_stride, double *dbg_matched0, long long *dbg_j0,
                                                                 size_t dbg_stride, int interleave)
 {
-    match_body<1>(ctrl, jobs, lut0, lut_stride, dbg_matched0, dbg_j0, dbg_stride, interleave);
+    match_body<1>(ctrl, jobs, lut0, lut_stride, dbg_matched0, dbg_j0, dbg_stride, interleave, nullptr);
 }
 
 // generic flavour (rct_match_cdf): jobs[0] = target, jobs[1] = source; payload = input index

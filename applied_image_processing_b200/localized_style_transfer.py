@@ -152,6 +152,17 @@ class Plan:
             out["matched"].ctypes.data if dbg else None))
         return out
 
+    def debug_keytab(self, slot=0, key_error=True) -> dict:
+        """Self-check of the key table of the last launch group (rct_plan_debug_keytab)."""
+        st = (C.c_ulonglong * 10)()
+        err = C.c_double(0.0)
+        check(_cabi.lib().rct_plan_debug_keytab(self.handle, slot, st, C.byref(err) if key_error else None))
+        names = ("valid", "runs", "cells", "flagged_cells", "colours_pure", "colours_wrong", "colours_flagged",
+                 "pixels_pure", "pixels_wrong", "pixels_flagged")
+        out = {k: int(v) for k, v in zip(names, st)}
+        out["max_key_err"] = float(err.value)
+        return out
+
     def debug_lut(self, slot=0):
         lut = np.empty(1 << 24, np.uint32)
         check(_cabi.lib().rct_plan_debug_lut(self.handle, slot, lut.ctypes.data))
@@ -438,8 +449,8 @@ def regional_color_transfer_binned(content, stylized, background_mask, bins=1024
     """The same fused tail with the CDF-matching step (a-6) replaced by ``bins``-bin histogram matching
     (BASELINE.json configs[4] "1024-bin histograms"; ``rct_transfer_binned_async``).  NO COUNTERPART IN
     THE REFERENCE and not the parity path: an approximation of :func:`regional_color_transfer` (measured:
-    within 1 uint8 LSB on all but isolated tail pixels, max 3; 0.5-5 % of the pixels differ) that is bit-exact against its own oracle
-    (``oracle.transfer_binned``).  numpy in -> numpy out, CUDA tensors in -> CUDA tensor out."""
+    within 1 uint8 LSB on all but isolated tail pixels, max 3; 0.5-5 % of the pixels differ) that is bit-exact against
+    the oracle's statement of the same definition.  numpy in -> numpy out, CUDA tensors in -> CUDA tensor out."""
     L = _cabi.lib()
     if not _is_tensor(content):
         dev = _require_cuda()

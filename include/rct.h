@@ -110,6 +110,12 @@ int rct_plan_destroy(rct_plan *plan);
  * the apply pass gets 1.5x faster on noisy images, the three extra solve kernels cost more than that
  * (measured, profiles/r01_summary_v10.md), so it stays opt-in. */
 #define RCT_OPT_LUT 7
+/* RCT_OPT_KEYTAB (default 1): the key table in front of the colour -> RGB table (csrc/rct_keytab.cuh).  The output
+ * colour is a function of the colour's projection key alone; an fp32 key with a proven error bound picks the run of
+ * equal output colour from a ~300 KB L1/L2-resident cell table whenever no run boundary lies within the bound, and only
+ * the remaining ~10 % of the target pixels gather from the 64 MiB table.  Bit-identical results (every GPU parity test
+ * runs with it; rct_plan_debug_keytab re-checks every distinct target colour); 0 = colour table only (A/B runs). */
+#define RCT_OPT_KEYTAB 8
 int rct_plan_set_option(rct_plan *plan, int option, int value);
 /* accumulated device time per phase since the last reset, in ms: [0] workspace memsets,
  * [1] k_hist (pixels -> colour histograms), [2] solve (compact .. match -> LUT), [3] k_apply
@@ -122,7 +128,8 @@ int rct_plan_timing(rct_plan *plan, double *ms4, long long *groups, int reset);
 enum {
     RCT_TK_BEGIN = 0, RCT_TK_MEMSET, RCT_TK_FRONT_COUNT, RCT_TK_FRONT_SCAN, RCT_TK_FRONT_PART, RCT_TK_FRONT_HIST,
     RCT_TK_HIST, RCT_TK_COMPACT, RCT_TK_LAB_MOMENTS, RCT_TK_PCA, RCT_TK_KEYS, RCT_TK_PLAN_FINE, RCT_TK_FINE_HIST,
-    RCT_TK_PLAN_PARTS, RCT_TK_SCATTER, RCT_TK_PART_SORT, RCT_TK_PART_SCAN, RCT_TK_MATCH, RCT_TK_APPLY, RCT_TK_COUNT
+    RCT_TK_PLAN_PARTS, RCT_TK_SCATTER, RCT_TK_PART_SORT, RCT_TK_PART_SCAN, RCT_TK_MATCH, RCT_TK_APPLY, RCT_TK_KEYTAB,
+    RCT_TK_COUNT
 };
 int rct_plan_kernel_timing(rct_plan *plan, double *ms, long long *groups, int reset);
 const char *rct_kernel_timing_name(int id);
@@ -281,6 +288,12 @@ int rct_jpeg_decode_set_parallel(int on);
 int rct_jpeg_decode_info(const uint8_t *file_host, size_t nbytes, int *H, int *W, int *channels, size_t *workspace_bytes);
 int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspace, size_t workspace_bytes, uint8_t *pixels,
                           void *stream);
+
+/* key-table self-check of the last launch group's slot: stats[0] = 1 if the table was built, [1] runs recorded,
+ * [2] cells, [3] flagged cells, [4] distinct target colours resolved by a pure cell, [5] of those, colours whose cell
+ * disagrees with the colour table (must be 0), [6] colours sent to the table by a flagged cell, [7..9] the same three
+ * weighted by pixel count; *max_key_err = max |fp32 key - canonical fp64 key| over all 2^24 colours (bound: 2^-16) */
+int rct_plan_debug_keytab(rct_plan *plan, int slot, unsigned long long *stats10, double *max_key_err);
 
 /* ---- introspection for parity tests (RCT_FLAG_DEBUG plans; all synchronise) -------------- */
 typedef struct {
