@@ -86,6 +86,8 @@ SIGNATURES = {
     "rct_jpeg_decode_set_parallel": (_i, [_i]),
     "rct_jpeg_decode_info": (_i, [_vp, _sz, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_sz)]),
     "rct_jpeg_decode_async": (_i, [_vp, _sz, _vp, _sz, _vp, _vp]),
+    "rct_png_info": (_i, [_vp, _sz, C.POINTER(_i), C.POINTER(_i)]),
+    "rct_png_decode_host": (_i, [_vp, _sz, _vp, _sz]),
     "rct_plan_info": (_i, [_vp, _i, C.POINTER(FrameInfo)]),
     "rct_plan_debug_hist": (_i, [_vp, _i, _vp, _vp]),
     "rct_plan_debug_target": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp]),

@@ -14,6 +14,7 @@
 #include "rct_kernels.cuh"
 #include "rct_jpeg.cuh"
 #include "rct_jpeg_dec.cuh"
+#include "rct_png.h"
 
 using namespace rct;
 
@@ -835,6 +836,9 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
     if (p->lut_mode) {
         if (p->resample) LAUNCH((k_apply<true, 1>), grid, 256, st, a);
         else LAUNCH((k_apply<false, 1>), grid, 256, st, a);
+    } else if (a.kt) {
+        if (p->resample) LAUNCH((k_apply<true, 2>), grid, 256, st, a);
+        else LAUNCH((k_apply<false, 2>), grid, 256, st, a);
     } else if (p->resample) LAUNCH(k_apply<true>, grid, 256, st, a);
     else LAUNCH(k_apply<false>, grid, 256, st, a);
     KMARK(RCT_TK_APPLY);
@@ -1530,6 +1534,27 @@ int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspa
     }
     jpeg::free_plan(&pl);
     return rc;
+}
+
+// ---- f-3: PNG -> RGB8 on the host (rct_png.h explains why the host) -----------------------------------
+int rct_png_info(const uint8_t *file_host, size_t nbytes, int *H, int *W)
+{
+    if (!file_host) return fail(RCT_ERR_ARG, "null pointer");
+    rct_png::Info info;
+    if (!rct_png::parse_header(file_host, nbytes, &info)) return fail(RCT_ERR_ARG, "%s", info.error.c_str());
+    if (H) *H = info.H;
+    if (W) *W = info.W;
+    return RCT_OK;
+}
+
+int rct_png_decode_host(const uint8_t *file_host, size_t nbytes, uint8_t *rgb_host, size_t rgb_capacity)
+{
+    if (!file_host || !rgb_host) return fail(RCT_ERR_ARG, "null pointer");
+    rct_png::Info info;
+    if (!rct_png::parse_header(file_host, nbytes, &info)) return fail(RCT_ERR_ARG, "%s", info.error.c_str());
+    if ((size_t)info.H * (size_t)info.W * 3u > rgb_capacity) return fail(RCT_ERR_ARG, "PNG: output buffer too small");
+    if (!rct_png::decode(file_host, nbytes, &info, rgb_host)) return fail(RCT_ERR_ARG, "%s", info.error.c_str());
+    return RCT_OK;
 }
 
 // ---- phase timing (RCT_OPT_TIMING) -------------------------------------------------------------

@@ -299,72 +299,6 @@ __global__ void __launch_bounds__(256) k_hist(PixArgs a)
     }
 }
 
-// k_apply: a-7..a-9 for pixels: target non-black -> LUT[colour]; target black -> black;
-// MASK mode non-target -> stylised pixel (background_np); LABEL mode non-target untouched.
-template <bool RESAMPLE, int LUTM = 0>
-__global__ void __launch_bounds__(256, 3) k_apply(PixArgs a)
-{
-    const int slot = blockIdx.y;
-    const int frame = slot / a.lpf, label = a.label + slot % a.lpf;  // fused label pass: slot = (frame, label)
-    const uint8_t *content = a.content + (size_t)frame * a.content_stride;
-    const uint8_t *sty = a.sty + (size_t)frame * a.sty_stride;
-    const uint8_t *mask = a.mask ? a.mask + (size_t)frame * a.mask_stride : nullptr;
-    uint8_t *out = a.out + (size_t)frame * a.out_stride;
-    const unsigned *lut = a.lut + (size_t)slot * a.lut_stride;
-    const int status = a.ctrl[slot].status;
-    if (a.status_out && blockIdx.x == 0 && threadIdx.x == 0) a.status_out[slot] = status;
-    const size_t npix = a.p_end - a.p_begin;
-    const size_t ngroups = (npix + 15) / 16;
-    const bool vec_c = (((uintptr_t)(content + 3 * a.p_begin)) & 15) == 0;
-    const bool vec_s = !RESAMPLE && (((uintptr_t)(sty + 3 * a.p_begin)) & 15) == 0;
-    const bool vec_m = mask && (((uintptr_t)(mask + a.p_begin)) & 15) == 0;
-    const bool vec_o = (((uintptr_t)(out + 3 * a.p_begin)) & 15) == 0;
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += stride) {
-        size_t p0 = a.p_begin + 16 * g;
-        int nvalid = (int)min((size_t)16, a.p_end - p0);
-        uint32_t c[16], s[16], m[16], o[16];
-        load16_rgb(content, p0, nvalid, vec_c, c);
-        if (mask) load16_u8(mask, p0, nvalid, vec_m, m);
-        if (a.mode == 0) {
-            if (RESAMPLE) gather16_rgb(sty, a.xtab, a.ytab, a.W, a.sw, p0, nvalid, s);
-            else load16_rgb(sty, p0, nvalid, vec_s, s);
-        }
-        // every lane gathers (entry 0 where no lookup is wanted) and selects afterwards: gathers
-        // inside divergent branches serialise on their latency (see rct_apply.cuh)
-        unsigned keep = 0, tgt = 0;
-#pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            bool in_t, in_s;
-            region_flags(a.mode, label, mask ? m[k] : 0u, in_t, in_s);
-            if (in_t) tgt |= 1u << k;
-            if (in_t || a.mode == 0) keep |= 1u << k;
-        }
-        uint32_t t[16];
-#pragma unroll
-        for (int k = 0; k < 16; ++k)
-        {
-            const uint32_t idx = (((tgt >> k) & 1u) && status == 0 && k < nvalid) ? c[k] : 0u;
-            t[k] = LUTM ? (uint32_t)__ldg(reinterpret_cast<const unsigned short *>(lut) + idx) : __ldg(lut + idx);
-        }
-        if (LUTM) {
-#pragma unroll
-            for (int k = 0; k < 16; ++k) t[k] = __ldg(lut + kPaletteOffsetU32 + t[k]);
-        }
-#pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            uint32_t v = 0;
-            if ((tgt >> k) & 1u) {
-                if (c[k] != 0u && k < nvalid) v = (status == 0) ? t[k] : c[k];
-            } else if (a.mode == 0) {
-                v = s[k];
-            }
-            o[k] = v;
-        }
-        store16_rgb(out, p0, nvalid, vec_o, o, keep);
-    }
-}
-
 // ------------------------------------------------------------------------------------------
 // block-level helpers
 // ------------------------------------------------------------------------------------------

@@ -120,3 +120,37 @@ def decode_jpeg(data, device: bool = False, parallel: bool = False):
             lib.rct_jpeg_decode_set_parallel(before)
         torch.cuda.current_stream().synchronize()   # `work` and `buf` are released on return
     return out if device else out.cpu().numpy()
+
+
+_PNG_SIG = b"\x89PNG\r\n\x1a\n"
+
+
+def decode_png(data):
+    """`np.array(Image.open(path).convert("RGB"))` for a PNG file: uint8 [H,W,3].  Runs on the HOST inside the C
+    library (zlib inflate and the scanline filters are serial; csrc/rct_png.h), no GPU needed."""
+    import ctypes as C
+
+    raw = _file_bytes(data)
+    lib = _cabi.lib()
+    h, w = C.c_int(), C.c_int()
+    buf = (C.c_ubyte * len(raw)).from_buffer_copy(raw)
+    if lib.rct_png_info(buf, len(raw), C.byref(h), C.byref(w)) != 0:
+        raise ValueError(lib.rct_last_error().decode())
+    out = np.empty((h.value, w.value, 3), np.uint8)
+    if lib.rct_png_decode_host(buf, len(raw), out.ctypes.data, out.size) != 0:
+        raise ValueError(lib.rct_last_error().decode())
+    return out
+
+
+def decode_image(data, device: bool = False):
+    """`Image.open(path).convert("RGB")` (LST:200, 219) for the two formats of the reference's inputs: baseline JPEG
+    (decoded on the GPU, grey files replicated to three channels) and PNG (decoded on the host, uploaded when
+    ``device=True``).  Anything else raises ValueError."""
+    raw = _file_bytes(data)
+    if raw[:8] == _PNG_SIG:
+        px = decode_png(raw)
+        return torch.from_numpy(px).to(_dev()) if device else px
+    px = decode_jpeg(raw, device=True)
+    if px.dim() == 2:
+        px = px.unsqueeze(-1).expand(-1, -1, 3).contiguous()
+    return px if device else px.cpu().numpy()

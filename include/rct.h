@@ -289,6 +289,13 @@ int rct_jpeg_decode_info(const uint8_t *file_host, size_t nbytes, int *H, int *W
 int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspace, size_t workspace_bytes, uint8_t *pixels,
                           void *stream);
 
+/* f-3, PNG: `Image.open(path).convert("RGB")` for PNG files (LST:200, 219 take any format Pillow reads).  Decoded ON THE
+ * HOST (zlib inflate + scanline filters are serial by construction, see csrc/rct_png.h); the caller uploads the pixels.
+ * Non-interlaced, 8-bit grey / grey+alpha / RGB / RGBA and 1..8-bit palette / grey; alpha dropped as convert("RGB") does;
+ * anything else returns RCT_ERR_ARG with the reason.  rgb_host receives uint8 [H,W,3]. */
+int rct_png_info(const uint8_t *file_host, size_t nbytes, int *H, int *W);
+int rct_png_decode_host(const uint8_t *file_host, size_t nbytes, uint8_t *rgb_host, size_t rgb_capacity);
+
 /* key-table self-check of the last launch group's slot: stats[0] = 1 if the table was built, [1] runs recorded,
  * [2] cells, [3] flagged cells, [4] distinct target colours resolved by a pure cell, [5] of those, colours whose cell
  * disagrees with the colour table (must be 0), [6] colours sent to the table by a flagged cell, [7..9] the same three
