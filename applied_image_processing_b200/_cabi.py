@@ -21,6 +21,7 @@ OPT_MATCH = 5
 OPT_STAGE_SETS = 6
 OPT_LUT = 7
 OPT_KEYTAB = 8
+JPEG_SERIAL = 1
 TK_COUNT = 20
 
 _lib = None
@@ -83,9 +84,8 @@ SIGNATURES = {
     "rct_jpeg_workspace_bytes": (_sz, [_i, _i, _i]),
     "rct_jpeg_max_bytes": (_sz, [_i, _i]),
     "rct_jpeg_encode_async": (_i, [_vp, _sz, _i, _i, _i, _i, _vp, _vp, _sz, _sz, _vp, _vp]),
-    "rct_jpeg_decode_set_parallel": (_i, [_i]),
     "rct_jpeg_decode_info": (_i, [_vp, _sz, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_sz)]),
-    "rct_jpeg_decode_async": (_i, [_vp, _sz, _vp, _sz, _vp, _vp]),
+    "rct_jpeg_decode_async": (_i, [_vp, _sz, _vp, _sz, _vp, _i, _vp]),
     "rct_png_info": (_i, [_vp, _sz, C.POINTER(_i), C.POINTER(_i)]),
     "rct_png_decode_host": (_i, [_vp, _sz, _vp, _sz]),
     "rct_plan_info": (_i, [_vp, _i, C.POINTER(FrameInfo)]),

@@ -88,6 +88,9 @@ int ensure_device(int *dev_out)
     delete h;
     if (e1 != cudaSuccess) return fail(RCT_ERR_CUDA, "table upload failed: %s", cudaGetErrorString(e1));
     CK(cudaMemcpyToSymbol(c_mat, g_mat, sizeof g_mat));
+    float ktm[9];
+    for (int i = 0; i < 9; ++i) ktm[i] = (float)(g_mat[i] / 255.0);
+    CK(cudaMemcpyToSymbol(c_ktm, ktm, sizeof ktm));
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, dev));
     g_sm_count[dev] = prop.multiProcessorCount;
@@ -631,7 +634,6 @@ int phase_front(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
 }
 
 constexpr size_t kSmemFineHist = (size_t)(kFineMax + kCoarse + 1) * 4;
-constexpr size_t kKtSortSmem = (size_t)kKtRunCap * 12;
 constexpr size_t kSmemPartSort = (size_t)kPartCap * 16 + ((size_t)kPartCap + kPartCap / 32 + 2) * 4;  // records + padded counters
 
 int ensure_kernel_attrs()
@@ -685,6 +687,8 @@ int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)
 {
     unsigned eb = entry_blocks(p, nslots);
     CK(cudaMemsetAsync(p->ws + p->L.off_zero, 0, p->L.zero_bytes * 2 * (size_t)nslots, st));
+    if (p->keytab && !p->lut_mode)  // parameters, seeds and flags of the key tables (rct_keytab.cuh)
+        CK(cudaMemset2DAsync(p->ws + p->L.off_kt, kKtBytes, 0, kKtZeroBytes, (size_t)nslots, st));
     KMARK(RCT_TK_MEMSET);
     if (from_cube) {
         LAUNCH(k_compact, dim3(kCube / 1024, 2, nslots), 256, st, p->hist, p->L.hist_stride_u32, p->ctrl, p->jobs);
@@ -715,18 +719,10 @@ int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)
     }
     KMARK(RCT_TK_MATCH);
     p->kt_live = false;
-    if (p->keytab && !p->lut_mode) {  // key table: runs -> sorted thresholds + cell directory -> cells
-        static thread_local int attr_dev_kt = -1;
-        int dev = 0;
-        CK(cudaGetDevice(&dev));
-        if (attr_dev_kt != dev) {
-            CK(cudaFuncSetAttribute(k_kt_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKtSortSmem));
-            attr_dev_kt = dev;
-        }
-        k_kt_sort<<<nslots, 1024, kKtSortSmem, st>>>(p->ctrl, p->ws + p->L.off_kt, p->match_interleave);
-        ++t_launches;
-        CK(cudaGetLastError());
-        LAUNCH(k_kt_cells, dim3(64, nslots), 256, st, p->ctrl, p->ws + p->L.off_kt);
+    if (p->keytab && !p->lut_mode) {  // key table: run starts -> flagged cells + seeds -> prefix maximum -> cells
+        uint8_t *kt0 = p->ws + p->L.off_kt;
+        LAUNCH(k_kt_mark, dim3(8, nslots), 256, st, p->ctrl, kt0, p->match_interleave);
+        LAUNCH(k_kt_fill, dim3(nslots), 1024, st, p->ctrl, kt0, p->match_interleave);
         KMARK(RCT_TK_KEYTAB);
         p->kt_live = true;
     }
@@ -1507,16 +1503,8 @@ int rct_jpeg_decode_info(const uint8_t *file_host, size_t nbytes, int *H, int *W
     return RCT_OK;
 }
 
-static int g_jpeg_parallel = 0;
-int rct_jpeg_decode_set_parallel(int on)
-{
-    const int before = g_jpeg_parallel;
-    g_jpeg_parallel = on ? 1 : 0;
-    return before;
-}
-
 int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspace, size_t workspace_bytes, uint8_t *pixels,
-                          void *stream)
+                          int flags, void *stream)
 {
     if (!file_host || !workspace || !pixels) return fail(RCT_ERR_ARG, "null pointer");
     if (((uintptr_t)workspace & 255u) != 0) return fail(RCT_ERR_ARG, "workspace must be 256-byte aligned");
@@ -1528,7 +1516,7 @@ int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspa
     if (rc == RCT_OK) {
         int launches = 0;
         cudaError_t e = jpeg::decode_launch(file_host, pl, jpeg::carve_dec(pl.f, workspace), pixels, (cudaStream_t)stream, &launches,
-                                            g_jpeg_parallel != 0);
+                                            (flags & RCT_JPEG_SERIAL) == 0);
         t_launches += launches;
         if (e != cudaSuccess) rc = fail(RCT_ERR_CUDA, "JPEG decoder launch failed: %s", cudaGetErrorString(e));
     }
@@ -1704,7 +1692,7 @@ int rct_plan_debug_keytab(rct_plan *p, int slot, unsigned long long *stats10, do
     CK(cudaMemcpy(&hp, kt0 + (size_t)slot * kKtBytes, sizeof hp, cudaMemcpyDeviceToHost));
     stats10[0] = hp.valid;
     stats10[1] = hp.n_runs;
-    stats10[2] = hp.n_cells;
+    stats10[2] = (unsigned long long)kKtCells;
     stats10[3] = hp.n_flagged;
     if (!hp.valid) return RCT_OK;
     unsigned long long *d_counts = nullptr;

@@ -407,6 +407,16 @@ __device__ __forceinline__ void apply8(const uint32_t wc[6], const uint32_t ws[6
                                        const KtRegs *kr = nullptr, const KtView *kv = nullptr)
 {
     uint32_t c[8], s[8];
+    if (LUTM == 2) {
+        // a lane whose eight pixels are all background passes the stylised words through: no unpacking at all
+        // (regions are contiguous in real masks, so most lanes are all-background or all-target)
+        const uint32_t z0 = wm[0], z1 = wm[1];
+        if (__vcmpeq4(z0, 0u) == 0u && __vcmpeq4(z1, 0u) == 0u) {
+#pragma unroll
+            for (int q = 0; q < 6; ++q) wo[q] = ws[q];
+            return;
+        }
+    }
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
         c[4 * q + 0] = wc[3 * q] & 0xffffffu;
@@ -425,16 +435,33 @@ __device__ __forceinline__ void apply8(const uint32_t wc[6], const uint32_t ws[6
     }
     uint32_t t[8];
     if (LUTM == 2) {
+        if (want) {  // one branch around the whole batch: the eight table reads stay independent
 #pragma unroll
-        for (int k = 0; k < 8; ++k) t[k] = kt_lookup(*kr, *kv, c[k]);
-        // flagged cells: the exact table.  Every lane issues the gather (entry 0 where none is wanted: one
-        // broadcast sector per instruction), a gather inside a divergent branch would serialise on its latency
+            for (int k = 0; k < 8; ++k) t[k] = kt_lookup(*kr, *kv, c[k]);
+            unsigned amb = 0;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const bool fb = ((want >> k) & 1u) && (t[k] & kKtFlag);
-            const unsigned *g = lut + (fb ? c[k] : 0u);
-            const uint32_t v = HINT ? ldg_hint(g, pol_lut) : __ldg(g);
-            if (fb) t[k] = v;
+            for (int k = 0; k < 8; ++k)
+                if (((want >> k) & 1u) && (t[k] & kKtFlag)) amb |= 1u << k;
+            if (amb) {  // flagged cells (a few per cent of the pixels): the exact table
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const bool fb = (amb >> k) & 1u;
+                    const unsigned *g = lut + (fb ? c[k] : 0u);
+                    const uint32_t v = HINT ? ldg_hint(g, pol_lut) : __ldg(g);
+                    if (fb) t[k] = v;
+                }
+            }
+        }
+        if (tgt == 0xffu) {  // all eight pixels are target pixels: the stylised words are not needed
+#pragma unroll
+            for (int k = 0; k < 8; ++k) c[k] = ((want >> k) & 1u) ? t[k] : c[k];
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                wo[3 * q + 0] = c[4 * q] | (c[4 * q + 1] << 24);
+                wo[3 * q + 1] = (c[4 * q + 1] >> 8) | (c[4 * q + 2] << 16);
+                wo[3 * q + 2] = (c[4 * q + 2] >> 16) | (c[4 * q + 3] << 8);
+            }
+            return;
         }
     } else if (LUTM) {  // uint16 run index (L2-resident table), then the palette (L1-resident)
         const unsigned short *l16 = reinterpret_cast<const unsigned short *>(lut);

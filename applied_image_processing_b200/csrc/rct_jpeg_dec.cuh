@@ -447,6 +447,12 @@ inline bool parse_jpeg(const unsigned char *d, size_t n, DecPlan *p)
                     code <<= 1;
                 }
                 p->t.maxcode[tab][17] = 0x7fffffff;
+                // symbol ranges of 8-bit baseline data (jdhuff.c): DC size categories 0..11; AC run/size bytes with
+                // size 0..10 -- anything else would feed shifts by up to 255 bits into the decoder
+                for (int i = 0; i < total; ++i) {
+                    const int v = seg[k + 17 + i];
+                    if (tc == 0 ? v > 11 : (v & 15) > 10) return bad("Huffman table holds symbols outside the 8-bit baseline range");
+                }
                 memcpy(p->t.vals[tab], seg + k + 17, (size_t)total);
                 have_h[tab] = true;
                 k += 17 + (size_t)total;

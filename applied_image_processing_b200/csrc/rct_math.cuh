@@ -15,6 +15,8 @@ namespace rct {
 
 // Reinhard matrices (LST:12-19): RGB_TO_LMS, LMS_TO_LAB, LAB_TO_LMS, LMS_TO_RGB, row-major.
 __constant__ double c_mat[36];
+// RGB_TO_LMS / 255 in fp32, for the key table's fp32 key (rct_keytab.cuh); uploaded with c_mat
+__constant__ float c_ktm[9];
 
 // Tables live in global memory (filled once per device) and are staged into shared memory
 // by kernels that evaluate log10 / 10^x per lane with divergent indices.

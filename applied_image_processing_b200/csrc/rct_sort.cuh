@@ -860,13 +860,14 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
         return;
     }
     // Run starts for the key table (rct_keytab.cuh): wherever the output colour differs from the previous sorted
-    // entry's, (key, colour) is appended to the slot's run list; every part opens a run, so parts are independent.
+    // entry's, (key, sorted index, colour) is appended to the slot's run list; every part opens a run, so parts are
+    // independent.
     double *run_key = nullptr;
-    unsigned *run_col = nullptr;
+    uint2 *run_ic = nullptr;
     if (!LUTM && kt0) {
         uint8_t *blk = kt0 + (size_t)slot * kKtBytes;
         run_key = reinterpret_cast<double *>(blk + kKtOffRunKey);
-        run_col = reinterpret_cast<unsigned *>(blk + kKtOffRunCol);
+        run_ic = reinterpret_cast<uint2 *>(blk + kKtOffRunIc);
     }
     __shared__ unsigned s_tail[kMatchThreads / 32];
     __shared__ unsigned s_carry;
@@ -885,7 +886,7 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
                 const unsigned idx = atomicAdd(&ctrl[slot].n_runs, 1u);
                 if (idx < (unsigned)kKtRunCap) {
                     run_key[idx] = key_at(t, i);
-                    run_col[idx] = rgb;
+                    run_ic[idx] = make_uint2(i, rgb);  // the sorted index orders the runs without a sort
                 }
             }
             __syncthreads();

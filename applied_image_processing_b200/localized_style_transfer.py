@@ -574,24 +574,38 @@ def run_localized_style_transfer(
     [1,H,W] or [H,W], what extract_foreground_deeplab returns) and ``stylized_image`` (path or
     uint8 array, what adain_inference writes).  The in-scope tail (LST:218-243) is unchanged:
     resize -> masks -> colour transfer -> combine -> save JPEG (device encoder); returns the saved path."""
-    from PIL import Image
+    from .jpeg import decode_image
 
-    content_np = np.array(Image.open(content_img_path).convert("RGB"))
+    def _open_rgb(path):
+        """LST:200, 219 `Image.open(path).convert("RGB")`: baseline JPEG decoded on the device, PNG on the host inside
+        the C library (both bit-exact with Pillow).  A file the decoders refuse with a reason (progressive / CMYK JPEG,
+        interlaced or 16-bit PNG, another container) is read by Pillow itself: format handling only, the pixels then
+        take the same device path."""
+        try:
+            return decode_image(path, device=True)
+        except ValueError:
+            from PIL import Image
+
+            return torch.from_numpy(np.array(Image.open(path).convert("RGB"))).to(_require_cuda())
+
+    content_t = _open_rgb(content_img_path)
     if background_mask is None:
-        background_mask = extract_foreground_deeplab(content_np)
+        background_mask = extract_foreground_deeplab(content_t.cpu().numpy())
     if stylized_image is None:
         raise NotImplementedError("AdaIN inference is outside the accelerated path; pass stylized_image=")
     background_mask = np.asarray(background_mask, np.uint8)
     if background_mask.ndim == 3:
         background_mask = background_mask[0]
     if isinstance(stylized_image, str):
-        stylized_np = np.array(Image.open(stylized_image).convert("RGB"))
+        stylized_t = _open_rgb(stylized_image)
     else:
-        stylized_np = np.asarray(stylized_image, np.uint8)
-    combined_image = regional_color_transfer(content_np, stylized_np, background_mask)
+        stylized_t = torch.from_numpy(np.ascontiguousarray(np.asarray(stylized_image, np.uint8))).to(content_t.device)
+    mask_t = torch.from_numpy(np.ascontiguousarray(background_mask)).to(content_t.device)
+    # decode -> transfer -> encode without the pixels leaving the device
+    combined_image, status = regional_color_transfer(content_t.contiguous(), stylized_t.contiguous(), mask_t, return_status=True)
     save_path = f"{output_path}/localized_style_transfer_result.jpg"
     # LST:243 `Image.fromarray(combined_image.astype(np.uint8)).save(save_path)`: the same bytes, encoded on the GPU
     from .jpeg import save_jpeg
 
-    save_jpeg(combined_image.astype(np.uint8), save_path)
+    save_jpeg(combined_image, save_path)
     return save_path

@@ -72,6 +72,8 @@ def parse_args():
     ap.add_argument("--labels-fused", type=int, default=1, choices=[0, 1],
                     help="labels workload: 1 all labels of a frame group in one launch group (rct_transfer_labels_async), "
                          "0 one pass per label (A/B runs)")
+    ap.add_argument("--keytab", type=int, default=1, choices=[0, 1],
+                    help="RCT_OPT_KEYTAB: 1 key table in front of the colour LUT (default), 0 colour LUT only (A/B runs)")
     ap.add_argument("--lut", type=int, default=0, choices=[0, 1],
                     help="RCT_OPT_LUT: 0 uint32 RGB per colour (default), 1 uint16 run index + palette (A/B runs)")
     ap.add_argument("--sty-short", type=int, default=0,
@@ -354,6 +356,7 @@ def run_gpu_arm(a):
     plan.set_option(_cabi.OPT_APPLY, a.apply)
     plan.set_option(_cabi.OPT_MATCH, a.match)
     plan.set_option(_cabi.OPT_LUT, a.lut)
+    plan.set_option(_cabi.OPT_KEYTAB, a.keytab)
     st = torch.cuda.current_stream().cuda_stream
 
     def step():
@@ -413,7 +416,7 @@ def run_gpu_arm(a):
     ms_launch = {k: v / groups for k, v in kt.items()}           # average duration of one launch
     t_all = sum(ms_launch.values())
     frames_launch = min(a.slots, n)
-    apply_name = {0: "k_apply", 1: "k_apply_warp<bulk,8>", 2: "k_apply_warp<cp.async,8>", 3: "k_apply_tma",
+    apply_name = {0: "k_apply", 1: "k_apply_warp<bulk,8,keytab>" if a.keytab and not a.lut and not a.bins else "k_apply_warp<bulk,8>", 2: "k_apply_warp<cp.async,8>", 3: "k_apply_tma",
                   4: "k_apply_warp<bulk,16>", 5: "k_apply_warp<bulk,8>", 6: "k_apply_warp<bulk,8,3stage>", 7: "k_apply_warp<bulk,8,bulk-store>", 8: "k_apply_warp<bulk,8>"}[0 if labels else a.apply]
     if (sh, sw) != (H, W) and not labels:
         apply_name = "k_apply_warp_rs" if a.apply == 8 else "k_apply<resample>"

@@ -278,15 +278,16 @@ int rct_jpeg_encode_async(const uint8_t *rgb, size_t frame_stride, int n, int H,
  * rct_jpeg_decode_info parses the header on the host (no GPU needed).  rct_jpeg_decode_async takes the FILE BYTES IN
  * HOST MEMORY, copies the entropy-coded segment to the device and enqueues the decoder on `stream`; pixels (device)
  * receives uint8 [H,W,3] (or [H,W] for one component).  The host bytes may be released when the call returns.
- * Huffman decoding runs one thread per restart interval: a file without restart markers decodes serially (correct,
- * slow). */
-/* rct_jpeg_decode_set_parallel(1): files without restart markers are decoded by the self-synchronising parallel
- * Huffman decoder (subsequences of 256 bytes decoded speculatively, states iterated to a fixed point, which proves them
- * exact; the serial kernel takes over on the device if 32 rounds do not converge).  Same pixels, orders of magnitude
- * faster on large files.  Off by default until its kernels have had their first GPU run; returns the old setting. */
-int rct_jpeg_decode_set_parallel(int on);
+ * Files with restart markers decode one thread per restart interval. */
+/* flags of rct_jpeg_decode_async.  Files WITHOUT restart markers (what Pillow writes by default) are decoded by the
+ * self-synchronising parallel Huffman decoder: subsequences of 256 bytes decoded speculatively, their entry states
+ * iterated to a fixed point (which proves them exact; the serial kernel takes over on the device if the rounds do not
+ * converge) -- same pixels, orders of magnitude faster on large files.  RCT_JPEG_SERIAL forces one thread per restart
+ * interval for every file (A/B runs, tests). */
+#define RCT_JPEG_SERIAL 1
 int rct_jpeg_decode_info(const uint8_t *file_host, size_t nbytes, int *H, int *W, int *channels, size_t *workspace_bytes);
 int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspace, size_t workspace_bytes, uint8_t *pixels,
+                          int flags,
                           void *stream);
 
 /* f-3, PNG: `Image.open(path).convert("RGB")` for PNG files (LST:200, 219 take any format Pillow reads).  Decoded ON THE

@@ -90,9 +90,6 @@ def test_pipeline_tail_writes_the_file_the_reference_would(tmp_path):
     assert np.array_equal(aip.decode_jpeg(path), _pillow(buf.getvalue()))
 
 
-@pytest.mark.skipif(not __import__("os").environ.get("RCT_TEST_UNVALIDATED"),
-                    reason="self-synchronising decoder: kernels written after the round's GPU budget ran out; host-run bodies are "
-                           "pinned in test_jpeg_device_core.py, set RCT_TEST_UNVALIDATED=1 for the first GPU run")
 @pytest.mark.parametrize("h,w,kw", [(270, 480, {}), (540, 960, {"quality": 90}), (1080, 1920, {}), (96, 128, {"subsampling": 0}),
                                     (37, 53, {"optimize": True})])
 def test_self_synchronising_decoder_matches_pillow(h, w, kw):
@@ -100,4 +97,5 @@ def test_self_synchronising_decoder_matches_pillow(h, w, kw):
 
     data = _file(h, w, h + w, **kw)
     assert np.array_equal(aip.decode_jpeg(data, parallel=True), _pillow(data))
+    assert np.array_equal(aip.decode_jpeg(data, parallel=False), _pillow(data))
     assert np.array_equal(aip.decode_jpeg(data), _pillow(data))
