@@ -21,7 +21,9 @@ from .localized_style_transfer import (  # noqa: F401
 )
 from .adjacent import adain_mask_blend, deeplab_background_mask, deeplab_label_map  # noqa: F401
 from .video import blend_images, blend_sequence, normalize_image, warp_blend, warp_image  # noqa: F401
-from .jpeg import decode_image, decode_jpeg, decode_png, encode_jpeg, jpeg_info, save_jpeg  # noqa: F401
+from .jpeg import (  # noqa: F401
+    decode_image, decode_jpeg, decode_png, encode_jpeg, image_info, jpeg_info, regional_color_transfer_files, save_jpeg,
+)
 
 __all__ = [
     "RGB_TO_LMS", "LMS_TO_LAB", "LAB_TO_LMS", "LMS_TO_RGB", "RegionPCA", "apply_pca",

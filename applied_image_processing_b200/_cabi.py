@@ -86,6 +86,8 @@ SIGNATURES = {
     "rct_jpeg_encode_async": (_i, [_vp, _sz, _i, _i, _i, _i, _vp, _vp, _sz, _sz, _vp, _vp]),
     "rct_jpeg_decode_info": (_i, [_vp, _sz, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_sz)]),
     "rct_jpeg_decode_async": (_i, [_vp, _sz, _vp, _sz, _vp, _i, _vp]),
+    "rct_files_out_capacity": (_sz, [_i, _i]),
+    "rct_transfer_files_host": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _i, _vp, _sz, C.POINTER(_sz), C.POINTER(_i)]),
     "rct_png_info": (_i, [_vp, _sz, C.POINTER(_i), C.POINTER(_i)]),
     "rct_png_decode_host": (_i, [_vp, _sz, _vp, _sz]),
     "rct_plan_info": (_i, [_vp, _i, C.POINTER(FrameInfo)]),

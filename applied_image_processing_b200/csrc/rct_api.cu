@@ -222,6 +222,8 @@ struct rct_plan {
     bool ev_last_valid;
     int lpf;         // labels per frame of the call in progress (rct_transfer_labels_async), else 1
     int lut_mode;    // RCT_OPT_LUT: 1 = uint16 run indices + palette, 0 = uint32 RGB per colour
+    uint8_t *files_ws;   // decode / encode workspaces and the JPEG output of rct_transfer_files_host
+    size_t files_ws_bytes;
     int keytab;      // RCT_OPT_KEYTAB: 1 = key table in front of the colour LUT (rct_keytab.cuh)
     bool kt_live;    // the tables of the launch group in flight were built (exact path, interleaved match)
     int stage_sets;  // RCT_OPT_STAGE_SETS: staging sets of the host entry point (2..kStageSetsMax)
@@ -433,6 +435,7 @@ int rct_plan_destroy(rct_plan *p)
     if (p->owns_ws && p->ws) cudaFree(p->ws);
     if (p->status_frames) cudaFree(p->status_frames);
     if (p->stage) cudaFree(p->stage);
+    if (p->files_ws) cudaFree(p->files_ws);
     delete p;
     return RCT_OK;
 }
@@ -1543,6 +1546,112 @@ int rct_png_decode_host(const uint8_t *file_host, size_t nbytes, uint8_t *rgb_ho
     if ((size_t)info.H * (size_t)info.W * 3u > rgb_capacity) return fail(RCT_ERR_ARG, "PNG: output buffer too small");
     if (!rct_png::decode(file_host, nbytes, &info, rgb_host)) return fail(RCT_ERR_ARG, "%s", info.error.c_str());
     return RCT_OK;
+}
+
+
+// ---- f-3 on the e2e path: files in, file out ------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) k_gray_to_rgb(const uint8_t *g, uint8_t *rgb, size_t n)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const uint8_t v = g[i];
+        rgb[3 * i] = v;
+        rgb[3 * i + 1] = v;
+        rgb[3 * i + 2] = v;
+    }
+}
+bool is_png(const uint8_t *f, size_t n) { return n >= 8 && f[0] == 0x89 && f[1] == 'P' && f[2] == 'N' && f[3] == 'G'; }
+
+// one image file (host bytes) -> RGB8 pixels at `dst` (device, H*W*3); `scratch` holds the decoder workspace
+int decode_file_to_device(const uint8_t *file, size_t nbytes, int H, int W, const char *what, uint8_t *dst, uint8_t *scratch,
+                          size_t scratch_bytes, uint8_t *gray_tmp, std::vector<uint8_t> &host_tmp, int sm, cudaStream_t st)
+{
+    if (is_png(file, nbytes)) {
+        rct_png::Info info;
+        if (!rct_png::parse_header(file, nbytes, &info)) return fail(RCT_ERR_ARG, "%s: %s", what, info.error.c_str());
+        if (info.H != H || info.W != W) return fail(RCT_ERR_ARG, "%s is %dx%d, the plan expects %dx%d", what, info.W, info.H, W, H);
+        host_tmp.resize((size_t)H * W * 3);
+        if (!rct_png::decode(file, nbytes, &info, host_tmp.data())) return fail(RCT_ERR_ARG, "%s: %s", what, info.error.c_str());
+        CK(cudaMemcpyAsync(dst, host_tmp.data(), host_tmp.size(), cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));  // host_tmp is reused for the next file
+        return RCT_OK;
+    }
+    jpeg::DecPlan pl;
+    if (!jpeg::parse_jpeg(file, nbytes, &pl)) return fail(RCT_ERR_ARG, "%s: JPEG decoder: %s", what, pl.error);
+    int rc = RCT_OK;
+    if (pl.f.H != H || pl.f.W != W) rc = fail(RCT_ERR_ARG, "%s is %dx%d, the plan expects %dx%d", what, pl.f.W, pl.f.H, W, H);
+    else if (jpeg::carve_dec(pl.f, nullptr).bytes > scratch_bytes) rc = fail(RCT_ERR_ARG, "%s: decoder workspace too small", what);
+    if (rc == RCT_OK) {
+        int launches = 0;
+        const bool gray = pl.f.ncomp != 3;
+        cudaError_t e = jpeg::decode_launch(file, pl, jpeg::carve_dec(pl.f, scratch), gray ? gray_tmp : dst, st, &launches, true);
+        t_launches += launches;
+        if (e != cudaSuccess) rc = fail(RCT_ERR_CUDA, "%s: JPEG decoder launch failed: %s", what, cudaGetErrorString(e));
+        else if (gray) {
+            k_gray_to_rgb<<<sm * 4, 256, 0, st>>>(gray_tmp, dst, (size_t)H * W);
+            ++t_launches;
+        }
+    }
+    jpeg::free_plan(&pl);
+    return rc;
+}
+}  // namespace
+
+size_t rct_files_out_capacity(int H, int W) { return rct_jpeg_max_bytes(H, W); }
+
+int rct_transfer_files_host(rct_plan *p, const uint8_t *content_file, size_t content_bytes, const uint8_t *stylised_file,
+                            size_t stylised_bytes, const uint8_t *mask_h, int quality, uint8_t *out_file, size_t out_capacity,
+                            size_t *out_bytes, int *status_host)
+{
+    if (!p || !content_file || !stylised_file || !mask_h || !out_file || !out_bytes) return fail(RCT_ERR_ARG, "null argument");
+    if (quality < 1 || quality > 100) return fail(RCT_ERR_ARG, "quality %d outside 1..100", quality);
+    DeviceGuard guard(p->device);
+    const int H = p->H, W = p->W, sh = p->sh, sw = p->sw;
+    const size_t npix = (size_t)H * W, spix = (size_t)sh * sw;
+    const size_t cb = align_up(npix * 3), sb = align_up(spix * 3), mb = align_up(npix);
+    // device buffers: content | stylised | mask | out pixels (one frame), then decoder / encoder workspaces and the file
+    const size_t enc_ws = align_up(rct_jpeg_workspace_bytes(H, W, 1));
+    const size_t cap = align_up(rct_jpeg_max_bytes(H, W));
+    const size_t big = npix > spix ? npix : spix;
+    // decoder workspace bound: coefficients (2 bytes per sample incl. padding to MCUs) + planes + scan + states
+    const size_t dec_ws = align_up(big * 16 + (content_bytes > stylised_bytes ? content_bytes : stylised_bytes) * 8 + (1u << 20));
+    const size_t need = cb + sb + mb + cb + dec_ws + enc_ws + cap + 256;
+    if (p->files_ws_bytes < need) {
+        if (p->files_ws) CK(cudaFree(p->files_ws));
+        p->files_ws = nullptr;
+        p->files_ws_bytes = 0;
+        CK(cudaMalloc((void **)&p->files_ws, need));
+        p->files_ws_bytes = need;
+    }
+    uint8_t *d_c = p->files_ws, *d_s = d_c + cb, *d_m = d_s + sb, *d_o = d_m + mb, *d_dec = d_o + cb, *d_enc = d_dec + dec_ws,
+            *d_file = d_enc + enc_ws;
+    unsigned long long *d_n = reinterpret_cast<unsigned long long *>(d_file + cap);
+    cudaStream_t st = p->own_stream;
+    int rc = plan_enter(p, st);
+    if (rc) return rc;
+    std::vector<uint8_t> host_tmp;
+    // d_o doubles as the grey plane of a one-component JPEG before its expansion
+    if ((rc = decode_file_to_device(content_file, content_bytes, H, W, "content file", d_c, d_dec, dec_ws, d_o, host_tmp, p->sm, st))) return rc;
+    if ((rc = decode_file_to_device(stylised_file, stylised_bytes, sh, sw, "stylised file", d_s, d_dec, dec_ws, d_o, host_tmp, p->sm, st))) return rc;
+    CK(cudaMemcpyAsync(d_m, mask_h, npix, cudaMemcpyHostToDevice, st));
+    if ((rc = ensure_status_frames(p, 1))) return rc;
+    FrameSet f{d_c, d_s, d_m, d_o, cb, sb, mb, cb};
+    if ((rc = p->front ? phase_front(p, f, 1, RCT_MODE_MASK, 0, 0, npix, st) : phase_hist(p, f, 1, RCT_MODE_MASK, 0, 0, npix, st))) return rc;
+    if ((rc = phase_solve(p, 1, st, !p->front))) return rc;
+    if ((rc = phase_apply(p, f, 1, RCT_MODE_MASK, 0, 0, npix, p->status_frames, st))) return rc;
+    if ((rc = rct_jpeg_encode_async(d_o, cb, 1, H, W, quality, d_enc, d_file, cap, cap, d_n, st))) return rc;
+    unsigned long long nb = 0;
+    int status = 0;
+    CK(cudaMemcpyAsync(&nb, d_n, sizeof nb, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&status, p->status_frames, sizeof status, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (status_host) *status_host = status;
+    *out_bytes = (size_t)nb;
+    if (nb > out_capacity) return fail(RCT_ERR_ARG, "output file needs %llu bytes, capacity is %zu", nb, out_capacity);
+    CK(cudaMemcpyAsync(out_file, d_file, (size_t)nb, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if ((rc = plan_leave(p, st))) return rc;
+    return status;
 }
 
 // ---- phase timing (RCT_OPT_TIMING) -------------------------------------------------------------

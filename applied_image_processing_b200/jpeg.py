@@ -158,3 +158,50 @@ def decode_image(data, device: bool = False):
     if px.dim() == 2:
         px = px.unsqueeze(-1).expand(-1, -1, 3).contiguous()
     return px if device else px.cpu().numpy()
+
+
+def image_info(data):
+    """(H, W) of a baseline JPEG or PNG file from its header (host only)."""
+    import ctypes as C
+
+    raw = _file_bytes(data)
+    if raw[:8] == _PNG_SIG:
+        lib = _cabi.lib()
+        h, w = C.c_int(), C.c_int()
+        buf = (C.c_ubyte * len(raw)).from_buffer_copy(raw)
+        if lib.rct_png_info(buf, len(raw), C.byref(h), C.byref(w)) != 0:
+            raise ValueError(lib.rct_last_error().decode())
+        return h.value, w.value
+    return jpeg_info(raw)[:2]
+
+
+def regional_color_transfer_files(content_file, stylized_file, background_mask, quality: int = 75) -> bytes:
+    """The reference's real boundary (LST:191-245: image files in, ``localized_style_transfer_result.jpg`` out) as ONE
+    C-ABI call, ``rct_transfer_files_host``: content / stylised file bytes (or paths; baseline JPEG or PNG) and the uint8
+    background mask -> decode, NEAREST resample, regional colour transfer, combination, JPEG encode on the device ->
+    the bytes of the file Pillow's ``save(path, quality=quality)`` would write for the same pixels."""
+    import ctypes as C
+
+    from . import localized_style_transfer as lst
+
+    c_raw, s_raw = _file_bytes(content_file), _file_bytes(stylized_file)
+    H, W = image_info(c_raw)
+    sh, sw = image_info(s_raw)
+    mask = np.ascontiguousarray(background_mask, np.uint8)
+    if mask.ndim == 3:
+        mask = np.ascontiguousarray(mask[0])
+    if mask.shape != (H, W):
+        raise ValueError(f"mask is {mask.shape}, the content file is {(H, W)}")
+    dev = _dev()
+    plan = lst.get_plan(dev, H, W, sh, sw, 1)
+    lib = _cabi.lib()
+    cap = lib.rct_files_out_capacity(H, W)
+    out = np.empty(cap, np.uint8)
+    nbytes, status = C.c_size_t(0), C.c_int(0)
+    cbuf = (C.c_ubyte * len(c_raw)).from_buffer_copy(c_raw)
+    sbuf = (C.c_ubyte * len(s_raw)).from_buffer_copy(s_raw)
+    with torch.cuda.device(dev), plan.lock:
+        check(lib.rct_transfer_files_host(plan.handle, cbuf, len(c_raw), sbuf, len(s_raw), mask.ctypes.data, int(quality),
+                                          out.ctypes.data, cap, C.byref(nbytes), C.byref(status)))
+    lst._warn(status.value)
+    return out[:nbytes.value].tobytes()

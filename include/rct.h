@@ -297,6 +297,18 @@ int rct_jpeg_decode_async(const uint8_t *file_host, size_t nbytes, void *workspa
 int rct_png_info(const uint8_t *file_host, size_t nbytes, int *H, int *W);
 int rct_png_decode_host(const uint8_t *file_host, size_t nbytes, uint8_t *rgb_host, size_t rgb_capacity);
 
+/* f-3 on the end-to-end path: the reference's real boundary is FILES (run_localized_style_transfer(content_img_path, ...)
+ * -> ".../localized_style_transfer_result.jpg", LST:191-245).  One call: content file + stylised file (baseline JPEG decoded
+ * on the device, PNG decoded on the host; sizes must match the plan's H x W / sh x sw) + the uint8 [H*W] background mask in
+ * host memory -> decode -> NEAREST resample -> regional colour transfer -> combine -> baseline JPEG (the bytes Pillow's
+ * save(quality) writes) in out_file.  A 4K frame then crosses PCIe as ~3 MB of files + the mask instead of 83 MB of
+ * pixels.  Returns the frame status (0 / 1 / 2) or < 0; *out_bytes = size of the file; synchronises.
+ * out_capacity: rct_files_out_capacity(H, W) always suffices. */
+size_t rct_files_out_capacity(int H, int W);
+int rct_transfer_files_host(rct_plan *plan, const uint8_t *content_file, size_t content_bytes, const uint8_t *stylised_file,
+                            size_t stylised_bytes, const uint8_t *mask_h, int quality, uint8_t *out_file, size_t out_capacity,
+                            size_t *out_bytes, int *status_host);
+
 /* key-table self-check of the last launch group's slot: stats[0] = 1 if the table was built, [1] runs recorded,
  * [2] cells, [3] flagged cells, [4] distinct target colours resolved by a pure cell, [5] of those, colours whose cell
  * disagrees with the colour table (must be 0), [6] colours sent to the table by a flagged cell, [7..9] the same three

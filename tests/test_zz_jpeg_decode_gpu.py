@@ -90,6 +90,61 @@ def test_pipeline_tail_writes_the_file_the_reference_would(tmp_path):
     assert np.array_equal(aip.decode_jpeg(path), _pillow(buf.getvalue()))
 
 
+def test_pipeline_tail_from_jpeg_files_stays_on_the_device(tmp_path):
+    """content.jpg + stylised.jpg (LST:200, 219) -> device decode -> transfer -> device encode: the file equals
+    Pillow-decode -> oracle -> Pillow-encode byte for byte; a progressive file goes through Pillow's reader."""
+    from applied_image_processing_b200.localized_style_transfer import run_localized_style_transfer
+    from oracle import oracle as orc
+    from tests.synth import ellipse_mask, synth_image
+
+    H, W = 360, 640
+    PIL.fromarray(synth_image(H, W, 3, "N")).save(tmp_path / "content.jpg", quality=90)
+    PIL.fromarray(synth_image(256, 455, 4, "N")).save(tmp_path / "sty.jpg")
+    PIL.fromarray(synth_image(256, 455, 4, "N")).save(tmp_path / "sty_prog.jpg", progressive=True)
+    mask = ellipse_mask(H, W, 0.45, 6)
+    for sty_name in ("sty.jpg", "sty_prog.jpg"):
+        c = np.array(PIL.open(tmp_path / "content.jpg").convert("RGB"))
+        s = np.array(PIL.open(tmp_path / sty_name).convert("RGB"))
+        ref, status, _ = orc.transfer(c, s, mask)
+        buf = io.BytesIO()
+        PIL.fromarray(ref).save(buf, "JPEG")
+        path = run_localized_style_transfer(str(tmp_path / "content.jpg"), None, output_path=str(tmp_path),
+                                            background_mask=mask, stylized_image=str(tmp_path / sty_name))
+        assert status == 0 and open(path, "rb").read() == buf.getvalue(), sty_name
+
+
+@pytest.mark.parametrize("cfmt,sfmt,H,W,sh,sw", [("JPEG", "JPEG", 360, 640, 256, 455), ("PNG", "JPEG", 270, 480, 270, 480),
+                                                 ("JPEG", "PNG", 97, 131, 64, 80), ("GRAY", "JPEG", 128, 192, 128, 192)])
+def test_files_entry_point_matches_pillow_plus_oracle(cfmt, sfmt, H, W, sh, sw):
+    """rct_transfer_files_host: file bytes in (JPEG on the device, PNG on the host, a grey JPEG replicated to RGB as
+    convert("RGB") does), mask, JPEG bytes out == Pillow decode -> oracle -> Pillow encode, byte for byte."""
+    import applied_image_processing_b200 as aip
+    from oracle import oracle as orc
+    from tests.synth import ellipse_mask, synth_image
+
+    def enc(a, fmt):
+        buf = io.BytesIO()
+        if fmt == "GRAY":
+            PIL.fromarray(a[..., 0]).save(buf, "JPEG", quality=85)
+        else:
+            PIL.fromarray(a).save(buf, fmt, **({"quality": 90} if fmt == "JPEG" else {}))
+        return buf.getvalue()
+
+    cf, sf = enc(synth_image(H, W, 3, "N"), cfmt), enc(synth_image(sh, sw, 4, "N"), sfmt)
+    mask = ellipse_mask(H, W, 0.45, 6)
+    c = np.array(PIL.open(io.BytesIO(cf)).convert("RGB"))
+    s = np.array(PIL.open(io.BytesIO(sf)).convert("RGB"))
+    ref, status, _ = orc.transfer(c, s, mask)
+    for q in (75, 92):
+        buf = io.BytesIO()
+        PIL.fromarray(ref).save(buf, "JPEG", quality=q)
+        got = aip.regional_color_transfer_files(cf, sf, mask, quality=q)
+        assert status == 0 and got == buf.getvalue(), (cfmt, sfmt, q)
+    assert aip.image_info(cf) == (H, W) and aip.image_info(sf) == (sh, sw)
+    with pytest.raises(ValueError, match="mask is"):
+        aip.regional_color_transfer_files(cf, sf, mask[:-1])
+
+
 @pytest.mark.parametrize("h,w,kw", [(270, 480, {}), (540, 960, {"quality": 90}), (1080, 1920, {}), (96, 128, {"subsampling": 0}),
                                     (37, 53, {"optimize": True})])
 def test_self_synchronising_decoder_matches_pillow(h, w, kw):
