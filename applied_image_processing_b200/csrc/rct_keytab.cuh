@@ -32,8 +32,9 @@
 //   total <= 1.3 * 3.7e-6 + 3.8e-6 = 8.6e-6 < kKtEpsKey = 2^-16 = 1.53e-5.  k_kt_keyerr measures the true maximum
 //   over all 2^24 colours for a frame's parameters (tests assert it stays below kKtEpsKey / 2).
 //   (the constant pmk = pm + klo enters as the addend of the first fma: its rounding, 2^-24 * 16, is inside the bound)
-// Cell coordinate c = (k~ - klo) * tscale in fp32, 0 <= c <= 65536: rounding of the product and of tscale
-//   <= 2 * 2^-24 * 65536 = 0.008 cells = 5e-4 coarse bins, round-to-nearest ties included: kKtEpsT = 2^-9.
+// Cell coordinate c = (k~ - kmin) * tscale in fp32, 0 <= c <= 65536, the cells spanning [smallest, largest] target
+//   key (+0.1 %): rounding of the product and of tscale <= 2 * 2^-24 * 65536 = 0.008 cells, round-to-nearest ties
+//   included: kKtEpsC = 1/64 cell.
 #pragma once
 
 struct KtView {
@@ -58,7 +59,7 @@ __device__ __forceinline__ KtRegs kt_load(const KtParams *p)
     r.tscale = __ldg(&p->tscale);
     return r;
 }
-// (w . lg2(M' rgb)) - pmk in fp32 = key - klo: the arithmetic whose error kKtEpsKey bounds
+// (w . lg2(M' rgb)) - pmk in fp32 = key - kmin: the arithmetic whose error kKtEpsKey bounds
 __device__ __forceinline__ float kt_dot(const KtRegs &r, uint32_t col)
 {
     // bytes -> floats without a conversion instruction: 0x4B0000kk is 8388608 + kk
@@ -88,37 +89,47 @@ __device__ __forceinline__ unsigned kt_lookup(const KtRegs &r, const KtView &v, 
 }
 
 // ---- builder ---------------------------------------------------------------------------------------------------
-// exact cell coordinate (coarse-bin units * kKtMult) of an exact key, for the builder
-__device__ __forceinline__ double kt_coord(const RegionCtrl *rc, double key) { return (key - rc->klo) * rc->cscale; }
-
-__device__ __forceinline__ bool kt_buildable(const FrameCtrl *fc, int interleave)
+// The cells span [kmin, kmax + 0.1 %] of the frame's target keys (k_match leaves both in KtParams by atomic max):
+// exact coordinate of a key = (key - kmin) * scale.  Keys above kmax do not exist; the top cells belong to the last run.
+struct KtGeom {
+    double kmin, scale;
+    bool ok;
+};
+__device__ __forceinline__ KtGeom kt_geom(const FrameCtrl *fc, const KtParams *par, int interleave)
 {
-    const RegionCtrl *rc = &fc->r[0];
-    return fc->status == 0 && interleave && fc->n_runs > 0 && fc->n_runs <= (unsigned)kKtRunCap && rc->cscale > 0.0 &&
-           rc->cscale < 1e300 && rc->d > 0;
+    KtGeom g;
+    g.ok = fc->status == 0 && interleave && fc->n_runs > 0 && fc->n_runs <= (unsigned)kKtRunCap && par->kmax_enc != 0ull;
+    g.kmin = g.scale = 0.0;
+    if (g.ok) {
+        const double kmax = ord_dec(par->kmax_enc);
+        g.kmin = ord_dec(~par->kmin_enc_inv);
+        const double span = (kmax - g.kmin) * 1.001;
+        g.ok = span > 0.0 && span < 1e300;
+        if (g.ok) g.scale = (double)(kKtCells - 1) / span;
+    }
+    return g;
 }
 
 // per run start (threshold key thr, sorted index i, colour): the cells c whose widened interval contains thr, i.e.
-//   c in [ M*((thr - epsK - klo)*cscale - epsT) - 0.5 , M*((thr + epsK - klo)*cscale + epsT) + 0.5 ],
+//   c in [ (thr - epsK - kmin) * scale - epsC - 0.5 , (thr + epsK - kmin) * scale + epsC + 0.5 ],
 // are flagged; the first cell after them is seeded with the run
 __global__ void __launch_bounds__(256) k_kt_mark(const FrameCtrl *ctrl, uint8_t *kt0, int interleave)
 {
     const int slot = blockIdx.y;
-    if (!kt_buildable(&ctrl[slot], interleave)) return;
     uint8_t *blk = kt0 + (size_t)slot * kKtBytes;
+    const KtGeom g = kt_geom(&ctrl[slot], reinterpret_cast<const KtParams *>(blk), interleave);
+    if (!g.ok) return;
     unsigned long long *seeds = reinterpret_cast<unsigned long long *>(blk + kKtOffSeeds);
     uint8_t *flags = blk + kKtOffFlags;
     const double *rkey = reinterpret_cast<const double *>(blk + kKtOffRunKey);
     const uint2 *ric = reinterpret_cast<const uint2 *>(blk + kKtOffRunIc);
-    const RegionCtrl *rc = &ctrl[slot].r[0];
     const unsigned n = ctrl[slot].n_runs;
     for (unsigned q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x) {
         const double thr = rkey[q];
         const uint2 ic = ric[q];
         // (the 1e-6 of a cell covers the fp64 rounding of these two expressions themselves, ~1e-10 of a cell)
-        double lo = ceil((double)kKtMult * (kt_coord(rc, thr - kKtEpsKey) - kKtEpsT) - 0.5 - 1e-6);
-        double hi = floor((double)kKtMult * (kt_coord(rc, thr + kKtEpsKey) + kKtEpsT) + 0.5 + 1e-6);
-        // keys clamped at the ends of the range share the edge cells with the thresholds out there
+        double lo = ceil((thr - kKtEpsKey - g.kmin) * g.scale - kKtEpsC - 0.5 - 1e-6);
+        double hi = floor((thr + kKtEpsKey - g.kmin) * g.scale + kKtEpsC + 0.5 + 1e-6);
         if (!(lo > 0.0)) lo = 0.0;
         if (!(hi > 0.0)) hi = 0.0;
         if (lo > (double)(kKtCells - 1)) lo = (double)(kKtCells - 1);
@@ -129,13 +140,17 @@ __global__ void __launch_bounds__(256) k_kt_mark(const FrameCtrl *ctrl, uint8_t 
     }
 }
 
-// one CTA of 1024 threads per slot: prefix maximum of the seeds -> cells
+// one CTA of 1024 threads per slot: prefix maximum of the seeds -> cells.  Warp w owns the contiguous chunk of
+// kKtChunk cells starting at w * kKtChunk and walks it 32 cells at a time (coalesced), twice: chunk maximum first,
+// then -- with the maxima of the chunks before it -- the running maximum per cell.
+constexpr int kKtChunk = (kKtCells + 31) / 32;
 __global__ void __launch_bounds__(1024) k_kt_fill(const FrameCtrl *ctrl, uint8_t *kt0, int interleave)
 {
     const int slot = blockIdx.x;
     uint8_t *blk = kt0 + (size_t)slot * kKtBytes;
     KtParams *par = reinterpret_cast<KtParams *>(blk);
-    if (!kt_buildable(&ctrl[slot], interleave)) {
+    const KtGeom g = kt_geom(&ctrl[slot], par, interleave);
+    if (!g.ok) {
         if (threadIdx.x == 0) {
             par->valid = 0;
             par->n_runs = ctrl[slot].n_runs;
@@ -145,39 +160,39 @@ __global__ void __launch_bounds__(1024) k_kt_fill(const FrameCtrl *ctrl, uint8_t
     const unsigned long long *seeds = reinterpret_cast<const unsigned long long *>(blk + kKtOffSeeds);
     const uint8_t *flags = blk + kKtOffFlags;
     unsigned *cells = reinterpret_cast<unsigned *>(blk + kKtOffCells);
-    constexpr int kPer = (kKtCells + 1023) / 1024;
-    const int c0 = threadIdx.x * kPer;
-    unsigned long long run = 0;
-    for (int k = 0; k < kPer; ++k) {
-        const int c = c0 + k;
-        if (c < kKtCells) {
-            const unsigned long long s = seeds[c];
-            run = s > run ? s : run;
-        }
-    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c0 = warp * kKtChunk, c1 = min(c0 + kKtChunk, kKtCells);
     __shared__ unsigned long long s_w[32];
-    unsigned long long inc = run;  // inclusive max-scan across the warp, then across the warps
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const unsigned long long y = __shfl_up_sync(0xffffffffu, inc, o);
-        if ((threadIdx.x & 31) >= o) inc = y > inc ? y : inc;
+    unsigned long long mx = 0;
+    for (int c = c0 + lane; c < c1; c += 32) {
+        const unsigned long long s = seeds[c];
+        mx = s > mx ? s : mx;
     }
-    if ((threadIdx.x & 31) == 31) s_w[threadIdx.x >> 5] = inc;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long y = __shfl_xor_sync(0xffffffffu, mx, o);
+        mx = y > mx ? y : mx;
+    }
+    if (lane == 0) s_w[warp] = mx;
     __syncthreads();
-    unsigned long long before = __shfl_up_sync(0xffffffffu, inc, 1);  // maximum over the lower lanes of this warp
-    if ((threadIdx.x & 31) == 0) before = 0;
-    for (unsigned w = 0; w < (threadIdx.x >> 5); ++w) before = s_w[w] > before ? s_w[w] : before;
+    unsigned long long carry = 0;
+    for (int w = 0; w < warp; ++w) carry = s_w[w] > carry ? s_w[w] : carry;
     unsigned flagged = 0;
-    run = before;
-    for (int k = 0; k < kPer; ++k) {
-        const int c = c0 + k;
-        if (c < kKtCells) {
-            const unsigned long long s = seeds[c];
-            run = s > run ? s : run;
-            const unsigned v = (flags[c] || run == 0ull) ? kKtFlag : (unsigned)run;
+    for (int base = c0; base < c1; base += 32) {  // warp-uniform trip count
+        const int c = base + lane;
+        unsigned long long inc = c < c1 ? seeds[c] : 0ull;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long y = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc = y > inc ? y : inc;
+        }
+        inc = carry > inc ? carry : inc;
+        if (c < c1) {
+            const unsigned v = (flags[c] || inc == 0ull) ? kKtFlag : (unsigned)inc;
             cells[c] = v;
             flagged += v == kKtFlag;
         }
+        carry = __shfl_sync(0xffffffffu, inc, 31);
     }
     if (flagged) atomicAdd(&par->n_flagged, flagged);
     if (threadIdx.x == 0) {
@@ -189,8 +204,10 @@ __global__ void __launch_bounds__(1024) k_kt_fill(const FrameCtrl *ctrl, uint8_t
             for (int j = 0; j < 3; ++j) a += rc->pca.comp[j] * c_mat[9 + 3 * j + i];
             par->w[i] = (float)(a * L2);
         }
-        par->pmk = (float)(rc->pca.pm + rc->klo);
-        par->tscale = (float)(rc->cscale * (double)kKtMult);
+        par->pmk = (float)(rc->pca.pm + g.kmin);
+        par->tscale = (float)g.scale;
+        par->kmin = g.kmin;
+        par->scale = g.scale;
         par->n_runs = ctrl[slot].n_runs;
         par->valid = 1;
     }
@@ -210,7 +227,7 @@ __global__ void __launch_bounds__(256) k_kt_keyerr(const FrameCtrl *ctrl, const 
     for (unsigned col = blockIdx.x * blockDim.x + threadIdx.x + 1u; col < kCube; col += gridDim.x * blockDim.x) {
         double lab[3];
         rgb2lab(col, &T, lab);
-        const double err = fabs((double)kt_dot(r, col) - (project(lab, comp, pm) - rc->klo));
+        const double err = fabs((double)kt_dot(r, col) - (project(lab, comp, pm) - v.par->kmin));
         worst = fmax(worst, err);
     }
 #pragma unroll

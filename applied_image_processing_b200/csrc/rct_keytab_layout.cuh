@@ -2,20 +2,21 @@
 // separate so that k_match (rct_sort.cuh), which records the run starts, can address the block.
 #pragma once
 
-constexpr int kKtMult = 16;                                // cells per coarse key bin
-constexpr int kKtCells = kCoarse * kKtMult + 1;            // cell c covers t * kKtMult in [c - 0.5, c + 0.5), t in [0, kCoarse]
+constexpr int kKtCells = 65537;                            // cell c covers the coordinate interval [c - 0.5, c + 0.5)
 constexpr int kKtRunCap = 16384;                           // run starts per frame the table is built for (else: LUT only)
 constexpr unsigned kKtFlag = 0x80000000u;                  // cell is ambiguous: resolve through the colour LUT
 constexpr double kKtEpsKey = 0x1p-16;
-constexpr double kKtEpsT = 0x1p-9;                         // in coarse-bin units
+constexpr double kKtEpsC = 1.0 / 64.0;                     // error bound of the fp32 cell coordinate, in cells
 
 struct KtParams {
     float m[9];        // RGB_TO_LMS / 255
     float w[3];        // log10(2) * (components_ @ LMS_TO_LAB)
-    float pmk, tscale; // cell coordinate = (w . lg2(lms) - pmk) * tscale, pmk = projected mean + lower end of the key range
+    float pmk, tscale; // cell coordinate = (w . lg2(lms) - pmk) * tscale, pmk = projected mean + smallest target key
     unsigned valid;    // 0: the apply pass uses the colour LUT only
     unsigned n_flagged, n_runs;
-    unsigned pad_[47];
+    unsigned long long kmax_enc, kmin_enc_inv;  // ord_enc(largest target key), ~ord_enc(smallest): atomic max by k_match
+    double kmin, scale;                         // the builder's exact coordinate: (key - kmin) * scale
+    unsigned pad_[38];
 };
 static_assert(sizeof(KtParams) == 256, "KtParams is one 256-byte block");
 

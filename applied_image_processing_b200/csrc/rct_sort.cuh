@@ -859,38 +859,37 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
         for (unsigned i = first; i < last; ++i) one(i);
         return;
     }
+    if (LUTM || !kt0) {
+        for (unsigned i = ps + threadIdx.x; i < pe; i += kMatchThreads) one(i);
+        return;
+    }
     // Run starts for the key table (rct_keytab.cuh): wherever the output colour differs from the previous sorted
     // entry's, (key, sorted index, colour) is appended to the slot's run list; every part opens a run, so parts are
-    // independent.
-    double *run_key = nullptr;
-    uint2 *run_ic = nullptr;
-    if (!LUTM && kt0) {
-        uint8_t *blk = kt0 + (size_t)slot * kKtBytes;
-        run_key = reinterpret_cast<double *>(blk + kKtOffRunKey);
-        run_ic = reinterpret_cast<uint2 *>(blk + kKtOffRunIc);
+    // independent.  Each warp takes groups of 31 consecutive entries and lane 0 re-evaluates the entry before the
+    // group, so the comparison with the predecessor is a warp shuffle: no shared memory, no CTA barrier (the kernel
+    // is latency-bound; a barrier per sweep cost 5-10 % of it), 3 % redundant evaluations.
+    uint8_t *blk = kt0 + (size_t)slot * kKtBytes;
+    KtParams *par = reinterpret_cast<KtParams *>(blk);
+    double *run_key = reinterpret_cast<double *>(blk + kKtOffRunKey);
+    uint2 *run_ic = reinterpret_cast<uint2 *>(blk + kKtOffRunIc);
+    if (threadIdx.x == 0) {  // extremes of the target keys: the key table's cell range
+        atomicMax(&par->kmin_enc_inv, ~ord_enc(key_at(t, ps)));
+        atomicMax(&par->kmax_enc, ord_enc(key_at(t, pe - 1)));
     }
-    __shared__ unsigned s_tail[kMatchThreads / 32];
-    __shared__ unsigned s_carry;
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    for (unsigned base = ps; base < pe; base += kMatchThreads) {
-        const unsigned i = base + threadIdx.x;
-        const bool live = i < pe;
+    constexpr unsigned kWarps = kMatchThreads / 32;
+    for (unsigned g0 = ps + 31u * warp; g0 < pe; g0 += 31u * kWarps) {  // warp-uniform
+        const unsigned i = g0 + lane - 1u;                               // lane 0: the entry before the group
+        const bool live = (lane > 0u || g0 > ps) && i < pe;
         unsigned rgb = 0xffffffffu;
-        if (live) rgb = one(i);
-        if (run_key) {  // uniform across the CTA
-            unsigned prev = __shfl_up_sync(0xffffffffu, rgb, 1);
-            if (lane == 31) s_tail[warp] = rgb;
-            __syncthreads();
-            if (lane == 0) prev = warp ? s_tail[warp - 1] : (base == ps ? 0xffffffffu : s_carry);
-            if (live && rgb != prev) {
-                const unsigned idx = atomicAdd(&ctrl[slot].n_runs, 1u);
-                if (idx < (unsigned)kKtRunCap) {
-                    run_key[idx] = key_at(t, i);
-                    run_ic[idx] = make_uint2(i, rgb);  // the sorted index orders the runs without a sort
-                }
+        if (live) rgb = one(i);  // lane 0 stores the same values its owner stored: benign
+        const unsigned prev = __shfl_up_sync(0xffffffffu, rgb, 1);
+        if (lane > 0u && live && rgb != prev) {  // lane 1 of the part's first group sees the sentinel: forced start
+            const unsigned idx = atomicAdd(&ctrl[slot].n_runs, 1u);
+            if (idx < (unsigned)kKtRunCap) {
+                run_key[idx] = key_at(t, i);
+                run_ic[idx] = make_uint2(i, rgb);  // the sorted index orders the runs without a sort
             }
-            __syncthreads();
-            if (threadIdx.x == kMatchThreads - 1) s_carry = rgb;
         }
     }
 }

@@ -79,6 +79,9 @@ def parse_args():
     ap.add_argument("--sty-short", type=int, default=0,
                     help="stylised frames at this short-side size (512 = what AdaIN's Resize(512) hands the reference, "
                          "LST:223-230), NEAREST-resampled inside the kernels; 0 = same size as the content")
+    ap.add_argument("--files", type=int, default=1, choices=[0, 1],
+                    help="4k / 1080p workloads on one GPU: also report e2e_files, the same transfer through the reference's real "
+                         "boundary (JPEG files in, JPEG file out; rct_transfer_files_host) beside PIL decode + C port + PIL encode")
     ap.add_argument("--bins", type=int, default=0,
                     help="0 (default): the reference's exact CDF matching (the parity path); > 0: the BINNED approximation with "
                          "this many histogram bins (BASELINE.json configs[4] '1024-bin histograms'; reported separately, never "
@@ -237,6 +240,55 @@ def run_reference_arm(a):
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def files_leg(a, aip, cs, ss, ms, H, W):
+    """The step's frames as JPEG files (Pillow defaults) through regional_color_transfer_files (device decode ->
+    transfer -> device encode; file bytes and the mask cross PCIe, not pixels), and -- on a sample, one frame per host
+    thread -- the same thing on the CPU: PIL decode + C port + PIL encode.  Lossy inputs: parity here is against the
+    CPU chain on the SAME files, asserted byte for byte on the sample."""
+    import io
+    from concurrent.futures import ThreadPoolExecutor
+
+    from PIL import Image
+
+    from oracle import oracle as orc
+
+    def enc(arr):
+        buf = io.BytesIO()
+        Image.fromarray(arr).save(buf, "JPEG")
+        return buf.getvalue()
+
+    n = cs.shape[0]
+    cf, sf = [enc(cs[i]) for i in range(n)], [enc(ss[i]) for i in range(n)]
+    outs = [aip.regional_color_transfer_files(cf[i], sf[i], ms[i]) for i in range(min(2, n))]  # warm-up
+    t0 = time.perf_counter()
+    reps = 2
+    for _ in range(reps):
+        outs = [aip.regional_color_transfer_files(cf[i], sf[i], ms[i]) for i in range(n)]
+    t = (time.perf_counter() - t0) / reps
+    nc, threads = cpu_sample_size(a)
+    nc = min(nc, n)
+
+    def cpu_one(i):
+        c = np.array(Image.open(io.BytesIO(cf[i])).convert("RGB"))
+        s = np.array(Image.open(io.BytesIO(sf[i])).convert("RGB"))
+        buf = io.BytesIO()
+        Image.fromarray(orc.transfer(c, s, ms[i])[0]).save(buf, "JPEG")
+        return buf.getvalue()
+
+    t1 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=min(threads, nc)) as ex:
+        refs = list(ex.map(cpu_one, range(nc)))
+    t_cpu = time.perf_counter() - t1
+    for i in range(nc):
+        assert outs[i] == refs[i], f"e2e_files: frame {i} differs from PIL decode + oracle + PIL encode"
+    file_bytes = sum(len(x) for x in cf) + sum(len(x) for x in sf)
+    return {"value": n * H * W / 1e6 / t, "unit": UNIT, "ms_per_step": 1e3 * t, "frames": n,
+            "h2d_bytes_per_step": int(file_bytes + ms.size), "d2h_bytes_per_step": int(sum(len(x) for x in outs)),
+            "input": "the step's frames as JPEG files (Pillow defaults: quality 75, 4:2:0)", "parity_checked_files": nc,
+            "cpu_files_reference": {"value": nc * H * W / 1e6 / t_cpu, "unit": UNIT, "cores": min(threads, nc),
+                                    "what": "PIL decode x2 + C port + PIL encode, one frame per thread"}}
 
 
 # ---- clocks during the timed region -----------------------------------------------------------------
@@ -506,6 +558,11 @@ def run_gpu_arm(a):
                             "steps": ksteps, "host_buffers": "pageable numpy arrays in and out"}
             assert np.array_equal(po, hon)
 
+    # ---- e2e_files: the reference's real boundary (LST:191-245: files in, file out), one C-ABI call per frame ------
+    e2e_files = None
+    if world == 1 and a.files and not labels and not a.bins and not a.no_e2e:
+        e2e_files = files_leg(a, aip, cs, ss, ms, H, W)
+
     # ---- CPU baseline: C port of the reference on this box's host cores (rank 0, N=1 only) ------------
     cpu = None
     parity_frames = 0
@@ -530,7 +587,7 @@ def run_gpu_arm(a):
             "dtype": "f64", "data": "synthetic",
             "config": config_dict(a, world),
             "clocks": clocks, "e2e": e2e, "e2e_pageable": e2e_pageable, "gpu_launches": launches, "roofline": roofline,
-            "cpu_baseline": cpu, "parity_checked_frames": parity_frames,
+            "cpu_baseline": cpu, "parity_checked_frames": parity_frames, "e2e_files": e2e_files,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -607,6 +664,24 @@ def run_gpu_16k(a, torch, dist, world, rank, local, dev, barrier, max_over_ranks
                                  if world > 1 and phases["allreduce_ms"] > 0 else None),
         "pipeline_achieved_GBps_all_gpus": 10.0 * H * W / 1e9 / (ms_step * 1e-3),
     }
+    # the collective alone, on the plan's buffer and on a plain torch tensor of the same size (68 GB/s at
+    # N = 8 on the plan's buffer was never explained)
+    if world > 1 and not a.bins:
+        probe = {}
+        plain = torch.zeros(hist_bytes // 4, dtype=torch.int32, device=dev)
+        for name, buf in (("plan_buffer", tr.hist), ("torch_tensor", plain)):
+            for _ in range(2):
+                dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+            barrier()
+            ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ea.record()
+            for _ in range(5):
+                dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+            eb.record()
+            barrier()
+            ms = max_over_ranks(ea.elapsed_time(eb) / 5)
+            probe[name] = {"ms": ms, "busbw_GBps": 2.0 * (world - 1) / world * hist_bytes / 1e9 / (ms * 1e-3)}
+        roofline["allreduce_alone"] = probe
     e2e = None
     if not a.no_e2e:
         def api_call():
