@@ -164,7 +164,8 @@ __global__ void __launch_bounds__(1024) k_kt_fill(const FrameCtrl *ctrl, uint8_t
     const int c0 = warp * kKtChunk, c1 = min(c0 + kKtChunk, kKtCells);
     __shared__ unsigned long long s_w[32];
     unsigned long long mx = 0;
-    for (int c = c0 + lane; c < c1; c += 32) {
+#pragma unroll 8
+    for (int c = c0 + lane; c < c1; c += 32) {  // independent loads: all in flight at once
         const unsigned long long s = seeds[c];
         mx = s > mx ? s : mx;
     }
@@ -178,21 +179,36 @@ __global__ void __launch_bounds__(1024) k_kt_fill(const FrameCtrl *ctrl, uint8_t
     unsigned long long carry = 0;
     for (int w = 0; w < warp; ++w) carry = s_w[w] > carry ? s_w[w] : carry;
     unsigned flagged = 0;
-    for (int base = c0; base < c1; base += 32) {  // warp-uniform trip count
-        const int c = base + lane;
-        unsigned long long inc = c < c1 ? seeds[c] : 0ull;
+    constexpr int kRows = 8;  // rows of 32 cells loaded together (the scan itself is a dependent chain)
+    for (int base = c0; base < c1; base += 32 * kRows) {  // warp-uniform trip count
+        unsigned long long sv[kRows];
+        unsigned fv[kRows];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const unsigned long long y = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc = y > inc ? y : inc;
+        for (int r = 0; r < kRows; ++r) {
+            const int c = base + 32 * r + lane;
+            sv[r] = c < c1 ? seeds[c] : 0ull;
+            fv[r] = c < c1 ? (unsigned)flags[c] : 0u;
         }
-        inc = carry > inc ? carry : inc;
-        if (c < c1) {
-            const unsigned v = (flags[c] || inc == 0ull) ? kKtFlag : (unsigned)inc;
-            cells[c] = v;
-            flagged += v == kKtFlag;
+#pragma unroll
+        for (int r = 0; r < kRows; ++r) {
+            const int c = base + 32 * r + lane;
+            // the seeds of a row rarely number more than one: reduce to the row maximum first, scan only if needed
+            unsigned long long inc = sv[r];
+            if (__any_sync(0xffffffffu, inc != 0ull)) {
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const unsigned long long y = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc = y > inc ? y : inc;
+                }
+            }
+            inc = carry > inc ? carry : inc;
+            if (c < c1) {
+                const unsigned v = (fv[r] || inc == 0ull) ? kKtFlag : (unsigned)inc;
+                cells[c] = v;
+                flagged += v == kKtFlag;
+            }
+            carry = __shfl_sync(0xffffffffu, inc, 31);
         }
-        carry = __shfl_sync(0xffffffffu, inc, 31);
     }
     if (flagged) atomicAdd(&par->n_flagged, flagged);
     if (threadIdx.x == 0) {

@@ -835,9 +835,9 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
     // search starts from the position interpolated inside the source part.  Otherwise every
     // thread takes one contiguous run of entries and carries its search position along.
     hs.fresh = interleave != 0;
-    auto one = [&](unsigned i) -> unsigned {
+    auto one_in = [&](unsigned part, unsigned i) -> unsigned {
         long long j;
-        double m = match_one(t, s, p, i, ht, hs, j);
+        double m = match_one(t, s, part, i, ht, hs, j);
         double lab[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) lab[c] = m * pca.comp[c] + pca.mean[c];  // inverse_transform
@@ -852,6 +852,7 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
         }
         return rgb;
     };
+    auto one = [&](unsigned i) -> unsigned { return one_in(p, i); };
     if (!interleave) {
         const unsigned per = (pe - ps + kMatchThreads - 1) / kMatchThreads;
         const unsigned first = ps + threadIdx.x * per;
@@ -864,10 +865,11 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
         return;
     }
     // Run starts for the key table (rct_keytab.cuh): wherever the output colour differs from the previous sorted
-    // entry's, (key, sorted index, colour) is appended to the slot's run list; every part opens a run, so parts are
-    // independent.  Each warp takes groups of 31 consecutive entries and lane 0 re-evaluates the entry before the
-    // group, so the comparison with the predecessor is a warp shuffle: no shared memory, no CTA barrier (the kernel
-    // is latency-bound; a barrier per sweep cost 5-10 % of it), 3 % redundant evaluations.
+    // entry's, (key, sorted index, colour) is appended to the slot's run list.  Each warp takes groups of 31
+    // consecutive entries and lane 0 re-evaluates the entry before the group -- for the part's first group that is the
+    // last entry of the previous non-empty part -- so the comparison with the predecessor is a warp shuffle: no shared
+    // memory, no CTA barrier (the kernel is latency-bound; a barrier per sweep cost 5-10 % of it), no dependency
+    // between CTAs, 3 % redundant evaluations.  Only the region's very first entry opens a run unconditionally.
     uint8_t *blk = kt0 + (size_t)slot * kKtBytes;
     KtParams *par = reinterpret_cast<KtParams *>(blk);
     double *run_key = reinterpret_cast<double *>(blk + kKtOffRunKey);
@@ -880,11 +882,18 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
     constexpr unsigned kWarps = kMatchThreads / 32;
     for (unsigned g0 = ps + 31u * warp; g0 < pe; g0 += 31u * kWarps) {  // warp-uniform
         const unsigned i = g0 + lane - 1u;                               // lane 0: the entry before the group
-        const bool live = (lane > 0u || g0 > ps) && i < pe;
+        const bool live = (lane > 0u || g0 > 0u) && i < pe;
         unsigned rgb = 0xffffffffu;
-        if (live) rgb = one(i);  // lane 0 stores the same values its owner stored: benign
+        if (live) {  // lane 0 stores the same values its owner stored: benign
+            unsigned part = p;
+            if (i < ps) {  // the predecessor of the part's first entry lives in the previous non-empty part
+                part = p - 1u;
+                while (part > 0u && __ldg(t.pstart + part) > i) --part;
+            }
+            rgb = one_in(part, i);
+        }
         const unsigned prev = __shfl_up_sync(0xffffffffu, rgb, 1);
-        if (lane > 0u && live && rgb != prev) {  // lane 1 of the part's first group sees the sentinel: forced start
+        if (lane > 0u && live && rgb != prev) {  // entry 0 of the region sees the sentinel: the first run
             const unsigned idx = atomicAdd(&ctrl[slot].n_runs, 1u);
             if (idx < (unsigned)kKtRunCap) {
                 run_key[idx] = key_at(t, i);
