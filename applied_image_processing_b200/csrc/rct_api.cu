@@ -753,7 +753,7 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
             CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 3>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8, 3>)));
             CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 2, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8, 2, true>)));
             CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 2, false, 1>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
-            CK(cudaFuncSetAttribute((k_apply_warp<true, 8, 4, 2, false, 2>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
+            CK(cudaFuncSetAttribute(k_apply_kt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AwSmem<8>)));
             CK(cudaFuncSetAttribute((k_apply_warp<true, 16, 3>), cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             CK(cudaFuncSetAttribute(k_apply_tma, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             attr_dev = dev;
@@ -789,7 +789,7 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
             else if (p->apply_tma == 5)
                 k_apply_warp<true, 8, 5><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
             else if (b.kt)
-                k_apply_warp<true, 8, 4, 2, false, 2><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
+                k_apply_kt<<<grid, 256, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
             else
                 k_apply_warp<true, 8, 4><<<grid, AwCfg<8>::kThreads, sizeof(AwSmem<8>), st>>>(b, (unsigned)tiles, (unsigned)nslots);
         }
@@ -835,9 +835,6 @@ int phase_apply(rct_plan *p, const FrameSet &f, int nslots, int mode, int label,
     if (p->lut_mode) {
         if (p->resample) LAUNCH((k_apply<true, 1>), grid, 256, st, a);
         else LAUNCH((k_apply<false, 1>), grid, 256, st, a);
-    } else if (a.kt) {
-        if (p->resample) LAUNCH((k_apply<true, 2>), grid, 256, st, a);
-        else LAUNCH((k_apply<false, 2>), grid, 256, st, a);
     } else if (p->resample) LAUNCH(k_apply<true>, grid, 256, st, a);
     else LAUNCH(k_apply<false>, grid, 256, st, a);
     KMARK(RCT_TK_APPLY);

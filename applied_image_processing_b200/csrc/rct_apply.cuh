@@ -15,7 +15,8 @@
 
 // k_apply: a-7..a-9 for pixels: target non-black -> LUT[colour]; target black -> black;
 // MASK mode non-target -> stylised pixel (background_np); LABEL mode non-target untouched.
-// LUTM: 0 colour table, 1 uint16 run index + palette, 2 key table in front of the colour table (rct_keytab.cuh)
+// LUTM: 0 colour table, 1 uint16 run index + palette.  (The key table of rct_keytab.cuh is not used here: with the
+// resample gathers in the same thread the extra arithmetic made this kernel slower, 0.143 vs 0.115 ms on 8 x 1080p.)
 template <bool RESAMPLE, int LUTM = 0>
 __global__ void __launch_bounds__(256, 3) k_apply(PixArgs a)
 {
@@ -35,14 +36,6 @@ __global__ void __launch_bounds__(256, 3) k_apply(PixArgs a)
     const bool vec_m = mask && (((uintptr_t)(mask + a.p_begin)) & 15) == 0;
     const bool vec_o = (((uintptr_t)(out + 3 * a.p_begin)) & 15) == 0;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
-    KtView kv{};
-    KtRegs kr{};
-    bool kt_ok = false;
-    if (LUTM == 2 && a.kt) {
-        kv = kt_view(a.kt, (size_t)slot);
-        kt_ok = __ldg(&kv.par->valid) != 0u;
-        if (kt_ok) kr = kt_load(kv.par);
-    }
     for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += stride) {
         size_t p0 = a.p_begin + 16 * g;
         int nvalid = (int)min((size_t)16, a.p_end - p0);
@@ -64,22 +57,11 @@ __global__ void __launch_bounds__(256, 3) k_apply(PixArgs a)
             if (in_t || a.mode == 0) keep |= 1u << k;
         }
         uint32_t t[16];
-        if (LUTM == 2 && kt_ok) {  // warp-uniform: the slot's key table resolves most pixels, flagged cells gather
 #pragma unroll
-            for (int k = 0; k < 16; ++k) t[k] = kt_lookup(kr, kv, c[k]);
-#pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                const bool fb = ((tgt >> k) & 1u) && status == 0 && k < nvalid && (t[k] & kKtFlag);
-                const uint32_t v = __ldg(lut + (fb ? c[k] : 0u));
-                if (fb) t[k] = v;
-            }
-        } else {
-#pragma unroll
-            for (int k = 0; k < 16; ++k)
-            {
-                const uint32_t idx = (((tgt >> k) & 1u) && status == 0 && k < nvalid) ? c[k] : 0u;
-                t[k] = LUTM == 1 ? (uint32_t)__ldg(reinterpret_cast<const unsigned short *>(lut) + idx) : __ldg(lut + idx);
-            }
+        for (int k = 0; k < 16; ++k)
+        {
+            const uint32_t idx = (((tgt >> k) & 1u) && status == 0 && k < nvalid) ? c[k] : 0u;
+            t[k] = LUTM == 1 ? (uint32_t)__ldg(reinterpret_cast<const unsigned short *>(lut) + idx) : __ldg(lut + idx);
         }
         if (LUTM == 1) {
 #pragma unroll
@@ -447,7 +429,11 @@ __device__ __forceinline__ void apply8(const uint32_t wc[6], const uint32_t ws[6
                 for (int k = 0; k < 8; ++k) {
                     const bool fb = (amb >> k) & 1u;
                     const unsigned *g = lut + (fb ? c[k] : 0u);
+#ifdef RCT_KT_PLAINLDG
+                    const uint32_t v = __ldg(g);
+#else
                     const uint32_t v = HINT ? ldg_hint(g, pol_lut) : __ldg(g);
+#endif
                     if (fb) t[k] = v;
                 }
             }
@@ -864,5 +850,112 @@ __global__ void __launch_bounds__(256, 4) k_apply_warp_rs(PixArgs a, unsigned ti
             stg8_hint(qo + 8, wo[2], wo[3], pol_stream);
             stg8_hint(qo + 16, wo[4], wo[5], pol_stream);
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// k_apply_kt: the default fused apply pass (MASK mode, same geometry, 16-byte aligned frames): the per-warp
+// two-stage bulk-async pipeline of k_apply_warp<true, 8, 4> with the key table (rct_keytab.cuh) in front of the
+// colour LUT -- and a lean tile loop.  With the LUT gathers gone the pass is issue-bound (ncu r02: issue slots 70 %
+// busy, DRAM 58 %), and 230 of the ~540 warp instructions per tile were loop overhead: two integer divisions for
+// the tile geometry, per-tile reloads of the frame's status / LUT base / key-table parameters.  Here the geometry
+// of the tile to prefetch advances incrementally (no division), the tile consumed next inherits it, and everything
+// that depends on the frame alone is reloaded only when the frame changes.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256, 4) k_apply_kt(PixArgs a, unsigned tiles_per_frame, unsigned nslots)
+{
+    constexpr int kWarps = 8, kTile = 256;
+    extern __shared__ __align__(128) uint8_t aw_smem_raw[];
+    AwSmem<8> &S = *reinterpret_cast<AwSmem<8> *>(aw_smem_raw);
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    AwWarpSmem<8> &W = S.w[warp];
+    const unsigned total = tiles_per_frame * nslots;
+    if (a.status_out && blockIdx.x == 0)
+        for (unsigned q = threadIdx.x; q < nslots; q += 256u) a.status_out[q] = a.ctrl[q].status;
+    if (lane == 0) {
+        mbar_init(&S.full[warp][0], 1u);
+        mbar_init(&S.full[warp][1], 1u);
+        fence_mbar_init();
+        fence_proxy_async();
+    }
+    __syncwarp();
+    const unsigned GW = gridDim.x * kWarps;
+    unsigned Tn = blockIdx.x * kWarps + warp;  // global index of the next tile to prefetch
+    if (Tn >= total) return;
+    const unsigned long long pol_stream = l2_policy_evict_first(), pol_lut = l2_policy_evict_last();
+    const unsigned npix = (unsigned)(a.p_end - a.p_begin);  // per frame, a multiple of 16 (< 2^32: plan limit)
+    unsigned slot_n = Tn / tiles_per_frame, t_n = Tn - slot_n * tiles_per_frame;  // the only division
+
+    auto issue = [&](unsigned st, unsigned slot, unsigned t) {
+        if (lane == 0) {
+            const unsigned off = t * (unsigned)kTile, left = npix - off, n = left < (unsigned)kTile ? left : (unsigned)kTile;
+            const size_t p0 = a.p_begin + off;
+            mbar_expect_tx(&S.full[warp][st], 7u * n);
+            bulk_g2s_hint(W.c[st], a.content + (size_t)slot * a.content_stride + 3 * p0, 3u * n, &S.full[warp][st], pol_stream);
+            bulk_g2s_hint(W.s[st], a.sty + (size_t)slot * a.sty_stride + 3 * p0, 3u * n, &S.full[warp][st], pol_stream);
+            bulk_g2s_hint(W.m[st], a.mask + (size_t)slot * a.mask_stride + p0, n, &S.full[warp][st], pol_stream);
+        }
+    };
+    auto advance = [&]() {
+        Tn += GW;
+        t_n += GW;
+        while (t_n >= tiles_per_frame) {
+            t_n -= tiles_per_frame;
+            ++slot_n;
+        }
+    };
+    unsigned slot_c = slot_n, t_c = t_n;  // the tile consumed next
+    issue(0u, slot_n, t_n);
+    advance();
+    // per-frame state, reloaded when the frame changes
+    unsigned cur_slot = 0xffffffffu;
+    const unsigned *lut = nullptr;
+    uint8_t *out = nullptr;
+    int status = 0;
+    bool kt_ok = false;
+    KtRegs kr{};
+    KtView kv{};
+    for (unsigned i = 0;; ++i) {
+        const unsigned st = i & 1u;
+        const bool more = Tn < total;
+        const unsigned slot_x = slot_n, t_x = t_n;
+        if (more) {  // the other stage was released by the __syncwarp ending the previous iteration
+            issue(st ^ 1u, slot_n, t_n);
+            advance();
+        }
+        mbar_wait(&S.full[warp][st], (i >> 1) & 1u);
+        if (slot_c != cur_slot) {  // warp-uniform
+            cur_slot = slot_c;
+            lut = a.lut + (size_t)slot_c * a.lut_stride;
+            out = a.out + (size_t)slot_c * a.out_stride + 3 * a.p_begin;
+            status = a.ctrl[slot_c].status;
+            kv = kt_view(a.kt, slot_c);
+            kt_ok = a.kt != nullptr && __ldg(&kv.par->valid) != 0u;
+            if (kt_ok) kr = kt_load(kv.par);
+        }
+        const unsigned off = t_c * (unsigned)kTile, left = npix - off, n = left < (unsigned)kTile ? left : (unsigned)kTile;
+        const bool active = lane * 8u < n;
+        uint32_t wc[6], ws[6], wm[2], wo[6];
+        if (active) {
+            const uint2 *qc = reinterpret_cast<const uint2 *>(W.c[st] + 24u * lane);
+            const uint2 *qs = reinterpret_cast<const uint2 *>(W.s[st] + 24u * lane);
+            const uint2 x0 = qc[0], x1 = qc[1], x2 = qc[2], y0 = qs[0], y1 = qs[1], y2 = qs[2];
+            const uint2 z = *reinterpret_cast<const uint2 *>(W.m[st] + 8u * lane);
+            wc[0] = x0.x; wc[1] = x0.y; wc[2] = x1.x; wc[3] = x1.y; wc[4] = x2.x; wc[5] = x2.y;
+            ws[0] = y0.x; ws[1] = y0.y; ws[2] = y1.x; ws[3] = y1.y; ws[4] = y2.x; ws[5] = y2.y;
+            wm[0] = z.x; wm[1] = z.y;
+        }
+        __syncwarp();  // the stage is read: the next iteration may refill it
+        if (active) {
+            if (kt_ok) apply8<true, 2>(wc, ws, wm, lut, status, wo, pol_lut, &kr, &kv);
+            else apply8<true, 0>(wc, ws, wm, lut, status, wo, pol_lut);
+            uint8_t *qo = out + 3u * (size_t)off + 24u * lane;
+            stg8_hint(qo, wo[0], wo[1], pol_stream);
+            stg8_hint(qo + 8, wo[2], wo[3], pol_stream);
+            stg8_hint(qo + 16, wo[4], wo[5], pol_stream);
+        }
+        if (!more) break;
+        slot_c = slot_x;
+        t_c = t_x;
     }
 }

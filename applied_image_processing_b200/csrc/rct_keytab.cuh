@@ -80,8 +80,13 @@ __device__ __forceinline__ float kt_dot(const KtRegs &r, uint32_t col)
 __device__ __forceinline__ unsigned kt_cell(const KtRegs &r, uint32_t col)
 {
     float c = kt_dot(r, col) * r.tscale;
+#if RCT_KT_NOCLAMP
+    // no clamp: coordinates a little outside [0, 65536] (error bound) land in flagged entries, see kKtCellsAlloc
+    return __float_as_uint(c + 8388608.f) & 0x1ffffu;
+#else
     c = fminf(fmaxf(c, 0.f), (float)(kKtCells - 1));      // also catches NaN (black, never looked up)
     return __float_as_uint(c + 8388608.f) & 0x1ffffu;     // 0 .. 65536
+#endif
 }
 __device__ __forceinline__ unsigned kt_lookup(const KtRegs &r, const KtView &v, uint32_t col)
 {
@@ -106,6 +111,7 @@ __device__ __forceinline__ KtGeom kt_geom(const FrameCtrl *fc, const KtParams *p
         const double span = (kmax - g.kmin) * 1.001;
         g.ok = span > 0.0 && span < 1e300;
         if (g.ok) g.scale = (double)(kKtCells - 1) / span;
+        if (g.ok && kKtEpsKey * g.scale + kKtEpsC > kKtSlackCells) g.ok = false;  // a near-flat region: the LUT alone
     }
     return g;
 }
@@ -210,6 +216,7 @@ __global__ void __launch_bounds__(1024) k_kt_fill(const FrameCtrl *ctrl, uint8_t
             carry = __shfl_sync(0xffffffffu, inc, 31);
         }
     }
+    for (int c = kKtCells + (int)threadIdx.x; c < kKtCellsAlloc; c += 1024) cells[c] = kKtFlag;
     if (flagged) atomicAdd(&par->n_flagged, flagged);
     if (threadIdx.x == 0) {
         const RegionCtrl *rc = &ctrl[slot].r[0];

@@ -3,6 +3,14 @@
 #pragma once
 
 constexpr int kKtCells = 65537;                            // cell c covers the coordinate interval [c - 0.5, c + 0.5)
+// The table holds 2^17 entries: the apply pass masks the rounded coordinate instead of clamping it, and every entry
+// above kKtCells - 1 is flagged.  Real target colours stay below 2^16 + kKtSlackCells cells by the error bound (the
+// builder refuses frames whose bound is wider); whatever an unwanted lane (background pixel, black) computes is never used.
+#ifndef RCT_KT_NOCLAMP
+#define RCT_KT_NOCLAMP 1
+#endif
+constexpr int kKtCellsAlloc = RCT_KT_NOCLAMP ? 131072 : 65537;
+constexpr double kKtSlackCells = 1024.0;
 constexpr int kKtRunCap = 16384;                           // run starts per frame the table is built for (else: LUT only)
 constexpr unsigned kKtFlag = 0x80000000u;                  // cell is ambiguous: resolve through the colour LUT
 constexpr double kKtEpsKey = 0x1p-16;
@@ -28,7 +36,7 @@ constexpr size_t kt_align(size_t v) { return (v + 255) / 256 * 256; }
 constexpr size_t kKtOffSeeds = 256;
 constexpr size_t kKtOffFlags = kKtOffSeeds + kt_align((size_t)kKtCells * 8);
 constexpr size_t kKtOffCells = kKtOffFlags + kt_align((size_t)kKtCells);
-constexpr size_t kKtOffRunKey = kKtOffCells + kt_align((size_t)kKtCells * 4);
+constexpr size_t kKtOffRunKey = kKtOffCells + kt_align((size_t)kKtCellsAlloc * 4);
 constexpr size_t kKtOffRunIc = kKtOffRunKey + (size_t)kKtRunCap * 8;
 constexpr size_t kKtBytes = kKtOffRunIc + (size_t)kKtRunCap * 8;
 constexpr size_t kKtZeroBytes = kKtOffCells;

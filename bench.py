@@ -580,6 +580,11 @@ def run_gpu_arm(a):
             assert nbad == 0, f"bench parity: frame {i}: {nbad} bytes differ from the oracle"
         parity_frames = nc
 
+    if a.keytab and not a.lut and not a.bins and not labels:  # key-table self-check of the last launch group's first frame
+        try:
+            roofline["keytab_slot0"] = plan.debug_keytab(0, key_error=False)
+        except Exception as e:  # noqa: BLE001
+            roofline["keytab_slot0"] = {"error": str(e)}
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
