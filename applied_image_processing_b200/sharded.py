@@ -139,6 +139,12 @@ class ShardedTransfer:
 
     # ---- binned mode: the only cross-GPU state is 56 integers, 4 doubles and 2 x bins counters ----------
     def _xchg(self, which, bins):
+        cache = self.__dict__.setdefault("_xchg_views", {})
+        if (which, bins) not in cache:
+            cache[(which, bins)] = self._xchg_view(which, bins)
+        return cache[(which, bins)]
+
+    def _xchg_view(self, which, bins):
         L = _cabi.lib()
         ptr = L.rct_plan_xchg_ptr(self.plan.handle)
         nbytes = L.rct_plan_xchg_bytes(which, bins)
