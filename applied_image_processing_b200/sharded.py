@@ -86,6 +86,12 @@ class ShardedTransfer:
         self._via_host = backend == "gloo"
         self._ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
         self.last_ms = None
+        self.host_s = {}   # host seconds spent ENQUEUEING each phase / collective (perf_counter; the calls are async)
+
+    def _host(self, name, t0):
+        import time
+
+        self.host_s[name] = self.host_s.get(name, 0.0) + (time.perf_counter() - t0)
 
     def allreduce(self):
         if self.world == 1:
@@ -120,18 +126,28 @@ class ShardedTransfer:
         with torch.cuda.device(self.device), self.plan.lock:
             if timed:
                 ev[0].record(st)
+            import time
+
+            t0 = time.perf_counter()
             check(L.rct_shard_hist_async(self.plan.handle, c_ptr, s_ptr, m_ptr, mode, label, self.row0,
                                          self.rows, sp))
+            self._host("hist", t0)
             if timed:
                 ev[1].record(st)
+            t0 = time.perf_counter()
             self.allreduce()
+            self._host("allreduce", t0)
             if timed:
                 ev[2].record(st)
+            t0 = time.perf_counter()
             check(L.rct_shard_solve_async(self.plan.handle, sp))
+            self._host("solve", t0)
             if timed:
                 ev[3].record(st)
+            t0 = time.perf_counter()
             check(L.rct_shard_apply_async(self.plan.handle, c_ptr, s_ptr, m_ptr, o_ptr, mode, label,
                                           self.row0, self.rows, sp))
+            self._host("apply", t0)
             if timed:
                 ev[4].record(st)
         self._timed = timed
@@ -189,12 +205,18 @@ class ShardedTransfer:
             for phase in range(4):
                 if timed:
                     ev[2 * phase].record(st)
+                import time
+
+                t0 = time.perf_counter()
                 check(L.rct_shard_binned_phase_async(self.plan.handle, phase, c_ptr, s_ptr, m_ptr, o_ptr, mode, label,
                                                      self.row0, self.rows, int(bins), sp))
+                self._host(f"phase{phase}", t0)
                 if timed:
                     ev[2 * phase + 1].record(st)
                 if phase < 3:
+                    t0 = time.perf_counter()
                     self._allreduce_small(self._xchg(phase, bins), ops[phase])
+                    self._host("allreduce", t0)
         return out_band
 
     def binned_phase_ms(self):

@@ -626,14 +626,20 @@ def run_gpu_16k(a, torch, dist, world, rank, local, dev, barrier, max_over_ranks
     L.rct_launch_count(1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.start()
+    tr.host_s.clear()
     e0.record()
+    t_host0 = time.perf_counter()
     for _ in range(a.steps):
         run()
+    host_enqueue_ms = 1e3 * (time.perf_counter() - t_host0) / a.steps  # host time to ENQUEUE a step (no sync inside)
     e1.record()
     barrier()
     clocks = sampler.stop()
     launches = int(L.rct_launch_count(0))
     ms_step = max_over_ranks(e0.elapsed_time(e1)) / a.steps
+    host_enqueue = {"total_ms_per_step_max_over_ranks": max_over_ranks(host_enqueue_ms)}
+    for k in sorted(tr.host_s):
+        host_enqueue[k + "_ms"] = max_over_ranks(1e3 * tr.host_s[k] / a.steps)
     assert tr.status() == 0
     mp_step = H * W / 1e6
     value = mp_step / (ms_step * 1e-3)
@@ -669,7 +675,7 @@ def run_gpu_16k(a, torch, dist, world, rank, local, dev, barrier, max_over_ranks
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_GBps"], "peak": peak, "unit": "GB/s",
         "frac": kern[dom]["achieved_GBps"] / peak, "traffic": None, "peak_source": peak_src, "kernels": kern,
-        "phase_ms_max_over_ranks": phases, "allreduce_bytes": hist_bytes,
+        "phase_ms_max_over_ranks": phases, "host_enqueue": host_enqueue, "allreduce_bytes": hist_bytes,
         "allreduce_busbw_GBps": (2.0 * (world - 1) / world * hist_bytes / 1e9 / (phases["allreduce_ms"] * 1e-3)
                                  if world > 1 and phases["allreduce_ms"] > 0 else None),
         "pipeline_achieved_GBps_all_gpus": 10.0 * H * W / 1e9 / (ms_step * 1e-3),

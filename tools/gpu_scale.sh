@@ -41,6 +41,6 @@ for spec in "${RL[@]}"; do
   echo "[$wl n=$n $extra] exit $?"
   grep -o '"value": [0-9.]*, "unit": "MP/s", "n_gpus": [0-9]*' $out | head -1
   grep -o '"e2e": {"value": [0-9.]*' $out | head -1
-  grep -o '"phase_ms_max_over_ranks": {[^}]*}' $out | head -1
+  grep -o '"phase_ms_max_over_ranks": {[^}]*}' $out | head -1; grep -o '"host_enqueue": {[^}]*}' $out | head -1
   tail -2 ${out%.log}.err | cut -c1-300
 done
