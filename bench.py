@@ -434,11 +434,11 @@ def run_gpu_arm(a):
 
     for _ in range(max(a.warmup, 3)):
         step()
-    barrier()
     sampler = ClockSampler(local)
     L.rct_launch_count(1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.start()
+    barrier()
     e0.record()
     for _ in range(a.steps):
         step()
@@ -621,12 +621,15 @@ def run_gpu_16k(a, torch, dist, world, rank, local, dev, barrier, max_over_ranks
         lambda timed=False: tr(dc, ds, dm, do, timed=timed))
     for _ in range(max(a.warmup, 3)):
         run()
-    barrier()
+    # everything slow and rank-dependent (NVML init of the clock sampler) happens BEFORE the barrier: the step contains
+    # a collective, so a rank that enters the timed loop late makes every other rank wait inside its first all-reduce
+    # (measured: 20-30 ms of skew = 4-6 ms per step over 5 steps, charged to the "all-reduce")
     sampler = ClockSampler(local)
     L.rct_launch_count(1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.start()
     tr.host_s.clear()
+    barrier()
     e0.record()
     t_host0 = time.perf_counter()
     for _ in range(a.steps):
@@ -644,7 +647,7 @@ def run_gpu_16k(a, torch, dist, world, rank, local, dev, barrier, max_over_ranks
     mp_step = H * W / 1e6
     value = mp_step / (ms_step * 1e-3)
     # phase breakdown: a second pass with CUDA events around the phases and a host synchronisation per step (the value
-    # above is measured without either: at 8 ranks a per-step host sync alone costs milliseconds of rank skew)
+    # above is measured without either)
     acc = ({"front_moments_ms": 0.0, "keys_ms": 0.0, "hist_ms": 0.0, "match_apply_ms": 0.0, "allreduce_ms": 0.0} if a.bins
            else {"hist_ms": 0.0, "allreduce_ms": 0.0, "solve_ms": 0.0, "apply_ms": 0.0})
     for _ in range(a.steps):
