@@ -854,6 +854,9 @@ __global__ void __launch_bounds__(256, 4) k_apply_warp_rs(PixArgs a, unsigned ti
 }
 
 // ------------------------------------------------------------------------------------------
+#ifndef RCT_AKB
+#define RCT_AKB 4
+#endif
 // k_apply_kt: the default fused apply pass (MASK mode, same geometry, 16-byte aligned frames): the per-warp
 // two-stage bulk-async pipeline of k_apply_warp<true, 8, 4> with the key table (rct_keytab.cuh) in front of the
 // colour LUT -- and a lean tile loop.  With the LUT gathers gone the pass is issue-bound (ncu r02: issue slots 70 %
@@ -862,7 +865,7 @@ __global__ void __launch_bounds__(256, 4) k_apply_warp_rs(PixArgs a, unsigned ti
 // of the tile to prefetch advances incrementally (no division), the tile consumed next inherits it, and everything
 // that depends on the frame alone is reloaded only when the frame changes.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256, 4) k_apply_kt(PixArgs a, unsigned tiles_per_frame, unsigned nslots)
+__global__ void __launch_bounds__(256, RCT_AKB) k_apply_kt(PixArgs a, unsigned tiles_per_frame, unsigned nslots)
 {
     constexpr int kWarps = 8, kTile = 256;
     extern __shared__ __align__(128) uint8_t aw_smem_raw[];

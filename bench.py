@@ -561,7 +561,12 @@ def run_gpu_arm(a):
     # ---- e2e_files: the reference's real boundary (LST:191-245: files in, file out), one C-ABI call per frame ------
     e2e_files = None
     if world == 1 and a.files and not labels and not a.bins and not a.no_e2e:
-        e2e_files = files_leg(a, aip, cs, ss, ms, H, W)
+        try:
+            e2e_files = files_leg(a, aip, cs, ss, ms, H, W)
+        except AssertionError:
+            raise  # a parity failure must fail the bench
+        except Exception as e:  # noqa: BLE001 -- an auxiliary leg must not take the headline line down with it
+            e2e_files = {"error": f"{type(e).__name__}: {e}"}
 
     # ---- CPU baseline: C port of the reference on this box's host cores (rank 0, N=1 only) ------------
     cpu = None
