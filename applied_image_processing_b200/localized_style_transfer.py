@@ -449,7 +449,7 @@ def regional_color_transfer_binned(content, stylized, background_mask, bins=1024
     """The same fused tail with the CDF-matching step (a-6) replaced by ``bins``-bin histogram matching
     (BASELINE.json configs[4] "1024-bin histograms"; ``rct_transfer_binned_async``).  NO COUNTERPART IN
     THE REFERENCE and not the parity path: an approximation of :func:`regional_color_transfer` (measured:
-    within 1 uint8 LSB on all but isolated tail pixels, max 3; 0.5-5 % of the pixels differ) that is bit-exact against
+    within 1 uint8 LSB on all but isolated tail pixels (max 3-4 observed); 0.5-5 % of the pixels differ) that is bit-exact against
     the oracle's statement of the same definition.  numpy in -> numpy out, CUDA tensors in -> CUDA tensor out."""
     L = _cabi.lib()
     if not _is_tensor(content):

@@ -36,7 +36,7 @@ H4K, W4K = 2160, 3840
 ALG_BYTES_PER_PIXEL = {"hist": 7.0, "apply": 10.0, "pipeline": 10.0}  # SURVEY.md 8(d), DESIGN.md
 # kernels that stream the pixels and their algorithmic bytes per pixel: content 3 + stylised 3 + mask 1
 # read (+ combined 3 written by the apply pass)
-PIXEL_KERNELS = {"k_front_count": 7.0, "k_front_part": 7.0, "k_hist": 7.0, "k_apply": 10.0}
+PIXEL_KERNELS = {"k_front_count": 7.0, "k_front_part": 7.0, "k_hist": 7.0, "k_apply": 10.0}  # "k_apply" = the timing slot of the apply pass
 
 
 TRAFFIC_FILE = "profiles/r02_traffic.json"
@@ -468,7 +468,7 @@ def run_gpu_arm(a):
     ms_launch = {k: v / groups for k, v in kt.items()}           # average duration of one launch
     t_all = sum(ms_launch.values())
     frames_launch = min(a.slots, n)
-    apply_name = {0: "k_apply", 1: "k_apply_warp<bulk,8,keytab>" if a.keytab and not a.lut and not a.bins else "k_apply_warp<bulk,8>", 2: "k_apply_warp<cp.async,8>", 3: "k_apply_tma",
+    apply_name = {0: "k_apply", 1: "k_apply_kt" if a.keytab and not a.lut and not a.bins else "k_apply_warp<bulk,8>", 2: "k_apply_warp<cp.async,8>", 3: "k_apply_tma",
                   4: "k_apply_warp<bulk,16>", 5: "k_apply_warp<bulk,8>", 6: "k_apply_warp<bulk,8,3stage>", 7: "k_apply_warp<bulk,8,bulk-store>", 8: "k_apply_warp<bulk,8>"}[0 if labels else a.apply]
     if (sh, sw) != (H, W) and not labels:
         apply_name = "k_apply_warp_rs" if a.apply == 8 else "k_apply<resample>"

@@ -185,7 +185,7 @@ int rct_shard_apply_async(rct_plan *plan, const uint8_t *content, const uint8_t 
  * it exactly.  This mode replaces only that step by classic histogram matching (equal-width bins over the region's
  * key range, in-bin rank lerp, inverse lookup in the source CDF; definition in csrc/rct_binned.cuh and
  * oracle/rct_oracle.c:orc_match_binned); everything else (a-1..a-5, a-7..a-9) is the exact path's arithmetic.  It is an
- * APPROXIMATION (measured: within 1 uint8 LSB of the exact result on all but isolated tail pixels, max 3; 0.5-5 % of the pixels differ), bit-exact against its own
+ * APPROXIMATION (measured: within 1 uint8 LSB of the exact result on all but isolated tail pixels (max 3-4 observed); 0.5-5 % of the pixels differ), bit-exact against its own
  * oracle, never the parity path.  2 <= bins <= 4096.  Same arguments as rct_transfer_async otherwise. */
 int rct_transfer_binned_async(rct_plan *plan, const uint8_t *content, size_t content_stride, const uint8_t *stylised,
                               size_t stylised_stride, const uint8_t *mask, size_t mask_stride, uint8_t *out,

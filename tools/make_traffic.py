@@ -1,5 +1,5 @@
 #!/usr/bin/env python3
-"""profiles/r01_traffic.json from ncu --set full reports.
+"""profiles/rNN_traffic.json from ncu reports (--set full, or just the dram / duration metrics).
 
     python tools/make_traffic.py U=gpurun_out/prof_U.ncu-rep N=gpurun_out/prof_N.ncu-rep --frames 4 [--csv-prefix profiles/r01_ncu_full_4k]
 
@@ -44,6 +44,8 @@ def main():
         ir, iw, it = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("gpu__time_duration.sum")
         for r in data:
             b = float(r[ir]) * SCALE[units[ir]] + float(r[iw]) * SCALE[units[iw]]
+            if not r[ir] or not r[iw]:
+                continue
             out.setdefault(fam, {})[shown(r[hdr.index("Kernel Name")])] = {
                 "dram_bytes_per_frame": b / frames, "ncu_duration": r[it] + " " + units[it], "frames_in_capture": frames}
     json.dump(out, sys.stdout, indent=1)
