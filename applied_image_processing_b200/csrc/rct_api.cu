@@ -648,6 +648,7 @@ int ensure_kernel_attrs()
     CK(cudaFuncSetAttribute(k_fine_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemFineHist));
     CK(cudaFuncSetAttribute(k_part_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemPartSort));
     CK(cudaFuncSetAttribute(k_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemScatter));
+    CK(cudaFuncSetAttribute(k_scatter_tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemScatter2));
     done_dev = dev;
     return RCT_OK;
 }
@@ -673,7 +674,16 @@ int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t 
 #endif
     unsigned sblocks = (unsigned)((p ? p->sm : 148) * RCT_SB / (njobs > 0 ? njobs : 1));  // ~4 waves of 3 CTAs per SM
     if (sblocks < 16u) sblocks = 16u;
-    k_scatter<<<dim3(sblocks, njobs), RCT_SCT, kSmemScatter, st>>>(jobs);
+    static const bool tiled_off = getenv("RCT_SCATTER_TILED") && atoi(getenv("RCT_SCATTER_TILED")) == 0;  // A/B runs
+    if (!tiled_off && maxparts <= (size_t)kScat2MaxParts) {
+        // one CTA per SM and job at most; tiles of 16 K entries
+        unsigned tb = (unsigned)((cap + kScat2Tile - 1) / kScat2Tile);
+        const unsigned per_job = (unsigned)((p ? p->sm : 148) * 2 / (njobs > 0 ? njobs : 1));
+        if (tb > (per_job ? per_job : 1u)) tb = per_job ? per_job : 1u;
+        k_scatter_tiled<<<dim3(tb ? tb : 1u, njobs), kScat2Threads, kSmemScatter2, st>>>(jobs);
+    } else {
+        k_scatter<<<dim3(sblocks, njobs), RCT_SCT, kSmemScatter, st>>>(jobs);
+    }
     ++t_launches;
     CK(cudaGetLastError());
     KMARK(RCT_TK_SCATTER);

@@ -257,6 +257,71 @@ __global__ void RCT_SCT_LB k_scatter(const Job *jobs)
     }
 }
 
+// k_scatter_tiled: the same scatter with one GLOBAL reservation per (CTA tile, part) instead of one per entry.
+// A CTA of 1024 threads takes tiles of kScat2Tile = 16 K entries: every entry's part is ranked inside the tile by a
+// shared-memory atomic, each part the tile touches reserves its run of the part's slice once, and the records go
+// out in runs (~10 consecutive 16-byte records per part on a 4K noise frame: the atomics to L2 drop ~10x and the
+// stores become 160-byte runs).  The second sweep re-reads the tile's keys / payloads (L2-resident: 256 KB per CTA)
+// rather than holding 16 records per thread in registers.  Shared memory: fine-bin tables as in k_scatter + one
+// counter per part (parts <= kScat2MaxParts); jobs with more parts take k_scatter.
+constexpr int kScat2Threads = 1024;
+constexpr int kScat2Per = 16;
+constexpr int kScat2Tile = kScat2Threads * kScat2Per;
+constexpr int kScat2MaxParts = 8192;
+constexpr size_t kSmemScatter2 = kSmemScatter + (size_t)kScat2MaxParts * 4;
+__global__ void __launch_bounds__(kScat2Threads, 1) k_scatter_tiled(const Job *jobs)
+{
+    const Job &job = jobs[blockIdx.y];
+    RegionCtrl *rc = job.rc;
+    if (rc->skip) return;
+    const unsigned d = rc->d;
+    if ((size_t)blockIdx.x * kScat2Tile >= d) return;
+    extern __shared__ __align__(16) unsigned s_scat[];
+    unsigned *s_base = s_scat;                                                         // [kCoarse + 1]
+    unsigned short *s_pof = reinterpret_cast<unsigned short *>(s_scat + kCoarse + 2);  // [n_fine]
+    unsigned *s_cnt = s_scat + (kSmemScatter / 4);                                     // [n_parts]: count, then base
+    const unsigned np = rc->n_parts;
+    {
+        const unsigned nf2 = (rc->n_fine + 1u) / 2u;
+        const unsigned *pof32 = reinterpret_cast<const unsigned *>(job.pof);
+        unsigned *s_pof32 = s_scat + kCoarse + 2;
+        for (unsigned i = threadIdx.x; i <= (unsigned)kCoarse; i += blockDim.x) s_base[i] = rc->fine_base[i];
+        for (unsigned i = threadIdx.x; i < nf2; i += blockDim.x) s_pof32[i] = pof32[i];
+    }
+    const double klo = rc->klo, cscale = rc->cscale;
+    Rec *recP = job.recP;
+    for (size_t t0 = (size_t)blockIdx.x * kScat2Tile; t0 < d; t0 += (size_t)gridDim.x * kScat2Tile) {
+        for (unsigned i = threadIdx.x; i < np; i += blockDim.x) s_cnt[i] = 0u;
+        __syncthreads();
+        unsigned pr[kScat2Per];  // part | rank inside (tile, part) << 16  (rank < 16384)
+#pragma unroll
+        for (int k = 0; k < kScat2Per; ++k) {
+            const size_t e = t0 + (size_t)k * kScat2Threads + threadIdx.x;
+            pr[k] = 0xffffffffu;
+            if (e < d) {
+                double ff;
+                const unsigned p = s_pof[fine_bin(job.keyA[e], klo, cscale, s_base, ff)];
+                pr[k] = p | (atomicAdd(&s_cnt[p], 1u) << 16);
+            }
+        }
+        __syncthreads();
+        for (unsigned i = threadIdx.x; i < np; i += blockDim.x) {
+            const unsigned c = s_cnt[i];
+            if (c) s_cnt[i] = atomicAdd(&job.pfill[(size_t)i * kFillStride], c);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < kScat2Per; ++k) {
+            const size_t e = t0 + (size_t)k * kScat2Threads + threadIdx.x;
+            if (pr[k] != 0xffffffffu) {
+                const unsigned pos = s_cnt[pr[k] & 0xffffu] + (pr[k] >> 16);
+                recP[pos] = make_rec(job.keyA[e], job.payA ? job.payA[e] : (unsigned)e, job.cntA ? job.cntA[e] : 1u);
+            }
+        }
+        __syncthreads();
+    }
+}
+
 // ascending bitonic network over n (any n) records by (key, payload); works on shared or
 // global memory (generic pointers); implicit +inf padding above n.
 __device__ void block_bitonic(Rec *rec, unsigned n)
