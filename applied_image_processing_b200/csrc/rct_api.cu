@@ -674,8 +674,11 @@ int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t 
 #endif
     unsigned sblocks = (unsigned)((p ? p->sm : 148) * RCT_SB / (njobs > 0 ? njobs : 1));  // ~4 waves of 3 CTAs per SM
     if (sblocks < 16u) sblocks = 16u;
-    static const bool tiled_off = getenv("RCT_SCATTER_TILED") && atoi(getenv("RCT_SCATTER_TILED")) == 0;  // A/B runs
-    if (!tiled_off && maxparts <= (size_t)kScat2MaxParts) {
+    // k_scatter_tiled (one global reservation per 16K-entry tile and part) is opt-in: measured on 8 x 4K it is 9 % faster
+    // than k_scatter on N (0.507 vs 0.558 ms) but 6 % slower on U (1.079 vs 1.017 ms) -- the per-entry global atomics were
+    // not what bounds this kernel (profiles/r02_summary.md)
+    static const bool tiled_on = getenv("RCT_SCATTER_TILED") && atoi(getenv("RCT_SCATTER_TILED")) != 0;
+    if (tiled_on && maxparts <= (size_t)kScat2MaxParts) {
         // one CTA per SM and job at most; tiles of 16 K entries
         unsigned tb = (unsigned)((cap + kScat2Tile - 1) / kScat2Tile);
         const unsigned per_job = (unsigned)((p ? p->sm : 148) * 2 / (njobs > 0 ? njobs : 1));
