@@ -169,11 +169,12 @@ class Plan:
         return lut
 
 
-def get_plan(device, H, W, sh, sw, slots=1, flags=0) -> Plan:
+def get_plan(device, H, W, sh, sw, slots=1, flags=0, lane=0) -> Plan:
     """Per-(device, geometry) plan cache (workspace cache behind a mutex), least recently
     used plans are dropped once the cached workspaces exceed PLAN_CACHE_BYTES.  A dropped plan that a
-    caller still holds stays valid (it is destroyed when the last reference goes)."""
-    key = (device.index, H, W, sh, sw, slots, flags)
+    caller still holds stays valid (it is destroyed when the last reference goes).  `lane` distinguishes
+    the plans of launch groups that run concurrently on separate streams (see LANES)."""
+    key = (device.index, H, W, sh, sw, slots, flags, lane)
     with _plan_lock:
         p = _plans.get(key)
         if p is None:
@@ -217,6 +218,22 @@ def _np_u8(a, name):
     return np.ascontiguousarray(a)
 
 
+# Launch groups in flight at once on the tensor path.  The solve kernels are latency-bound (ncu: k_scatter issues on 17 %
+# of its cycles), so two groups on two streams, each with its own plan, overlap their stalls: 8 + 8 frames of 4K take
+# 11.03 ms instead of 11.68 ms back to back (measured on B200; four lanes are slower than two).
+LANES = 2
+_lane_streams: dict = {}
+
+
+def _lane_stream(device, lane) -> torch.cuda.Stream:
+    key = (device.index, lane)
+    with _plan_lock:
+        st = _lane_streams.get(key)
+        if st is None:
+            st = _lane_streams[key] = torch.cuda.Stream(device=device)
+        return st
+
+
 def host_group_size(n: int) -> int:
     """Frames per copy/compute group of the host (numpy) entry point."""
     return max(1, min(8, n // 8))
@@ -241,9 +258,37 @@ def _transfer(content, stylised, mask, mode, label=0, out=None, slots=None, quie
         sty_b = stylised.dim() == 4
         sh, sw = stylised.shape[-3], stylised.shape[-2]
         mask_b = mask is not None and mask.dim() == 3
-        plan = get_plan(dev, H, W, sh, sw, slots or min(n, 8))
+        group = slots or min(n, 8)
         if out is None:
             out = torch.empty_like(content) if mode != MODE_LABEL else content.clone()
+        nlanes = LANES if (LANES > 1 and n >= 2 * group and not return_status) else 1
+        if nlanes > 1:
+            # contiguous blocks of whole groups per lane, each lane its own plan and stream, joined on the caller's stream
+            main = torch.cuda.current_stream(dev)
+            start = torch.cuda.Event()
+            start.record(main)
+            ngroups = (n + group - 1) // group
+            f0 = 0
+            with torch.cuda.device(dev):
+                for lane in range(nlanes):
+                    g = ngroups // nlanes + (1 if lane < ngroups % nlanes else 0)
+                    cnt = min(n - f0, g * group)
+                    if cnt <= 0:
+                        break
+                    lp, ls = get_plan(dev, H, W, sh, sw, group, lane=lane), _lane_stream(dev, lane)
+                    ls.wait_event(start)
+                    with lp.lock:
+                        check(L.rct_transfer_async(
+                            lp.handle, content[f0:].data_ptr(), H * W * 3,
+                            (stylised[f0:] if sty_b else stylised).data_ptr(), sh * sw * 3 if sty_b else 0,
+                            (mask[f0:] if mask_b else mask).data_ptr() if mask is not None else None, H * W if mask_b else 0,
+                            out[f0:].data_ptr(), H * W * 3, cnt, mode, label, ls.cuda_stream))
+                    done = torch.cuda.Event()
+                    done.record(ls)
+                    main.wait_event(done)
+                    f0 += cnt
+            return out
+        plan = get_plan(dev, H, W, sh, sw, group)
         with torch.cuda.device(dev), plan.lock:
             check(L.rct_transfer_async(
                 plan.handle, content.data_ptr(), H * W * 3, stylised.data_ptr(), sh * sw * 3 if sty_b else 0,

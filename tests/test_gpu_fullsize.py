@@ -194,3 +194,20 @@ def test_plan_cache_is_bounded_and_status_reaches_the_tensor_path(capsys):
     out, status = aip.regional_color_transfer(c, s, torch.ones((H, W), dtype=torch.uint8, device="cuda"), return_status=True)
     assert status.tolist() == [1] and "No foreground pixels" in capsys.readouterr().out
     assert torch.equal(out, s)
+
+
+def test_concurrent_launch_groups_on_the_tensor_path():
+    """Batches of at least two launch groups are split over two plans on two streams (LANES): same bytes as the
+    oracle, also with a ragged last group and a broadcast stylised image."""
+    n, H, W = 7, 120, 160
+    cs = np.stack([synth.synth_image(H, W, 100 + i, "UN"[i % 2]) for i in range(n)])
+    ss = np.stack([synth.synth_image(H, W, 200 + i, "NU"[i % 2]) for i in range(n)])
+    ms = np.stack([synth.ellipse_mask(H, W, 0.2 + 0.08 * i, i) for i in range(n)])
+    refs = np.stack([orc.transfer(cs[i], ss[i], ms[i])[0] for i in range(n)])
+    tc, ts, tm = (torch.from_numpy(x).cuda() for x in (cs, ss, ms))
+    assert lst.LANES == 2
+    out = aip.regional_color_transfer(tc, ts, tm, slots=2)          # 4 groups: 2 + 2 (ragged: 4 + 3 frames)
+    assert np.array_equal(out.cpu().numpy(), refs)
+    refs1 = np.stack([orc.transfer(cs[i], ss[0], ms[i])[0] for i in range(n)])
+    out1 = aip.regional_color_transfer(tc, ts[0].contiguous(), tm, slots=3)
+    assert np.array_equal(out1.cpu().numpy(), refs1)
