@@ -575,6 +575,32 @@ def run_gpu_arm(a):
                "h2d_bytes_per_step": int(hc.numel() + hs.numel() + hm.numel()),
                "d2h_bytes_per_step": int(ho.numel()), "ms_per_step": 1e3 * t_e2e / a.steps}
         assert np.array_equal(hon, do.cpu().numpy()), "host path and device path disagree"
+        # the box's raw copy ceiling for this step, measured in the same run: the same pinned buffers copied H2D and D2H
+        # on two streams with nothing else, all ranks at once (8 GPUs of this box share one host memory system: 136 GB/s
+        # in total, profiles/r02_pcie_ceiling.json) -- e2e cannot exceed it, whatever the kernels do
+        s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+        dprobe = torch.empty_like(dc), torch.empty_like(ds), torch.empty_like(dm)
+
+        def raw_copies():
+            with torch.cuda.stream(s_in):
+                dprobe[0].copy_(hc, non_blocking=True)
+                dprobe[1].copy_(hs, non_blocking=True)
+                dprobe[2].copy_(hm, non_blocking=True)
+            with torch.cuda.stream(s_out):
+                ho.copy_(do, non_blocking=True)
+
+        raw_copies()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(5):
+            raw_copies()
+        torch.cuda.synchronize()
+        t_raw = max_over_ranks(time.perf_counter() - t0) / 5
+        barrier()
+        del dprobe
+        e2e["raw_copy_ceiling"] = {"value": mp_step / t_raw, "unit": UNIT, "ms_per_step": 1e3 * t_raw,
+                                   "what": "this step's H2D + D2H bytes from / to the same pinned buffers on two streams, no kernels, all ranks at once"}
+        e2e["frac_of_ceiling"] = e2e["value"] / e2e["raw_copy_ceiling"]["value"]
         # the same call with plain (pageable) numpy arrays: what the reference's caller holds
         # (np.array(Image.open(...)), LST:200-219); the driver stages such copies itself
         if not labels and not a.bins:
