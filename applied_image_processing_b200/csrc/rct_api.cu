@@ -226,6 +226,7 @@ struct rct_plan {
     size_t files_ws_bytes;
     int keytab;      // RCT_OPT_KEYTAB: 1 = key table in front of the colour LUT (rct_keytab.cuh)
     bool kt_live;    // the tables of the launch group in flight were built (exact path, interleaved match)
+    int kt_mode;     // mode of the call in progress: the key table is built only where the apply pass can use it
     int stage_sets;  // RCT_OPT_STAGE_SETS: staging sets of the host entry point (2..kStageSetsMax)
     // RCT_OPT_TIMING: five events per launch group (memset | k_hist | solve | k_apply)
     int timing;
@@ -699,11 +700,18 @@ int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t 
     return RCT_OK;
 }
 
+// The key table pays for itself only in front of k_apply_kt: MASK mode, stylised image at the content's size, one
+// label per frame.  Elsewhere (resampled / label geometries: register-staged apply kernel) it is not built at all.
+inline bool want_keytab(const rct_plan *p)
+{
+    return p->keytab && !p->lut_mode && !p->resample && p->lpf == 1 && p->kt_mode == RCT_MODE_MASK;
+}
+
 int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)
 {
     unsigned eb = entry_blocks(p, nslots);
     CK(cudaMemsetAsync(p->ws + p->L.off_zero, 0, p->L.zero_bytes * 2 * (size_t)nslots, st));
-    if (p->keytab && !p->lut_mode)  // parameters, seeds and flags of the key tables (rct_keytab.cuh)
+    if (want_keytab(p))  // parameters, seeds and flags of the key tables (rct_keytab.cuh)
         CK(cudaMemset2DAsync(p->ws + p->L.off_kt, kKtBytes, 0, kKtZeroBytes, (size_t)nslots, st));
     KMARK(RCT_TK_MEMSET);
     if (from_cube) {
@@ -727,7 +735,7 @@ int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)
     else
         LAUNCH(k_match, dim3((unsigned)p->L.maxparts, nslots), kMatchThreads, st, p->ctrl, p->jobs, p->lut,
                p->L.lut_stride_u32, p->dbg_m, p->dbg_j, p->L.dbg_stride, p->match_interleave,
-               p->keytab ? p->ws + p->L.off_kt : nullptr);
+               want_keytab(p) ? p->ws + p->L.off_kt : nullptr);
     if (p->lut_mode) {  // palette LUT: runs of equal output colour along the sorted target -> uint16 indices + palette
         LAUNCH(k_pal_count, dim3((unsigned)p->L.maxparts, nslots), kPalThreads, st, p->ctrl, p->jobs);
         LAUNCH(k_pal_scan, dim3(nslots), 1024, st, p->ctrl, p->jobs);
@@ -735,7 +743,7 @@ int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)
     }
     KMARK(RCT_TK_MATCH);
     p->kt_live = false;
-    if (p->keytab && !p->lut_mode) {  // key table: run starts -> flagged cells + seeds -> prefix maximum -> cells
+    if (want_keytab(p)) {  // key table: run starts -> flagged cells + seeds -> prefix maximum -> cells
         uint8_t *kt0 = p->ws + p->L.off_kt;
         LAUNCH(k_kt_mark, dim3(8, nslots), 256, st, p->ctrl, kt0, p->match_interleave);
         LAUNCH(k_kt_fill, dim3(nslots), 1024, st, p->ctrl, kt0, p->match_interleave);
@@ -901,6 +909,7 @@ int rct_transfer_async(rct_plan *p, const uint8_t *content, size_t content_strid
     rc = ensure_status_frames(p, n_frames);
     if (rc) return rc;
     if ((rc = plan_enter(p, st))) return rc;
+    p->kt_mode = mode;
     const size_t npix = (size_t)p->H * (size_t)p->W;
     for (int f0 = 0; f0 < n_frames; f0 += p->slots) {
         int ns = n_frames - f0 < p->slots ? n_frames - f0 : p->slots;
@@ -943,6 +952,7 @@ int rct_transfer_labels_async(rct_plan *p, const uint8_t *content, size_t conten
     const size_t npix = (size_t)p->H * (size_t)p->W;
     const int fpg = p->slots / n_labels;  // frames per launch group
     if ((rc = plan_enter(p, st))) return rc;
+    p->kt_mode = RCT_MODE_LABEL;
     p->lpf = n_labels;
     for (int f0 = 0; f0 < n_frames && rc == RCT_OK; f0 += fpg) {
         const int nf = n_frames - f0 < fpg ? n_frames - f0 : fpg, ns = nf * n_labels;
@@ -986,6 +996,7 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
     if (rc) return rc;
     cudaStream_t st = p->own_stream, sin = p->h2d_stream, sout = p->d2h_stream;
     if ((rc = plan_enter(p, st))) return rc;
+    p->kt_mode = mode;
     int k = 0;
     for (int f0 = 0; f0 < n_frames; f0 += p->slots, ++k) {
         const int b = k % S;
@@ -1041,6 +1052,7 @@ int rct_shard_hist_async(rct_plan *p, const uint8_t *content, const uint8_t *sty
     cudaStream_t st = (cudaStream_t)stream;
     const size_t pb = (size_t)row0 * p->W, pe = (size_t)(row0 + rows) * p->W;
     if ((rc = plan_enter(p, st))) return rc;
+    p->kt_mode = mode;  // rct_shard_solve_async follows on the same plan
     if (!p->front) {
         rc = phase_hist(p, f, 1, mode, label, pb, pe, st);
         return rc ? rc : plan_leave(p, st);
@@ -1639,6 +1651,7 @@ int rct_transfer_files_host(rct_plan *p, const uint8_t *content_file, size_t con
     cudaStream_t st = p->own_stream;
     int rc = plan_enter(p, st);
     if (rc) return rc;
+    p->kt_mode = RCT_MODE_MASK;
     std::vector<uint8_t> host_tmp;
     // d_o doubles as the grey plane of a one-component JPEG before its expansion
     if ((rc = decode_file_to_device(content_file, content_bytes, H, W, "content file", d_c, d_dec, dec_ws, d_o, host_tmp, p->sm, st))) return rc;
