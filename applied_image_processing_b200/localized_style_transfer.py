@@ -534,9 +534,10 @@ def regional_color_transfer_binned(content, stylized, background_mask, bins=1024
     return out
 
 
-def regional_color_transfer_labels(content, stylized, labels, n_labels, slots=None, fused=True):
+def regional_color_transfer_labels(content, stylized, labels, n_labels, slots=None, fused=True, out=None):
     """BASELINE.json config 5 (no counterpart in the reference): for every label l the content
-    pixels with that label are matched to the stylised pixels with that label."""
+    pixels with that label are matched to the stylised pixels with that label.  numpy in -> numpy out
+    (``out``: optional uint8 array to receive the result; a pinned one makes the copy-out a plain DMA)."""
     if not _is_tensor(content):
         # numpy calling convention: one upload, the n_labels passes on the device, one download
         # (per-pass host round trips would move every image 2 * n_labels times over PCIe)
@@ -547,7 +548,13 @@ def regional_color_transfer_labels(content, stylized, labels, n_labels, slots=No
             s = s.unsqueeze(0).expand(c.shape[0], -1, -1, -1).contiguous()
         if c.dim() == 4 and l.dim() == 2:
             l = l.unsqueeze(0).expand(c.shape[0], -1, -1).contiguous()
-        return regional_color_transfer_labels(c, s, l, n_labels, slots=slots, fused=fused).cpu().numpy()
+        res = regional_color_transfer_labels(c, s, l, n_labels, slots=slots, fused=fused)
+        if out is None:
+            return res.cpu().numpy()
+        if out.dtype != np.uint8 or tuple(out.shape) != tuple(res.shape) or not out.flags.c_contiguous:
+            raise ValueError("out must be a C-contiguous uint8 array of the content's shape")
+        torch.from_numpy(out).copy_(res)  # straight into the caller's memory (DMA when it is pinned)
+        return out
     if fused and 0 < n_labels <= 64:
         return _transfer_labels_fused(content, stylized, labels, n_labels, slots)
     out = None

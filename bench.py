@@ -556,7 +556,7 @@ def run_gpu_arm(a):
 
         def api_call():
             if labels:
-                hon[...] = aip.regional_color_transfer_labels(hcn, hsn, hmn, 8, slots=e2e_slots, fused=bool(a.labels_fused))
+                aip.regional_color_transfer_labels(hcn, hsn, hmn, 8, slots=e2e_slots, fused=bool(a.labels_fused), out=hon)
             elif a.bins:
                 aip.regional_color_transfer_binned(hcn, hsn, hmn, a.bins, out=hon)
             else:

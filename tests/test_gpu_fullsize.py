@@ -75,6 +75,8 @@ def test_fullsize_labels8_vs_oracle_and_reference_hash():
     seq = aip.regional_color_transfer_labels(torch.from_numpy(c).cuda(), torch.from_numpy(s).cuda(),
                                              torch.from_numpy(labels).cuda(), 8, fused=False)
     assert np.array_equal(seq.cpu().numpy(), ref)
+    buf = torch.empty(c.shape, dtype=torch.uint8).pin_memory().numpy()      # copy-out straight into a pinned caller buffer
+    assert aip.regional_color_transfer_labels(c, s, labels, 8, out=buf) is buf and np.array_equal(buf, ref)
 
 
 def test_config1_literal_vs_reference():
