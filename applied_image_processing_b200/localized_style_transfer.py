@@ -234,11 +234,15 @@ def _lane_stream(device, lane) -> torch.cuda.Stream:
         return st
 
 
-def host_group_size(n: int) -> int:
-    """Frames per copy/compute group of the host (numpy) entry point.  Small groups keep the un-overlapped tail (the
-    last group's compute and copy-out) short: measured on B200, 4K frames, MP/s end to end: 16 frames in groups of
-    1 / 2: 6 751 / 6 467; 8 frames in groups of 1 / 2 / 4: 6 290 / 5 670 / 4 700; 32 frames in groups of 1 / 4: 6 017 / 6 410."""
-    return max(1, min(8, n // 16))
+def host_group_size(n: int, frame_bytes: int = 58_060_800) -> int:
+    """Frames per copy/compute group of the host (numpy) entry point: about 60 MB of input per group, at least four
+    groups per call when there are that many frames.  Small groups keep the un-overlapped tail (the last group's compute
+    and copy-out) short, but a group must be large enough for its kernels to run efficiently while the next one is
+    copied in.  Measured on B200, MP/s end to end: 16 x 4K frames (58 MB each) in groups of 1 / 2: 6 751 / 6 467;
+    32 x 1080p frames (14.5 MB each) in groups of 1 / 2 / 4 / 8: 3 369 / 4 745 / 5 733 / 5 550."""
+    g = int(round(60e6 / max(1, frame_bytes)))
+    g = max(1, min(8, g))
+    return max(1, min(g, n // 4)) if n >= 4 else 1
 
 
 def _transfer(content, stylised, mask, mode, label=0, out=None, slots=None, quiet=False, return_status=False):
@@ -322,7 +326,7 @@ def _transfer(content, stylised, mask, mode, label=0, out=None, slots=None, quie
     # overlap inside rct_transfer_host (a ring of staging sets, three streams) and the un-overlapped
     # head (first copy-in) and tail (last compute + copy-out) stay one small group each
     # (measured, 8 x 4K: groups of 1 -> 10.6 ms per call, 2 -> 11.7, 4 -> 14.1; PCIe floor 9.0)
-    plan = get_plan(dev, H, W, sh, sw, slots or host_group_size(n))
+    plan = get_plan(dev, H, W, sh, sw, slots or host_group_size(n, 4 * H * W + 3 * sh * sw))
     if out is None:
         out = np.empty_like(content) if mode != MODE_LABEL else content.copy()
     status = np.zeros(n, np.int32)

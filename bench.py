@@ -551,7 +551,7 @@ def run_gpu_arm(a):
 
         e2e_slots = a.e2e_slots or None
         if a.stage_sets:
-            lst.get_plan(dev, H, W, sh, sw, slots=e2e_slots or lst.host_group_size(n)).set_option(
+            lst.get_plan(dev, H, W, sh, sw, slots=e2e_slots or lst.host_group_size(n, 4 * H * W + 3 * sh * sw)).set_option(
                 _cabi.OPT_STAGE_SETS, a.stage_sets)
 
         def api_call():

@@ -33,5 +33,6 @@ def test_defaults():
 
 
 def test_host_group_size_and_lanes():
-    assert [lst.host_group_size(n) for n in (1, 8, 16, 31, 32, 64, 1024)] == [1, 1, 1, 1, 2, 4, 8]
+    assert [lst.host_group_size(n) for n in (1, 8, 16, 32, 1024)] == [1, 1, 1, 1, 1]                     # 4K frames: one per group
+    assert [lst.host_group_size(n, 14_515_200) for n in (1, 3, 8, 16, 32, 128)] == [1, 1, 2, 4, 4, 4]     # 1080p frames
     assert lst.LANES == 2
