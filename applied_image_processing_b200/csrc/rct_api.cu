@@ -700,11 +700,13 @@ int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t 
     return RCT_OK;
 }
 
-// The key table pays for itself only in front of k_apply_kt: MASK mode, stylised image at the content's size, one
-// label per frame.  Elsewhere (resampled / label geometries: register-staged apply kernel) it is not built at all.
+// The key table pays for itself only in front of the bulk-async apply kernels: MASK mode, one label per frame, stylised
+// image at the content's size (k_apply_kt) or resampled through k_apply_warp_rs.  Elsewhere (label geometries, the
+// register-staged resample kernel) it is not built at all.
 inline bool want_keytab(const rct_plan *p)
 {
-    return p->keytab && !p->lut_mode && !p->resample && p->lpf == 1 && p->kt_mode == RCT_MODE_MASK;
+    if (!p->keytab || p->lut_mode || p->lpf != 1 || p->kt_mode != RCT_MODE_MASK) return false;
+    return !p->resample || (p->apply_tma == 8 && p->rs_tma_ok);  // resampled: only the TMA-staged kernel takes it
 }
 
 int phase_solve(rct_plan *p, int nslots, cudaStream_t st, bool from_cube)

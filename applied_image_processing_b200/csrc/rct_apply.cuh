@@ -792,6 +792,10 @@ __global__ void __launch_bounds__(256, 4) k_apply_warp_rs(PixArgs a, unsigned ti
         if (sb.bytes) bulk_g2s(Wm.s[st] + sb.smem_off, sb.g, sb.bytes, bar);
     };
 
+    unsigned kt_slot = 0xffffffffu;
+    bool kt_ok = false;
+    KtRegs kr{};
+    KtView kv{};
     if (cnt > 0 && lane == 0) issue(0);
     for (unsigned i = 0; i < cnt; ++i) {
         const unsigned st = i % kAwStages;
@@ -823,6 +827,12 @@ __global__ void __launch_bounds__(256, 4) k_apply_warp_rs(PixArgs a, unsigned ti
         mbar_wait(&S.full[warp][st], (i / kAwStages) & 1u);
         const unsigned *lut = a.lut + (size_t)slot * a.lut_stride;
         const int status = a.ctrl[slot].status;
+        if (slot != kt_slot) {  // a new frame: its key table (warp-uniform)
+            kt_slot = slot;
+            kv = kt_view(a.kt, slot);
+            kt_ok = a.kt != nullptr && __ldg(&kv.par->valid) != 0u;
+            if (kt_ok) kr = kt_load(kv.par);
+        }
         uint32_t wc[6], ws[6], wm[2], wo[6];
         if (active) {
             const uint2 *qc = reinterpret_cast<const uint2 *>(Wm.c[st] + 24u * lane);
@@ -844,7 +854,8 @@ __global__ void __launch_bounds__(256, 4) k_apply_warp_rs(PixArgs a, unsigned ti
         }
         __syncwarp();  // the stage is read: the next iteration may refill it
         if (active) {
-            apply8<true>(wc, ws, wm, lut, status, wo, pol_lut);
+            if (kt_ok) apply8<true, 2>(wc, ws, wm, lut, status, wo, pol_lut, &kr, &kv);
+            else apply8<true>(wc, ws, wm, lut, status, wo, pol_lut);
             uint8_t *qo = a.out + (size_t)slot * a.out_stride + 3 * p0 + 24u * lane;
             stg8_hint(qo, wo[0], wo[1], pol_stream);
             stg8_hint(qo + 8, wo[2], wo[3], pol_stream);
