@@ -4,19 +4,21 @@
 // Why.  The apply pass resolves every target pixel through LUT[colour], a random 4-byte gather into a 64 MiB table
 // per frame: on noisy images every gather drags a 32-byte sector out of DRAM (ncu r01: 776 MB read for 232 MB of
 // pixels) and the pass sits at 0.26 of the HBM roofline.  But the output colour is a function of ONE scalar: along
-// the sorted target keys the outputs form a few thousand runs of equal RGB (a-7: all recoloured pixels lie on the
+// the sorted target keys the outputs form a few hundred runs of equal RGB (a-7: all recoloured pixels lie on the
 // curve mean + m * component).  So
 //     out(colour) = run_colour[ number of run thresholds <= key(colour) ].
 // The exact key is fp64 (C2/C3/C7, 3 log10 per colour: per-pixel evaluation is what the LUT avoids), but an fp32
-// key k~ with a PROVEN error bound eps decides the run whenever no threshold lies within eps of it.  The key axis
-// (the coarse key range the sort uses anyway) is cut into 65537 uniform cells; a cell whose eps-widened interval
+// key k~ with a PROVEN error bound eps decides the run whenever no threshold lies within eps of it.  The key axis,
+// from the smallest to the largest target key of the frame, is cut into 65537 uniform cells; a cell whose eps-widened interval
 // meets no threshold is PURE and stores the run colour, every other cell is flagged and the pixel falls back to
 // the exact LUT gather.  ~96 % of the gathers become one read of a 256 KB L1/L2-resident table plus ~30 fp32
 // instructions; results are bit-identical by construction, and k_kt_verify (tests) re-checks every distinct target
 // colour of a frame against the LUT.
 //
 //   k_match        (rct_sort.cuh) records a run start (key, sorted index, colour) whenever the output colour changes
-//                  along the sorted target; every part starts a run, so no cross-CTA dependency and no ordering
+//                  along the sorted target (the predecessor of a part's first entry is re-evaluated by the part's
+//                  own CTA, so there is no cross-CTA dependency, no ordering and no forced start per part), and the
+//                  smallest / largest target key by atomic max
 //   k_kt_mark      per run start: flags the cells its eps-widened threshold can reach and seeds the first cell
 //                  after them with (sorted index, colour) by a 64-bit atomic max -- no sort needed
 //   k_kt_fill      one CTA per slot: prefix maximum of the seeds along the cells = colour of the run each pure cell
@@ -28,10 +30,11 @@
 //        unit[k] = fp32(k / 255) rounded once more: relative error <= 6 * 2^-24                -> 5.2e-7 in lg2
 //   lg2.approx.f32: absolute error <= 2^-22 on [0.5, 2], relative <= 2^-22 elsewhere; |lg2| <= 13.3 (LMS >= 9.4e-5
 //        for every non-black colour)                                                           -> 3.2e-6
-//   dot with w (|w|_1 <= 1.3), 3 fma + 1 subtraction on magnitudes <= 16: 4 * 2^-24 * 16       -> 3.8e-6
-//   total <= 1.3 * 3.7e-6 + 3.8e-6 = 8.6e-6 < kKtEpsKey = 2^-16 = 1.53e-5.  k_kt_keyerr measures the true maximum
+//   dot with w (|w_i| <= log10(2) * |column i of LMS_TO_LAB|_2 = 0.301, |w|_1 <= 0.91), 3 fma on magnitudes <= 16
+//        (the constant pmk = pm + kmin = the smallest w . lg2 of the frame enters as the addend of the first fma: its
+//        rounding is one of the four):  4 * 2^-24 * 16                                            -> 3.8e-6
+//   total <= 0.91 * 3.7e-6 + 3.8e-6 = 7.2e-6 < kKtEpsKey = 2^-16 = 1.53e-5.  k_kt_keyerr measures the true maximum
 //   over all 2^24 colours for a frame's parameters (tests assert it stays below kKtEpsKey / 2).
-//   (the constant pmk = pm + klo enters as the addend of the first fma: its rounding, 2^-24 * 16, is inside the bound)
 // Cell coordinate c = (k~ - kmin) * tscale in fp32, 0 <= c <= 65536, the cells spanning [smallest, largest] target
 //   key (+0.1 %): rounding of the product and of tscale <= 2 * 2^-24 * 65536 = 0.008 cells, round-to-nearest ties
 //   included: kKtEpsC = 1/64 cell.
