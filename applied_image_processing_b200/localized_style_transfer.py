@@ -282,6 +282,9 @@ def _transfer(content, stylised, mask, mode, label=0, out=None, slots=None, quie
                     if cnt <= 0:
                         break
                     lp, ls = get_plan(dev, H, W, sh, sw, group, lane=lane), _lane_stream(dev, lane)
+                    # the workspace was allocated on another stream: if the plan is evicted from the cache and freed
+                    # while this lane still runs, the allocator must not hand the memory out before the lane is done
+                    lp.workspace.record_stream(ls)
                     ls.wait_event(start)
                     with lp.lock:
                         check(L.rct_transfer_async(

@@ -72,7 +72,7 @@ def parse_args():
     ap.add_argument("--labels-fused", type=int, default=1, choices=[0, 1],
                     help="labels workload: 1 all labels of a frame group in one launch group (rct_transfer_labels_async), "
                          "0 one pass per label (A/B runs)")
-    ap.add_argument("--lanes", type=int, default=0, choices=[0, 1, 2, 4],
+    ap.add_argument("--lanes", type=int, default=0, choices=[0, 1, 2, 3, 4],
                     help="launch groups in flight at once: the step's frames are split over this many plans, each on its own "
                          "stream (the solve kernels are latency-bound: concurrent groups overlap their stalls)")
     ap.add_argument("--keytab", type=int, default=1, choices=[0, 1],
