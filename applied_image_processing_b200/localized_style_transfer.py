@@ -93,6 +93,15 @@ class Plan:
         except Exception:
             pass
 
+    def on_current_stream(self):
+        """Context for enqueueing on the caller's current stream: tells the caching allocator that the workspace (allocated on
+        whatever stream was current when the plan was made) is in use there, so that a plan dropped from the LRU cache right
+        after the call cannot have its memory handed out while the kernels still run."""
+        import contextlib
+
+        self.workspace.record_stream(torch.cuda.current_stream(self.device))
+        return contextlib.nullcontext()
+
     def set_option(self, option: int, value: int):
         check(_cabi.lib().rct_plan_set_option(self.handle, option, value))
 
@@ -298,7 +307,7 @@ def _transfer(content, stylised, mask, mode, label=0, out=None, slots=None, quie
                     f0 += cnt
             return out
         plan = get_plan(dev, H, W, sh, sw, group)
-        with torch.cuda.device(dev), plan.lock:
+        with torch.cuda.device(dev), plan.lock, plan.on_current_stream():
             check(L.rct_transfer_async(
                 plan.handle, content.data_ptr(), H * W * 3, stylised.data_ptr(), sh * sw * 3 if sty_b else 0,
                 mask.data_ptr() if mask is not None else None, H * W if mask_b else 0, out.data_ptr(),
@@ -333,7 +342,7 @@ def _transfer(content, stylised, mask, mode, label=0, out=None, slots=None, quie
     if out is None:
         out = np.empty_like(content) if mode != MODE_LABEL else content.copy()
     status = np.zeros(n, np.int32)
-    with torch.cuda.device(dev), plan.lock:
+    with torch.cuda.device(dev), plan.lock, plan.on_current_stream():
         check(L.rct_transfer_host(plan.handle, content.ctypes.data, stylised.ctypes.data,
                                   mask.ctypes.data if mask is not None else None, out.ctypes.data, n, mode,
                                   label, status.ctypes.data))
@@ -533,7 +542,7 @@ def regional_color_transfer_binned(content, stylized, background_mask, bins=1024
     plan = get_plan(dev, H, W, sh, sw, slots or min(n, 8))
     if out is None:
         out = torch.empty_like(content) if mode != MODE_LABEL else content.clone()
-    with torch.cuda.device(dev), plan.lock:
+    with torch.cuda.device(dev), plan.lock, plan.on_current_stream():
         check(L.rct_transfer_binned_async(
             plan.handle, content.data_ptr(), H * W * 3, stylized.data_ptr(), sh * sw * 3 if sty_b else 0,
             background_mask.data_ptr() if background_mask is not None else None, H * W if mask_b else 0,
@@ -591,7 +600,7 @@ def _transfer_labels_fused(content, stylized, labels, n_labels, frames_per_group
         fpg -= 1
     plan = get_plan(dev, H, W, sh, sw, fpg * n_labels)
     out = content.clone()  # pixels of labels >= n_labels keep the content
-    with torch.cuda.device(dev), plan.lock:
+    with torch.cuda.device(dev), plan.lock, plan.on_current_stream():
         check(L.rct_transfer_labels_async(
             plan.handle, content.data_ptr(), H * W * 3, stylized.data_ptr(), sh * sw * 3 if sty_b else 0,
             labels.data_ptr(), H * W if lab_b else 0, out.data_ptr(), H * W * 3, n, n_labels, _stream_ptr()))
