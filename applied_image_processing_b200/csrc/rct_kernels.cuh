@@ -414,48 +414,69 @@ __global__ void __launch_bounds__(256, RCT_LMB) k_lab_moments(FrameCtrl *ctrl, c
         col = job.payA[e];
         cnt = job.cntA[e];
     }
+    // The hot loop holds nothing but fast-path entries (its 25 accumulators then stay in fixed register pairs); an
+    // entry that cannot take the fast path, or the 128th term, leaves it for the cold code below.
     while (e < d) {
-        const size_t en = e + stride;
-        unsigned coln = 0, cntn = 0;
-        if (en < d) {
-            coln = job.payA[en];
-            cntn = job.cntA[en];
-        }
+        bool slow = false;
         double lab[3];
-        rgb2lab(col, &T, lab);
-        long long q[3];
-#pragma unroll
-        for (int i = 0; i < 3; ++i) q[i] = __double2ll_rn(lab[i] * 0x1p40);
-        cmx = __vmaxu4(cmx, col);
-        cmn = __vminu4(cmn, col);
-        npx += cnt;
-        if (cnt < 128u) {
-            fast_add(f, q, cnt);
-            if (++terms == kFastTerms) {
-                i128 s1[3], s2[6];
-#pragma unroll
-                for (int k = 0; k < 3; ++k) s1[k] = fast_s1(f, k);
-#pragma unroll
-                for (int k = 0; k < 6; ++k) s2[k] = fast_s2(f, k);
-                spill(s1, s2);
-                fast_zero(f);
-                terms = 0;
+        unsigned coln = 0, cntn = 0;
+        size_t en = e;
+        auto step = [&]() -> bool {  // one entry; false: it has to take the slow path
+            en = e + stride;
+            coln = cntn = 0;
+            if (en < d) {
+                coln = job.payA[en];
+                cntn = job.cntA[en];
             }
-        } else {
+            rgb2lab(col, &T, lab);
+            cmx = __vmaxu4(cmx, col);
+            cmn = __vminu4(cmn, col);
+            npx += cnt;
+            if (!(cnt < 128u && fast_add(f, lab, cnt))) return false;
+            col = coln;
+            cnt = cntn;
+            e = en;
+            ++terms;
+            return true;
+        };
+#pragma unroll 1
+        do {  // two entries per trip: halves the register shuffling at the back edge
+            if (!step()) {
+                slow = true;
+                break;
+            }
+            if (!(terms < kFastTerms && e < d)) break;
+            if (!step()) {
+                slow = true;
+                break;
+            }
+        } while (terms < kFastTerms && e < d);
+        if (slow) {
             Moments m;
             moments_zero(m);
             moments_add(m, lab, (long long)cnt);
             spill(m.s1, m.s2);
+            col = coln;
+            cnt = cntn;
+            e = en;
         }
-        col = coln;
-        cnt = cntn;
-        e = en;
+        if (terms == kFastTerms) {
+            i128 s1[3], s2[6];
+            fast_finish(f, s1, s2);
+            spill(s1, s2);
+            fast_zero(f);
+            terms = 0;
+        }
     }
     long long v[28];
+    {
+        i128 s1[3], s2[6];
+        fast_finish(f, s1, s2);
 #pragma unroll
-    for (int k = 0; k < 3; ++k) split_limbs(fast_s1(f, k), v + 3 * k);
+        for (int k = 0; k < 3; ++k) split_limbs(s1[k], v + 3 * k);
 #pragma unroll
-    for (int k = 0; k < 6; ++k) split_limbs(fast_s2(f, k), v + 9 + 3 * k);
+        for (int k = 0; k < 6; ++k) split_limbs(s2[k], v + 9 + 3 * k);
+    }
     v[27] = npx;
     const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
 #pragma unroll

@@ -152,34 +152,52 @@ __device__ __forceinline__ void moments_add(Moments &m, const double lab[3], lon
         for (int j = i; j < 3; ++j) m.s2[k++] += (i128)q[i] * q[j] * cnt;
 }
 
-// Fast exact accumulation for small multiplicities (cnt < 128): q = qh * 2^24 + ql with
-// |qh| < 2^22, 0 <= ql < 2^24, so every partial product below is ONE 32x32->64 multiply-add
-// and the 64-bit partial sums cannot overflow within kFastTerms additions:
-//   cnt*q_i*q_j = A*2^48 + B*2^24 + C,  A = (cnt*qh_i)*qh_j, B = (cnt*qh_i)*ql_j + (cnt*ql_i)*qh_j,
-//   C = (cnt*ql_i)*ql_j.  Same integers as moments_add, an order of magnitude fewer instructions.
+// Fast exact accumulation for small multiplicities (cnt < 128), all in UNSIGNED 32x32->64 multiply-adds.
+// The fixed-point value is taken with a bias, q' = q + 2^44 >= 0 (|lab| < 11 < 2^4, so |q| < 2^44): the fused
+// fma(lab, 2^40, 2^52 + 2^44) rounds lab * 2^40 to the nearest integer, ties to even -- the same integer as
+// __double2ll_rn(lab * 2^40), the scaling being exact and the magic constant even -- and leaves q' in the low 52 bits
+// of the result.  q' = qh * 2^24 + ql with qh < 2^22, ql < 2^24, so with u = cnt*qh < 2^29, v = cnt*ql < 2^31
+//   cnt*q'_i*q'_j = A*2^48 + B*2^24 + C,  A = u_i*qh_j < 2^51,  B = u_i*ql_j + v_i*qh_j < 2^54,  C = v_i*ql_j < 2^55
+// and none of the 64-bit partial sums can overflow within kFastTerms = 128 additions.  The bias comes out again,
+// exactly, when the partial sums are turned into 128-bit integers (fast_finish): with w = sum of cnt,
+//   s1_i = s1'_i - 2^44 w,   s2_ij = s2'_ij - 2^44 (s1_i + s1_j) - 2^88 w.
+// Same integers as moments_add.  A value outside the biased range (cannot happen for a-4's clamped logarithms) makes
+// fast_add return false and the entry takes moments_add.  (Signed operands cost three times the instructions: the
+// compiler has no signed 32x32+64 multiply-add.)
 constexpr int kFastTerms = 128;
 struct MomentsFast {
-    long long U[3], V[3];
-    long long A[6], B[6], C[6];
+    unsigned long long U[3], V[3];
+    unsigned long long A[6], B[6], C[6];
+    unsigned w;
 };
 
 __device__ __forceinline__ void fast_zero(MomentsFast &f)
 {
 #pragma unroll
-    for (int i = 0; i < 3; ++i) f.U[i] = f.V[i] = 0;
+    for (int i = 0; i < 3; ++i) f.U[i] = f.V[i] = 0ull;
 #pragma unroll
-    for (int i = 0; i < 6; ++i) f.A[i] = f.B[i] = f.C[i] = 0;
+    for (int i = 0; i < 6; ++i) f.A[i] = f.B[i] = f.C[i] = 0ull;
+    f.w = 0u;
 }
 
-__device__ __forceinline__ void fast_add(MomentsFast &f, const long long q[3], unsigned cnt /* < 128 */)
+__device__ __forceinline__ bool fast_add(MomentsFast &f, const double lab[3], unsigned cnt /* < 128 */)
 {
-    int qh[3], ql[3], u[3], v[3];
+    unsigned qh[3], ql[3];
+    bool ok = true;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-        qh[i] = (int)(q[i] >> 24);
-        ql[i] = (int)(q[i] & 0xffffff);
-        u[i] = (int)cnt * qh[i];
-        v[i] = (int)cnt * ql[i];
+        const double x = fma(lab[i], 0x1p40, 0x1p52 + 0x1p44);
+        const unsigned hi = (unsigned)__double2hiint(x), lo = (unsigned)__double2loint(x);
+        ok = ok && (hi >> 14) == (0x43300000u >> 14);  // exponent of 2^52 and q' < 2^46
+        qh[i] = __funnelshift_r(lo, hi, 24) & 0x3fffffu;
+        ql[i] = lo & 0xffffffu;
+    }
+    if (!ok) return false;
+    unsigned u[3], v[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        u[i] = cnt * qh[i];
+        v[i] = cnt * ql[i];
         f.U[i] += u[i];
         f.V[i] += v[i];
     }
@@ -188,18 +206,29 @@ __device__ __forceinline__ void fast_add(MomentsFast &f, const long long q[3], u
     for (int i = 0; i < 3; ++i)
 #pragma unroll
         for (int j = i; j < 3; ++j) {
-            f.A[k] += (long long)u[i] * (long long)qh[j];
-            f.B[k] += (long long)u[i] * (long long)ql[j] + (long long)v[i] * (long long)qh[j];
-            f.C[k] += (long long)v[i] * (long long)ql[j];
+            f.A[k] += (unsigned long long)u[i] * qh[j];
+            f.B[k] += (unsigned long long)u[i] * ql[j] + (unsigned long long)v[i] * qh[j];
+            f.C[k] += (unsigned long long)v[i] * ql[j];
             ++k;
         }
+    f.w += cnt;
+    return true;
 }
 
-// exact values of the nine moments held in f: s1[0..2], s2[0..5]
-__device__ __forceinline__ i128 fast_s1(const MomentsFast &f, int i) { return ((i128)f.U[i] << 24) + (i128)f.V[i]; }
-__device__ __forceinline__ i128 fast_s2(const MomentsFast &f, int k)
+// exact (unbiased) values of the nine moments held in f: s1[0..2], s2[00,01,02,11,12,22]
+__device__ __forceinline__ void fast_finish(const MomentsFast &f, i128 s1[3], i128 s2[6])
 {
-    return ((i128)f.A[k] << 48) + ((i128)f.B[k] << 24) + (i128)f.C[k];
+    const i128 w = (i128)f.w;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) s1[i] = ((i128)f.U[i] << 24) + (i128)f.V[i] - (w << 44);
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = i; j < 3; ++j) {
+            s2[k] = ((i128)f.A[k] << 48) + ((i128)f.B[k] << 24) + (i128)f.C[k] - ((s1[i] + s1[j]) << 44) - (w << 88);
+            ++k;
+        }
 }
 
 __device__ __forceinline__ double i128_to_double(i128 v)
