@@ -521,22 +521,30 @@ __global__ void __launch_bounds__(1024) k_part_scan(const Job *jobs)
 // representation.  A multiset of n values is d distinct-entry records; the q-th smallest
 // value (0-based) is the key of the first entry whose cumulative count exceeds q.
 // ------------------------------------------------------------------------------------------
-struct Sorted {
+// Ranks are carried in the integer type R: int when both regions hold fewer than 2^31 pixels (every real frame; the
+// 64-bit compares, conversions and register pairs of long long ranks were a third of k_match's instructions), long long
+// otherwise.  Same values, same floating-point operations in the same order, for either type.
+template <class R>
+struct SortedT {
     const Rec *rec;                  // sorted; hi word of .y = part-local inclusive cumulative count
     const unsigned *pstart, *pbase;  // [n_parts+1]
     unsigned n_parts, d;
-    long long n;
+    R n;
     double inv;                      // 1.0 / (n - 1): the step of np.linspace(0, 1, n)
 };
+typedef SortedT<long long> Sorted;
 
-__device__ __forceinline__ Sorted sorted_of(const Job &j)
+template <class R>
+__device__ __forceinline__ SortedT<R> sorted_as(const Job &j)
 {
-    long long n = (long long)j.rc->n_pix;
-    return Sorted{j.recP, j.pstart, j.ppix, j.rc->n_parts, j.rc->d, n, n > 1 ? 1.0 / (double)(n - 1) : 0.0};
+    const R n = (R)j.rc->n_pix;
+    return SortedT<R>{j.recP, j.pstart, j.ppix, j.rc->n_parts, j.rc->d, n, n > 1 ? 1.0 / (double)(n - 1) : 0.0};
 }
+__device__ __forceinline__ Sorted sorted_of(const Job &j) { return sorted_as<long long>(j); }
 
 // np.linspace(0, 1, v.n)[k]  (same arithmetic as lin(), with the reciprocal hoisted)
-__device__ __forceinline__ double lin_of(const Sorted &v, long long k)
+template <class R>
+__device__ __forceinline__ double lin_of(const SortedT<R> &v, R k)
 {
     if (v.n == 1) return 0.0;
     if (k == v.n - 1) return 1.0;
@@ -549,40 +557,43 @@ struct Hint {
     bool fresh;  // ignore .i: start every search from the interpolated position (interleaved traversal)
 };
 
-__device__ __forceinline__ unsigned cum_local(const Sorted &v, unsigned i)
+template <class R>
+__device__ __forceinline__ unsigned cum_local(const SortedT<R> &v, unsigned i)
 {
     return (unsigned)(__ldg(reinterpret_cast<const unsigned long long *>(v.rec + i) + 1) >> 32);
 }
-__device__ __forceinline__ double key_at(const Sorted &v, unsigned i)
+template <class R>
+__device__ __forceinline__ double key_at(const SortedT<R> &v, unsigned i)
 {
     return __longlong_as_double((long long)__ldg(reinterpret_cast<const unsigned long long *>(v.rec + i)));
 }
 
 // index of the entry holding the q-th smallest value; h carries the last position found
-__device__ unsigned os_index(const Sorted &v, long long q, Hint &h)
+template <class R>
+__device__ unsigned os_index(const SortedT<R> &v, R q, Hint &h)
 {
     unsigned p;
     bool near = false;
-    if (h.valid && q >= (long long)__ldg(v.pbase + h.p)) {
+    if (h.valid && q >= (R)__ldg(v.pbase + h.p)) {
         // ranks move forward slowly: same part, or one of the next two
         p = h.p;
         int hop = 0;
-        while (hop < 3 && q >= (long long)__ldg(v.pbase + p + 1)) {
+        while (hop < 3 && q >= (R)__ldg(v.pbase + p + 1)) {
             ++p;
             ++hop;
         }
-        near = q < (long long)__ldg(v.pbase + p + 1);
+        near = q < (R)__ldg(v.pbase + p + 1);
     }
     if (!near) {
         unsigned lo = 0, hi = v.n_parts - 1;  // last part with pbase <= q
         while (lo < hi) {
             unsigned mid = (lo + hi + 1) >> 1;
-            if ((long long)__ldg(v.pbase + mid) <= q) lo = mid; else hi = mid - 1;
+            if ((R)__ldg(v.pbase + mid) <= q) lo = mid; else hi = mid - 1;
         }
         p = lo;
     }
     const unsigned b0 = __ldg(v.pbase + p);
-    const unsigned ql = (unsigned)(q - (long long)b0);
+    const unsigned ql = (unsigned)(q - (R)b0);
     const unsigned ps = __ldg(v.pstart + p), pe = __ldg(v.pstart + p + 1);
     // entries per rank inside this part (multiplicities are roughly even within a part)
     const float scale = __fdividef((float)(pe - ps), (float)(__ldg(v.pbase + p + 1) - b0));
@@ -625,84 +636,130 @@ __device__ unsigned os_index(const Sorted &v, long long q, Hint &h)
     return lo;
 }
 
-__device__ __forceinline__ double os_value(const Sorted &v, long long q, Hint &h) { return key_at(v, os_index(v, q, h)); }
+template <class R>
+__device__ __forceinline__ double os_value(const SortedT<R> &v, R q, Hint &h) { return key_at(v, os_index(v, q, h)); }
 
 // values at ranks q and q+1 with one search (q+1 < v.n)
-__device__ __forceinline__ void os_pair(const Sorted &v, long long q, Hint &h, double &v0, double &v1)
+template <class R>
+__device__ __forceinline__ void os_pair(const SortedT<R> &v, R q, Hint &h, double &v0, double &v1)
 {
     unsigned idx = os_index(v, q, h);
     v0 = key_at(v, idx);
-    long long g_end = (long long)__ldg(v.pbase + h.p) + (long long)cum_local(v, idx);  // first rank after idx
+    R g_end = (R)__ldg(v.pbase + h.p) + (R)cum_local(v, idx);  // first rank after idx
     v1 = (q + 1 < g_end) ? v0 : key_at(v, idx + 1);
 }
 
-// np.interp(x, np.linspace(0,1,v.n), sorted(v)) for 0 <= x <= 1
-__device__ double interp_lin_os(double x, const Sorted &v, Hint &h)
+// np.interp's bracket for 0 <= x <= 1 over np.linspace(0, 1, v.n), v.n >= 2: the largest m with lin(m) <= x, starting
+// from the estimate floor(x * (n - 1)).  lin() is non-decreasing in its index, so either the upward or the downward
+// walk runs, never both; xm = lin(m), and x1 = lin(m + 1) when m < n - 1.
+template <class R>
+__device__ __forceinline__ R lin_bracket(const SortedT<R> &v, double x, double &xm, double &x1)
 {
-    const long long n = v.n;
-    if (n == 1) return os_value(v, 0, h);
-    long long m = (long long)(x * (double)(n - 1));
+    const R n = v.n;
+    R m = (R)(x * (double)(n - 1));
     if (m < 0) m = 0;
     if (m > n - 1) m = n - 1;
-    while (m + 1 <= n - 1 && lin_of(v, m + 1) <= x) ++m;
-    while (m > 0 && lin_of(v, m) > x) --m;
-    if (m >= n - 1) return os_value(v, n - 1, h);
-    double xm = lin_of(v, m);
+    xm = lin_of(v, m);
+    x1 = 1.0;
+    if (xm <= x) {
+        while (m + 1 <= n - 1) {
+            x1 = lin_of(v, (R)(m + 1));
+            if (!(x1 <= x)) break;
+            ++m;
+            xm = x1;
+        }
+    } else {
+        while (m > 0 && xm > x) {
+            --m;
+            x1 = xm;
+            xm = lin_of(v, m);
+        }
+    }
+    return m;
+}
+
+// np.interp(x, np.linspace(0,1,v.n), sorted(v)) for 0 <= x <= 1
+template <class R>
+__device__ double interp_lin_os(double x, const SortedT<R> &v, Hint &h)
+{
+    const R n = v.n;
+    if (n == 1) return os_value(v, (R)0, h);
+    double xm, x1;
+    const R m = lin_bracket(v, x, xm, x1);
+    if (m >= n - 1) return os_value(v, (R)(n - 1), h);
     double fm, fm1;
     os_pair(v, m, h, fm, fm1);
     if (xm == x) return fm;
-    double slope = (fm1 - fm) / (lin_of(v, m + 1) - xm);
+    double slope = (fm1 - fm) / (x1 - xm);
     return slope * (x - xm) + fm;
 }
 
 // The neighbourhood of one target entry in rank space: ranks [g_lo, g_hi) hold `key`, rank g_hi
 // holds k_next, rank g_lo-1 holds k_prev.  The stretched-target evaluations of a-6 only ever
 // look at ranks next to the entry's own, so they resolve here without any search.
-struct TWin {
-    long long g_lo, g_hi;
+template <class R>
+struct TWinT {
+    R g_lo, g_hi;
     double key, k_prev, k_next;
 };
 
-__device__ __forceinline__ double t_value(const Sorted &t, const TWin &w, long long m, Hint &ht)
+// value at rank q by a full search, as a real function call: for call sites that (almost) never execute, so that the
+// search is not inlined a dozen times into the kernel (k_match was 210 KB of SASS, i-cache misses showed in the stalls)
+#ifndef RCT_OSCOLD
+#define RCT_OSCOLD 0
+#endif
+#if RCT_OSCOLD
+#define RCT_COLD_FN __noinline__
+#else
+#define RCT_COLD_FN __forceinline__
+#endif
+template <class R>
+__device__ RCT_COLD_FN double os_value_cold(const Rec *rec, const unsigned *pstart, const unsigned *pbase, unsigned n_parts, R q)
+{
+    SortedT<R> v{rec, pstart, pbase, n_parts, 0u, (R)0, 0.0};
+    Hint h{0, 0, false, true};
+    return os_value(v, q, h);
+}
+
+template <class R>
+__device__ __forceinline__ double t_value(const SortedT<R> &t, const TWinT<R> &w, R m, Hint &ht)
 {
     if (m >= w.g_lo && m < w.g_hi) return w.key;
     if (m == w.g_hi) return w.k_next;
     if (m == w.g_lo - 1) return w.k_prev;
-    return os_value(t, m, ht);
+    return os_value_cold<R>(t.rec, t.pstart, t.pbase, t.n_parts, m);
 }
 
-// t'[.] at x: np.interp(x, np.linspace(0,1,T), sorted target)
-__device__ double interp_target(double x, const Sorted &t, const TWin &w, Hint &ht)
+// t'[.] at x: np.interp(x, np.linspace(0,1,T), sorted target), T >= 2
+template <class R>
+__device__ double interp_target(double x, const SortedT<R> &t, const TWinT<R> &w, Hint &ht)
 {
-    const long long n = t.n;
-    long long m = (long long)(x * (double)(n - 1));
-    if (m < 0) m = 0;
-    if (m > n - 1) m = n - 1;
-    while (m + 1 <= n - 1 && lin_of(t, m + 1) <= x) ++m;
-    while (m > 0 && lin_of(t, m) > x) --m;
-    if (m >= n - 1) return t_value(t, w, n - 1, ht);
-    double xm = lin_of(t, m);
+    const R n = t.n;
+    double xm, x1;
+    const R m = lin_bracket(t, x, xm, x1);
+    if (m >= n - 1) return t_value(t, w, (R)(n - 1), ht);
     double fm = t_value(t, w, m, ht);
     if (xm == x) return fm;
-    double fm1 = t_value(t, w, m + 1, ht);
-    double slope = (fm1 - fm) / (lin_of(t, m + 1) - xm);
+    double fm1 = t_value(t, w, (R)(m + 1), ht);
+    double slope = (fm1 - fm) / (x1 - xm);
     return slope * (x - xm) + fm;
 }
 
 // entry i of the sorted target (inside part p); ht / hs: search hints into target / source
-__device__ double match_one(const Sorted &t, const Sorted &s, unsigned p, unsigned i, Hint &ht, Hint &hs,
+template <class R>
+__device__ double match_one(const SortedT<R> &t, const SortedT<R> &s, unsigned p, unsigned i, Hint &ht, Hint &hs,
                             long long &j_out)
 {
     const double key = key_at(t, i);
     const unsigned ps = __ldg(t.pstart + p), pe = __ldg(t.pstart + p + 1);
     unsigned i2 = i;
     while (i2 + 1 < pe && key_at(t, i2 + 1) == key) ++i2;  // ties share the upper rank
-    const long long base = (long long)__ldg(t.pbase + p);
-    const long long g_hi = base + (long long)cum_local(t, i2);
-    const long long r = g_hi - 1;
-    const long long T = t.n, S = s.n;
+    const R base = (R)__ldg(t.pbase + p);
+    const R g_hi = base + (R)cum_local(t, i2);
+    const R r = g_hi - 1;
+    const R T = t.n, S = s.n;
     double m;
-    long long j;
+    R j;
     if (T == S) {
         j = r;
         m = os_value(s, r, hs);
@@ -718,23 +775,23 @@ __device__ double match_one(const Sorted &t, const Sorted &s, unsigned p, unsign
         } else {
             unsigned i1 = i;
             while (i1 > ps && key_at(t, i1 - 1) == key) --i1;
-            TWin w;
+            TWinT<R> w;
             w.key = key;
             w.g_hi = g_hi;
-            w.g_lo = base + (i1 > ps ? (long long)cum_local(t, i1 - 1) : 0ll);
+            w.g_lo = base + (i1 > ps ? (R)cum_local(t, i1 - 1) : (R)0);
             w.k_prev = i1 > 0 ? key_at(t, i1 - 1) : key;
             w.k_next = i2 + 1 < t.d ? key_at(t, i2 + 1) : key;
             ht.p = p;
             ht.i = i2;
             ht.valid = true;
             double xr = lin_of(t, r);
-            long long k = (long long)(xr * (double)(S - 1));
+            R k = (R)(xr * (double)(S - 1));
             if (k < 0) k = 0;
             if (k > S - 1) k = S - 1;
             double tk = interp_target(lin_of(s, k), t, w, ht);
             if (tk <= key) {
                 while (k + 1 <= S - 1) {
-                    double tn = interp_target(lin_of(s, k + 1), t, w, ht);
+                    double tn = interp_target(lin_of(s, (R)(k + 1)), t, w, ht);
                     if (tn <= key) {
                         ++k;
                         tk = tn;
@@ -754,10 +811,10 @@ __device__ double match_one(const Sorted &t, const Sorted &s, unsigned p, unsign
             }
             j = k;
             tj = tk;
-            if (j < S - 1 && tj != key && !have_j1) tj1 = interp_target(lin_of(s, j + 1), t, w, ht);
+            if (j < S - 1 && tj != key && !have_j1) tj1 = interp_target(lin_of(s, (R)(j + 1)), t, w, ht);
         }
         if (j >= S - 1) {
-            m = os_value(s, S - 1, hs);
+            m = os_value(s, (R)(S - 1), hs);
         } else {
             double sj, sj1;
             os_pair(s, j, hs, sj, sj1);
@@ -769,7 +826,7 @@ __device__ double match_one(const Sorted &t, const Sorted &s, unsigned p, unsign
             }
         }
     }
-    j_out = j;
+    j_out = (long long)j;
     return m;
 }
 
@@ -876,21 +933,17 @@ __global__ void __launch_bounds__(kPalThreads) k_pal_write(FrameCtrl *ctrl, cons
 #define RCT_MATCHT 128
 #endif
 constexpr int kMatchThreads = RCT_MATCHT;
-template <int LUTM>
-__device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0,
-                                                         size_t lut_stride, double *dbg_matched0, long long *dbg_j0,
-                                                         size_t dbg_stride, int interleave, uint8_t *kt0)
+template <int LUTM, class R>
+__device__ __forceinline__ void match_body_r(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0, size_t lut_stride,
+                                             double *dbg_matched0, long long *dbg_j0, size_t dbg_stride, int interleave,
+                                             uint8_t *kt0, const MathTabs *Tp)
 {
     const int slot = blockIdx.y;
-    if (ctrl[slot].status != 0) return;
     const Job &jt = jobs[2 * slot], &js = jobs[2 * slot + 1];
     const unsigned p = blockIdx.x;
-    if (p >= jt.rc->n_parts) return;
-    const Sorted t = sorted_of(jt), s = sorted_of(js);
+    const SortedT<R> t = sorted_as<R>(jt), s = sorted_as<R>(js);
     const unsigned ps = jt.pstart[p], pe = jt.pstart[p + 1];
-    if (ps == pe) return;
-    __shared__ MathTabs T;
-    stage_tabs(&T);
+    const MathTabs &T = *Tp;
     const Pca pca = jt.rc->pca;
     unsigned *lut = lut0 + (size_t)slot * lut_stride;
     unsigned *rgb_sorted = pal_rgb_sorted(jt);
@@ -966,6 +1019,26 @@ __device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, uns
             }
         }
     }
+}
+
+template <int LUTM>
+__device__ __forceinline__ void match_body(FrameCtrl *ctrl, const Job *jobs, unsigned *lut0, size_t lut_stride,
+                                           double *dbg_matched0, long long *dbg_j0, size_t dbg_stride, int interleave,
+                                           uint8_t *kt0)
+{
+    const int slot = blockIdx.y;
+    if (ctrl[slot].status != 0) return;
+    const Job &jt = jobs[2 * slot], &js = jobs[2 * slot + 1];
+    const unsigned p = blockIdx.x;
+    if (p >= jt.rc->n_parts) return;
+    if (jt.pstart[p] == jt.pstart[p + 1]) return;
+    __shared__ MathTabs T;
+    stage_tabs(&T);
+    // block-uniform: ranks fit 32-bit integers unless a region holds 2^31 pixels or more
+    if ((jt.rc->n_pix | js.rc->n_pix) < (1ull << 31))
+        match_body_r<LUTM, int>(ctrl, jobs, lut0, lut_stride, dbg_matched0, dbg_j0, dbg_stride, interleave, kt0, &T);
+    else
+        match_body_r<LUTM, long long>(ctrl, jobs, lut0, lut_stride, dbg_matched0, dbg_j0, dbg_stride, interleave, kt0, &T);
 }
 
 #ifndef RCT_MATCHB
