@@ -650,6 +650,7 @@ int ensure_kernel_attrs()
     CK(cudaFuncSetAttribute(k_part_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemPartSort));
     CK(cudaFuncSetAttribute(k_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemScatter));
     CK(cudaFuncSetAttribute(k_scatter_tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemScatter2));
+    CK(cudaFuncSetAttribute(k_scatter_runs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemScatter3));
     done_dev = dev;
     return RCT_OK;
 }
@@ -673,16 +674,31 @@ int sort_jobs(rct_plan *p, const Job *jobs, int njobs, unsigned eblocks, size_t 
 #ifndef RCT_SB
 #define RCT_SB 12
 #endif
+#ifndef RCT_SCATTER_DEFAULT
+#define RCT_SCATTER_DEFAULT 0
+#endif
     unsigned sblocks = (unsigned)((p ? p->sm : 148) * RCT_SB / (njobs > 0 ? njobs : 1));  // ~4 waves of 3 CTAs per SM
     if (sblocks < 16u) sblocks = 16u;
-    // k_scatter_tiled (one global reservation per 16K-entry tile and part) is opt-in: measured on 8 x 4K it is 9 % faster
-    // than k_scatter on N (0.507 vs 0.558 ms) but 6 % slower on U (1.079 vs 1.017 ms) -- the per-entry global atomics were
-    // not what bounds this kernel (profiles/r02_summary.md)
-    static const bool tiled_on = getenv("RCT_SCATTER_TILED") && atoi(getenv("RCT_SCATTER_TILED")) != 0;
-    if (tiled_on && maxparts <= (size_t)kScat2MaxParts) {
+    // Three scatters, the same time on the worst case (8 x 4K U, ms; N in brackets): k_scatter 0.996 (0.576), one returning
+    // global atomic + one 16-byte store per entry; k_scatter_tiled 1.079 (0.507), one global reservation per 16K-entry tile
+    // and part; k_scatter_runs 0.999 (0.532), the tile sorted by part in shared memory and streamed out in runs.  Neither
+    // the per-entry atomics nor the store granularity at the L1 is what bounds it.  The tiled kernels hold a whole SM
+    // (1024 threads, 120-200 KB), which costs the overlap with the other launch group: the U step is 10.83 ms with
+    // k_scatter_runs against 10.57 ms with k_scatter, so k_scatter stays the default (profiles/r02_summary.md).
+    // RCT_SCATTER_TILED: 0 = k_scatter, 1 = k_scatter_tiled, 2 = k_scatter_runs (tile sorted by part in shared memory)
+    static const int tiled = getenv("RCT_SCATTER_TILED") ? atoi(getenv("RCT_SCATTER_TILED")) : RCT_SCATTER_DEFAULT;
+    const unsigned sm = (unsigned)(p ? p->sm : 148), nj = (unsigned)(njobs > 0 ? njobs : 1);
+    if (tiled == 2 && maxparts <= (size_t)kScat3MaxParts) {
+        // one resident CTA per SM; ~3 CTAs per SM in the grid so that jobs of different length balance
+        unsigned tb = (unsigned)((cap + kScat3Tile - 1) / kScat3Tile);
+        unsigned per_job = sm * 3u / nj;
+        if (per_job < 1u) per_job = 1u;
+        if (tb > per_job) tb = per_job;
+        k_scatter_runs<<<dim3(tb ? tb : 1u, njobs), kScat3Threads, kSmemScatter3, st>>>(jobs);
+    } else if (tiled == 1 && maxparts <= (size_t)kScat2MaxParts) {
         // one CTA per SM and job at most; tiles of 16 K entries
         unsigned tb = (unsigned)((cap + kScat2Tile - 1) / kScat2Tile);
-        const unsigned per_job = (unsigned)((p ? p->sm : 148) * 2 / (njobs > 0 ? njobs : 1));
+        const unsigned per_job = sm * 2u / nj;
         if (tb > (per_job ? per_job : 1u)) tb = per_job ? per_job : 1u;
         k_scatter_tiled<<<dim3(tb ? tb : 1u, njobs), kScat2Threads, kSmemScatter2, st>>>(jobs);
     } else {

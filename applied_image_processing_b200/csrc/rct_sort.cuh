@@ -322,6 +322,107 @@ __global__ void __launch_bounds__(kScat2Threads, 1) k_scatter_tiled(const Job *j
     }
 }
 
+// k_scatter_runs: the scatter with the tile SORTED BY PART in shared memory before it leaves the SM.
+// ncu on k_scatter (4 x 4K U): every entry costs the L1 three uncoalesced sectors (its fill-counter atomic, its 16-byte
+// record store, 0.9 of coalesced loads) and the kernel sits at 63 % of the L1's and 45 % of the L2's request
+// throughput with the warps waiting on the returning atomics -- request-bound, not byte-bound.  Here a CTA of 1024
+// threads takes tiles of kScat3Tile = 6144 entries: (1) every entry is ranked inside (tile, part) by a shared-memory
+// atomic, (2) the per-part counts are scanned into tile offsets and each part present reserves its run of the part's
+// slice with ONE global atomic, (3) the records are laid out part by part in shared memory, (4) the tile is streamed out
+// in order: neighbouring lanes write neighbouring records of the same run (~4 records = 2-3 sectors per run on a 4K
+// noise frame instead of one sector per record, and a quarter of the atomics).  The records stay in registers between
+// (1) and (3): nothing is read twice.  Jobs with more than kScat3MaxParts parts (a 16K frame) take k_scatter.
+constexpr int kScat3Threads = 1024;
+#ifndef RCT_SCAT3PER
+#define RCT_SCAT3PER 6
+#endif
+constexpr int kScat3Per = RCT_SCAT3PER;
+constexpr int kScat3Tile = kScat3Threads * kScat3Per;
+constexpr int kScat3MaxParts = 4096;
+constexpr int kScat3CP = kScat3MaxParts / kScat3Threads;  // counters per thread in the scan
+constexpr size_t kScat3OffCnt = (kSmemScatter + 15) / 16 * 16;
+constexpr size_t kScat3OffRec = kScat3OffCnt + (size_t)kScat3MaxParts * 8;
+constexpr size_t kSmemScatter3 = kScat3OffRec + (size_t)kScat3Tile * 18;
+__global__ void __launch_bounds__(kScat3Threads, 1) k_scatter_runs(const Job *jobs)
+{
+    const Job &job = jobs[blockIdx.y];
+    RegionCtrl *rc = job.rc;
+    if (rc->skip) return;
+    const unsigned d = rc->d;
+    if ((size_t)blockIdx.x * kScat3Tile >= d) return;
+    extern __shared__ __align__(16) unsigned s_scat[];
+    __shared__ unsigned s_warp[33];
+    unsigned *s_base = s_scat;                                                         // [kCoarse + 1]
+    unsigned short *s_pof = reinterpret_cast<unsigned short *>(s_scat + kCoarse + 2);  // [n_fine]
+    unsigned *s_cnt = s_scat + kScat3OffCnt / 4;   // [n_parts]: entries of the tile in the part, then its tile offset
+    unsigned *s_gb = s_cnt + kScat3MaxParts;       // [n_parts]: first global position of the run minus the tile offset
+    Rec *srec = reinterpret_cast<Rec *>(reinterpret_cast<unsigned char *>(s_scat) + kScat3OffRec);  // [kScat3Tile]
+    unsigned short *spart = reinterpret_cast<unsigned short *>(srec + kScat3Tile);                    // [kScat3Tile]
+    const unsigned np = rc->n_parts, tid = threadIdx.x;
+    {
+        const unsigned nf2 = (rc->n_fine + 1u) / 2u;
+        const unsigned *pof32 = reinterpret_cast<const unsigned *>(job.pof);
+        unsigned *s_pof32 = s_scat + kCoarse + 2;
+        for (unsigned i = tid; i <= (unsigned)kCoarse; i += kScat3Threads) s_base[i] = rc->fine_base[i];
+        for (unsigned i = tid; i < nf2; i += kScat3Threads) s_pof32[i] = pof32[i];
+    }
+    const double klo = rc->klo, cscale = rc->cscale;
+    Rec *recP = job.recP;
+    for (size_t t0 = (size_t)blockIdx.x * kScat3Tile; t0 < d; t0 += (size_t)gridDim.x * kScat3Tile) {
+        for (unsigned i = tid; i < np; i += kScat3Threads) s_cnt[i] = 0u;
+        double key[kScat3Per];
+        unsigned pay[kScat3Per], cnt[kScat3Per], pr[kScat3Per];  // pr: part | rank inside (tile, part) << 16
+#pragma unroll
+        for (int k = 0; k < kScat3Per; ++k) {
+            const size_t e = t0 + (size_t)k * kScat3Threads + tid;
+            key[k] = e < d ? job.keyA[e] : 0.0;
+            pay[k] = (e < d && job.payA) ? job.payA[e] : (unsigned)e;
+            cnt[k] = (e < d && job.cntA) ? job.cntA[e] : 1u;
+        }
+        __syncthreads();  // counters cleared (and, on the first trip, the tables staged)
+#pragma unroll
+        for (int k = 0; k < kScat3Per; ++k) {
+            const size_t e = t0 + (size_t)k * kScat3Threads + tid;
+            pr[k] = 0xffffffffu;
+            if (e < d) {
+                double ff;
+                const unsigned p = s_pof[fine_bin(key[k], klo, cscale, s_base, ff)];
+                pr[k] = p | (atomicAdd(&s_cnt[p], 1u) << 16);
+            }
+        }
+        __syncthreads();
+        unsigned c[kScat3CP], sum = 0;
+#pragma unroll
+        for (int k = 0; k < kScat3CP; ++k) {
+            const unsigned i = tid * kScat3CP + k;
+            c[k] = i < np ? s_cnt[i] : 0u;
+            sum += c[k];
+        }
+        unsigned n_tile;
+        unsigned off = block_excl_scan(sum, s_warp, n_tile);
+#pragma unroll
+        for (int k = 0; k < kScat3CP; ++k) {
+            const unsigned i = tid * kScat3CP + k;
+            if (i < np) {
+                s_cnt[i] = off;
+                if (c[k]) s_gb[i] = atomicAdd(&job.pfill[(size_t)i * kFillStride], c[k]) - off;
+                off += c[k];
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < kScat3Per; ++k)
+            if (pr[k] != 0xffffffffu) {
+                const unsigned p = pr[k] & 0xffffu, j = s_cnt[p] + (pr[k] >> 16);
+                srec[j] = make_rec(key[k], pay[k], cnt[k]);
+                spart[j] = (unsigned short)p;
+            }
+        __syncthreads();
+        for (unsigned j = tid; j < n_tile; j += kScat3Threads) recP[s_gb[spart[j]] + j] = srec[j];
+        __syncthreads();  // the tile is out before its counters and slots are reused
+    }
+}
+
 // ascending bitonic network over n (any n) records by (key, payload); works on shared or
 // global memory (generic pointers); implicit +inf padding above n.
 __device__ void block_bitonic(Rec *rec, unsigned n)
