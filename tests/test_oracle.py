@@ -131,3 +131,20 @@ def test_reference_edge_cases():
     assert np.array_equal(lst.color_transfer_foreground(c, blk), c)
     out, st, _ = orc.transfer(c, blk, None, mode=orc.MODE_ALL)
     assert st == 2 and np.array_equal(out, c)
+
+
+@needs_ref
+def test_match_cdf_sweep_vs_live_reference():
+    """300 seeded cases against the live reference, bit for bit: lengths that differ by 0..3 (the regime of the bench
+    frames, whose regions differ by the few forced-black pixels), unrelated lengths, length 1, and values quantised to
+    a coarse grid (long tie groups, as distinct colours with equal projection keys produce)."""
+    lst = ref_shim.load_reference()
+    rng = np.random.default_rng(3)
+    for trial in range(300):
+        nt = int(rng.integers(1, 4000))
+        ns = max(nt + int(rng.integers(-3, 4)), 1) if trial % 6 < 3 else int(rng.integers(1, 4000))
+        t, s = rng.normal(0, 1, (nt, 1)), rng.normal(0.3, 2, (ns, 1))
+        q = [None, 0.5, 0.05][trial % 3]
+        if q:
+            t, s = np.round(t / q) * q, np.round(s / q) * q
+        assert np.array_equal(orc.match_cdf(t, s), lst.match_cdf(t, s)), (trial, nt, ns, q)
