@@ -1584,7 +1584,11 @@ int rct_png_decode_host(const uint8_t *file_host, size_t nbytes, uint8_t *rgb_ho
     rct_png::Info info;
     if (!rct_png::parse_header(file_host, nbytes, &info)) return fail(RCT_ERR_ARG, "%s", info.error.c_str());
     if ((size_t)info.H * (size_t)info.W * 3u > rgb_capacity) return fail(RCT_ERR_ARG, "PNG: output buffer too small");
-    if (!rct_png::decode(file_host, nbytes, &info, rgb_host)) return fail(RCT_ERR_ARG, "%s", info.error.c_str());
+    try {  // the inflate / unfilter buffers are sized by the file's header: no exception may cross the C ABI
+        if (!rct_png::decode(file_host, nbytes, &info, rgb_host)) return fail(RCT_ERR_ARG, "%s", info.error.c_str());
+    } catch (const std::bad_alloc &) {
+        return fail(RCT_ERR_NOMEM, "PNG: out of host memory for a %d x %d image", info.W, info.H);
+    }
     return RCT_OK;
 }
 
@@ -1610,8 +1614,12 @@ int decode_file_to_device(const uint8_t *file, size_t nbytes, int H, int W, cons
         rct_png::Info info;
         if (!rct_png::parse_header(file, nbytes, &info)) return fail(RCT_ERR_ARG, "%s: %s", what, info.error.c_str());
         if (info.H != H || info.W != W) return fail(RCT_ERR_ARG, "%s is %dx%d, the plan expects %dx%d", what, info.W, info.H, W, H);
-        host_tmp.resize((size_t)H * W * 3);
-        if (!rct_png::decode(file, nbytes, &info, host_tmp.data())) return fail(RCT_ERR_ARG, "%s: %s", what, info.error.c_str());
+        try {  // sized by the plan / the file's header: no exception may cross the C ABI
+            host_tmp.resize((size_t)H * W * 3);
+            if (!rct_png::decode(file, nbytes, &info, host_tmp.data())) return fail(RCT_ERR_ARG, "%s: %s", what, info.error.c_str());
+        } catch (const std::bad_alloc &) {
+            return fail(RCT_ERR_NOMEM, "%s: out of host memory for a %d x %d PNG", what, W, H);
+        }
         CK(cudaMemcpyAsync(dst, host_tmp.data(), host_tmp.size(), cudaMemcpyHostToDevice, st));
         CK(cudaStreamSynchronize(st));  // host_tmp is reused for the next file
         return RCT_OK;
