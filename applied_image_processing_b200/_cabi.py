@@ -75,6 +75,7 @@ SIGNATURES = {
     "rct_pca_inverse": (_i, [_vp, _sz, _vp, _vp, _vp, _vp]),
     "rct_match_scratch_bytes": (_sz, [_sz, _sz]),
     "rct_match_cdf": (_i, [_vp, _sz, _vp, _sz, _vp, _vp, _vp, _vp]),
+    "rct_match_cdf_static": (_i, [_vp, _sz, _vp, _sz, _vp, _vp, _vp]),
     "rct_adain_mask_blend": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _sz, _vp]),
     "rct_softmax_threshold_mask": (_i, [_vp, _i, _sz, _i, C.c_float, _vp, _vp]),
     "rct_argmax_labels": (_i, [_vp, _i, _sz, _vp, _vp]),

@@ -1410,6 +1410,64 @@ int rct_match_cdf(const double *target_proj, size_t nt, const double *source_pro
     return RCT_OK;
 }
 
+// ---- match_cdf with built-in scratch: for callers that must not allocate device memory -------------
+// Some hosts of this library are not allowed to call cudaMalloc at the point where they need a CDF match: code running
+// while a CUDA graph is being built or under a memory pool whose budget is fixed at start-up, plug-ins of an
+// application that owns the device heap and hands out no allocator, and latency-critical loops in which an implicit
+// device synchronisation (cudaMalloc / cudaFree can cause one) is not acceptable.  For them the work arrays of the
+// sort (rct_match_scratch_bytes) live in the library image itself: one array per GPU that loads librct.so, present
+// from module load until the process exits.  Bounded on purpose: RCT_MATCH_STATIC_MAX entries on either side.
+namespace {
+constexpr size_t kStaticMatchMax = RCT_MATCH_STATIC_MAX;
+constexpr size_t kStaticMatchBytes = (size_t)34 << 20;  // >= match_layout(max, max).total = 33 961 728; checked at set-up
+}  // namespace
+static __device__ __align__(256) unsigned char g_match_static[kStaticMatchBytes];
+namespace {
+// g_match_static above is, in host code, only a handle of the symbol: it is NOT a device address and must never be
+// given to a kernel or a cudaMemset.  The address a kernel can use differs per GPU and comes from
+// cudaGetSymbolAddress with that GPU current; it is looked up once per device and kept here (guarded by g_mu).
+void *g_match_static_ptr[64] = {nullptr};
+
+int match_static_scratch(int dev, void **out)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_match_static_ptr[dev]) {
+        if (match_layout(kStaticMatchMax, kStaticMatchMax).total > kStaticMatchBytes)
+            return fail(RCT_ERR_ARG, "built-in match scratch (%zu bytes) is smaller than the layout of %zu entries needs",
+                        kStaticMatchBytes, kStaticMatchMax);
+        void *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_match_static);
+        if (e != cudaSuccess || !ptr)
+            return fail(RCT_ERR_CUDA, "cudaGetSymbolAddress(built-in match scratch) failed on device %d: %s", dev,
+                        cudaGetErrorString(e));
+        g_match_static_ptr[dev] = ptr;
+    }
+    *out = g_match_static_ptr[dev];
+    return RCT_OK;
+}
+}  // namespace
+
+int rct_match_cdf_static(const double *target_proj, size_t nt, const double *source_proj, size_t ns, double *matched,
+                         int64_t *j_index, void *stream)
+{
+    if (nt == 0 || ns == 0) return fail(RCT_ERR_ARG, "empty input");
+    if (nt > kStaticMatchMax || ns > kStaticMatchMax)
+        return fail(RCT_ERR_ARG,
+                    "rct_match_cdf_static: %zu target / %zu source entries exceed the built-in scratch "
+                    "(RCT_MATCH_STATIC_MAX = %zu per side); use rct_match_cdf with caller-provided scratch",
+                    nt, ns, kStaticMatchMax);
+    if (!target_proj || !source_proj || !matched) return fail(RCT_ERR_ARG, "null pointer");
+    int dev, rc = ensure_device(&dev);  // first call on a device: uploads the constant tables (no device allocation)
+    if (rc) return rc;
+    void *scratch = nullptr;
+    rc = match_static_scratch(dev, &scratch);  // first call on a device: resolves the array's device address
+    if (rc) return rc;
+    if (match_layout(nt, ns).total > kStaticMatchBytes) return fail(RCT_ERR_ARG, "layout exceeds the built-in scratch");
+    // The array still holds what the previous call left there; rct_match_cdf zeroes the counters it needs at zero
+    // (cudaMemsetAsync of the head of the layout, on `stream`) before the first kernel and overwrites the rest.
+    return rct_match_cdf(target_proj, nt, source_proj, ns, matched, j_index, scratch, stream);
+}
+
 // ---- adjacent rows: AdaIN mask-blend tail, DeepLab post-processing ------------------
 int rct_adain_mask_blend(const float *content, const float *output, const float *mask, float *stylized,
                          uint8_t *rgb8, int n, int H, int W, int oh, int ow, int mh, int mw, size_t mask_stride,

@@ -229,6 +229,25 @@ int rct_pca_inverse(const double *matched, size_t n, const double *mean3, const 
 size_t rct_match_scratch_bytes(size_t nt, size_t ns);
 int rct_match_cdf(const double *target_proj, size_t nt, const double *source_proj, size_t ns,
                   double *matched, int64_t *j_index, void *scratch, void *stream);
+/* match_cdf for callers that cannot allocate device memory.  No counterpart in the reference (numpy allocates freely);
+ * it exists for hosts where cudaMalloc is off limits at the call site: a plug-in inside an application that owns the
+ * whole device heap, a process whose memory pool is sized once at start-up, a real-time loop that cannot afford the
+ * device-wide synchronisation an allocation may cause.  Same arguments and same results (bit for bit) as
+ * rct_match_cdf, minus `scratch`: the work arrays are a fixed array inside the library image, 34 MiB on every GPU
+ * that loads librct.so, held until the process exits.
+ *  - limit: nt <= RCT_MATCH_STATIC_MAX and ns <= RCT_MATCH_STATIC_MAX; larger inputs return RCT_ERR_ARG with the
+ *    limit in rct_last_error() and touch nothing.
+ *  - the call itself performs no cudaMalloc / cudaFree and calls no allocating routine; the caller still provides
+ *    target_proj, source_proj, matched and (optionally) j_index in device memory.
+ *  - the first call on each device also does one-time set-up (constant tables, kernel attributes, looking up the
+ *    array's device address): make that first call during initialisation, before any stream capture begins.
+ *  - there is ONE array per device and every call uses it: two calls whose GPU work can overlap (different streams
+ *    without an ordering between them, or two host threads) race on it and corrupt each other's result.  Calls on one
+ *    stream, or ordered by events, are safe; the array keeps the previous call's contents and the call clears the
+ *    parts that must start at zero itself. */
+#define RCT_MATCH_STATIC_MAX ((size_t)1 << 20)
+int rct_match_cdf_static(const double *target_proj, size_t nt, const double *source_proj, size_t ns,
+                         double *matched, int64_t *j_index, void *stream);
 
 /* ---- the steps either side of the hot path --------------------------------
  * f-1: mask-blend tail of AdaIN inference (Style_3DGS/AdaIN/test.py:222-236): mask [mh,mw] float32
