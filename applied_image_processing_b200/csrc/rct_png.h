@@ -9,12 +9,20 @@
 // Scope: non-interlaced, bit depth 8 for grey / grey+alpha / RGB / RGBA, 1/2/4/8 for palette and grey; alpha is dropped
 // exactly as Pillow's convert("RGB") does (no compositing), 1/2/4-bit grey is scaled to 0..255 as Pillow does.
 // Interlaced and 16-bit files are refused with a reason, never decoded approximately.
+// Damaged files follow Pillow 's verdicts (probed against PIL.Image.open().convert("RGB"), tests/test_png.py): a wrong
+// CRC on any chunk in front of the first IDAT is an error, the CRCs of IDAT chunks and of what follows them are not
+// looked at; a zlib stream that delivers every row is accepted even when its Adler-32 trailer or the IEND chunk is cut
+// off or more data follows, a WRONG Adler-32 is an error, and so is a stream that ends before the last row.
 #pragma once
 #include <cstdint>
 #include <cstring>
 #include <string>
 #include <vector>
 #include <zlib.h>
+
+#ifndef RCT_PNG_ZCHUNK
+#define RCT_PNG_ZCHUNK (1u << 30)  // bytes handed to zlib per step: its counters are 32-bit, a PNG can hold > 4 GiB
+#endif
 
 namespace rct_png {
 
@@ -61,11 +69,24 @@ inline bool decode(const uint8_t *f, size_t n, Info *info, uint8_t *rgb)
     memset(pal, 0, sizeof pal);
     int npal = 0;
     size_t pos = 8;
-    bool end = false;
+    bool end = false, seen_idat = false;
     while (pos + 12 <= n && !end) {
         const uint32_t len = be32(f + pos);
         const uint8_t *type = f + pos + 4, *data = f + pos + 8;
         if ((size_t)len > n - pos - 12) { info->error = "PNG: truncated chunk"; return false; }
+        if (!memcmp(type, "IDAT", 4)) seen_idat = true;
+        if (!seen_idat) {  // header, palette and everything else in front of the pixels: checksum enforced (as Pillow)
+            uLong crc = crc32(0L, Z_NULL, 0);
+            for (size_t o = 0, left = (size_t)len + 4; left;) {
+                const uInt step = left > RCT_PNG_ZCHUNK ? (uInt)RCT_PNG_ZCHUNK : (uInt)left;
+                crc = crc32(crc, type + o, step);
+                o += step; left -= step;
+            }
+            if ((uint32_t)crc != be32(data + len)) {
+                info->error = std::string("PNG: bad checksum in chunk ") + std::string((const char *)type, 4);
+                return false;
+            }
+        }
         if (!memcmp(type, "IDAT", 4)) idat.insert(idat.end(), data, data + len);
         else if (!memcmp(type, "PLTE", 4)) {
             npal = (int)(len / 3) > 256 ? 256 : (int)(len / 3);
@@ -82,10 +103,16 @@ inline bool decode(const uint8_t *f, size_t n, Info *info, uint8_t *rgb)
     z_stream zs;
     memset(&zs, 0, sizeof zs);
     if (inflateInit(&zs) != Z_OK) { info->error = "PNG: zlib init failed"; return false; }
-    zs.next_in = idat.data(); zs.avail_in = (uInt)idat.size();
-    zs.next_out = raw.data(); zs.avail_out = (uInt)raw.size();
-    const int zr = inflate(&zs, Z_FINISH);
-    const size_t got = raw.size() - zs.avail_out;
+    // zlib counts avail_in / avail_out in 32 bits: feed both sides in steps so that rows x bytes >= 4 GiB inflate fully
+    size_t in_left = idat.size(), out_left = raw.size();
+    zs.next_in = idat.data(); zs.next_out = raw.data();
+    int zr = Z_OK;
+    do {  // Z_OK = progress was made; Z_BUF_ERROR = none possible: the input is used up or every row is there
+        if (zs.avail_in == 0 && in_left) { zs.avail_in = in_left > RCT_PNG_ZCHUNK ? (uInt)RCT_PNG_ZCHUNK : (uInt)in_left; in_left -= zs.avail_in; }
+        if (zs.avail_out == 0 && out_left) { zs.avail_out = out_left > RCT_PNG_ZCHUNK ? (uInt)RCT_PNG_ZCHUNK : (uInt)out_left; out_left -= zs.avail_out; }
+        zr = inflate(&zs, Z_NO_FLUSH);
+    } while (zr == Z_OK);
+    const size_t got = raw.size() - out_left - zs.avail_out;
     inflateEnd(&zs);
     if ((zr != Z_STREAM_END && zr != Z_OK && zr != Z_BUF_ERROR) || got != raw.size()) {
         info->error = "PNG: corrupt or truncated zlib stream";
