@@ -893,6 +893,42 @@ int plan_leave(rct_plan *p, cudaStream_t st)
     return RCT_OK;
 }
 
+// Every entry point that enqueues work on a plan's workspace runs inside one of these.  On the success path the entry
+// point calls leave() itself (so that a failing event record is reported); on ANY other exit the destructor records the
+// plan's ordering event behind the work already enqueued - a later call on the plan from another stream then waits for
+// it instead of overlapping it in the shared workspace - and puts back the plan fields the failed call had changed.
+struct PlanScope {
+    rct_plan *p;
+    cudaStream_t st;
+    bool entered = false;
+    int front_saved, kt_saved;
+    cudaStream_t drain[2] = {nullptr, nullptr};  // host entry points: copy streams that touch the CALLER's host buffers
+    PlanScope(rct_plan *plan, cudaStream_t stream) : p(plan), st(stream), front_saved(plan->front), kt_saved(plan->kt_mode) {}
+    PlanScope(const PlanScope &) = delete;
+    PlanScope &operator=(const PlanScope &) = delete;
+    int enter()
+    {
+        int rc = plan_enter(p, st);
+        entered = rc == RCT_OK;
+        return rc;
+    }
+    int leave()
+    {
+        entered = false;
+        return plan_leave(p, st);
+    }
+    ~PlanScope()
+    {
+        if (!entered) return;
+        if (cudaEventRecord(p->ev_last, st) == cudaSuccess) p->ev_last_valid = true;
+        for (cudaStream_t d : drain)  // the caller may release its host buffers as soon as the error is returned
+            if (d) cudaStreamSynchronize(d);
+        if (drain[0] || drain[1]) cudaStreamSynchronize(st);
+        p->front = front_saved;
+        p->kt_mode = kt_saved;
+    }
+};
+
 int check_mode(int mode, const void *mask)
 {
     if (mode < 0 || mode > 2) return fail(RCT_ERR_ARG, "bad mode %d", mode);
@@ -926,7 +962,8 @@ int rct_transfer_async(rct_plan *p, const uint8_t *content, size_t content_strid
     cudaStream_t st = (cudaStream_t)stream;
     rc = ensure_status_frames(p, n_frames);
     if (rc) return rc;
-    if ((rc = plan_enter(p, st))) return rc;
+    PlanScope scope(p, st);
+    if ((rc = scope.enter())) return rc;
     p->kt_mode = mode;
     const size_t npix = (size_t)p->H * (size_t)p->W;
     for (int f0 = 0; f0 < n_frames; f0 += p->slots) {
@@ -939,7 +976,7 @@ int rct_transfer_async(rct_plan *p, const uint8_t *content, size_t content_strid
         if ((rc = phase_solve(p, ns, st, !p->front))) return rc;
         if ((rc = phase_apply(p, f, ns, mode, label, 0, npix, p->status_frames + f0, st))) return rc;
     }
-    return plan_leave(p, st);
+    return scope.leave();
 }
 
 int rct_plan_status(rct_plan *p, int *status_host, int n_frames, void *stream)
@@ -969,7 +1006,8 @@ int rct_transfer_labels_async(rct_plan *p, const uint8_t *content, size_t conten
     if (rc) return rc;
     const size_t npix = (size_t)p->H * (size_t)p->W;
     const int fpg = p->slots / n_labels;  // frames per launch group
-    if ((rc = plan_enter(p, st))) return rc;
+    PlanScope scope(p, st);
+    if ((rc = scope.enter())) return rc;
     p->kt_mode = RCT_MODE_LABEL;
     p->lpf = n_labels;
     for (int f0 = 0; f0 < n_frames && rc == RCT_OK; f0 += fpg) {
@@ -982,7 +1020,7 @@ int rct_transfer_labels_async(rct_plan *p, const uint8_t *content, size_t conten
         if (rc == RCT_OK) rc = phase_apply(p, f, ns, RCT_MODE_LABEL, 0, 0, npix, p->status_frames + (size_t)f0 * n_labels, st);
     }
     p->lpf = 1;
-    if (rc == RCT_OK) rc = plan_leave(p, st);
+    if (rc == RCT_OK) rc = scope.leave();
     return rc;
 }
 
@@ -1013,7 +1051,10 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
     rc = ensure_status_frames(p, n_frames);
     if (rc) return rc;
     cudaStream_t st = p->own_stream, sin = p->h2d_stream, sout = p->d2h_stream;
-    if ((rc = plan_enter(p, st))) return rc;
+    PlanScope scope(p, st);
+    scope.drain[0] = sin;
+    scope.drain[1] = sout;
+    if ((rc = scope.enter())) return rc;
     p->kt_mode = mode;
     int k = 0;
     for (int f0 = 0; f0 < n_frames; f0 += p->slots, ++k) {
@@ -1054,7 +1095,7 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
             if (tmp[i] > worst) worst = tmp[i];
     if (!status_host) delete[] tmp;
     if (e != cudaSuccess) return fail(RCT_ERR_CUDA, "host transfer failed: %s", cudaGetErrorString(e));
-    if ((rc = plan_leave(p, st))) return rc;
+    if ((rc = scope.leave())) return rc;
     return worst;
 }
 
@@ -1069,11 +1110,12 @@ int rct_shard_hist_async(rct_plan *p, const uint8_t *content, const uint8_t *sty
     FrameSet f{content, stylised, mask, nullptr, 0, 0, 0, 0};
     cudaStream_t st = (cudaStream_t)stream;
     const size_t pb = (size_t)row0 * p->W, pe = (size_t)(row0 + rows) * p->W;
-    if ((rc = plan_enter(p, st))) return rc;
+    PlanScope scope(p, st);
+    if ((rc = scope.enter())) return rc;
     p->kt_mode = mode;  // rct_shard_solve_async follows on the same plan
     if (!p->front) {
         rc = phase_hist(p, f, 1, mode, label, pb, pe, st);
-        return rc ? rc : plan_leave(p, st);
+        return rc ? rc : scope.leave();
     }
     // Colour-partitioned front end on the band (streaming passes, no global atomics), then the band's
     // (colour, count) lists are written into the zeroed colour cubes the ranks all-reduce: one plain
@@ -1085,16 +1127,17 @@ int rct_shard_hist_async(rct_plan *p, const uint8_t *content, const uint8_t *sty
     p->cube_dirty = true;
     CK(cudaMemsetAsync(p->ctrl, 0, sizeof(FrameCtrl), st));  // the solve rebuilds the lists from the reduced cubes
     if ((rc = mark(p, st))) return rc;
-    return plan_leave(p, st);
+    return scope.leave();
 }
 void *rct_plan_hist_ptr(rct_plan *p) { return p ? (void *)p->hist : nullptr; }
 size_t rct_plan_hist_bytes(rct_plan *p) { return p ? 4 * p->L.hist_stride_u32 : 0; }
 int rct_shard_solve_async(rct_plan *p, void *stream)
 {
     if (!p) return fail(RCT_ERR_ARG, "null plan");
-    int rc = plan_enter(p, (cudaStream_t)stream);
+    PlanScope scope(p, (cudaStream_t)stream);
+    int rc = scope.enter();
     if (rc == RCT_OK) rc = phase_solve(p, 1, (cudaStream_t)stream, true);
-    return rc ? rc : plan_leave(p, (cudaStream_t)stream);
+    return rc ? rc : scope.leave();
 }
 int rct_shard_apply_async(rct_plan *p, const uint8_t *content, const uint8_t *stylised, const uint8_t *mask,
                           uint8_t *out, int mode, int label, int row0, int rows, void *stream)
@@ -1106,10 +1149,11 @@ int rct_shard_apply_async(rct_plan *p, const uint8_t *content, const uint8_t *st
     rc = ensure_status_frames(p, 1);
     if (rc) return rc;
     FrameSet f{content, stylised, mask, out, 0, 0, 0, 0};
-    if ((rc = plan_enter(p, (cudaStream_t)stream))) return rc;
+    PlanScope scope(p, (cudaStream_t)stream);
+    if ((rc = scope.enter())) return rc;
     rc = phase_apply(p, f, 1, mode, label, (size_t)row0 * p->W, (size_t)(row0 + rows) * p->W, p->status_frames,
                      (cudaStream_t)stream);
-    return rc ? rc : plan_leave(p, (cudaStream_t)stream);
+    return rc ? rc : scope.leave();
 }
 
 
@@ -1160,7 +1204,8 @@ int rct_transfer_binned_async(rct_plan *p, const uint8_t *content, size_t conten
     cudaStream_t st = (cudaStream_t)stream;
     rc = ensure_status_frames(p, n_frames);
     if (rc) return rc;
-    if ((rc = plan_enter(p, st))) return rc;
+    PlanScope scope(p, st);
+    if ((rc = scope.enter())) return rc;
     const size_t npix = (size_t)p->H * (size_t)p->W;
     const int front_saved = p->front;
     p->front = 1;  // the colour-partition front end produces the (colour, count) lists directly
@@ -1175,7 +1220,7 @@ int rct_transfer_binned_async(rct_plan *p, const uint8_t *content, size_t conten
         if (rc == RCT_OK) rc = phase_apply(p, f, ns, mode, label, 0, npix, p->status_frames + f0, st);
     }
     p->front = front_saved;
-    return rc ? rc : plan_leave(p, st);
+    return rc ? rc : scope.leave();
 }
 
 /* Row-sharded binned path (one image, rows [row0, row0+rows) on this rank; slot 0).  Between the phases the caller
@@ -1197,7 +1242,8 @@ int rct_shard_binned_phase_async(rct_plan *p, int phase, const uint8_t *content,
     cudaStream_t st = (cudaStream_t)stream;
     void *xchg = p->ws + p->L.off_xchg;
     const size_t pb = (size_t)row0 * p->W, pe = (size_t)(row0 + rows) * p->W;
-    if ((rc = plan_enter(p, st))) return rc;
+    PlanScope scope(p, st);
+    if ((rc = scope.enter())) return rc;
     if (phase == 0) {
         FrameSet f{content, stylised, mask, nullptr, 0, 0, 0, 0};
         const int front_saved = p->front;
@@ -1223,7 +1269,7 @@ int rct_shard_binned_phase_async(rct_plan *p, int phase, const uint8_t *content,
         FrameSet f{content, stylised, mask, out, 0, 0, 0, 0};
         if ((rc = phase_apply(p, f, 1, mode, label, pb, pe, p->status_frames, st))) return rc;
     }
-    return plan_leave(p, st);
+    return scope.leave();
 }
 void *rct_plan_xchg_ptr(rct_plan *p) { return p ? (void *)(p->ws + p->L.off_xchg) : nullptr; }
 size_t rct_plan_xchg_bytes(int which, int bins)
@@ -1721,7 +1767,10 @@ int rct_transfer_files_host(rct_plan *p, const uint8_t *content_file, size_t con
     const size_t big = npix > spix ? npix : spix;
     // decoder workspace bound: coefficients (2 bytes per sample incl. padding to MCUs) + planes + scan + states
     const size_t dec_ws = align_up(big * 16 + (content_bytes > stylised_bytes ? content_bytes : stylised_bytes) * 8 + (1u << 20));
-    const size_t need = cb + sb + mb + cb + dec_ws + enc_ws + cap + 256;
+    // grey plane of a one-component JPEG before its expansion to RGB: a region of its own, sized for the larger image
+    // (it once borrowed d_o, which holds 3*H*W bytes: a grey stylised file of more than 3*H*W pixels ran into d_dec)
+    const size_t gb = align_up(big);
+    const size_t need = cb + sb + mb + cb + dec_ws + enc_ws + cap + 256 + gb;
     if (p->files_ws_bytes < need) {
         if (p->files_ws) CK(cudaFree(p->files_ws));
         p->files_ws = nullptr;
@@ -1732,14 +1781,16 @@ int rct_transfer_files_host(rct_plan *p, const uint8_t *content_file, size_t con
     uint8_t *d_c = p->files_ws, *d_s = d_c + cb, *d_m = d_s + sb, *d_o = d_m + mb, *d_dec = d_o + cb, *d_enc = d_dec + dec_ws,
             *d_file = d_enc + enc_ws;
     unsigned long long *d_n = reinterpret_cast<unsigned long long *>(d_file + cap);
+    uint8_t *d_gray = d_file + cap + 256;
     cudaStream_t st = p->own_stream;
-    int rc = plan_enter(p, st);
+    PlanScope scope(p, st);
+    scope.drain[0] = st;  // on failure: the files / mask / output of the caller may be in flight on st
+    int rc = scope.enter();
     if (rc) return rc;
     p->kt_mode = RCT_MODE_MASK;
     std::vector<uint8_t> host_tmp;
-    // d_o doubles as the grey plane of a one-component JPEG before its expansion
-    if ((rc = decode_file_to_device(content_file, content_bytes, H, W, "content file", d_c, d_dec, dec_ws, d_o, host_tmp, p->sm, st))) return rc;
-    if ((rc = decode_file_to_device(stylised_file, stylised_bytes, sh, sw, "stylised file", d_s, d_dec, dec_ws, d_o, host_tmp, p->sm, st))) return rc;
+    if ((rc = decode_file_to_device(content_file, content_bytes, H, W, "content file", d_c, d_dec, dec_ws, d_gray, host_tmp, p->sm, st))) return rc;
+    if ((rc = decode_file_to_device(stylised_file, stylised_bytes, sh, sw, "stylised file", d_s, d_dec, dec_ws, d_gray, host_tmp, p->sm, st))) return rc;
     CK(cudaMemcpyAsync(d_m, mask_h, npix, cudaMemcpyHostToDevice, st));
     if ((rc = ensure_status_frames(p, 1))) return rc;
     FrameSet f{d_c, d_s, d_m, d_o, cb, sb, mb, cb};
@@ -1757,7 +1808,7 @@ int rct_transfer_files_host(rct_plan *p, const uint8_t *content_file, size_t con
     if (nb > out_capacity) return fail(RCT_ERR_ARG, "output file needs %llu bytes, capacity is %zu", nb, out_capacity);
     CK(cudaMemcpyAsync(out_file, d_file, (size_t)nb, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    if ((rc = plan_leave(p, st))) return rc;
+    if ((rc = scope.leave())) return rc;
     return status;
 }
 

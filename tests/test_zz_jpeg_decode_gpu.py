@@ -114,7 +114,10 @@ def test_pipeline_tail_from_jpeg_files_stays_on_the_device(tmp_path):
 
 
 @pytest.mark.parametrize("cfmt,sfmt,H,W,sh,sw", [("JPEG", "JPEG", 360, 640, 256, 455), ("PNG", "JPEG", 270, 480, 270, 480),
-                                                 ("JPEG", "PNG", 97, 131, 64, 80), ("GRAY", "JPEG", 128, 192, 128, 192)])
+                                                 ("JPEG", "PNG", 97, 131, 64, 80), ("GRAY", "JPEG", 128, 192, 128, 192),
+                                                 # a grey stylised file of more than 3*H*W pixels: its grey plane once
+                                                 # overran the output buffer it borrowed
+                                                 ("JPEG", "GRAY", 64, 96, 256, 455), ("GRAY", "GRAY", 40, 56, 300, 300)])
 def test_files_entry_point_matches_pillow_plus_oracle(cfmt, sfmt, H, W, sh, sw):
     """rct_transfer_files_host: file bytes in (JPEG on the device, PNG on the host, a grey JPEG replicated to RGB as
     convert("RGB") does), mask, JPEG bytes out == Pillow decode -> oracle -> Pillow encode, byte for byte."""
