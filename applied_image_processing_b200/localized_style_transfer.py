@@ -230,7 +230,10 @@ def _np_u8(a, name):
 # Launch groups in flight at once on the tensor path.  The solve kernels are latency-bound (ncu: k_scatter issues on 17 %
 # of its cycles), so two groups on two streams, each with its own plan, overlap their stalls: 8 + 8 frames of 4K take
 # 11.03 ms instead of 11.68 ms back to back (measured on B200; four lanes are slower than two).
-LANES = 2
+# Memory: every lane holds a plan workspace of its own for the geometry (about 1 GB per 4K slot, so 2 x 8 GB for batches
+# of 8-frame groups at 4K), counted against PLAN_CACHE_BYTES like any other plan.  Set RCT_LANES=1 (or this attribute)
+# where device memory matters more than the last 5 % of throughput.
+LANES = max(1, int(os.environ.get("RCT_LANES", 2)))
 _lane_streams: dict = {}
 
 

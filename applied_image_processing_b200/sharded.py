@@ -111,13 +111,15 @@ class ShardedTransfer:
         W, sw = self.W, self.sw
         for t, shape in ((content_band, (self.rows, W, 3)), (stylised_band, (self.s1 - self.s0, sw, 3)),
                          (mask_band, (self.rows, W))):
+            if t is None and shape == (self.rows, W):
+                continue  # MODE_ALL has no mask: NULL goes to the library, which refuses MASK / LABEL calls without one
             if tuple(t.shape) != shape or t.dtype != torch.uint8 or not t.is_contiguous() or not t.is_cuda:
                 raise TypeError(f"expected a contiguous CUDA uint8 tensor of shape {shape}, got {tuple(t.shape)}")
         if out_band is None:
             out_band = torch.empty_like(content_band)
         # virtual full-image base pointers (only the band's rows are ever dereferenced)
         c_ptr = content_band.data_ptr() - self.row0 * W * 3
-        m_ptr = mask_band.data_ptr() - self.row0 * W
+        m_ptr = None if mask_band is None else mask_band.data_ptr() - self.row0 * W
         o_ptr = out_band.data_ptr() - self.row0 * W * 3
         s_ptr = stylised_band.data_ptr() - self.s0 * sw * 3
         st = torch.cuda.current_stream()
@@ -192,7 +194,7 @@ class ShardedTransfer:
         if out_band is None:
             out_band = torch.empty_like(content_band)
         c_ptr = content_band.data_ptr() - self.row0 * W * 3
-        m_ptr = mask_band.data_ptr() - self.row0 * W
+        m_ptr = None if mask_band is None else mask_band.data_ptr() - self.row0 * W
         o_ptr = out_band.data_ptr() - self.row0 * W * 3
         s_ptr = stylised_band.data_ptr() - self.s0 * sw * 3
         st = torch.cuda.current_stream()

@@ -341,6 +341,26 @@ def test_sharded_driver_two_ranks_one_gpu():
     assert np.array_equal(full, ref)
 
 
+def test_sharded_driver_without_a_mask_in_mode_all():
+    """MODE_ALL has no mask (LST:128-168 on whole images): the row-sharded drivers pass NULL like the unsharded paths,
+    and a MASK call without one is refused by the library instead of dereferencing None."""
+    from applied_image_processing_b200 import sharded
+
+    H, W, sh, sw = 90, 120, 90, 120
+    c, s = synth.synth_image(H, W, 92, "N"), synth.synth_image(sh, sw, 93, "N")
+    dc, ds = torch.from_numpy(c).cuda(), torch.from_numpy(s).cuda()
+    drv = sharded.ShardedTransfer(H, W, sh, sw)
+    out = drv(dc, ds, None, mode=_cabi.MODE_ALL)
+    outb = drv.binned(dc, ds, None, bins=1024, mode=_cabi.MODE_ALL)
+    torch.cuda.synchronize()
+    ref, st, _ = orc.transfer(c, s, None, mode=orc.MODE_ALL)
+    refb, stb, _ = orc.transfer_binned(c, s, None, 1024, mode=orc.MODE_ALL)
+    assert st == 0 and np.array_equal(out.cpu().numpy(), ref)
+    assert stb == 0 and np.array_equal(outb.cpu().numpy(), refb)
+    with pytest.raises(_cabi.RctError, match="mask required"):
+        drv(dc, ds, None, mode=_cabi.MODE_MASK)
+
+
 # ---- exact sort: fallback paths ---------------------------------------------------------------------
 @pytest.mark.parametrize("cap", [1, 64, 700])
 def test_sort_global_fallback_is_exact(cap):
