@@ -649,11 +649,18 @@ def run_gpu_arm(a):
             assert nbad == 0, f"bench parity: frame {i}: {nbad} bytes differ from the oracle"
         parity_frames = nc
 
-    if a.keytab and not a.lut and not a.bins and not labels:  # key-table self-check of the last launch group's first frame
-        try:
-            roofline["keytab_slot0"] = plan.debug_keytab(0, key_error=False)
-        except Exception as e:  # noqa: BLE001
-            roofline["keytab_slot0"] = {"error": str(e)}
+    if a.keytab and not a.lut and not a.bins and not labels:
+        # Key-table self-check, every slot of the last launch group: the table answers in fp32 (lg2.approx + an fma chain)
+        # under an error bound of 2^-16 on the key; each distinct target colour is re-checked against the exact LUT here.
+        # A toolchain or architecture that loosened lg2.approx must fail this run, not shift pixels silently.
+        nslots = min(int(getattr(plan, "slots", 1)), n)
+        checks = [plan.debug_keytab(k, key_error=(k == 0)) for k in range(nslots)]
+        roofline["keytab_slot0"] = checks[0]
+        roofline["keytab_slots_checked"] = nslots
+        for k, c in enumerate(checks):
+            assert c["colours_wrong"] == 0 and c["pixels_wrong"] == 0, f"bench: key table of slot {k} disagrees with the LUT: {c}"
+        if checks[0]["valid"]:
+            assert checks[0]["max_key_err"] < 2.0 ** -17, f"bench: fp32 key error {checks[0]['max_key_err']:.3g} >= 2^-17 (bound 2^-16)"
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
