@@ -210,8 +210,14 @@ def cpu_pass(frames, threads, labels=False, keep=False, bins=0):
 
 
 def cpu_sample_size(a):
-    # ~6.7 s per 4K frame per core: one frame per thread, at most 8 threads' worth of memory
-    threads = max(1, min(host_threads(), 8))
+    """(frames, threads) of the CPU arm: one frame per thread on EVERY core this process may use (~6.7 s per 4K frame per
+    core), fewer only where the host's free memory would not hold one oracle working set (~160 bytes per pixel) per thread."""
+    threads = max(1, host_threads())
+    try:
+        avail = next(int(l.split()[1]) * 1024 for l in open("/proc/meminfo") if l.startswith("MemAvailable:"))
+        threads = max(1, min(threads, int(0.5 * avail / (160 * a.height * a.width))))
+    except Exception:  # noqa: BLE001
+        pass
     n = a.cpu_frames or threads
     return n, min(threads, n)
 
@@ -231,6 +237,7 @@ def run_reference_arm(a):
     times = [cpu_pass(frames, threads, labels, bins=a.bins) for _ in range(a.steps)]
     mp = n * a.height * a.width / 1e6
     band_note = f" (each a {a.height}-row band of the {full_h}-row image)" if a.workload == "16k" else ""
+    rows_used = a.height
     a.height = full_h
     t = sum(times) / len(times)
     val = mp / t
@@ -241,7 +248,11 @@ def run_reference_arm(a):
         "scaling": "strong" if a.workload == "16k" else "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": config_dict(a, a.gpus),
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "host_cores_available": host_threads(), "kind": "port",
+                         "sample": sample},
+        # `config` is the repo arm's (the workload both arms are quoted on); what THIS arm ran per step is here
+        "reference_sample": {"frames_per_step": n, "threads": threads, "rows_per_frame": rows_used,
+                             "note": "MP/s is per pixel processed, so the sample size does not enter the ratio"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -640,7 +651,7 @@ def run_gpu_arm(a):
         nc = min(nc, n)
         threads = min(threads, nc)
         t, cpu_outs = cpu_pass((cs[:nc], ss[:nc], ms[:nc]), threads, labels, keep=True, bins=a.bins)
-        cpu = {"value": nc * H * W / 1e6 / t, "unit": UNIT, "cores": threads, "kind": "port",
+        cpu = {"value": nc * H * W / 1e6 / t, "unit": UNIT, "cores": threads, "host_cores_available": host_threads(), "kind": "port",
                "sample": f"{nc} frame(s) of the step's batch, {threads} thread(s), one pass ({t:.1f} s)"}
         # parity at the benchmarked size: the GPU output of the same frames equals the oracle's byte for byte
         got = do[:nc].cpu().numpy()
