@@ -5,7 +5,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
+#include <condition_variable>
 #include <mutex>
+#include <thread>
 #include <new>
 #include <string>
 #include <vector>
@@ -212,6 +215,8 @@ struct rct_plan {
     int status_frames_cap;
     uint8_t *stage;  // device staging of the host entry point
     size_t stage_bytes;
+    uint8_t *hstage;  // pinned host staging for callers that hand over pageable arrays (rct_transfer_host)
+    size_t hstage_bytes;
     cudaStream_t own_stream;            // compute stream of the host entry point
     cudaStream_t h2d_stream, d2h_stream; // copy streams of the host entry point (overlap with compute)
     cudaEvent_t ev_in[kStageSetsMax], ev_comp[kStageSetsMax], ev_out[kStageSetsMax];
@@ -436,6 +441,7 @@ int rct_plan_destroy(rct_plan *p)
     if (p->owns_ws && p->ws) cudaFree(p->ws);
     if (p->status_frames) cudaFree(p->status_frames);
     if (p->stage) cudaFree(p->stage);
+    if (p->hstage) cudaFreeHost(p->hstage);
     if (p->files_ws) cudaFree(p->files_ws);
     delete p;
     return RCT_OK;
@@ -950,6 +956,131 @@ int ensure_status_frames(rct_plan *p, int n)
 
 }  // namespace
 
+// ---- pageable callers of the host entry point ------------------------------------------------------------------
+// np.array(Image.open(...)) (LST:200-201, 219-220) is pageable memory.  Handed straight to cudaMemcpy2DAsync the driver
+// stages it through its own small pinned buffer on ONE thread, synchronously: ~11 GB/s, 1.1 GP/s end to end against
+// 6.7 GP/s from pinned buffers.  So rct_transfer_host copies pageable buffers into / out of a pinned ring of the plan
+// with a few host threads (below) while the DMA engines and the kernels work on the neighbouring groups.
+namespace {
+class HostPool {
+public:
+    struct Job { uint8_t *dst; const uint8_t *src; size_t bytes; };
+    static HostPool &get()
+    {
+        static HostPool pool;
+        return pool;
+    }
+    // copies every job, split into chunks of kChunk bytes over the workers and the calling thread; returns when done
+    void copy(const Job *jobs, int njobs)
+    {
+        std::lock_guard<std::mutex> one_call(call_mu_);  // one batch at a time: calls on different plans take turns
+        size_t total = 0;
+        for (int i = 0; i < njobs; ++i) total += (jobs[i].bytes + kChunk - 1) / kChunk;
+        if (total == 0) return;
+        if (total == 1 || workers_.empty()) {
+            for (int i = 0; i < njobs; ++i) memcpy(jobs[i].dst, jobs[i].src, jobs[i].bytes);
+            return;
+        }
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            jobs_ = jobs; njobs_ = njobs; total_ = total;
+            next_.store(0); done_.store(0);
+            ++epoch_;
+        }
+        cv_.notify_all();
+        work();
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_done_.wait(lk, [&] { return done_.load() == total_ && active_ == 0; });
+        jobs_ = nullptr;
+    }
+
+private:
+    static constexpr size_t kChunk = (size_t)1 << 20;
+    HostPool()
+    {
+        int n = 0;
+        if (const char *e = getenv("RCT_HOST_THREADS")) n = atoi(e);
+        if (n <= 0) {
+            unsigned hw = std::thread::hardware_concurrency();
+            n = hw >= 16 ? 8 : (hw >= 4 ? (int)hw / 2 : 1);
+        }
+        if (n > 32) n = 32;
+        for (int i = 0; i + 1 < n; ++i) {  // the calling thread is the n-th copier
+            try {
+                workers_.emplace_back([this] { loop(); });
+            } catch (...) {
+                break;  // fewer threads: slower, still correct
+            }
+        }
+    }
+    ~HostPool()
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        for (auto &t : workers_) t.join();
+    }
+    void work()
+    {
+        for (;;) {
+            size_t c = next_.fetch_add(1);
+            if (c >= total_) break;
+            size_t k = c;
+            for (int i = 0; i < njobs_; ++i) {
+                const size_t nc = (jobs_[i].bytes + kChunk - 1) / kChunk;
+                if (k < nc) {
+                    const size_t off = k * kChunk, len = jobs_[i].bytes - off < kChunk ? jobs_[i].bytes - off : kChunk;
+                    memcpy(jobs_[i].dst + off, jobs_[i].src + off, len);
+                    break;
+                }
+                k -= nc;
+            }
+            done_.fetch_add(1);
+        }
+    }
+    void loop()
+    {
+        unsigned long long seen = 0;
+        std::unique_lock<std::mutex> lk(mu_);
+        for (;;) {
+            cv_.wait(lk, [&] { return stop_ || epoch_ != seen; });
+            if (stop_) return;
+            seen = epoch_;
+            if (!jobs_) continue;  // woke up after that batch was finished by the others: never touch a batch half set up
+            ++active_;
+            lk.unlock();
+            work();
+            lk.lock();
+            --active_;
+            if (done_.load() == total_ && active_ == 0) cv_done_.notify_all();
+        }
+    }
+    std::vector<std::thread> workers_;
+    std::mutex mu_, call_mu_;
+    std::condition_variable cv_, cv_done_;
+    const Job *jobs_ = nullptr;
+    int njobs_ = 0, active_ = 0;
+    size_t total_ = 0;
+    std::atomic<size_t> next_{0}, done_{0};
+    unsigned long long epoch_ = 0;
+    bool stop_ = false;
+};
+
+// true when the driver knows nothing about this host pointer: plain malloc / numpy memory, not cudaHostAlloc'ed or registered
+bool is_pageable(const void *ptr)
+{
+    if (!ptr) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, ptr) != cudaSuccess) {
+        cudaGetLastError();  // older drivers report unregistered memory as an error: clear it
+        return true;
+    }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+}  // namespace
+
 extern "C" {
 
 int rct_transfer_async(rct_plan *p, const uint8_t *content, size_t content_stride, const uint8_t *stylised,
@@ -1048,9 +1179,42 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
         CK(cudaMalloc((void **)&p->stage, need));
         p->stage_bytes = need;
     }
+    // Pageable host buffers (what numpy / PIL hand over) go through a pinned ring of the plan, copied by HostPool's
+    // threads: group k is staged in while the GPU works on group k-1, group k-1's output is copied out to the caller
+    // while the GPU works on group k.  Pinned or registered buffers keep the direct DMA path.  RCT_HOST_STAGING=0: off.
+    static const bool staging_on = !(getenv("RCT_HOST_STAGING") && atoi(getenv("RCT_HOST_STAGING")) == 0);
+    const bool pg_c = staging_on && is_pageable(content_h), pg_s = staging_on && is_pageable(stylised_h),
+               pg_m = staging_on && is_pageable(mask_h), pg_o = staging_on && is_pageable(out_h);
+    const bool pg_in = pg_c || pg_s || pg_m || (pg_o && mode == RCT_MODE_LABEL);
+    const size_t hper_set = per_set + cb * (size_t)p->slots;  // inputs (device layout) + a separate output region
+    if (pg_in || pg_o) {
+        const size_t hneed = (size_t)S * hper_set;
+        if (p->hstage_bytes < hneed) {
+            if (p->hstage) CK(cudaFreeHost(p->hstage));
+            p->hstage = nullptr;
+            p->hstage_bytes = 0;
+            if (cudaHostAlloc((void **)&p->hstage, hneed, cudaHostAllocDefault) != cudaSuccess) {
+                cudaGetLastError();
+                return fail(RCT_ERR_NOMEM, "cudaHostAlloc(%zu) for the pinned staging ring failed", hneed);
+            }
+            p->hstage_bytes = hneed;
+        }
+    }
     rc = ensure_status_frames(p, n_frames);
     if (rc) return rc;
     cudaStream_t st = p->own_stream, sin = p->h2d_stream, sout = p->d2h_stream;
+    HostPool::Job jobs[4 * 64];
+    // copies the finished output of group `kk` (frames g0 .. g0+gn) from its pinned set to the caller's array
+    auto drain_out = [&](int kk, int g0, int gn) -> int {
+        const int bb = kk % S;
+        CK(cudaEventSynchronize(p->ev_out[bb]));
+        const uint8_t *h_o = p->hstage + hper_set * bb + per_set;
+        int nj = 0;
+        for (int i = 0; i < gn; ++i) jobs[nj++] = {out_h + (size_t)(g0 + i) * npix * 3, h_o + cb * i, npix * 3};
+        HostPool::get().copy(jobs, nj);
+        return RCT_OK;
+    };
+    if (p->slots > 64 && (pg_in || pg_o)) return fail(RCT_ERR_ARG, "pageable host buffers: at most 64 slots per plan");
     PlanScope scope(p, st);
     scope.drain[0] = sin;
     scope.drain[1] = sout;
@@ -1062,16 +1226,39 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
         int ns = n_frames - f0 < p->slots ? n_frames - f0 : p->slots;
         uint8_t *d_c = p->stage + per_set * b, *d_s = d_c + cb * p->slots, *d_m = d_s + sb * p->slots,
                 *d_o = d_m + mb * p->slots;
+        // pinned set b (only touched when something is pageable, in which case hstage exists): same layout as the device set
+        uint8_t *const h_base = (pg_in || pg_o) ? p->hstage + hper_set * b : p->stage + per_set * b;
+        uint8_t *h_c = h_base, *h_s = h_c + cb * p->slots, *h_m = h_s + sb * p->slots, *h_i = h_m + mb * p->slots;
+        uint8_t *h_o = (pg_in || pg_o) ? h_base + per_set : h_base;
+        if (pg_in) {  // stage this group's pageable inputs into pinned set b (free once group k-S's copy-in is done)
+            if (k >= S) CK(cudaEventSynchronize(p->ev_in[b]));
+            int nj = 0;
+            for (int i = 0; i < ns; ++i) {
+                if (pg_c) jobs[nj++] = {h_c + cb * i, content_h + (size_t)(f0 + i) * npix * 3, npix * 3};
+                if (pg_s) jobs[nj++] = {h_s + sb * i, stylised_h + (size_t)(f0 + i) * spix * 3, spix * 3};
+                if (pg_m) jobs[nj++] = {h_m + mb * i, mask_h + (size_t)(f0 + i) * npix, npix};
+                if (pg_o && mode == RCT_MODE_LABEL) jobs[nj++] = {h_i + cb * i, out_h + (size_t)(f0 + i) * npix * 3, npix * 3};
+            }
+            HostPool::get().copy(jobs, nj);
+        }
         if (k >= S) {  // set b was last used by group k-S
             CK(cudaStreamWaitEvent(sin, p->ev_comp[b], 0));
             if (mode == RCT_MODE_LABEL) CK(cudaStreamWaitEvent(sin, p->ev_out[b], 0));
             else CK(cudaStreamWaitEvent(st, p->ev_out[b], 0));
         }
-        CK(cudaMemcpy2DAsync(d_c, cb, content_h + (size_t)f0 * npix * 3, npix * 3, npix * 3, ns, cudaMemcpyHostToDevice, sin));
-        CK(cudaMemcpy2DAsync(d_s, sb, stylised_h + (size_t)f0 * spix * 3, spix * 3, spix * 3, ns, cudaMemcpyHostToDevice, sin));
-        if (mask_h) CK(cudaMemcpy2DAsync(d_m, mb, mask_h + (size_t)f0 * npix, npix, npix, ns, cudaMemcpyHostToDevice, sin));
-        if (mode == RCT_MODE_LABEL)  // untouched pixels keep the caller's values
-            CK(cudaMemcpy2DAsync(d_o, cb, out_h + (size_t)f0 * npix * 3, npix * 3, npix * 3, ns, cudaMemcpyHostToDevice, sin));
+        // pinned staging has the device layout (per-slot strides): one 2-D copy either way
+        if (pg_c) CK(cudaMemcpy2DAsync(d_c, cb, h_c, cb, npix * 3, ns, cudaMemcpyHostToDevice, sin));
+        else CK(cudaMemcpy2DAsync(d_c, cb, content_h + (size_t)f0 * npix * 3, npix * 3, npix * 3, ns, cudaMemcpyHostToDevice, sin));
+        if (pg_s) CK(cudaMemcpy2DAsync(d_s, sb, h_s, sb, spix * 3, ns, cudaMemcpyHostToDevice, sin));
+        else CK(cudaMemcpy2DAsync(d_s, sb, stylised_h + (size_t)f0 * spix * 3, spix * 3, spix * 3, ns, cudaMemcpyHostToDevice, sin));
+        if (mask_h) {
+            if (pg_m) CK(cudaMemcpy2DAsync(d_m, mb, h_m, mb, npix, ns, cudaMemcpyHostToDevice, sin));
+            else CK(cudaMemcpy2DAsync(d_m, mb, mask_h + (size_t)f0 * npix, npix, npix, ns, cudaMemcpyHostToDevice, sin));
+        }
+        if (mode == RCT_MODE_LABEL) {  // untouched pixels keep the caller's values
+            if (pg_o) CK(cudaMemcpy2DAsync(d_o, cb, h_i, cb, npix * 3, ns, cudaMemcpyHostToDevice, sin));
+            else CK(cudaMemcpy2DAsync(d_o, cb, out_h + (size_t)f0 * npix * 3, npix * 3, npix * 3, ns, cudaMemcpyHostToDevice, sin));
+        }
         CK(cudaEventRecord(p->ev_in[b], sin));
         CK(cudaStreamWaitEvent(st, p->ev_in[b], 0));
         FrameSet f{d_c, d_s, mask_h ? d_m : nullptr, d_o, cb, sb, mb, cb};
@@ -1081,8 +1268,15 @@ int rct_transfer_host(rct_plan *p, const uint8_t *content_h, const uint8_t *styl
         if ((rc = phase_apply(p, f, ns, mode, label, 0, npix, p->status_frames + f0, st))) return rc;
         CK(cudaEventRecord(p->ev_comp[b], st));
         CK(cudaStreamWaitEvent(sout, p->ev_comp[b], 0));
-        CK(cudaMemcpy2DAsync(out_h + (size_t)f0 * npix * 3, npix * 3, d_o, cb, npix * 3, ns, cudaMemcpyDeviceToHost, sout));
+        if (pg_o) CK(cudaMemcpy2DAsync(h_o, cb, d_o, cb, npix * 3, ns, cudaMemcpyDeviceToHost, sout));
+        else CK(cudaMemcpy2DAsync(out_h + (size_t)f0 * npix * 3, npix * 3, d_o, cb, npix * 3, ns, cudaMemcpyDeviceToHost, sout));
         CK(cudaEventRecord(p->ev_out[b], sout));
+        // while the GPU works on this group, hand the previous group's output to the caller
+        if (pg_o && k >= 1 && (rc = drain_out(k - 1, f0 - p->slots, p->slots))) return rc;
+    }
+    if (pg_o && k >= 1) {  // the last group
+        const int g0 = (k - 1) * p->slots;
+        if ((rc = drain_out(k - 1, g0, n_frames - g0))) return rc;
     }
     CK(cudaStreamSynchronize(sout));
     int worst = 0;

@@ -361,6 +361,36 @@ def test_sharded_driver_without_a_mask_in_mode_all():
         drv(dc, ds, None, mode=_cabi.MODE_MASK)
 
 
+@pytest.mark.parametrize("slots", [1, 2])
+def test_host_entry_point_pageable_pinned_and_mixed_buffers(slots):
+    """rct_transfer_host stages pageable arrays (what np.array(Image.open(...)) gives, LST:200-201) through a pinned ring
+    with host threads and takes pinned arrays directly: every combination gives the oracle's bytes.  7 frames in groups
+    of `slots` frames = more groups than staging sets, so every pinned set is reused, and an odd tail group."""
+    n, H, W, sh, sw = 7, 96, 136, 64, 90
+    cs = np.stack([synth.synth_image(H, W, 300 + i, "U") for i in range(n)])
+    ss = np.stack([synth.synth_image(sh, sw, 320 + i, "N") for i in range(n)])
+    ms = np.stack([synth.ellipse_mask(H, W, 0.4, 340 + i) for i in range(n)])
+    ref = np.stack([orc.transfer(cs[i], ss[i], ms[i])[0] for i in range(n)])
+
+    def pinned(a):
+        return torch.from_numpy(a).pin_memory().numpy()
+
+    pc, ps, pm, po = pinned(cs), pinned(ss), pinned(ms), pinned(np.zeros_like(cs))
+    assert np.array_equal(aip.regional_color_transfer(cs, ss, ms, slots=slots), ref)                   # all pageable
+    assert np.array_equal(aip.regional_color_transfer(pc, ps, pm, slots=slots, out=po), ref)           # all pinned
+    assert np.array_equal(aip.regional_color_transfer(pc, ss, pm, slots=slots), ref)                   # mixed in, pageable out
+    po[:] = 0
+    assert np.array_equal(aip.regional_color_transfer(cs, ps, ms, slots=slots, out=po), ref)           # pageable in, pinned out
+    # LABEL mode reads the output array as an input too (untouched pixels keep the caller's values)
+    labels = np.stack([synth.voronoi_labels(H, W, 3, 360 + i) for i in range(n)])
+    want = cs.copy()
+    for i in range(n):
+        orc.transfer(cs[i], ss[i], labels[i], mode=orc.MODE_LABEL, label=1, out=want[i])
+    for out in (cs.copy(), pinned(cs.copy())):
+        got = lst._transfer(cs, ss, labels, _cabi.MODE_LABEL, label=1, out=out, slots=slots, quiet=True)
+        assert np.array_equal(got, want)
+
+
 # ---- exact sort: fallback paths ---------------------------------------------------------------------
 @pytest.mark.parametrize("cap", [1, 64, 700])
 def test_sort_global_fallback_is_exact(cap):
