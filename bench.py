@@ -553,6 +553,11 @@ def run_gpu_arm(a):
         * n * H * W / 1e9 / (ms_step * 1e-3),
     }
     roofline["pipeline_frac"] = roofline["pipeline_achieved_GBps_per_gpu"] / peak
+    if dom == "k_apply_kt" and "k_keytab" in ms_launch:
+        # the key table exists only to serve this pass: the same bytes over apply + table build (k_kt_mark / k_kt_fill)
+        t_both = ms_launch["k_apply"] + ms_launch["k_keytab"]
+        roofline["frac_with_table_build"] = roofline["algorithmic_bytes_per_launch"] / 1e9 / (t_both * 1e-3) / peak
+        roofline["table_build_ms_per_launch"] = ms_launch["k_keytab"]
 
     # ---- e2e: the public numpy API, pinned host buffers, copies inside the timed region ----------------
     e2e = None
